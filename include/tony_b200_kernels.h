@@ -1,0 +1,178 @@
+/* tony_b200 kernel library — public C ABI (libtony_b200_kernels.so, sm_100a only).
+ *
+ * Every function returns 0 on success or a TONY_ERR_* code; tony_last_error() gives the
+ * text of the most recent failure on the calling thread's process.  All device pointers
+ * are raw CUDA device addresses, `stream` is a cudaStream_t passed as void*, and every
+ * launch is asynchronous on that stream.  A C ABI (rather than a torch extension) is
+ * deliberate: TonY launches TensorFlow, PyTorch, MXNet and Horovod jobs alike
+ * (reference: tony-core/src/main/java/com/linkedin/tony/runtime/*.java), so the data
+ * plane must be loadable from any of them (ctypes / cffi / dlopen).
+ *
+ * The reference ships no device code; each entry point below cites
+ * the stock op sequence it replaces in the jobs the reference launches.
+ */
+#ifndef TONY_B200_KERNELS_H_
+#define TONY_B200_KERNELS_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- error codes -------------------------------------------------------------------- */
+#define TONY_OK 0
+#define TONY_ERR_INVALID 1
+#define TONY_ERR_CUDA 2
+#define TONY_ERR_UNSUPPORTED 3
+#define TONY_ERR_TOO_LARGE 4
+#define TONY_ERR_TIMEOUT 5
+
+const char* tony_last_error(void);
+int tony_version(void);
+/* Number of kernels this library has launched in this process (for bench accounting). */
+unsigned long long tony_launch_count(void);
+
+/* ---- GEMM epilogue flags ------------------------------------------------------------ */
+#define TONY_EPI_BIAS 0x001u        /* + bias[n]                                   */
+#define TONY_EPI_GELU_ERF 0x002u    /* exact GELU (BERT)                           */
+#define TONY_EPI_GELU_TANH 0x004u   /* tanh GELU (GPT-2 "gelu_new")                */
+#define TONY_EPI_RESIDUAL 0x008u    /* + aux[m,n]                                  */
+#define TONY_EPI_DGELU_ERF 0x010u   /* * gelu_erf'(aux[m,n])   (backward)          */
+#define TONY_EPI_DGELU_TANH 0x020u  /* * gelu_tanh'(aux[m,n])  (backward)          */
+#define TONY_EPI_ACCUMULATE 0x040u  /* C += result (gradient accumulation)         */
+#define TONY_EPI_SAVE_PREACT 0x080u /* aux_out[m,n] = value before the activation  */
+#define TONY_EPI_RELU 0x100u        /* max(x, 0)                                   */
+#define TONY_EPI_DRELU 0x200u       /* * (aux[m,n] > 0)        (backward)          */
+
+/* C[m,n] = epi(alpha * sum_k A(m,k) B(n,k)), bf16 in/out, fp32 accumulation in TMEM.
+ *   a_mn_major = 0: A stored [M,K] row-major (ld = lda);  1: stored [K,M] row-major.
+ *   b_mn_major = 0: B stored [N,K] row-major (ld = ldb);  1: stored [K,N] row-major.
+ * Linear layer: forward (0,0), dgrad (0,1), wgrad (1,1) — no transposes are materialised.
+ * `workspace` (optional, fp32 scratch) enables split-K for shapes that cannot fill the GPU.
+ * Replaces cuBLASLt GEMM + separate bias/GELU/residual elementwise kernels
+ * (the nn.Linear / F.gelu calls in the jobs TonY launches, e.g.
+ *  tony-examples/mnist-pytorch/mnist_distributed.py:129-136). */
+int tony_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                   int b_mn_major, long long lda, long long ldb, long long ldc, unsigned int flags,
+                   float alpha, const void* bias, const void* aux, long long ld_aux, void* aux_out,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* Extended form: tile/split overrides (0 = auto; force_splits = 1 disables split-K),
+ * B-readiness flags and reserved copy CTAs used by the all-gather-fused GEMM,
+ * and an SM budget (max_ctas, 0 = all SMs) so the GEMM can share the GPU with a
+ * concurrently running communication kernel. */
+int tony_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                      int b_mn_major, long long lda, long long ldb, long long ldc,
+                      unsigned int flags, float alpha, const void* bias, const void* aux,
+                      long long ld_aux, void* aux_out, void* workspace, size_t workspace_bytes,
+                      int force_block_n, int force_splits, const unsigned int* b_ready,
+                      unsigned int b_ready_epoch, int copy_ctas, int max_ctas, void* stream);
+
+/* ---- LayerNorm (replaces ATen layer_norm fwd/bwd) ----------------------------------- */
+/* y = (x - mean) * rstd * gamma + beta over the last dim H (H % 256 == 0, H <= 4096 fwd,
+ * H <= 2048 bwd); mean/rstd (fp32, [rows]) are saved for backward. */
+int tony_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean,
+                       float* rstd, int rows, int H, float eps, void* stream);
+/* dx, dgamma, dbeta.  `scratch` holds per-CTA fp32 partials for dgamma/dbeta:
+ * tony_layernorm_bwd_scratch_bytes(H) bytes.  accumulate != 0 adds into dgamma/dbeta. */
+size_t tony_layernorm_bwd_scratch_bytes(int H);
+int tony_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
+                       const float* rstd, void* dx, void* dgamma, void* dbeta, int rows, int H,
+                       float* scratch, size_t scratch_bytes, int accumulate, void* stream);
+
+/* ---- softmax cross-entropy, forward + backward in one pass --------------------------- */
+/* logits [rows, V] bf16 (row stride ld) are overwritten with dlogits =
+ * (softmax - onehot) * grad_scale * (*grad_scale_dev if non-null); loss[row] (fp32) =
+ * -log softmax[target]; rows whose target == ignore_index get loss 0 and zero gradient.
+ * Replaces log_softmax + nll_loss + their backward
+ * (F.cross_entropy, tony-examples/mnist-pytorch/mnist_distributed.py:81). */
+int tony_softmax_xent_fwd_bwd(void* logits, const long long* targets, float* loss, int rows, int V,
+                              long long ld, long long ignore_index, float grad_scale,
+                              const float* grad_scale_dev, void* stream);
+
+/* ---- column sum (bias gradient) ------------------------------------------------------ */
+/* out[c] (bf16) (+)= sum_r x[r,c];  scratch: tony_colsum_scratch_bytes(cols) bytes fp32. */
+size_t tony_colsum_scratch_bytes(int cols);
+int tony_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out, float* scratch,
+                     size_t scratch_bytes, int accumulate, void* stream);
+
+/* ---- optimizers on flat buffers ------------------------------------------------------ */
+/* AdamW / Adam over n elements: fp32 master weights + moments, bf16 gradients in, bf16
+ * weights out.  wd_mask (optional) has one byte per 256 elements: 0 = no weight decay.
+ * bc1 = 1 - beta1^t, bc2 = 1 - beta2^t.  Replaces torch.optim.AdamW(fused=True)
+ * plus the bf16 re-cast of the parameters. */
+int tony_adamw_flat(float* master, float* exp_avg, float* exp_avg_sq, const void* grad_bf16,
+                    void* param_bf16, size_t n, float lr, float beta1, float beta2, float eps,
+                    float weight_decay, float bc1, float bc2, float grad_scale,
+                    const unsigned char* wd_mask, size_t mask_offset_elems, void* stream);
+/* SGD with momentum (+ optional Nesterov) on the same layout. */
+int tony_sgd_flat(float* master, float* momentum_buf, const void* grad_bf16, void* param_bf16,
+                  size_t n, float lr, float momentum, float weight_decay, int nesterov,
+                  float grad_scale, const unsigned char* wd_mask, size_t mask_offset_elems,
+                  void* stream);
+
+/* ---- symmetric (peer-mapped) memory -------------------------------------------------- */
+/* Device allocations that other ranks on the same NVSwitch domain can map.  The 64-byte
+ * handle is exchanged out of band (the launcher's rendezvous or torch.distributed). */
+#define TONY_IPC_HANDLE_BYTES 64
+int tony_symm_alloc(size_t bytes, void** ptr);
+int tony_symm_free(void* ptr);
+int tony_ipc_get_handle(void* ptr, unsigned char* handle_out);
+int tony_ipc_open(const unsigned char* handle, void** peer_ptr);
+int tony_ipc_close(void* peer_ptr);
+
+/* ---- fused gradient collective + optimizer (K1 / K2 in SURVEY.md section 8) ---------- */
+#define TONY_MAX_RANKS 8
+#define TONY_OPT_ADAMW 0
+#define TONY_OPT_SGD 1
+typedef struct tony_fused_comm {
+    int rank, world;
+    const void* grad[TONY_MAX_RANKS]; /* bf16 gradient buffers of every rank (peer-mapped)   */
+    void* param[TONY_MAX_RANKS];      /* bf16 parameter buffers of every rank (peer-mapped)  */
+    unsigned int* flags[TONY_MAX_RANKS]; /* each rank's flag block: 2*TONY_MAX_RANKS words   */
+    unsigned int* counter;            /* local: one word, zero-initialised                   */
+    int* status;                      /* local: set to TONY_ERR_TIMEOUT if a peer never came */
+} tony_fused_comm;
+
+/* One launch per gradient bucket [begin, begin+count) (elements; count % (world*8) == 0):
+ * wait for every rank's bucket -> each rank reduces its 1/world shard straight out of
+ * the peers' gradient buffers over NVLink (fp32 accumulation) -> scales -> applies the
+ * optimizer to its shard of the fp32 master state (ZeRO-1 sharding, state index
+ * state_offset + i) -> writes the new bf16 weights into every rank's parameter buffer
+ * (broadcast != 0; the DDP / Horovod path) or only its own (broadcast == 0; the
+ * parameter-server path, where the all-gather is fused into the next forward GEMM).
+ * Replaces ncclAllReduce + grad unscale + optimizer.step() (+ DDP bucket copies):
+ * tony-examples/mnist-pytorch/mnist_distributed.py:113-126,
+ * tony-examples/horovod-on-tony/tensorflow2_mnist.py:73-76. */
+int tony_fused_reduce_optim(const tony_fused_comm* comm, size_t begin, size_t count,
+                            float* master, float* state1, float* state2, size_t state_offset,
+                            int optimizer, float lr, float beta1_or_momentum, float beta2,
+                            float eps, float weight_decay, float bc1, float bc2, float grad_scale,
+                            const unsigned char* wd_mask, int broadcast, unsigned int epoch,
+                            int num_ctas, void* stream);
+
+/* Plain collectives on symmetric buffers (validation + hvd.allreduce/broadcast shims).
+ * out-of-place all-reduce(sum) * scale of `count` bf16 elements at element offset `begin`
+ * of every rank's `grad[]` buffer, result written to every rank's `param[]` buffer. */
+int tony_symm_allreduce_bf16(const tony_fused_comm* comm, size_t begin, size_t count, float scale,
+                             unsigned int epoch, int num_ctas, void* stream);
+/* All-rank barrier on the GPU (arrive + wait on flag words). */
+int tony_symm_barrier(const tony_fused_comm* comm, unsigned int epoch, void* stream);
+
+/* ---- all-gather fused into a GEMM (K3) ---------------------------------------------- */
+/* Y = epi(X . W^T) where W [N,K] is row-sharded over `world` ranks (rows
+ * [r*N/world, (r+1)*N/world) live on rank r at w_shard[r]).  Copy CTAs pull the remote
+ * shards over NVLink into w_full (local, [N,K]) slab by slab and publish per-n-block
+ * flags; GEMM CTAs in the same launch consume each slab as soon as it lands, local
+ * shard first.  Replaces ncclAllGather + cuBLASLt GEMM (the ps "pull variables" step:
+ * tony-examples/mnist-tensorflow/mnist_distributed.py:213-241). */
+int tony_allgather_gemm_bf16(const void* X, const void* const* w_shard, void* w_full, void* Y,
+                             int M, int N, int K, int rank, int world, unsigned int flags,
+                             const void* bias, void* aux_out, unsigned int* ready_flags,
+                             unsigned int epoch, int copy_ctas, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TONY_B200_KERNELS_H_ */

@@ -1,0 +1,195 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 reference (SURVEY.md §4 tier 4)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def _rand(*shape, scale=1.0):
+    return (torch.randn(*shape, device=DEV, dtype=torch.float32) * scale).to(torch.bfloat16)
+
+
+def _close(out, ref, rel=2e-2):
+    ref = ref.float()
+    err = (out.float() - ref).abs().max().item()
+    tol = rel * ref.abs().max().item() + 1e-3
+    assert err <= tol, f"max err {err} > tol {tol}"
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (512, 1024, 512), (200, 264, 72), (1000, 136, 1032)])
+def test_gemm_majors(a_mn, b_mn, M, N, K):
+    from tony_b200.ops import functional as F
+
+    A = _rand(M, K)
+    B = _rand(N, K)
+    a = A.t().contiguous() if a_mn else A
+    b = B.t().contiguous() if b_mn else B
+    out = F.gemm(a, b, a_mn=a_mn, b_mn=b_mn)
+    _close(out, A.float() @ B.float().t())
+
+
+def test_gemm_epilogues():
+    from tony_b200.ops import functional as F
+    from tony_b200.ops._lib import (EPI_ACCUMULATE, EPI_BIAS, EPI_DGELU_ERF, EPI_GELU_ERF,
+                                    EPI_GELU_TANH, EPI_RELU, EPI_RESIDUAL, EPI_SAVE_PREACT)
+
+    M, N, K = 384, 768, 256
+    A, B, bias, aux = _rand(M, K), _rand(N, K), _rand(N), _rand(M, N)
+    base = A.float() @ B.float().t()
+    _close(F.gemm(A, B, flags=EPI_BIAS, bias=bias), base + bias.float())
+    pre = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    out = F.gemm(A, B, flags=EPI_BIAS | EPI_GELU_ERF | EPI_SAVE_PREACT, bias=bias, aux_out=pre)
+    _close(pre, base + bias.float())
+    _close(out, torch.nn.functional.gelu(base + bias.float()))
+    _close(F.gemm(A, B, flags=EPI_GELU_TANH), torch.nn.functional.gelu(base, approximate="tanh"))
+    _close(F.gemm(A, B, flags=EPI_BIAS | EPI_RESIDUAL, bias=bias, aux=aux), base + bias.float() + aux.float())
+    _close(F.gemm(A, B, flags=EPI_RELU), torch.relu(base))
+    x = aux.float().requires_grad_(True)
+    torch.nn.functional.gelu(x).sum().backward()
+    _close(F.gemm(A, B, flags=EPI_DGELU_ERF, aux=aux), base * x.grad)
+    c = _rand(M, N)
+    c0 = c.clone()
+    _close(F.gemm(A, B, out=c, flags=EPI_ACCUMULATE), base + c0.float())
+    _close(F.gemm(A, B, alpha=0.25), base * 0.25)
+
+
+def test_gemm_splitk():
+    from tony_b200.ops import functional as F
+
+    M, N, K = 1024, 1024, 8192  # wgrad-like: few tiles, long reduction
+    dY, X = _rand(K, M), _rand(K, N)
+    out = F.gemm(dY, X, a_mn=True, b_mn=True)
+    _close(out, dY.float().t() @ X.float())
+
+
+def test_linear_autograd():
+    from tony_b200.ops import functional as F
+
+    x = _rand(4, 96, 512).requires_grad_(True)
+    w = _rand(768, 512, scale=0.05).requires_grad_(True)
+    b = _rand(768).requires_grad_(True)
+    res = _rand(4, 96, 768).requires_grad_(True)
+    y = F.linear(x, w, b, res)
+    g = _rand(4, 96, 768)
+    y.backward(g)
+    xr, wr, br, rr = (t.detach().float().requires_grad_(True) for t in (x, w, b, res))
+    yr = torch.nn.functional.linear(xr, wr, br) + rr
+    yr.backward(g.float())
+    _close(y, yr)
+    _close(x.grad, xr.grad)
+    _close(w.grad, wr.grad)
+    _close(b.grad, br.grad)
+    _close(res.grad, rr.grad)
+
+
+@pytest.mark.parametrize("act", ["gelu", "gelu_tanh", "relu"])
+def test_mlp_autograd(act):
+    from tony_b200.ops import functional as F
+
+    x = _rand(512, 256).requires_grad_(True)
+    w1, b1 = _rand(1024, 256, scale=0.06).requires_grad_(True), _rand(1024, scale=0.1).requires_grad_(True)
+    w2, b2 = _rand(256, 1024, scale=0.03).requires_grad_(True), _rand(256, scale=0.1).requires_grad_(True)
+    y = F.mlp(x, w1, b1, w2, b2, residual=x, act=act)
+    g = _rand(512, 256)
+    y.backward(g)
+    ts = [t.detach().float().requires_grad_(True) for t in (x, w1, b1, w2, b2)]
+    fn = {"gelu": torch.nn.functional.gelu, "relu": torch.relu,
+          "gelu_tanh": lambda t: torch.nn.functional.gelu(t, approximate="tanh")}[act]
+    # the kernel rounds the hidden activation to bf16 between the two GEMMs
+    h = fn(torch.nn.functional.linear(ts[0], ts[1], ts[2]))
+    yr = torch.nn.functional.linear(h, ts[3], ts[4]) + ts[0]
+    yr.backward(g.float())
+    _close(y, yr, rel=3e-2)
+    for got, want in zip((x, w1, b1, w2, b2), ts):
+        _close(got.grad, want.grad, rel=3e-2)
+
+
+@pytest.mark.parametrize("H", [256, 768, 1024, 2048])
+def test_layernorm(H):
+    from tony_b200.ops import functional as F
+
+    rows = 777
+    x = _rand(rows, H, scale=2.0).requires_grad_(True)
+    g = (_rand(H, scale=0.2).float() + 1).to(torch.bfloat16).requires_grad_(True)
+    b = _rand(H, scale=0.2).requires_grad_(True)
+    y = F.layer_norm(x, g, b, 1e-5)
+    dy = _rand(rows, H)
+    y.backward(dy)
+    xr, gr, br = (t.detach().float().requires_grad_(True) for t in (x, g, b))
+    yr = torch.nn.functional.layer_norm(xr, (H,), gr, br, 1e-5)
+    yr.backward(dy.float())
+    _close(y, yr)
+    _close(x.grad, xr.grad)
+    _close(g.grad, gr.grad)
+    _close(b.grad, br.grad)
+
+
+@pytest.mark.parametrize("V,ld", [(30522, 30528), (1000, 1000), (50257, 50304)])
+def test_softmax_xent(V, ld):
+    from tony_b200.ops import functional as F
+
+    rows = 300
+    logits = torch.zeros(rows, ld, device=DEV, dtype=torch.bfloat16)
+    logits[:, :V] = _rand(rows, V, scale=3.0)
+    tgt = torch.randint(0, V, (rows,), device=DEV)
+    tgt[::7] = -100
+    lr = logits[:, :V].detach().float().requires_grad_(True)
+    loss_ref = torch.nn.functional.cross_entropy(lr, tgt, ignore_index=-100)
+    loss_ref.backward()
+    lg = logits.clone().requires_grad_(True)
+    loss = F.softmax_cross_entropy(lg, tgt, vocab=V)
+    loss.backward()
+    assert abs(loss.item() - loss_ref.item()) <= 2e-3 * abs(loss_ref.item()) + 1e-3
+    got = lg.grad
+    assert got[:, V:].abs().max().item() == 0 if ld > V else True
+    err = (got[:, :V].float() - lr.grad).abs().max().item()
+    assert err <= 2e-2 * lr.grad.abs().max().item() + 1e-6
+
+
+def test_colsum():
+    from tony_b200.ops import functional as F
+
+    x = _rand(5000, 1032)
+    _close(F.colsum(x), x.float().sum(0), rel=1e-2)
+    out = _rand(1032)
+    o0 = out.clone()
+    F.colsum(x, out=out, accumulate=True)
+    _close(out, x.float().sum(0) + o0.float(), rel=1e-2)
+
+
+def test_adamw_flat_matches_torch():
+    from tony_b200.ops import optim as O
+
+    n = 1 << 20
+    p32 = torch.randn(n, device=DEV)
+    ref = p32.clone().requires_grad_(True)
+    opt = torch.optim.AdamW([ref], lr=1e-3, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01)
+    st = O.FlatAdamW(p32.clone(), lr=1e-3, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01)
+    w = torch.empty(n, device=DEV, dtype=torch.bfloat16)
+    for _ in range(3):
+        g = _rand(n)
+        ref.grad = g.float()
+        opt.step()
+        st.step(g, w)
+    assert (st.master - ref.detach()).abs().max().item() < 1e-5
+    _close(w, ref.detach(), rel=1e-2)
+
+
+def test_sgd_flat_matches_torch():
+    from tony_b200.ops import optim as O
+
+    n = 1 << 18
+    p32 = torch.randn(n, device=DEV)
+    ref = p32.clone().requires_grad_(True)
+    opt = torch.optim.SGD([ref], lr=0.1, momentum=0.9, weight_decay=1e-4)
+    st = O.FlatSGD(p32.clone(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    w = torch.empty(n, device=DEV, dtype=torch.bfloat16)
+    for _ in range(3):
+        g = _rand(n)
+        ref.grad = g.float()
+        opt.step()
+        st.step(g, w)
+    assert (st.master - ref.detach()).abs().max().item() < 1e-4

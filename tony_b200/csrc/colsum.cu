@@ -1,0 +1,93 @@
+// tony_b200 — column sum of a bf16 matrix (bias gradient: db[c] = sum_r dY[r,c]).
+//
+// Two-stage: a 2-D grid of CTAs (column tile x row slab) writes fp32 partial rows into
+// caller scratch, a finalize kernel folds the slabs and casts to bf16 (optionally
+// accumulating).  Reads dY exactly once with 16-byte loads.
+// Replaces the sum(dim=0) ATen reduction inside addmm backward in launched jobs.
+#include "common.cuh"
+#include "tony_b200_kernels.h"
+
+#include <algorithm>
+
+namespace tony {
+
+constexpr int CS_MAX_SLABS = 64;
+constexpr int CS_THREADS = 256;  // 8 warps: 32 lanes x 8 columns = 256 columns per CTA
+
+__global__ void __launch_bounds__(CS_THREADS)
+colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, long long ld,
+                      int rows_per_slab, float* __restrict__ partials) {
+    __shared__ float red[CS_THREADS / 32][256];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int col = blockIdx.x * 256 + lane * 8;
+    const int r0 = blockIdx.y * rows_per_slab;
+    const int r1 = min(rows, r0 + rows_per_slab);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (col < cols) {
+        for (int r = r0 + warp; r < r1; r += CS_THREADS / 32) {
+            const uint4 u = ld_global_nc_v4(x + static_cast<size_t>(r) * ld + col);
+            const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(w[j]);
+                acc[2 * j] += f.x;
+                acc[2 * j + 1] += f.y;
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = acc[j];
+    __syncthreads();
+    const int c = threadIdx.x;  // 256 threads <-> 256 columns
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < CS_THREADS / 32; ++w) s += red[w][c];
+    const int gc = blockIdx.x * 256 + c;
+    if (gc < cols) partials[static_cast<size_t>(blockIdx.y) * cols + gc] = s;
+}
+
+__global__ void colsum_finalize_kernel(const float* __restrict__ partials, int slabs, int cols,
+                                       __nv_bfloat16* __restrict__ out, int accumulate) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cols) return;
+    float s = 0.f;
+    for (int k = 0; k < slabs; ++k) s += partials[static_cast<size_t>(k) * cols + c];
+    if (accumulate) s += __bfloat162float(out[c]);
+    out[c] = __float2bfloat16(s);
+}
+
+}  // namespace tony
+
+using namespace tony;
+
+extern "C" size_t tony_colsum_scratch_bytes(int cols) {
+    return static_cast<size_t>(CS_MAX_SLABS) * static_cast<size_t>(cols) * sizeof(float);
+}
+
+extern "C" int tony_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out,
+                                float* scratch, size_t scratch_bytes, int accumulate,
+                                void* stream) {
+    if (!x || !out || !scratch || rows <= 0 || cols <= 0) return TONY_ERR_INVALID;
+    if ((cols % 8) != 0 || (ld % 8) != 0 || (reinterpret_cast<uintptr_t>(x) & 15)) {
+        set_last_error("tony_colsum_bf16", "cols and ld must be multiples of 8; x 16B aligned");
+        return TONY_ERR_INVALID;
+    }
+    if (scratch_bytes < tony_colsum_scratch_bytes(cols)) {
+        set_last_error("tony_colsum_bf16", "scratch too small (see tony_colsum_scratch_bytes)");
+        return TONY_ERR_INVALID;
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int col_tiles = (cols + 255) / 256;
+    int slabs = std::max(1, std::min(CS_MAX_SLABS, (device_sm_count() * 4) / col_tiles));
+    slabs = std::min(slabs, std::max(1, rows / 32));
+    const int rows_per_slab = (rows + slabs - 1) / slabs;
+    slabs = (rows + rows_per_slab - 1) / rows_per_slab;
+    colsum_partial_kernel<<<dim3(col_tiles, slabs), CS_THREADS, 0, s>>>(
+        static_cast<const __nv_bfloat16*>(x), rows, cols, ld, rows_per_slab, scratch);
+    TONY_CUDA_CHECK(cudaGetLastError());
+    colsum_finalize_kernel<<<(cols + 255) / 256, 256, 0, s>>>(
+        scratch, slabs, cols, static_cast<__nv_bfloat16*>(out), accumulate);
+    count_launch(2);
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}

@@ -1,0 +1,735 @@
+// tony_b200 — bf16 GEMM on 5th-gen tensor cores (tcgen05 + TMEM + TMA), sm_100a only.
+//
+//   C[m,n] = epilogue( alpha * sum_k A(m,k) * B(n,k) )
+//
+// * persistent kernel, one CTA per SM, 192 threads = 6 warps, warp-specialised:
+//     warp 0      TMA producer (one elected lane): global -> 128B-swizzled smem ring
+//     warp 1      TMEM allocator + tcgen05.mma issuer (one lane), commits to mbarriers
+//     warps 2..5  epilogue: tcgen05.ld (TMEM -> registers) -> bias/activation/residual
+//                 -> 16-byte global stores; runs concurrently with the next tile's MMAs
+//                 because the accumulator is double-buffered in TMEM (2 x BLOCK_N columns)
+// * both operands may be K-major (reduction dim contiguous) or MN-major (the other
+//   dim contiguous), selected at run time; this is what lets forward (X.W^T), dgrad
+//   (dY.W) and wgrad (dY^T.X) of a Linear layer run without any transpose copy.
+// * optional split-K (fp32 partials in caller-provided workspace + a reduce kernel)
+//   for the small-output / long-reduction wgrad shapes that cannot fill 148 SMs.
+// * optional "B readiness" flags: the producer acquires a per-n-block flag before
+//   loading B tiles; the all-gather-fused GEMM (parallel/ps path, K3 in SURVEY.md §8)
+//   uses this to consume weight shards as copy CTAs pull them over NVLink.
+//
+// The reference (zuston/TonY) contains no GEMM or any device code;
+// this kernel replaces cuBLASLt + separate elementwise kernels in the jobs it launches.
+#include "common.cuh"
+#include "tony_b200_kernels.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <mutex>
+
+namespace tony {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;  // 64 bf16 = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int GEMM_THREADS = 192;
+constexpr int CHUNK_BYTES = BLOCK_K * 128;  // one [64 x 128B] MN-major chunk = 8 KB
+
+struct GemmParams {
+    int M, N, K;
+    int a_mn_major, b_mn_major;
+    int num_m_blocks, num_n_blocks, num_k_blocks;
+    int splits, kb_per_split;
+    uint32_t flags;
+    float alpha;
+    __nv_bfloat16* C;
+    long long ldc;
+    const __nv_bfloat16* bias;
+    const __nv_bfloat16* aux;
+    long long ld_aux;
+    __nv_bfloat16* aux_out;
+    float* workspace;              // split-K partials [splits][M][N]
+    const uint32_t* b_ready;       // optional per-n-block readiness flags (gpu scope)
+    uint32_t b_ready_epoch;
+    int copy_ctas;                 // CTAs [0, copy_ctas) are not GEMM workers (fused AG)
+    // fused all-gather: copy CTAs pull peer-owned rows of B into ag_dst ([N,K] row-major)
+    const __nv_bfloat16* ag_src[TONY_MAX_RANKS];
+    __nv_bfloat16* ag_dst;
+    uint32_t* ag_flags;
+    int ag_rows_per_rank;
+    int n_rot;                     // n-block sweep starts here (the local shard)
+};
+
+__device__ __forceinline__ void tile_coords(const GemmParams& p, int tile, int& m_blk, int& n_blk) {
+    // grouped ordering: 16 m-blocks share each sweep over n so A stays L2 resident
+    constexpr int GROUP_M = 16;
+    const int per_group = GROUP_M * p.num_n_blocks;
+    const int group = tile / per_group;
+    const int within = tile - group * per_group;
+    const int first_m = group * GROUP_M;
+    const int gm = min(GROUP_M, p.num_m_blocks - first_m);
+    m_blk = first_m + within % gm;
+    n_blk = within / gm + p.n_rot;
+    if (n_blk >= p.num_n_blocks) n_blk -= p.num_n_blocks;
+}
+
+// Copy-CTA role of the all-gather-fused GEMM: walk the n-blocks in the same rotated order
+// the GEMM workers consume them, pull every row that lives on a peer over NVLink with
+// 16-byte loads (8 in flight per thread), then publish the slab with a release increment.
+template <int BLOCK_N>
+__device__ __forceinline__ void allgather_copy_role(const GemmParams& p) {
+    const int vec_per_row = p.K / 8;
+    const int nthreads = p.copy_ctas * GEMM_THREADS;
+    const int gtid = blockIdx.x * GEMM_THREADS + threadIdx.x;
+    for (int j = 0; j < p.num_n_blocks; ++j) {
+        int nb = p.n_rot + j;
+        if (nb >= p.num_n_blocks) nb -= p.num_n_blocks;
+        const int r0 = nb * BLOCK_N;
+        const int r1 = min(p.N, r0 + BLOCK_N);
+        const int total = (r1 - r0) * vec_per_row;
+        constexpr int U = 8;
+        for (int v0 = gtid; v0 < total; v0 += nthreads * U) {
+            uint4 buf[U];
+            __nv_bfloat16* dst[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int v = v0 + u * nthreads;
+                dst[u] = nullptr;
+                if (v < total) {
+                    const int row = r0 + v / vec_per_row;
+                    const int cv = v - (row - r0) * vec_per_row;
+                    const int owner = row / p.ag_rows_per_rank;
+                    const __nv_bfloat16* src =
+                        p.ag_src[owner] +
+                        static_cast<size_t>(row - owner * p.ag_rows_per_rank) * p.K + cv * 8;
+                    __nv_bfloat16* d = p.ag_dst + static_cast<size_t>(row) * p.K + cv * 8;
+                    if (src != d) {
+                        dst[u] = d;
+                        buf[u] = ld_global_v4(src);
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (dst[u]) st_global_v4(dst[u], buf[u]);
+        }
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.ag_flags + nb) : "memory");
+        }
+    }
+}
+
+template <int BLOCK_N>
+__device__ __forceinline__ void gemm_epilogue_chunk(const GemmParams& p, uint32_t (&r)[32], int row,
+                                                    int col0, int split) {
+    if (row >= p.M || col0 >= p.N) return;
+    if (p.splits > 1) {
+        float* dst = p.workspace + (static_cast<size_t>(split) * p.M + row) * p.N + col0;
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+            if (col0 + g * 4 < p.N) {
+                float4 v = make_float4(__uint_as_float(r[g * 4 + 0]), __uint_as_float(r[g * 4 + 1]),
+                                       __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]));
+                *reinterpret_cast<float4*>(dst + g * 4) = v;
+            }
+        }
+        return;
+    }
+    const uint32_t flags = p.flags;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {  // 8 columns (16 bytes of bf16) at a time
+        const int col = col0 + g * 8;
+        if (col >= p.N) break;
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]) * p.alpha;
+        if (flags & TONY_EPI_BIAS) {
+            const uint4 b = __ldg(reinterpret_cast<const uint4*>(p.bias + col));
+            const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(bw[j]);
+                v[2 * j] += f.x;
+                v[2 * j + 1] += f.y;
+            }
+        }
+        if (flags & (TONY_EPI_RESIDUAL | TONY_EPI_DGELU_ERF | TONY_EPI_DGELU_TANH | TONY_EPI_DRELU)) {
+            const uint4 a =
+                ld_global_nc_v4(p.aux + static_cast<size_t>(row) * p.ld_aux + col);
+            const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(aw[j]);
+                if (flags & TONY_EPI_RESIDUAL) {
+                    v[2 * j] += f.x;
+                    v[2 * j + 1] += f.y;
+                } else if (flags & TONY_EPI_DGELU_ERF) {
+                    v[2 * j] *= dgelu_erf(f.x);
+                    v[2 * j + 1] *= dgelu_erf(f.y);
+                } else if (flags & TONY_EPI_DGELU_TANH) {
+                    v[2 * j] *= dgelu_tanh(f.x);
+                    v[2 * j + 1] *= dgelu_tanh(f.y);
+                } else {
+                    v[2 * j] = f.x > 0.f ? v[2 * j] : 0.f;
+                    v[2 * j + 1] = f.y > 0.f ? v[2 * j + 1] : 0.f;
+                }
+            }
+        }
+        if (flags & TONY_EPI_SAVE_PREACT) {
+            uint4 o;
+            o.x = pack_bf16x2(v[0], v[1]);
+            o.y = pack_bf16x2(v[2], v[3]);
+            o.z = pack_bf16x2(v[4], v[5]);
+            o.w = pack_bf16x2(v[6], v[7]);
+            st_global_v4(p.aux_out + static_cast<size_t>(row) * p.ldc + col, o);
+        }
+        if (flags & TONY_EPI_GELU_ERF) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = gelu_erf(v[j]);
+        } else if (flags & TONY_EPI_GELU_TANH) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
+        } else if (flags & TONY_EPI_RELU) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+        }
+        __nv_bfloat16* cptr = p.C + static_cast<size_t>(row) * p.ldc + col;
+        if (flags & TONY_EPI_ACCUMULATE) {
+            const uint4 c = ld_global_v4(cptr);
+            const uint32_t cw[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(cw[j]);
+                v[2 * j] += f.x;
+                v[2 * j + 1] += f.y;
+            }
+        }
+        uint4 o;
+        o.x = pack_bf16x2(v[0], v[1]);
+        o.y = pack_bf16x2(v[2], v[3]);
+        o.z = pack_bf16x2(v[4], v[5]);
+        o.w = pack_bf16x2(v[6], v[7]);
+        st_global_v4(cptr, o);
+    }
+}
+
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                         const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
+    constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;
+    constexpr uint32_t B_BYTES = BLOCK_N * BLOCK_K * 2;
+    constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+    constexpr uint32_t TMEM_COLS = 2 * BLOCK_N;  // double-buffered fp32 accumulator
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(
+        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+    const int warp_idx = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp_idx == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full_bar[s], 1);
+            mbar_init(&tmem_empty_bar[s], 4);  // one arrive per epilogue warp
+        }
+        fence_barrier_init();
+    }
+    if (warp_idx == 1) tmem_alloc<TMEM_COLS>(tmem_base_slot);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_base_slot;
+
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    const int num_units = num_tiles * p.splits;
+    const int worker = static_cast<int>(blockIdx.x) - p.copy_ctas;
+    const int num_workers = static_cast<int>(gridDim.x) - p.copy_ctas;
+
+    if (worker >= 0) {
+        if (warp_idx == 0) {
+            // ------------------------------------------------ TMA producer
+            if (lane == 0) {
+                int stage = 0;
+                uint32_t phase = 0;
+                for (int unit = worker; unit < num_units; unit += num_workers) {
+                    const int tile = unit / p.splits;
+                    const int split = unit - tile * p.splits;
+                    int m_blk, n_blk;
+                    tile_coords(p, tile, m_blk, n_blk);
+                    if (p.b_ready != nullptr) {
+                        while (static_cast<int32_t>(ld_acquire_gpu(p.b_ready + n_blk) -
+                                                    p.b_ready_epoch) < 0) {
+                            __nanosleep(64);
+                        }
+                        fence_proxy_async();  // generic-proxy copies -> async-proxy TMA reads
+                    }
+                    const int kb0 = split * p.kb_per_split;
+                    const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
+                    for (int kb = kb0; kb < kb1; ++kb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        uint8_t* sa = smem + stage * STAGE_BYTES;
+                        uint8_t* sb = sa + A_BYTES;
+                        mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+                        if (!p.a_mn_major) {
+                            tma_load_2d(&tmap_a, &full_bar[stage], sa, kb * BLOCK_K, m_blk * BLOCK_M);
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < BLOCK_M / 64; ++c)
+                                tma_load_2d(&tmap_a, &full_bar[stage], sa + c * CHUNK_BYTES,
+                                            m_blk * BLOCK_M + c * 64, kb * BLOCK_K);
+                        }
+                        if (!p.b_mn_major) {
+                            tma_load_2d(&tmap_b, &full_bar[stage], sb, kb * BLOCK_K, n_blk * BLOCK_N);
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < BLOCK_N / 64; ++c)
+                                tma_load_2d(&tmap_b, &full_bar[stage], sb + c * CHUNK_BYTES,
+                                            n_blk * BLOCK_N + c * 64, kb * BLOCK_K);
+                        }
+                        if (++stage == STAGES) {
+                            stage = 0;
+                            phase ^= 1;
+                        }
+                    }
+                }
+            }
+        } else if (warp_idx == 1) {
+            // ------------------------------------------------ MMA issuer
+            if (lane == 0) {
+                const uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N, p.a_mn_major, p.b_mn_major);
+                // K-major: 8-row groups 1024 B apart, k-step = 32 B inside the swizzle row.
+                // MN-major: 64-wide chunks CHUNK_BYTES apart (LBO), 8 k-rows = 1024 B (SBO),
+                //           k-step = 16 rows = 2048 B.
+                const uint32_t a_lbo = p.a_mn_major ? CHUNK_BYTES : 16;
+                const uint32_t b_lbo = p.b_mn_major ? CHUNK_BYTES : 16;
+                const uint32_t a_kstep = p.a_mn_major ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+                const uint32_t b_kstep = p.b_mn_major ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+                int stage = 0;
+                uint32_t phase = 0;
+                int iter = 0;
+                for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
+                    const int tile = unit / p.splits;
+                    const int split = unit - tile * p.splits;
+                    const int as = iter & 1;
+                    const uint32_t aphase = (iter >> 1) & 1;
+                    mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
+                    tcgen05_fence_after();
+                    const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+                    const int kb0 = split * p.kb_per_split;
+                    const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
+                    for (int kb = kb0; kb < kb1; ++kb) {
+                        mbar_wait(&full_bar[stage], phase);
+                        tcgen05_fence_after();
+                        const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+                        const uint32_t sb = sa + A_BYTES;
+                        const uint64_t da = make_umma_desc_sw128(sa, a_lbo, 1024);
+                        const uint64_t db = make_umma_desc_sw128(sb, b_lbo, 1024);
+#pragma unroll
+                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                            umma_bf16(d_tmem, da + k * a_kstep, db + k * b_kstep, idesc,
+                                      (kb > kb0 || k > 0) ? 1u : 0u);
+                        }
+                        umma_commit(&empty_bar[stage]);  // frees the smem slot when MMAs retire
+                        if (++stage == STAGES) {
+                            stage = 0;
+                            phase ^= 1;
+                        }
+                    }
+                    umma_commit(&tmem_full_bar[as]);  // accumulator complete -> epilogue
+                }
+            }
+        } else {
+            // ------------------------------------------------ epilogue warps (2..5)
+            const int quarter = warp_idx & 3;  // TMEM lane quarter this warp may access
+            int iter = 0;
+            for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
+                const int tile = unit / p.splits;
+                const int split = unit - tile * p.splits;
+                int m_blk, n_blk;
+                tile_coords(p, tile, m_blk, n_blk);
+                const int as = iter & 1;
+                const uint32_t aphase = (iter >> 1) & 1;
+                mbar_wait(&tmem_full_bar[as], aphase);
+                tcgen05_fence_after();
+                const int row = m_blk * BLOCK_M + quarter * 32 + lane;
+                const uint32_t taddr0 =
+                    tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BLOCK_N;
+#pragma unroll 1
+                for (int c = 0; c < BLOCK_N / 32; ++c) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(taddr0 + c * 32, r);
+                    tmem_ld_wait();
+                    gemm_epilogue_chunk<BLOCK_N>(p, r, row, n_blk * BLOCK_N + c * 32, split);
+                }
+                tcgen05_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
+            }
+        }
+    }
+
+    else {
+        allgather_copy_role<BLOCK_N>(p);
+    }
+
+    __syncwarp();
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp_idx == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc<TMEM_COLS>(tmem_base);
+    }
+}
+
+// out = alpha * sum_s ws[s] (+ old out) (+ bias), fp32 partials -> bf16
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, int M, int N,
+                                     __nv_bfloat16* __restrict__ C, long long ldc, float alpha,
+                                     uint32_t flags, const __nv_bfloat16* __restrict__ bias) {
+    const size_t total4 = static_cast<size_t>(M) * N / 4;
+    const size_t plane = static_cast<size_t>(M) * N;
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total4;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const size_t e = i * 4;
+        const int row = static_cast<int>(e / N);
+        const int col = static_cast<int>(e - static_cast<size_t>(row) * N);
+        float4 acc = *reinterpret_cast<const float4*>(ws + e);
+        for (int s = 1; s < splits; ++s) {
+            const float4 v = *reinterpret_cast<const float4*>(ws + s * plane + e);
+            acc.x += v.x;
+            acc.y += v.y;
+            acc.z += v.z;
+            acc.w += v.w;
+        }
+        acc.x *= alpha;
+        acc.y *= alpha;
+        acc.z *= alpha;
+        acc.w *= alpha;
+        if (flags & TONY_EPI_BIAS) {
+            acc.x += __bfloat162float(bias[col]);
+            acc.y += __bfloat162float(bias[col + 1]);
+            acc.z += __bfloat162float(bias[col + 2]);
+            acc.w += __bfloat162float(bias[col + 3]);
+        }
+        __nv_bfloat16* cptr = C + static_cast<size_t>(row) * ldc + col;
+        if (flags & TONY_EPI_ACCUMULATE) {
+            const uint2 o = *reinterpret_cast<const uint2*>(cptr);
+            const float2 a = unpack_bf16x2(o.x), b = unpack_bf16x2(o.y);
+            acc.x += a.x;
+            acc.y += a.y;
+            acc.z += b.x;
+            acc.w += b.y;
+        }
+        uint2 o;
+        o.x = pack_bf16x2(acc.x, acc.y);
+        o.y = pack_bf16x2(acc.z, acc.w);
+        *reinterpret_cast<uint2*>(cptr) = o;
+    }
+}
+
+// ----------------------------------------------------------------------------
+// Host side
+// ----------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+    static PFN_encodeTiled fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) ==
+                cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess) {
+            fn = reinterpret_cast<PFN_encodeTiled>(ptr);
+        }
+    });
+    return fn;
+}
+
+// Operand of logical shape [mn_extent, k_extent]; `mn_major` says which dim is contiguous.
+int make_operand_tmap(CUtensorMap* map, const void* ptr, int mn_extent, int k_extent, long long ld,
+                      int mn_major, int block_mn) {
+    PFN_encodeTiled enc = get_encode_fn();
+    if (!enc) {
+        set_last_error("cuTensorMapEncodeTiled", "driver entry point not found");
+        return TONY_ERR_UNSUPPORTED;
+    }
+    cuuint64_t gdim[2];
+    cuuint32_t box[2];
+    if (!mn_major) {
+        gdim[0] = static_cast<cuuint64_t>(k_extent);
+        gdim[1] = static_cast<cuuint64_t>(mn_extent);
+        box[0] = BLOCK_K;
+        box[1] = static_cast<cuuint32_t>(block_mn);
+    } else {
+        gdim[0] = static_cast<cuuint64_t>(mn_extent);
+        gdim[1] = static_cast<cuuint64_t>(k_extent);
+        box[0] = 64;
+        box[1] = BLOCK_K;
+    }
+    cuuint64_t gstride[1] = {static_cast<cuuint64_t>(ld) * 2};
+    cuuint32_t estride[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride,
+                     box, estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[64];
+        snprintf(buf, sizeof(buf), "CUresult %d", static_cast<int>(r));
+        set_last_error("cuTensorMapEncodeTiled", buf);
+        return TONY_ERR_CUDA;
+    }
+    return TONY_OK;
+}
+
+int device_sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+template <int BLOCK_N, int STAGES>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
+                       cudaStream_t stream) {
+    constexpr size_t SMEM = static_cast<size_t>(STAGES) * (BLOCK_M + BLOCK_N) * BLOCK_K * 2 + 1024 + 256;
+    static bool configured[64] = {false};
+    int dev = 0;
+    TONY_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        TONY_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BLOCK_N, STAGES>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             static_cast<int>(SMEM)));
+        configured[dev] = true;
+    }
+    gemm_bf16_tcgen05_kernel<BLOCK_N, STAGES><<<grid, GEMM_THREADS, SMEM, stream>>>(ta, tb, p);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}
+
+static double wave_efficiency(long long units, int sms) {
+    const long long waves = (units + sms - 1) / sms;
+    return static_cast<double>(units) / static_cast<double>(waves * sms);
+}
+
+}  // namespace tony
+
+using namespace tony;
+
+struct AgHost {  // fused all-gather description (host side)
+    const void* const* src;
+    void* dst;
+    unsigned int* flags;
+    int world, rank, rows_per_rank;
+};
+
+static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                     int b_mn_major, long long lda, long long ldb, long long ldc,
+                     unsigned int flags, float alpha, const void* bias, const void* aux,
+                     long long ld_aux, void* aux_out, void* workspace, size_t workspace_bytes,
+                     int force_block_n, int force_splits, const unsigned int* b_ready,
+                     unsigned int b_ready_epoch, int copy_ctas, int max_ctas, const AgHost* ag,
+                     void* stream_v) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (!A || !B || !C || M <= 0 || N <= 0 || K <= 0) {
+        set_last_error("tony_gemm_bf16", "null pointer or non-positive dimension");
+        return TONY_ERR_INVALID;
+    }
+    if ((N % 8) != 0 || (lda % 8) != 0 || (ldb % 8) != 0 || (ldc % 8) != 0 ||
+        (reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15) ||
+        (reinterpret_cast<uintptr_t>(C) & 15)) {
+        set_last_error("tony_gemm_bf16", "N and leading dims must be multiples of 8; pointers 16B aligned");
+        return TONY_ERR_INVALID;
+    }
+    if ((flags & TONY_EPI_BIAS) && !bias) return TONY_ERR_INVALID;
+    if ((flags & (TONY_EPI_RESIDUAL | TONY_EPI_DGELU_ERF | TONY_EPI_DGELU_TANH | TONY_EPI_DRELU)) &&
+        (!aux || (ld_aux % 8) != 0))
+        return TONY_ERR_INVALID;
+    if ((flags & TONY_EPI_SAVE_PREACT) && !aux_out) return TONY_ERR_INVALID;
+
+    const int sms = device_sm_count();
+    int workers = sms - copy_ctas;
+    if (max_ctas > 0) workers = std::min(workers, max_ctas - copy_ctas);
+    if (workers <= 0) return TONY_ERR_INVALID;
+
+    const int num_m = (M + BLOCK_M - 1) / BLOCK_M;
+    const int num_k = (K + BLOCK_K - 1) / BLOCK_K;
+    int block_n = force_block_n;
+    if (block_n != 128 && block_n != 256) {
+        const long long t256 = static_cast<long long>(num_m) * ((N + 255) / 256);
+        const long long t128 = static_cast<long long>(num_m) * ((N + 127) / 128);
+        block_n = (N <= 128 || wave_efficiency(t128, workers) > 1.12 * wave_efficiency(t256, workers))
+                      ? 128
+                      : 256;
+    }
+    const int num_n = (N + block_n - 1) / block_n;
+    const long long tiles = static_cast<long long>(num_m) * num_n;
+
+    // split-K only for plain / accumulate / bias epilogues, and only if it fills the machine better
+    int splits = 1;
+    const bool splittable =
+        (flags & ~(TONY_EPI_ACCUMULATE | TONY_EPI_BIAS)) == 0 && workspace != nullptr && (N % 4) == 0;
+    if (splittable) {
+        if (force_splits > 1) {
+            splits = force_splits;
+        } else if (force_splits == 0 && tiles * 2 <= workers) {
+            double best = wave_efficiency(tiles, workers);
+            for (int s = 2; s <= 16; ++s) {
+                if (num_k / s < 8) break;  // keep >= 512 reduction elements per split
+                const double e = wave_efficiency(tiles * s, workers);
+                if (e > best + 0.05) {
+                    best = e;
+                    splits = s;
+                }
+            }
+        }
+        splits = std::min(splits, num_k);
+        while (splits > 1 &&
+               static_cast<size_t>(splits) * M * static_cast<size_t>(N) * 4 > workspace_bytes)
+            --splits;
+    }
+    int kb_per_split = (num_k + splits - 1) / splits;
+    splits = (num_k + kb_per_split - 1) / kb_per_split;  // no empty splits
+
+    CUtensorMap ta, tb;
+    int rc = make_operand_tmap(&ta, A, M, K, lda, a_mn_major, BLOCK_M);
+    if (rc) return rc;
+    rc = make_operand_tmap(&tb, B, N, K, ldb, b_mn_major, block_n);
+    if (rc) return rc;
+
+    GemmParams p;
+    p.M = M;
+    p.N = N;
+    p.K = K;
+    p.a_mn_major = a_mn_major ? 1 : 0;
+    p.b_mn_major = b_mn_major ? 1 : 0;
+    p.num_m_blocks = num_m;
+    p.num_n_blocks = num_n;
+    p.num_k_blocks = num_k;
+    p.splits = splits;
+    p.kb_per_split = kb_per_split;
+    p.flags = flags;
+    p.alpha = alpha;
+    p.C = static_cast<__nv_bfloat16*>(C);
+    p.ldc = ldc;
+    p.bias = static_cast<const __nv_bfloat16*>(bias);
+    p.aux = static_cast<const __nv_bfloat16*>(aux);
+    p.ld_aux = ld_aux;
+    p.aux_out = static_cast<__nv_bfloat16*>(aux_out);
+    p.workspace = static_cast<float*>(workspace);
+    p.b_ready = b_ready;
+    p.b_ready_epoch = b_ready_epoch;
+    p.copy_ctas = copy_ctas;
+    for (int r = 0; r < TONY_MAX_RANKS; ++r) p.ag_src[r] = nullptr;
+    p.ag_dst = nullptr;
+    p.ag_flags = nullptr;
+    p.ag_rows_per_rank = 1;
+    p.n_rot = 0;
+    if (ag) {
+        for (int r = 0; r < ag->world; ++r) p.ag_src[r] = static_cast<const __nv_bfloat16*>(ag->src[r]);
+        p.ag_dst = static_cast<__nv_bfloat16*>(ag->dst);
+        p.ag_flags = ag->flags;
+        p.ag_rows_per_rank = ag->rows_per_rank;
+        p.n_rot = (ag->rank * ag->rows_per_rank) / block_n;
+    }
+
+    const long long units = tiles * splits;
+    const int grid = static_cast<int>(std::min<long long>(units, workers)) + copy_ctas;
+    if (block_n == 256)
+        rc = launch_gemm<256, 4>(ta, tb, p, grid, stream);
+    else
+        rc = launch_gemm<128, 6>(ta, tb, p, grid, stream);
+    if (rc) return rc;
+
+    if (splits > 1) {
+        const size_t total4 = static_cast<size_t>(M) * N / 4;
+        const int threads = 256;
+        const int blocks = static_cast<int>(std::min<size_t>((total4 + threads - 1) / threads,
+                                                             static_cast<size_t>(sms) * 8));
+        splitk_reduce_kernel<<<blocks, threads, 0, stream>>>(
+            static_cast<const float*>(workspace), splits, M, N, static_cast<__nv_bfloat16*>(C), ldc,
+            alpha, flags, static_cast<const __nv_bfloat16*>(bias));
+        count_launch();
+        TONY_CUDA_CHECK(cudaGetLastError());
+    }
+    return TONY_OK;
+}
+
+extern "C" int tony_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K,
+                                 int a_mn_major, int b_mn_major, long long lda, long long ldb,
+                                 long long ldc, unsigned int flags, float alpha, const void* bias,
+                                 const void* aux, long long ld_aux, void* aux_out, void* workspace,
+                                 size_t workspace_bytes, int force_block_n, int force_splits,
+                                 const unsigned int* b_ready, unsigned int b_ready_epoch,
+                                 int copy_ctas, int max_ctas, void* stream) {
+    if (copy_ctas != 0) {
+        set_last_error("tony_gemm_bf16_ex", "copy_ctas is reserved for tony_allgather_gemm_bf16");
+        return TONY_ERR_INVALID;
+    }
+    return gemm_host(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, flags, alpha, bias, aux,
+                     ld_aux, aux_out, workspace, workspace_bytes, force_block_n, force_splits, b_ready,
+                     b_ready_epoch, 0, max_ctas, nullptr, stream);
+}
+
+extern "C" int tony_allgather_gemm_bf16(const void* X, const void* const* w_shard, void* w_full,
+                                        void* Y, int M, int N, int K, int rank, int world,
+                                        unsigned int flags, const void* bias, void* aux_out,
+                                        unsigned int* ready_flags, unsigned int epoch,
+                                        int copy_ctas, void* stream) {
+    if (!w_shard || !w_full || !ready_flags || world < 1 || world > TONY_MAX_RANKS || rank < 0 ||
+        rank >= world || (N % world) != 0 || (K % 8) != 0 || epoch == 0) {
+        set_last_error("tony_allgather_gemm_bf16", "bad arguments (N % world, K % 8, epoch >= 1)");
+        return TONY_ERR_INVALID;
+    }
+    if (flags & ~(TONY_EPI_BIAS | TONY_EPI_GELU_ERF | TONY_EPI_GELU_TANH | TONY_EPI_RELU |
+                  TONY_EPI_SAVE_PREACT)) {
+        set_last_error("tony_allgather_gemm_bf16", "unsupported epilogue flag");
+        return TONY_ERR_INVALID;
+    }
+    if (copy_ctas <= 0) copy_ctas = 24;
+    copy_ctas = std::min(copy_ctas, device_sm_count() / 2);
+    AgHost ag;
+    ag.src = w_shard;
+    ag.dst = w_full;
+    ag.flags = ready_flags;
+    ag.world = world;
+    ag.rank = rank;
+    ag.rows_per_rank = N / world;
+    // every copy CTA bumps a slab's flag once per call, so call #epoch completes at epoch*copy_ctas
+    return gemm_host(X, w_full, Y, M, N, K, 0, 0, K, K, N, flags, 1.0f, bias, nullptr, 0, aux_out,
+                     nullptr, 0, 0, 1, ready_flags, epoch * static_cast<unsigned int>(copy_ctas),
+                     copy_ctas, 0, &ag, stream);
+}
+
+extern "C" int tony_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
+                              int a_mn_major, int b_mn_major, long long lda, long long ldb,
+                              long long ldc, unsigned int flags, float alpha, const void* bias,
+                              const void* aux, long long ld_aux, void* aux_out, void* workspace,
+                              size_t workspace_bytes, void* stream) {
+    return gemm_host(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, flags, alpha, bias, aux,
+                     ld_aux, aux_out, workspace, workspace_bytes, 0, 0, nullptr, 0, 0, 0, nullptr,
+                     stream);
+}

@@ -1,0 +1,407 @@
+// tony_b200 — optimizers on flat buffers, and the fused gradient-collective + optimizer
+// kernel (K1/K2 of SURVEY.md §8) that is the heart of the DDP / Horovod / ps-worker data plane.
+//
+// fused_reduce_optim_kernel, one launch per gradient bucket, on every rank:
+//   A. arrive/wait on per-rank flag words in peer-mapped memory (st.release.sys /
+//      ld.acquire.sys) so every rank's bucket is known to be complete;
+//   B. each rank reduces ITS 1/world shard directly out of all peers' bf16 gradient
+//      buffers with 16-byte loads over NVLink (fp32 accumulation), applies unscale +
+//      AdamW/SGD to its shard of the fp32 master weights and moments (optimizer state is
+//      therefore sharded across ranks, ZeRO-1 style), and stores the new bf16 weights
+//      into every rank's parameter buffer with 16-byte peer stores (or only locally for
+//      the parameter-server path);
+//   C. last CTA out signals "done" to every peer and waits for theirs, so kernel
+//      completion on a rank implies its parameters are fully updated and its gradient
+//      buffer is free to be overwritten by the next backward.
+// NVLink traffic per rank: (world-1)/world * S in, (world-1)/world * S out — the
+// reduce-scatter + all-gather optimum — with the optimizer's HBM traffic cut by `world`.
+// Every wait is bounded (globaltimer budget) and reports TONY_ERR_TIMEOUT through a
+// status word instead of hanging the GPU when a peer died.
+//
+// Replaces: ncclAllReduce + grad unscale + optimizer.step() + DDP bucket copies, i.e.
+// what tony-examples/mnist-pytorch/mnist_distributed.py:113-126 (average_gradients) and
+// Horovod's DistributedOptimizer (tony-examples/horovod-on-tony/tensorflow2_keras_mnist.py:55-56)
+// do in the jobs the reference launches.
+#include "common.cuh"
+#include "tony_b200_kernels.h"
+
+#include <algorithm>
+#include <cstdlib>
+
+namespace tony {
+
+struct OptHyper {
+    int optimizer;  // TONY_OPT_ADAMW, TONY_OPT_SGD, or -1 = none (plain all-reduce)
+    float lr, beta1, beta2, eps, weight_decay, inv_bc1, inv_sqrt_bc2, grad_scale;
+    int nesterov;
+};
+
+__device__ __forceinline__ void unpack8f(const uint4& u, float (&f)[8]) {
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float2 t = unpack_bf16x2(w[j]);
+        f[2 * j] = t.x;
+        f[2 * j + 1] = t.y;
+    }
+}
+
+// Update 8 consecutive elements of (master, s1, s2) at index i with gradient g (already
+// summed over ranks, not yet scaled); returns the new weights packed as 8 bf16.
+__device__ __forceinline__ uint4 optim_update8(const OptHyper& h, float* __restrict__ master,
+                                               float* __restrict__ s1, float* __restrict__ s2,
+                                               size_t i, float (&g)[8], float wd) {
+    float4 p0 = *reinterpret_cast<float4*>(master + i), p1 = *reinterpret_cast<float4*>(master + i + 4);
+    float4 m0 = *reinterpret_cast<float4*>(s1 + i), m1 = *reinterpret_cast<float4*>(s1 + i + 4);
+    float p[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+    float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+    if (h.optimizer == TONY_OPT_ADAMW) {
+        float4 v0 = *reinterpret_cast<float4*>(s2 + i), v1 = *reinterpret_cast<float4*>(s2 + i + 4);
+        float v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float gj = g[j] * h.grad_scale;
+            m[j] = h.beta1 * m[j] + (1.0f - h.beta1) * gj;
+            v[j] = h.beta2 * v[j] + (1.0f - h.beta2) * gj * gj;
+            const float denom = sqrtf(v[j]) * h.inv_sqrt_bc2 + h.eps;
+            p[j] = p[j] * (1.0f - h.lr * wd) - h.lr * (m[j] * h.inv_bc1) / denom;
+        }
+        *reinterpret_cast<float4*>(s2 + i) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(s2 + i + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    } else {  // SGD with momentum (beta1 = momentum)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float gj = g[j] * h.grad_scale + wd * p[j];
+            m[j] = h.beta1 * m[j] + gj;
+            const float step = h.nesterov ? gj + h.beta1 * m[j] : m[j];
+            p[j] -= h.lr * step;
+        }
+    }
+    *reinterpret_cast<float4*>(master + i) = make_float4(p[0], p[1], p[2], p[3]);
+    *reinterpret_cast<float4*>(master + i + 4) = make_float4(p[4], p[5], p[6], p[7]);
+    *reinterpret_cast<float4*>(s1 + i) = make_float4(m[0], m[1], m[2], m[3]);
+    *reinterpret_cast<float4*>(s1 + i + 4) = make_float4(m[4], m[5], m[6], m[7]);
+    uint4 o;
+    o.x = pack_bf16x2(p[0], p[1]);
+    o.y = pack_bf16x2(p[2], p[3]);
+    o.z = pack_bf16x2(p[4], p[5]);
+    o.w = pack_bf16x2(p[6], p[7]);
+    return o;
+}
+
+__global__ void __launch_bounds__(512)
+flat_optim_kernel(OptHyper h, float* __restrict__ master, float* __restrict__ s1,
+                  float* __restrict__ s2, const __nv_bfloat16* __restrict__ grad,
+                  __nv_bfloat16* __restrict__ param, size_t n, const unsigned char* __restrict__ wd_mask,
+                  size_t mask_offset) {
+    const size_t nvec = n / 8;
+    for (size_t v = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; v < nvec;
+         v += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const size_t i = v * 8;
+        float g[8];
+        unpack8f(ld_global_nc_v4(grad + i), g);
+        const float wd = (wd_mask == nullptr || wd_mask[(mask_offset + i) >> 8]) ? h.weight_decay : 0.f;
+        const uint4 w = optim_update8(h, master, s1, s2, i, g, wd);
+        st_global_v4(param + i, w);
+    }
+}
+
+struct FusedArgs {
+    tony_fused_comm comm;
+    size_t begin, count, state_offset;
+    float* master;
+    float* s1;
+    float* s2;
+    const unsigned char* wd_mask;
+    int broadcast;
+    uint32_t epoch;
+    unsigned long long timeout_ns;
+    float ar_scale;  // plain all-reduce: out = sum * ar_scale
+};
+
+// Phase A/C helper: tell every peer we reached `epoch` in flag slot `slot`, then wait for all.
+__device__ __forceinline__ bool arrive_and_wait_all(const FusedArgs& a, int slot, int tid) {
+    const int world = a.comm.world, rank = a.comm.rank;
+    bool ok = true;
+    if (tid < world && tid != rank) {
+        st_release_sys(a.comm.flags[tid] + slot * TONY_MAX_RANKS + rank, a.epoch);
+        ok = wait_flag_sys(a.comm.flags[rank] + slot * TONY_MAX_RANKS + tid, a.epoch, a.timeout_ns);
+        if (!ok) *a.comm.status = TONY_ERR_TIMEOUT;
+    }
+    return ok;
+}
+
+__global__ void __launch_bounds__(512)
+fused_reduce_optim_kernel(OptHyper h, FusedArgs a) {
+    __shared__ int sh_flag;
+    const int world = a.comm.world, rank = a.comm.rank;
+    const int tid = threadIdx.x;
+
+    // ---- A: every rank's bucket is complete (stream order covers our own) -------------
+    if (world > 1) {
+        if (tid == 0) sh_flag = 1;
+        __syncthreads();
+        if (blockIdx.x == 0) {
+            __threadfence_system();
+            if (!arrive_and_wait_all(a, 0, tid)) sh_flag = 0;
+        } else if (tid < world && tid != rank) {
+            if (!wait_flag_sys(a.comm.flags[rank] + tid, a.epoch, a.timeout_ns)) {
+                *a.comm.status = TONY_ERR_TIMEOUT;
+                sh_flag = 0;
+            }
+        }
+        __syncthreads();
+        if (!sh_flag) return;  // a peer never arrived: leave state untouched, host sees status
+    }
+
+    // ---- B: reduce my shard from all peers, update, broadcast ---------------------------
+    const size_t chunk = a.count / world;
+    const size_t my_begin = a.begin + static_cast<size_t>(rank) * chunk;
+    const size_t nvec = chunk / 8;
+    for (size_t v = blockIdx.x * static_cast<size_t>(blockDim.x) + tid; v < nvec;
+         v += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const size_t idx = my_begin + v * 8;
+        uint4 gv[TONY_MAX_RANKS];
+#pragma unroll
+        for (int j = 0; j < TONY_MAX_RANKS; ++j) {
+            if (j < world) {
+                int r = rank + j;
+                if (r >= world) r -= world;
+                gv[j] = ld_global_v4(static_cast<const __nv_bfloat16*>(a.comm.grad[r]) + idx);
+            }
+        }
+        float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < TONY_MAX_RANKS; ++j) {
+            if (j < world) {
+                float t[8];
+                unpack8f(gv[j], t);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) g[k] += t[k];
+            }
+        }
+        uint4 w;
+        if (h.optimizer >= 0) {
+            const size_t si = a.state_offset + v * 8;
+            const float wd = (a.wd_mask == nullptr || a.wd_mask[idx >> 8]) ? h.weight_decay : 0.f;
+            w = optim_update8(h, a.master, a.s1, a.s2, si, g, wd);
+        } else {
+            w.x = pack_bf16x2(g[0] * a.ar_scale, g[1] * a.ar_scale);
+            w.y = pack_bf16x2(g[2] * a.ar_scale, g[3] * a.ar_scale);
+            w.z = pack_bf16x2(g[4] * a.ar_scale, g[5] * a.ar_scale);
+            w.w = pack_bf16x2(g[6] * a.ar_scale, g[7] * a.ar_scale);
+        }
+        if (a.broadcast) {
+#pragma unroll
+            for (int j = 0; j < TONY_MAX_RANKS; ++j) {
+                if (j < world) {
+                    int r = rank + j;
+                    if (r >= world) r -= world;
+                    st_global_v4(static_cast<__nv_bfloat16*>(a.comm.param[r]) + idx, w);
+                }
+            }
+        } else {
+            st_global_v4(static_cast<__nv_bfloat16*>(a.comm.param[rank]) + idx, w);
+        }
+    }
+
+    // ---- C: last CTA out signals "done" and waits for every peer's "done" ------------
+    if (world > 1) {
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0) {
+            const unsigned int prev = atomicAdd(a.comm.counter, 1u);
+            sh_flag = (prev == gridDim.x - 1) ? 2 : 1;
+        }
+        __syncthreads();
+        if (sh_flag == 2) {
+            __threadfence_system();
+            if (tid == 0) *a.comm.counter = 0;  // ready for the next launch
+            arrive_and_wait_all(a, 1, tid);
+        }
+    }
+}
+
+__global__ void symm_barrier_kernel(FusedArgs a) {
+    __threadfence_system();
+    arrive_and_wait_all(a, 0, threadIdx.x);
+}
+
+static unsigned long long comm_timeout_ns() {
+    static unsigned long long cached = 0;
+    if (cached == 0) {
+        const char* e = getenv("TONY_B200_COMM_TIMEOUT_MS");
+        long long ms = e ? atoll(e) : 60000;
+        if (ms <= 0) ms = 60000;
+        cached = static_cast<unsigned long long>(ms) * 1000000ull;
+    }
+    return cached;
+}
+
+static int check_comm(const tony_fused_comm* c, const char* who) {
+    if (!c || c->world < 1 || c->world > TONY_MAX_RANKS || c->rank < 0 || c->rank >= c->world) {
+        set_last_error(who, "bad comm descriptor (world must be 1..8)");
+        return TONY_ERR_INVALID;
+    }
+    if (c->world > 1 && (!c->counter || !c->status)) {
+        set_last_error(who, "comm.counter / comm.status must be set when world > 1");
+        return TONY_ERR_INVALID;
+    }
+    for (int r = 0; r < c->world; ++r)
+        if (!c->grad[r] || !c->param[r] || (c->world > 1 && !c->flags[r])) {
+            set_last_error(who, "comm has a null peer pointer");
+            return TONY_ERR_INVALID;
+        }
+    return TONY_OK;
+}
+
+}  // namespace tony
+
+using namespace tony;
+
+static OptHyper make_hyper(int optimizer, float lr, float b1, float b2, float eps, float wd, float bc1,
+                           float bc2, float grad_scale, int nesterov) {
+    OptHyper h;
+    h.optimizer = optimizer;
+    h.lr = lr;
+    h.beta1 = b1;
+    h.beta2 = b2;
+    h.eps = eps;
+    h.weight_decay = wd;
+    h.inv_bc1 = bc1 > 0.f ? 1.0f / bc1 : 1.0f;
+    h.inv_sqrt_bc2 = bc2 > 0.f ? 1.0f / sqrtf(bc2) : 1.0f;
+    h.grad_scale = grad_scale;
+    h.nesterov = nesterov;
+    return h;
+}
+
+static int launch_flat(const OptHyper& h, float* master, float* s1, float* s2, const void* grad,
+                       void* param, size_t n, const unsigned char* wd_mask, size_t mask_offset,
+                       void* stream) {
+    if (!master || !s1 || !grad || !param || n == 0 || (n % 8) != 0) {
+        set_last_error("flat optimizer", "null pointer, or n not a multiple of 8");
+        return TONY_ERR_INVALID;
+    }
+    const int threads = 512;
+    const size_t nvec = n / 8;
+    const int grid = static_cast<int>(
+        std::min<size_t>((nvec + threads - 1) / threads, static_cast<size_t>(device_sm_count()) * 4));
+    flat_optim_kernel<<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+        h, master, s1, s2, static_cast<const __nv_bfloat16*>(grad), static_cast<__nv_bfloat16*>(param),
+        n, wd_mask, mask_offset);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}
+
+extern "C" int tony_adamw_flat(float* master, float* exp_avg, float* exp_avg_sq,
+                               const void* grad_bf16, void* param_bf16, size_t n, float lr,
+                               float beta1, float beta2, float eps, float weight_decay, float bc1,
+                               float bc2, float grad_scale, const unsigned char* wd_mask,
+                               size_t mask_offset_elems, void* stream) {
+    if (!exp_avg_sq) return TONY_ERR_INVALID;
+    return launch_flat(make_hyper(TONY_OPT_ADAMW, lr, beta1, beta2, eps, weight_decay, bc1, bc2,
+                                  grad_scale, 0),
+                       master, exp_avg, exp_avg_sq, grad_bf16, param_bf16, n, wd_mask,
+                       mask_offset_elems, stream);
+}
+
+extern "C" int tony_sgd_flat(float* master, float* momentum_buf, const void* grad_bf16,
+                             void* param_bf16, size_t n, float lr, float momentum,
+                             float weight_decay, int nesterov, float grad_scale,
+                             const unsigned char* wd_mask, size_t mask_offset_elems, void* stream) {
+    return launch_flat(make_hyper(TONY_OPT_SGD, lr, momentum, 0.f, 0.f, weight_decay, 1.f, 1.f,
+                                  grad_scale, nesterov),
+                       master, momentum_buf, nullptr, grad_bf16, param_bf16, n, wd_mask,
+                       mask_offset_elems, stream);
+}
+
+static int launch_fused(const OptHyper& h, FusedArgs& a, int num_ctas, void* stream) {
+    a.timeout_ns = comm_timeout_ns();
+    const int threads = 512;
+    const size_t nvec = a.count / a.comm.world / 8;
+    int grid = num_ctas > 0 ? num_ctas : 32;
+    grid = static_cast<int>(std::min<size_t>(grid, std::max<size_t>(1, (nvec + threads - 1) / threads)));
+    grid = std::min(grid, device_sm_count());  // phase C needs every CTA eventually resident
+    fused_reduce_optim_kernel<<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(h, a);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}
+
+extern "C" int tony_fused_reduce_optim(const tony_fused_comm* comm, size_t begin, size_t count,
+                                       float* master, float* state1, float* state2,
+                                       size_t state_offset, int optimizer, float lr,
+                                       float beta1_or_momentum, float beta2, float eps,
+                                       float weight_decay, float bc1, float bc2, float grad_scale,
+                                       const unsigned char* wd_mask, int broadcast,
+                                       unsigned int epoch, int num_ctas, void* stream) {
+    int rc = check_comm(comm, "tony_fused_reduce_optim");
+    if (rc) return rc;
+    if (count == 0 || (count % (static_cast<size_t>(comm->world) * 8)) != 0 || (begin % 8) != 0 ||
+        (state_offset % 8) != 0) {
+        set_last_error("tony_fused_reduce_optim", "count must be a multiple of world*8; begin/state_offset of 8");
+        return TONY_ERR_INVALID;
+    }
+    if (!master || !state1 || (optimizer == TONY_OPT_ADAMW && !state2) ||
+        (optimizer != TONY_OPT_ADAMW && optimizer != TONY_OPT_SGD))
+        return TONY_ERR_INVALID;
+    FusedArgs a;
+    a.comm = *comm;
+    a.begin = begin;
+    a.count = count;
+    a.state_offset = state_offset;
+    a.master = master;
+    a.s1 = state1;
+    a.s2 = state2;
+    a.wd_mask = wd_mask;
+    a.broadcast = broadcast;
+    a.epoch = epoch;
+    a.ar_scale = 1.f;
+    return launch_fused(make_hyper(optimizer, lr, beta1_or_momentum, beta2, eps, weight_decay, bc1, bc2,
+                                   grad_scale, 0),
+                        a, num_ctas, stream);
+}
+
+extern "C" int tony_symm_allreduce_bf16(const tony_fused_comm* comm, size_t begin, size_t count,
+                                        float scale, unsigned int epoch, int num_ctas,
+                                        void* stream) {
+    int rc = check_comm(comm, "tony_symm_allreduce_bf16");
+    if (rc) return rc;
+    if (count == 0 || (count % (static_cast<size_t>(comm->world) * 8)) != 0 || (begin % 8) != 0) {
+        set_last_error("tony_symm_allreduce_bf16", "count must be a multiple of world*8; begin of 8");
+        return TONY_ERR_INVALID;
+    }
+    FusedArgs a;
+    a.comm = *comm;
+    a.begin = begin;
+    a.count = count;
+    a.state_offset = 0;
+    a.master = a.s1 = a.s2 = nullptr;
+    a.wd_mask = nullptr;
+    a.broadcast = 1;
+    a.epoch = epoch;
+    a.ar_scale = scale;
+    return launch_fused(make_hyper(-1, 0, 0, 0, 0, 0, 1, 1, 1, 0), a, num_ctas, stream);
+}
+
+extern "C" int tony_symm_barrier(const tony_fused_comm* comm, unsigned int epoch, void* stream) {
+    if (!comm || comm->world < 1 || comm->world > TONY_MAX_RANKS) return TONY_ERR_INVALID;
+    if (comm->world == 1) return TONY_OK;
+    for (int r = 0; r < comm->world; ++r)
+        if (!comm->flags[r]) return TONY_ERR_INVALID;
+    if (!comm->status) return TONY_ERR_INVALID;
+    FusedArgs a;
+    a.comm = *comm;
+    a.begin = a.count = a.state_offset = 0;
+    a.master = a.s1 = a.s2 = nullptr;
+    a.wd_mask = nullptr;
+    a.broadcast = 0;
+    a.epoch = epoch;
+    a.ar_scale = 1.f;
+    a.timeout_ns = comm_timeout_ns();
+    symm_barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(a);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}

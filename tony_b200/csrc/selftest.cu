@@ -1,0 +1,350 @@
+// tony_b200 — stand-alone GPU self test + micro-benchmark for the GEMM entry points.
+//
+//   tony_selftest [--perf] [--probe]
+//
+// Checks tony_gemm_bf16 against a naive fp32-accumulating reference kernel for every
+// operand-major combination, ragged shapes, every epilogue and split-K; on an
+// MN-major mismatch it runs "probe" GEMMs with integer-coded operands that reveal
+// which (n, k) element the tensor core actually fetched, so a descriptor mistake can be
+// diagnosed from one run.  --perf times the BERT-large / GPT-2 shapes with CUDA events
+// (3 warm-ups, L2 flushed between iterations) and prints achieved TFLOP/s.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "tony_b200_kernels.h"
+
+#define CK(x)                                                                          \
+    do {                                                                               \
+        cudaError_t e_ = (x);                                                          \
+        if (e_ != cudaSuccess) {                                                       \
+            printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); \
+            exit(2);                                                                   \
+        }                                                                              \
+    } while (0)
+
+__device__ __host__ inline float gelu_erf_ref(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678f)); }
+__device__ __host__ inline float dgelu_erf_ref(float x) {
+    return 0.5f * (1.0f + erff(x * 0.70710678f)) + x * 0.39894228f * expf(-0.5f * x * x);
+}
+__device__ __host__ inline float gelu_tanh_ref(float x) {
+    return 0.5f * x * (1.0f + tanhf(0.79788456f * (x + 0.044715f * x * x * x)));
+}
+
+// A(m,k): a_mn ? A[k*lda+m] : A[m*lda+k];  B(n,k): b_mn ? B[k*ldb+n] : B[n*ldb+k]
+__global__ void ref_gemm(const __nv_bfloat16* A, const __nv_bfloat16* B, float* C, int M, int N, int K,
+                         int a_mn, int b_mn, long long lda, long long ldb, unsigned flags, float alpha,
+                         const __nv_bfloat16* bias, const __nv_bfloat16* aux, const __nv_bfloat16* c_old,
+                         float* pre) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const int m = blockIdx.y;
+    if (n >= N || m >= M) return;
+    float acc = 0.f;
+    for (int k = 0; k < K; ++k) {
+        const float a = __bfloat162float(a_mn ? A[(size_t)k * lda + m] : A[(size_t)m * lda + k]);
+        const float b = __bfloat162float(b_mn ? B[(size_t)k * ldb + n] : B[(size_t)n * ldb + k]);
+        acc += a * b;
+    }
+    float v = acc * alpha;
+    if (flags & TONY_EPI_BIAS) v += __bfloat162float(bias[n]);
+    if (flags & TONY_EPI_RESIDUAL) v += __bfloat162float(aux[(size_t)m * N + n]);
+    if (flags & TONY_EPI_DGELU_ERF) v *= dgelu_erf_ref(__bfloat162float(aux[(size_t)m * N + n]));
+    if (flags & TONY_EPI_DRELU) v = __bfloat162float(aux[(size_t)m * N + n]) > 0.f ? v : 0.f;
+    if (pre) pre[(size_t)m * N + n] = v;
+    if (flags & TONY_EPI_GELU_ERF) v = gelu_erf_ref(v);
+    if (flags & TONY_EPI_GELU_TANH) v = gelu_tanh_ref(v);
+    if (flags & TONY_EPI_RELU) v = fmaxf(v, 0.f);
+    if (flags & TONY_EPI_ACCUMULATE) v += __bfloat162float(c_old[(size_t)m * N + n]);
+    C[(size_t)m * N + n] = v;
+}
+
+static std::vector<__nv_bfloat16> rand_bf16(size_t n, unsigned seed, float scale = 1.0f) {
+    std::vector<__nv_bfloat16> v(n);
+    unsigned s = seed * 2654435761u + 12345u;
+    for (size_t i = 0; i < n; ++i) {
+        s = s * 1664525u + 1013904223u;
+        const float f = ((s >> 8) & 0xFFFF) / 65536.0f * 2.0f - 1.0f;
+        v[i] = __float2bfloat16(f * scale);
+    }
+    return v;
+}
+
+template <class T>
+static T* to_dev(const std::vector<T>& h) {
+    T* d;
+    CK(cudaMalloc(&d, h.size() * sizeof(T)));
+    CK(cudaMemcpy(d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return d;
+}
+
+static int g_fail = 0;
+
+struct Case {
+    const char* name;
+    int M, N, K, a_mn, b_mn;
+    unsigned flags;
+    float alpha;
+    int use_ws;
+};
+
+static void probe(int a_mn, int b_mn);
+
+static bool run_case(const Case& c) {
+    const int M = c.M, N = c.N, K = c.K;
+    const long long lda = c.a_mn ? M : K, ldb = c.b_mn ? N : K;
+    auto hA = rand_bf16((size_t)M * K, 1), hB = rand_bf16((size_t)N * K, 2);
+    auto hbias = rand_bf16(N, 3), haux = rand_bf16((size_t)M * N, 4, 2.0f), hC0 = rand_bf16((size_t)M * N, 5);
+    __nv_bfloat16 *dA = to_dev(hA), *dB = to_dev(hB), *dbias = to_dev(hbias), *daux = to_dev(haux);
+    __nv_bfloat16* dC = to_dev(hC0);
+    __nv_bfloat16* dCold = to_dev(hC0);
+    __nv_bfloat16* dpre;
+    CK(cudaMalloc(&dpre, (size_t)M * N * 2));
+    CK(cudaMemset(dpre, 0, (size_t)M * N * 2));
+    float *dref, *dpre_ref;
+    CK(cudaMalloc(&dref, (size_t)M * N * 4));
+    CK(cudaMalloc(&dpre_ref, (size_t)M * N * 4));
+    void* ws = nullptr;
+    size_t ws_bytes = 0;
+    if (c.use_ws) {
+        ws_bytes = (size_t)64 << 20;
+        CK(cudaMalloc(&ws, ws_bytes));
+    }
+    ref_gemm<<<dim3((N + 127) / 128, M), 128>>>(dA, dB, dref, M, N, K, c.a_mn, c.b_mn, lda, ldb, c.flags,
+                                                c.alpha, dbias, daux, dCold, dpre_ref);
+    CK(cudaGetLastError());
+    int rc = tony_gemm_bf16(dA, dB, dC, M, N, K, c.a_mn, c.b_mn, lda, ldb, N, c.flags, c.alpha, dbias,
+                            daux, N, dpre, ws, ws_bytes, nullptr);
+    if (rc != 0) {
+        printf("[FAIL] %-34s rc=%d (%s)\n", c.name, rc, tony_last_error());
+        g_fail++;
+        return false;
+    }
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        printf("[FAIL] %-34s CUDA error after launch: %s\n", c.name, cudaGetErrorString(e));
+        exit(3);  // context is dead: nothing else can run
+    }
+    std::vector<__nv_bfloat16> out((size_t)M * N), pre((size_t)M * N);
+    std::vector<float> ref((size_t)M * N), pre_ref((size_t)M * N);
+    CK(cudaMemcpy(out.data(), dC, out.size() * 2, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(pre.data(), dpre, pre.size() * 2, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(ref.data(), dref, ref.size() * 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(pre_ref.data(), dpre_ref, ref.size() * 4, cudaMemcpyDeviceToHost));
+    double max_ref = 0, max_err = 0;
+    size_t bad = 0, first_bad = (size_t)-1;
+    for (size_t i = 0; i < ref.size(); ++i) max_ref = fmax(max_ref, fabs(ref[i]));
+    const double tol = 1.5e-2 * max_ref + 1e-3;
+    for (size_t i = 0; i < ref.size(); ++i) {
+        const double err = fabs((double)__bfloat162float(out[i]) - ref[i]);
+        max_err = fmax(max_err, err);
+        if (!(err <= tol)) {
+            if (first_bad == (size_t)-1) first_bad = i;
+            bad++;
+        }
+    }
+    size_t bad_pre = 0;
+    if (c.flags & TONY_EPI_SAVE_PREACT) {
+        for (size_t i = 0; i < ref.size(); ++i)
+            if (!(fabs((double)__bfloat162float(pre[i]) - pre_ref[i]) <= tol)) bad_pre++;
+    }
+    const bool ok = bad == 0 && bad_pre == 0;
+    printf("[%s] %-34s M=%d N=%d K=%d maj=(%d,%d) flags=0x%x max_err=%.4g max_ref=%.4g bad=%zu/%zu",
+           ok ? " ok " : "FAIL", c.name, M, N, K, c.a_mn, c.b_mn, c.flags, max_err, max_ref, bad, ref.size());
+    if (bad_pre) printf(" bad_preact=%zu", bad_pre);
+    if (!ok && first_bad != (size_t)-1) {
+        printf(" first_bad=(%zu,%zu) got=%g want=%g", first_bad / N, first_bad % N,
+               __bfloat162float(out[first_bad]), ref[first_bad]);
+    }
+    printf("\n");
+    if (!ok) {
+        g_fail++;
+        // error map over the first 128x(min(N,256)) tile: '.' ok, 'x' bad, per 8x8 block
+        const int rows = M < 128 ? M : 128, cols = N < 256 ? N : 256;
+        for (int rb = 0; rb < rows; rb += 8) {
+            printf("    r%3d ", rb);
+            for (int cb = 0; cb < cols; cb += 8) {
+                int nb = 0;
+                for (int r = rb; r < rb + 8 && r < rows; ++r)
+                    for (int cc = cb; cc < cb + 8 && cc < cols; ++cc) {
+                        const size_t i = (size_t)r * N + cc;
+                        if (!(fabs((double)__bfloat162float(out[i]) - ref[i]) <= tol)) nb++;
+                    }
+                putchar(nb == 0 ? '.' : (nb == 64 ? 'X' : 'x'));
+            }
+            printf("\n");
+        }
+    }
+    cudaFree(dA); cudaFree(dB); cudaFree(dbias); cudaFree(daux); cudaFree(dC); cudaFree(dCold);
+    cudaFree(dpre); cudaFree(dref); cudaFree(dpre_ref);
+    if (ws) cudaFree(ws);
+    return ok;
+}
+
+// Integer-coded operands: which (n,k) does the hardware fetch for logical (n,k)?
+static void probe(int a_mn, int b_mn) {
+    const int M = 128, N = 128, K = 64;
+    printf("  probe maj=(%d,%d): the operand under test holds an index code, the other is one-hot/ones\n", a_mn, b_mn);
+    for (int which = 0; which < 2; ++which) {       // 0: probe B, 1: probe A
+        if ((which == 0 && !b_mn) || (which == 1 && !a_mn)) continue;
+        for (int mode = 0; mode < 2; ++mode) {       // 0: code = mn index, 1: code = k index
+            std::vector<__nv_bfloat16> hA((size_t)M * K), hB((size_t)N * K);
+            const int k0s[4] = {0, 1, 9, 37};
+            for (int t = 0; t < (mode == 0 ? 1 : 4); ++t) {
+                const int k0 = k0s[t];
+                for (int m = 0; m < M; ++m)
+                    for (int k = 0; k < K; ++k) {
+                        float va, vb;
+                        if (which == 0) {  // A one-hot in k (mode 1) or ones at k0 only
+                            va = (k == k0) ? 1.f : 0.f;
+                            vb = 0.f;
+                        } else {
+                            va = mode == 0 ? (float)(m) : (float)k;
+                            vb = 0.f;
+                        }
+                        (void)vb;
+                        const size_t ia = a_mn ? (size_t)k * M + m : (size_t)m * K + k;
+                        hA[ia] = __float2bfloat16(va);
+                    }
+                for (int n = 0; n < N; ++n)
+                    for (int k = 0; k < K; ++k) {
+                        float vb;
+                        if (which == 0) vb = mode == 0 ? (float)n : (float)k;
+                        else vb = (k == k0) ? 1.f : 0.f;
+                        const size_t ib = b_mn ? (size_t)k * N + n : (size_t)n * K + k;
+                        hB[ib] = __float2bfloat16(vb);
+                    }
+                __nv_bfloat16 *dA = to_dev(hA), *dB = to_dev(hB), *dC;
+                CK(cudaMalloc(&dC, (size_t)M * N * 2));
+                int rc = tony_gemm_bf16(dA, dB, dC, M, N, K, a_mn, b_mn, a_mn ? M : K, b_mn ? N : K, N, 0,
+                                        1.0f, nullptr, nullptr, 0, nullptr, nullptr, 0, nullptr);
+                if (rc) { printf("  probe rc=%d\n", rc); return; }
+                CK(cudaDeviceSynchronize());
+                std::vector<__nv_bfloat16> out((size_t)M * N);
+                CK(cudaMemcpy(out.data(), dC, out.size() * 2, cudaMemcpyDeviceToHost));
+                printf("    probe %c mode=%s k0=%d:", which == 0 ? 'B' : 'A', mode == 0 ? "mn" : "k", k0);
+                if (which == 0) {
+                    for (int n = 0; n < N; n += (mode == 0 ? 1 : 16)) printf(" %g", __bfloat162float(out[n]));
+                } else {
+                    for (int m = 0; m < M; m += (mode == 0 ? 1 : 16)) printf(" %g", __bfloat162float(out[(size_t)m * N]));
+                }
+                printf("\n");
+                cudaFree(dA); cudaFree(dB); cudaFree(dC);
+            }
+        }
+    }
+}
+
+static void perf_case(const char* name, int M, int N, int K, int a_mn, int b_mn, unsigned flags, int use_ws) {
+    const long long lda = a_mn ? M : K, ldb = b_mn ? N : K;
+    auto hA = rand_bf16((size_t)M * K, 11), hB = rand_bf16((size_t)N * K, 12), hbias = rand_bf16(N, 13);
+    __nv_bfloat16 *dA = to_dev(hA), *dB = to_dev(hB), *dbias = to_dev(hbias), *dC, *dpre;
+    CK(cudaMalloc(&dC, (size_t)M * N * 2));
+    CK(cudaMalloc(&dpre, (size_t)M * N * 2));
+    void* ws = nullptr;
+    size_t ws_bytes = 0;
+    if (use_ws) {
+        ws_bytes = (size_t)256 << 20;
+        CK(cudaMalloc(&ws, ws_bytes));
+    }
+    void* flush;
+    const size_t flush_bytes = (size_t)256 << 20;
+    CK(cudaMalloc(&flush, flush_bytes));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    float best = 1e30f, total = 0.f;
+    const int iters = 10;
+    for (int it = 0; it < iters + 3; ++it) {
+        CK(cudaMemsetAsync(flush, it, flush_bytes));
+        CK(cudaEventRecord(e0));
+        int rc = tony_gemm_bf16(dA, dB, dC, M, N, K, a_mn, b_mn, lda, ldb, N, flags, 1.0f, dbias, dC, N, dpre,
+                                ws, ws_bytes, nullptr);
+        CK(cudaEventRecord(e1));
+        if (rc) { printf("perf %s rc=%d %s\n", name, rc, tony_last_error()); return; }
+        CK(cudaEventSynchronize(e1));
+        float ms;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        if (it >= 3) { best = fminf(best, ms); total += ms; }
+    }
+    const double fl = 2.0 * M * N * (double)K;
+    printf("[perf] %-28s M=%d N=%d K=%d maj=(%d,%d) flags=0x%x  best %.3f ms = %.1f TFLOP/s  mean %.3f ms = %.1f TFLOP/s\n",
+           name, M, N, K, a_mn, b_mn, flags, best, fl / best / 1e9, total / iters, fl / (total / iters) / 1e9);
+    cudaFree(dA); cudaFree(dB); cudaFree(dbias); cudaFree(dC); cudaFree(dpre); cudaFree(flush);
+    if (ws) cudaFree(ws);
+}
+
+int main(int argc, char** argv) {
+    bool perf = false, want_probe = false;
+    for (int i = 1; i < argc; ++i) {
+        if (!strcmp(argv[i], "--perf")) perf = true;
+        if (!strcmp(argv[i], "--probe")) want_probe = true;
+    }
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, 0));
+    printf("device: %s sm_%d%d, %d SMs, lib version %d\n", prop.name, prop.major, prop.minor,
+           prop.multiProcessorCount, tony_version());
+
+    const Case cases[] = {
+        {"kmajor_k16", 128, 128, 16, 0, 0, 0, 1.f, 0},
+        {"kmajor_k64", 128, 128, 64, 0, 0, 0, 1.f, 0},
+        {"kmajor_k128", 128, 256, 128, 0, 0, 0, 1.f, 0},
+        {"kmajor_multi_tile", 512, 1024, 512, 0, 0, 0, 1.f, 0},
+        {"kmajor_many_tiles(persist)", 2048, 4096, 256, 0, 0, 0, 1.f, 0},
+        {"kmajor_ragged", 200, 264, 72, 0, 0, 0, 1.f, 0},
+        {"kmajor_alpha", 256, 256, 256, 0, 0, 0, 0.5f, 0},
+        {"b_mn_k16", 128, 128, 16, 0, 1, 0, 1.f, 0},
+        {"b_mn_k64", 128, 128, 64, 0, 1, 0, 1.f, 0},
+        {"b_mn (dgrad)", 512, 1024, 512, 0, 1, 0, 1.f, 0},
+        {"a_mn_k16", 128, 128, 16, 1, 0, 0, 1.f, 0},
+        {"a_mn", 512, 1024, 512, 1, 0, 0, 1.f, 0},
+        {"ab_mn (wgrad)", 512, 1024, 512, 1, 1, 0, 1.f, 0},
+        {"ab_mn_ragged", 200, 264, 72, 1, 1, 0, 1.f, 0},
+        {"ab_mn_n128", 384, 128, 320, 1, 1, 0, 1.f, 0},
+        {"epi_bias", 256, 512, 256, 0, 0, TONY_EPI_BIAS, 1.f, 0},
+        {"epi_bias_gelu_erf_save", 256, 512, 256, 0, 0, TONY_EPI_BIAS | TONY_EPI_GELU_ERF | TONY_EPI_SAVE_PREACT, 1.f, 0},
+        {"epi_bias_gelu_tanh", 256, 512, 256, 0, 0, TONY_EPI_BIAS | TONY_EPI_GELU_TANH, 1.f, 0},
+        {"epi_bias_residual", 256, 512, 256, 0, 0, TONY_EPI_BIAS | TONY_EPI_RESIDUAL, 1.f, 0},
+        {"epi_dgelu_erf", 256, 512, 256, 0, 1, TONY_EPI_DGELU_ERF, 1.f, 0},
+        {"epi_relu_drelu", 256, 512, 256, 0, 1, TONY_EPI_DRELU, 1.f, 0},
+        {"epi_bias_relu", 256, 512, 256, 0, 0, TONY_EPI_BIAS | TONY_EPI_RELU, 1.f, 0},
+        {"epi_accumulate", 256, 512, 256, 1, 1, TONY_EPI_ACCUMULATE, 1.f, 0},
+        {"splitk_wgrad", 1024, 1024, 8192, 1, 1, 0, 1.f, 1},
+        {"splitk_wgrad_accum", 1024, 1024, 4096, 1, 1, TONY_EPI_ACCUMULATE, 1.f, 1},
+        {"splitk_ragged", 200, 264, 4104, 1, 1, 0, 1.f, 1},
+    };
+    bool mn_fail[2][2] = {{false, false}, {false, false}};
+    for (const Case& c : cases) {
+        const bool ok = run_case(c);
+        if (!ok) mn_fail[c.a_mn][c.b_mn] = true;
+    }
+    if (want_probe || mn_fail[0][1] || mn_fail[1][0] || mn_fail[1][1]) {
+        if (!mn_fail[0][0]) {
+            probe(0, 1);
+            probe(1, 0);
+        } else {
+            printf("  (K-major baseline failing: probes skipped, fix that first)\n");
+        }
+    }
+    if (perf && g_fail == 0) {
+        // BERT-large (tokens = 16 x 512 = 8192) and GPT-2 medium shapes: fwd, dgrad, wgrad
+        perf_case("fwd qkv", 8192, 3072, 1024, 0, 0, TONY_EPI_BIAS, 0);
+        perf_case("fwd attn_out(+res)", 8192, 1024, 1024, 0, 0, TONY_EPI_BIAS | TONY_EPI_RESIDUAL, 0);
+        perf_case("fwd ffn1(+gelu)", 8192, 4096, 1024, 0, 0, TONY_EPI_BIAS | TONY_EPI_GELU_ERF | TONY_EPI_SAVE_PREACT, 0);
+        perf_case("fwd ffn2(+res)", 8192, 1024, 4096, 0, 0, TONY_EPI_BIAS | TONY_EPI_RESIDUAL, 0);
+        perf_case("dgrad ffn2(dgelu)", 8192, 4096, 1024, 0, 1, TONY_EPI_DGELU_ERF, 0);
+        perf_case("dgrad ffn1", 8192, 1024, 4096, 0, 1, 0, 0);
+        perf_case("wgrad ffn1", 4096, 1024, 8192, 1, 1, 0, 1);
+        perf_case("wgrad ffn2", 1024, 4096, 8192, 1, 1, 0, 1);
+        perf_case("wgrad attn_out", 1024, 1024, 8192, 1, 1, 0, 1);
+        perf_case("wgrad qkv", 3072, 1024, 8192, 1, 1, 0, 1);
+        perf_case("square 8192", 8192, 8192, 8192, 0, 0, 0, 0);
+        perf_case("square 4096", 4096, 4096, 4096, 0, 0, 0, 0);
+    }
+    printf("%s: %d failing case(s)\n", g_fail ? "SELFTEST FAILED" : "SELFTEST PASSED", g_fail);
+    return g_fail ? 1 : 0;
+}

@@ -1,0 +1,165 @@
+"""ctypes binding of ``libtony_b200_kernels.so`` (C ABI in ``include/tony_b200_kernels.h``).
+
+The library is built in-tree by :mod:`tony_b200.csrc.build`.  There is deliberately no
+PyTorch/eager fallback: on a machine with a GPU a missing or unloadable library raises, so
+a "passing" run can never silently be a stock-kernel run.  The reference ships no native
+code; this loader has no counterpart there.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+from ctypes import (
+    POINTER,
+    Structure,
+    c_char_p,
+    c_float,
+    c_int,
+    c_longlong,
+    c_size_t,
+    c_ubyte,
+    c_uint,
+    c_ulonglong,
+    c_void_p,
+)
+from pathlib import Path
+
+LIB_PATH = Path(__file__).resolve().parent.parent / "lib" / "libtony_b200_kernels.so"
+MAX_RANKS = 8
+
+# epilogue flags (keep in sync with include/tony_b200_kernels.h)
+EPI_BIAS = 0x001
+EPI_GELU_ERF = 0x002
+EPI_GELU_TANH = 0x004
+EPI_RESIDUAL = 0x008
+EPI_DGELU_ERF = 0x010
+EPI_DGELU_TANH = 0x020
+EPI_ACCUMULATE = 0x040
+EPI_SAVE_PREACT = 0x080
+EPI_RELU = 0x100
+EPI_DRELU = 0x200
+
+OPT_ADAMW = 0
+OPT_SGD = 1
+
+ERR_TIMEOUT = 5
+
+
+class KernelError(RuntimeError):
+    pass
+
+
+class FusedComm(Structure):
+    """Mirror of ``tony_fused_comm``."""
+
+    _fields_ = [
+        ("rank", c_int),
+        ("world", c_int),
+        ("grad", c_void_p * MAX_RANKS),
+        ("param", c_void_p * MAX_RANKS),
+        ("flags", c_void_p * MAX_RANKS),
+        ("counter", c_void_p),
+        ("status", c_void_p),
+    ]
+
+
+_lock = threading.Lock()
+_lib = None
+
+
+def _declare(lib) -> None:
+    vp = c_void_p
+    lib.tony_last_error.restype = c_char_p
+    lib.tony_version.restype = c_int
+    lib.tony_launch_count.restype = c_ulonglong
+    lib.tony_gemm_bf16.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_longlong,
+                                   c_longlong, c_longlong, c_uint, c_float, vp, vp, c_longlong, vp,
+                                   vp, c_size_t, vp]
+    lib.tony_gemm_bf16_ex.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_longlong,
+                                      c_longlong, c_longlong, c_uint, c_float, vp, vp, c_longlong,
+                                      vp, vp, c_size_t, c_int, c_int, vp, c_uint, c_int, c_int, vp]
+    lib.tony_layernorm_fwd.argtypes = [vp, vp, vp, vp, vp, vp, c_int, c_int, c_float, vp]
+    lib.tony_layernorm_bwd_scratch_bytes.argtypes = [c_int]
+    lib.tony_layernorm_bwd_scratch_bytes.restype = c_size_t
+    lib.tony_layernorm_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, c_int, c_int, vp, c_size_t,
+                                       c_int, vp]
+    lib.tony_softmax_xent_fwd_bwd.argtypes = [vp, vp, vp, c_int, c_int, c_longlong, c_longlong,
+                                              c_float, vp, vp]
+    lib.tony_colsum_scratch_bytes.argtypes = [c_int]
+    lib.tony_colsum_scratch_bytes.restype = c_size_t
+    lib.tony_colsum_bf16.argtypes = [vp, c_int, c_int, c_longlong, vp, vp, c_size_t, c_int, vp]
+    lib.tony_adamw_flat.argtypes = [vp, vp, vp, vp, vp, c_size_t, c_float, c_float, c_float, c_float,
+                                    c_float, c_float, c_float, c_float, vp, c_size_t, vp]
+    lib.tony_sgd_flat.argtypes = [vp, vp, vp, vp, c_size_t, c_float, c_float, c_float, c_int,
+                                  c_float, vp, c_size_t, vp]
+    lib.tony_symm_alloc.argtypes = [c_size_t, POINTER(c_void_p)]
+    lib.tony_symm_free.argtypes = [vp]
+    lib.tony_ipc_get_handle.argtypes = [vp, POINTER(c_ubyte)]
+    lib.tony_ipc_open.argtypes = [POINTER(c_ubyte), POINTER(c_void_p)]
+    lib.tony_ipc_close.argtypes = [vp]
+    lib.tony_fused_reduce_optim.argtypes = [POINTER(FusedComm), c_size_t, c_size_t, vp, vp, vp,
+                                            c_size_t, c_int, c_float, c_float, c_float, c_float,
+                                            c_float, c_float, c_float, c_float, vp, c_int, c_uint,
+                                            c_int, vp]
+    lib.tony_symm_allreduce_bf16.argtypes = [POINTER(FusedComm), c_size_t, c_size_t, c_float, c_uint,
+                                             c_int, vp]
+    lib.tony_symm_barrier.argtypes = [POINTER(FusedComm), c_uint, vp]
+    lib.tony_allgather_gemm_bf16.argtypes = [vp, POINTER(c_void_p), vp, vp, c_int, c_int, c_int,
+                                             c_int, c_int, c_uint, vp, vp, vp, c_uint, c_int, vp]
+    for name in ("tony_embedding_fwd", "tony_embedding_bwd"):
+        if hasattr(lib, name):
+            getattr(lib, name).restype = c_int
+
+
+def lib():
+    """Return the loaded kernel library (building it first if the .so is absent)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not LIB_PATH.exists():
+            if os.environ.get("TONY_B200_NO_BUILD") == "1":
+                raise KernelError(f"{LIB_PATH} is missing and TONY_B200_NO_BUILD=1")
+            from tony_b200.csrc.build import build
+
+            build()
+        try:
+            handle = ctypes.CDLL(str(LIB_PATH))
+        except OSError as exc:  # pragma: no cover - depends on the box
+            raise KernelError(f"cannot load {LIB_PATH}: {exc}") from exc
+        _declare(handle)
+        _lib = handle
+    return _lib
+
+
+def available() -> bool:
+    """True when the sm_100a kernels can run here (library loads and a CUDA device exists)."""
+    try:
+        import torch
+
+        return torch.cuda.is_available() and lib() is not None
+    except Exception:
+        return False
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = lib().tony_last_error()
+        raise KernelError(f"{what} failed (code {rc}): {msg.decode() if msg else ''}")
+
+
+def launch_count() -> int:
+    return int(lib().tony_launch_count())
+
+
+def ptr(t):
+    return c_void_p(t.data_ptr()) if t is not None else c_void_p(None)
+
+
+def cur_stream():
+    import torch
+
+    return c_void_p(torch.cuda.current_stream().cuda_stream)

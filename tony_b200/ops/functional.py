@@ -1,0 +1,440 @@
+"""Autograd-aware functional API over the sm_100a kernels.
+
+Every op here launches hand-written kernels from ``libtony_b200_kernels.so``; none has an
+eager fallback.  The ops mirror what the jobs launched by the reference spend their time in
+(``nn.Linear`` / ``F.cross_entropy`` in tony-examples/mnist-pytorch/mnist_distributed.py:76-90,129-136;
+dense layers in tony-examples/horovod-on-tony/tensorflow2_mnist.py), re-designed so that
+
+* bias / GELU / residual / dGELU live in the GEMM epilogue,
+* forward, dgrad and wgrad of a Linear run off the same buffers with no transpose copies,
+* weight/bias/LayerNorm gradients are written *directly into the flat gradient bucket* that
+  the fused all-reduce+optimizer kernel consumes (see ``tony_b200.parallel.flat``) — the
+  parameter's ``_tony_slot`` attribute carries that destination.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import (
+    EPI_ACCUMULATE,
+    EPI_BIAS,
+    EPI_DGELU_ERF,
+    EPI_DGELU_TANH,
+    EPI_DRELU,
+    EPI_GELU_ERF,
+    EPI_GELU_TANH,
+    EPI_RELU,
+    EPI_RESIDUAL,
+    EPI_SAVE_PREACT,
+    check,
+    cur_stream,
+    ptr,
+)
+
+_ACT_FWD = {None: 0, "none": 0, "gelu": EPI_GELU_ERF, "gelu_tanh": EPI_GELU_TANH, "relu": EPI_RELU}
+_ACT_BWD = {"gelu": EPI_DGELU_ERF, "gelu_tanh": EPI_DGELU_TANH, "relu": EPI_DRELU}
+
+_workspaces: dict = {}
+
+
+def workspace(name: str, nbytes: int, device) -> torch.Tensor:
+    """Per-device cached scratch buffer (never shrinks)."""
+    key = (name, torch.device(device).index)
+    buf = _workspaces.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        _workspaces[key] = buf
+    return buf
+
+
+SPLITK_WORKSPACE_BYTES = 128 << 20
+
+
+def _check_bf16(*tensors):
+    for t in tensors:
+        if t is not None and (t.dtype != torch.bfloat16 or not t.is_cuda):
+            raise TypeError("tony_b200 kernels take CUDA bf16 tensors")
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
+         out: Optional[torch.Tensor] = None, flags: int = 0, bias: Optional[torch.Tensor] = None,
+         aux: Optional[torch.Tensor] = None, aux_out: Optional[torch.Tensor] = None,
+         alpha: float = 1.0, allow_splitk: bool = True) -> torch.Tensor:
+    """``out[m,n] = epi(alpha * sum_k A(m,k) B(n,k))`` on the tcgen05 tensor cores.
+
+    ``a`` is ``[M,K]`` (``a_mn=False``) or ``[K,M]`` (``a_mn=True``); ``b`` is ``[N,K]`` or
+    ``[K,N]``.  2-D, last dim contiguous, row stride a multiple of 8 elements.
+    """
+    _check_bf16(a, b, bias, aux, aux_out, out)
+    if a.dim() != 2 or b.dim() != 2 or a.stride(1) != 1 or b.stride(1) != 1:
+        raise ValueError("gemm operands must be 2-D with a contiguous last dim")
+    if a_mn:
+        K, M = a.shape
+    else:
+        M, K = a.shape
+    if b_mn:
+        Kb, N = b.shape
+    else:
+        N, Kb = b.shape
+    if K != Kb:
+        raise ValueError(f"reduction dims differ: {K} vs {Kb}")
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    elif out.shape != (M, N) or out.stride(1) != 1:
+        raise ValueError("bad out tensor")
+    ws = workspace("splitk", SPLITK_WORKSPACE_BYTES, a.device) if allow_splitk else None
+    rc = _lib.lib().tony_gemm_bf16(
+        ptr(a), ptr(b), ptr(out), M, N, K, int(a_mn), int(b_mn), a.stride(0), b.stride(0),
+        out.stride(0), flags, float(alpha), ptr(bias), ptr(aux),
+        aux.stride(0) if aux is not None else 0, ptr(aux_out), ptr(ws),
+        ws.numel() if ws is not None else 0, cur_stream())
+    check(rc, "tony_gemm_bf16")
+    return out
+
+
+def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
+    """``out[c] (+)= sum_r x[r,c]`` (bias gradient)."""
+    _check_bf16(x, out)
+    rows, cols = x.shape
+    if out is None:
+        out = torch.empty(cols, dtype=torch.bfloat16, device=x.device)
+        accumulate = False
+    lib = _lib.lib()
+    nbytes = int(lib.tony_colsum_scratch_bytes(cols))
+    scratch = workspace("colsum", nbytes, x.device)
+    check(lib.tony_colsum_bf16(ptr(x), rows, cols, x.stride(0), ptr(out), ptr(scratch), nbytes,
+                               int(accumulate), cur_stream()), "tony_colsum_bf16")
+    return out
+
+
+# ---------------------------------------------------------------------------------------
+# gradient destinations: either a fresh tensor (plain autograd) or the parameter's slot in
+# the flat gradient bucket (tony_b200.parallel.flat.ParamSlot)
+# ---------------------------------------------------------------------------------------
+class _GradDest:
+    __slots__ = ("slot", "tensor", "accumulate")
+
+    def __init__(self, param: Optional[torch.Tensor], shape=None):
+        self.slot = getattr(param, "_tony_slot", None) if param is not None else None
+        if self.slot is not None:
+            self.tensor = self.slot.grad_view
+            self.accumulate = self.slot.begin_write()
+        else:
+            self.tensor = None
+            self.accumulate = False
+
+    def finish(self, produced: Optional[torch.Tensor]):
+        """Return what autograd should see for this parameter."""
+        if self.slot is not None:
+            self.slot.end_write()
+            return None
+        return produced
+
+
+def _weight_grad(dy2: torch.Tensor, x2: torch.Tensor, weight: torch.Tensor):
+    """dW[N,K] = dY^T . X  (both operands MN-major: no transposes)."""
+    dest = _GradDest(weight)
+    out = gemm(dy2, x2, a_mn=True, b_mn=True, out=dest.tensor,
+               flags=EPI_ACCUMULATE if dest.accumulate else 0)
+    return dest.finish(out)
+
+
+def _bias_grad(dy2: torch.Tensor, bias: Optional[torch.Tensor]):
+    if bias is None:
+        return None
+    dest = _GradDest(bias)
+    out = colsum(dy2, out=dest.tensor, accumulate=dest.accumulate)
+    return dest.finish(out)
+
+
+class _LinearFn(torch.autograd.Function):
+    """y = x W^T (+ b) (+ residual); activation-free so dgrad/wgrad need nothing but dy."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual):
+        K = weight.shape[1]
+        x2 = x.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        N = weight.shape[0]
+        flags = (EPI_BIAS if bias is not None else 0) | (EPI_RESIDUAL if residual is not None else 0)
+        res2 = residual.reshape(-1, N) if residual is not None else None
+        y = gemm(x2, weight, flags=flags, bias=bias, aux=res2)
+        ctx.save_for_backward(x2, weight)
+        ctx.bias = bias
+        ctx.x_shape = x.shape
+        ctx.has_res = residual is not None
+        return y.view(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight = ctx.saved_tensors
+        N = weight.shape[0]
+        dy2 = dy.reshape(-1, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm(dy2, weight, b_mn=True).view(ctx.x_shape)  # dX = dY . W
+        dw = _weight_grad(dy2, x2, weight)
+        db = _bias_grad(dy2, ctx.bias)
+        return dx, dw, db, (dy if ctx.has_res else None)
+
+
+def linear(x, weight, bias=None, residual=None):
+    """``x @ weight.T + bias (+ residual)`` with the adds fused into the GEMM epilogue."""
+    return _LinearFn.apply(x, weight, bias, residual)
+
+
+class _MlpFn(torch.autograd.Function):
+    """Transformer FFN: y = act(x W1^T + b1) W2^T + b2 (+ residual), fully fused.
+
+    forward : GEMM1 epilogue = bias + activation (+ saves the pre-activation),
+              GEMM2 epilogue = bias + residual.
+    backward: dgrad-2 epilogue multiplies by act'(pre) so the activation gradient never
+              makes its own pass over memory.
+    """
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, residual, act):
+        K = w1.shape[1]
+        x2 = x.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        F = w1.shape[0]
+        N = w2.shape[0]
+        pre = torch.empty((x2.shape[0], F), dtype=torch.bfloat16, device=x.device)
+        h = gemm(x2, w1, flags=EPI_BIAS | _ACT_FWD[act] | EPI_SAVE_PREACT, bias=b1, aux_out=pre)
+        res2 = residual.reshape(-1, N) if residual is not None else None
+        y = gemm(h, w2, flags=EPI_BIAS | (EPI_RESIDUAL if residual is not None else 0), bias=b2,
+                 aux=res2)
+        ctx.save_for_backward(x2, w1, w2, pre, h)
+        ctx.b1, ctx.b2, ctx.act = b1, b2, act
+        ctx.x_shape = x.shape
+        ctx.has_res = residual is not None
+        return y.view(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w1, w2, pre, h = ctx.saved_tensors
+        N = w2.shape[0]
+        dy2 = dy.reshape(-1, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dw2 = _weight_grad(dy2, h, w2)
+        db2 = _bias_grad(dy2, ctx.b2)
+        dpre = gemm(dy2, w2, b_mn=True, flags=_ACT_BWD[ctx.act], aux=pre)  # (dY.W2) * act'(pre)
+        dw1 = _weight_grad(dpre, x2, w1)
+        db1 = _bias_grad(dpre, ctx.b1)
+        dx = gemm(dpre, w1, b_mn=True).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        return dx, dw1, db1, dw2, db2, (dy if ctx.has_res else None), None
+
+
+def mlp(x, w1, b1, w2, b2, residual=None, act="gelu"):
+    return _MlpFn.apply(x, w1, b1, w2, b2, residual, act)
+
+
+class _LinearActFn(torch.autograd.Function):
+    """Single Linear with a fused activation (heads, recommender towers)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, act):
+        K = weight.shape[1]
+        x2 = x.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        N = weight.shape[0]
+        pre = torch.empty((x2.shape[0], N), dtype=torch.bfloat16, device=x.device)
+        y = gemm(x2, weight, flags=(EPI_BIAS if bias is not None else 0) | _ACT_FWD[act] | EPI_SAVE_PREACT,
+                 bias=bias, aux_out=pre)
+        ctx.save_for_backward(x2, weight, pre)
+        ctx.bias, ctx.act, ctx.x_shape = bias, act, x.shape
+        return y.view(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight, pre = ctx.saved_tensors
+        N = weight.shape[0]
+        dy2 = dy.reshape(-1, N)
+        if ctx.act == "relu":
+            dpre = dy2 * (pre > 0)
+        elif ctx.act == "gelu":
+            p = pre.float()
+            dpre = (dy2.float() * (0.5 * (1 + torch.erf(p * 0.7071067811865476))
+                                   + p * torch.exp(-0.5 * p * p) * 0.3989422804014327)).to(torch.bfloat16)
+        else:
+            p = pre.float()
+            u = 0.7978845608028654 * (p + 0.044715 * p ** 3)
+            t = torch.tanh(u)
+            dpre = (dy2.float() * (0.5 * (1 + t) + 0.5 * p * (1 - t * t) * 0.7978845608028654
+                                   * (1 + 3 * 0.044715 * p * p))).to(torch.bfloat16)
+        dpre = dpre.contiguous()
+        dx = gemm(dpre, weight, b_mn=True).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        dw = _weight_grad(dpre, x2, weight)
+        db = _bias_grad(dpre, ctx.bias)
+        return dx, dw, db, None
+
+
+def linear_act(x, weight, bias=None, act="relu"):
+    if act in (None, "none"):
+        return linear(x, weight, bias)
+    return _LinearActFn.apply(x, weight, bias, act)
+
+
+# ---------------------------------------------------------------------------------------
+class _LayerNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        H = x.shape[-1]
+        x2 = x.reshape(-1, H)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        _check_bf16(x2, gamma, beta)
+        rows = x2.shape[0]
+        y = torch.empty_like(x2)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        check(_lib.lib().tony_layernorm_fwd(ptr(x2), ptr(gamma), ptr(beta), ptr(y), ptr(mean),
+                                            ptr(rstd), rows, H, float(eps), cur_stream()),
+              "tony_layernorm_fwd")
+        ctx.save_for_backward(x2, gamma, mean, rstd)
+        ctx.beta = beta
+        ctx.x_shape = x.shape
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, gamma, mean, rstd = ctx.saved_tensors
+        H = x2.shape[1]
+        dy2 = dy.reshape(-1, H)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        rows = x2.shape[0]
+        lib = _lib.lib()
+        dx = torch.empty_like(x2)
+        dg, db = _GradDest(gamma), _GradDest(ctx.beta)
+        if dg.tensor is None:
+            dg_t = torch.empty(H, dtype=torch.bfloat16, device=x2.device)
+            db_t = torch.empty(H, dtype=torch.bfloat16, device=x2.device)
+            acc = False
+        else:
+            dg_t, db_t = dg.tensor, db.tensor
+            acc = dg.accumulate
+        nbytes = int(lib.tony_layernorm_bwd_scratch_bytes(H))
+        scratch = workspace("ln_bwd", nbytes, x2.device)
+        check(lib.tony_layernorm_bwd(ptr(dy2), ptr(x2), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx),
+                                     ptr(dg_t), ptr(db_t), rows, H, ptr(scratch), nbytes, int(acc),
+                                     cur_stream()), "tony_layernorm_bwd")
+        return dx.view(ctx.x_shape), dg.finish(dg_t), db.finish(db_t), None
+
+
+def layer_norm(x, gamma, beta, eps: float = 1e-5):
+    return _LayerNormFn.apply(x, gamma, beta, eps)
+
+
+# ---------------------------------------------------------------------------------------
+class _SoftmaxXentFn(torch.autograd.Function):
+    """Fused softmax cross-entropy.  The logits buffer is consumed: forward overwrites it
+    with the gradient, backward just hands it back — so the loss must be the root of the
+    backward pass (any constant factor goes in ``loss_scale``)."""
+
+    @staticmethod
+    def forward(ctx, logits, targets, vocab, ignore_index, reduction, loss_scale):
+        _check_bf16(logits)
+        ld = logits.shape[-1]
+        lg2 = logits.view(-1, ld)
+        rows = lg2.shape[0]
+        tg = targets.reshape(-1)
+        if tg.dtype != torch.int64:
+            tg = tg.long()
+        loss_rows = torch.empty(rows, dtype=torch.float32, device=logits.device)
+        if reduction == "mean":
+            inv = (tg != ignore_index).sum().clamp_(min=1).to(torch.float32).reciprocal_()
+        else:
+            inv = None
+        check(_lib.lib().tony_softmax_xent_fwd_bwd(ptr(lg2), ptr(tg), ptr(loss_rows), rows, vocab,
+                                                   lg2.stride(0), ignore_index, float(loss_scale),
+                                                   ptr(inv), cur_stream()),
+              "tony_softmax_xent_fwd_bwd")
+        ctx.save_for_backward(logits)
+        loss = loss_rows.sum()
+        if inv is not None:
+            loss = loss * inv
+        return loss * loss_scale if loss_scale != 1.0 else loss
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (dlogits,) = ctx.saved_tensors
+        return dlogits, None, None, None, None, None
+
+
+def softmax_cross_entropy(logits, targets, *, vocab: Optional[int] = None, ignore_index: int = -100,
+                          reduction: str = "mean", loss_scale: float = 1.0):
+    """Cross-entropy over the last dim of ``logits`` ([..., V_padded] bf16, destroyed).
+
+    ``vocab`` is the true class count when the last dim carries alignment padding.
+    """
+    if reduction not in ("mean", "sum"):
+        raise ValueError("reduction must be 'mean' or 'sum'")
+    return _SoftmaxXentFn.apply(logits, targets, vocab or logits.shape[-1], ignore_index, reduction,
+                                loss_scale)
+
+
+# ---------------------------------------------------------------------------------------
+class _EmbeddingFn(torch.autograd.Function):
+    """Row gather; the backward scatter-adds into the gradient bucket slot when present."""
+
+    @staticmethod
+    def forward(ctx, weight, idx):
+        ctx.save_for_backward(idx)
+        ctx.weight = weight
+        return weight.index_select(0, idx.reshape(-1)).view(*idx.shape, weight.shape[1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        weight = ctx.weight
+        dest = _GradDest(weight)
+        dy2 = dy.reshape(-1, weight.shape[1])
+        if dest.tensor is not None:
+            if not dest.accumulate:
+                dest.tensor.zero_()
+            dest.tensor.index_add_(0, idx.reshape(-1), dy2)
+            return dest.finish(None), None
+        g = torch.zeros_like(weight)
+        g.index_add_(0, idx.reshape(-1), dy2)
+        return g, None
+
+
+def embedding(weight, idx):
+    return _EmbeddingFn.apply(weight, idx)
+
+
+class _BroadcastAddParamFn(torch.autograd.Function):
+    """x + p where p broadcasts over the leading dims (position embeddings)."""
+
+    @staticmethod
+    def forward(ctx, x, p):
+        ctx.p = p
+        return x + p
+
+    @staticmethod
+    def backward(ctx, dy):
+        p = ctx.p
+        dest = _GradDest(p)
+        lead = dy.dim() - p.dim()
+        g = dy.sum(dim=tuple(range(lead))) if lead > 0 else dy
+        if dest.tensor is not None:
+            if dest.accumulate:
+                dest.tensor.add_(g)
+            else:
+                dest.tensor.copy_(g)
+            return dy, dest.finish(None)
+        return dy, g
+
+
+def add_broadcast_param(x, p):
+    return _BroadcastAddParamFn.apply(x, p)
