@@ -193,3 +193,30 @@ def test_sgd_flat_matches_torch():
         opt.step()
         st.step(g, w)
     assert (st.master - ref.detach()).abs().max().item() < 1e-4
+
+
+def test_gemm_from_fresh_thread():
+    """Autograd runs backward on worker threads with no CUDA context bound yet; the GEMM's
+    tensor-map encode (a raw driver call) must still work there."""
+    import threading
+
+    from tony_b200.ops import functional as F
+
+    A, B = _rand(256, 128), _rand(256, 128)
+    out = torch.empty(256, 256, device=DEV, dtype=torch.bfloat16)
+    F.workspace("splitk", F.SPLITK_WORKSPACE_BYTES, A.device)
+    torch.cuda.synchronize()
+    err = []
+
+    def run():
+        try:
+            F.gemm(A, B, out=out)
+            torch.cuda.synchronize()
+        except Exception as e:  # noqa: BLE001
+            err.append(e)
+
+    t = threading.Thread(target=run)
+    t.start()
+    t.join()
+    assert not err, err
+    _close(out, A.float() @ B.float().t())

@@ -466,6 +466,14 @@ static PFN_encodeTiled get_encode_fn() {
 // Operand of logical shape [mn_extent, k_extent]; `mn_major` says which dim is contiguous.
 int make_operand_tmap(CUtensorMap* map, const void* ptr, int mn_extent, int k_extent, long long ld,
                       int mn_major, int block_mn) {
+    // cuTensorMapEncodeTiled is a raw driver call: it needs a context bound to THIS thread.
+    // Autograd worker threads for device 0 may not have one yet (torch binds lazily), so
+    // force the runtime to bind the primary context once per thread.
+    static thread_local bool tls_ctx_bound = false;
+    if (!tls_ctx_bound) {
+        cudaFree(nullptr);
+        tls_ctx_bound = true;
+    }
     PFN_encodeTiled enc = get_encode_fn();
     if (!enc) {
         set_last_error("cuTensorMapEncodeTiled", "driver entry point not found");

@@ -1,0 +1,129 @@
+"""The PyTorch runtime package handed to launched jobs.
+
+``init()`` turns the per-task environment contract the launcher exports into an
+initialised ``torch.distributed`` process group + CUDA device.  It accepts both the
+reference's names (``INIT_METHOD`` / ``RANK`` / ``WORLD``:
+tony-core/src/main/java/com/linkedin/tony/runtime/PyTorchRuntime.java:45-56,
+Constants.java:56-60) and torch's ``env://`` names (``MASTER_ADDR``/``MASTER_PORT``/
+``WORLD_SIZE``/``LOCAL_RANK``), which torchrun and our launcher also set.
+
+``Trainer`` is the user-facing training step: it owns the flat parameter store and the
+fused collective+optimizer, copies each batch from pinned host memory, runs
+forward/backward on the sm_100a kernels and returns the loss as a Python float.
+"""
+from __future__ import annotations
+
+import os
+import time
+from typing import Callable, Dict, Optional
+
+_T0 = time.time()
+_state = {"initialised": False, "first_step_marked": False}
+
+
+def env_rank_world():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", os.environ.get("WORLD", "1")))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def init(backend: Optional[str] = None, device: Optional[str] = None):
+    """Initialise torch.distributed from the TonY env contract; returns (rank, world, device)."""
+    import torch
+    import torch.distributed as dist
+
+    rank, world, local = env_rank_world()
+    use_cuda = torch.cuda.is_available() and device != "cpu"
+    if use_cuda:
+        visible = torch.cuda.device_count()
+        torch.cuda.set_device(local % max(visible, 1))
+        dev = torch.device("cuda", local % max(visible, 1))
+    else:
+        dev = torch.device("cpu")
+    if world > 1 and not dist.is_initialized():
+        backend = backend or ("nccl" if use_cuda else "gloo")
+        init_method = os.environ.get("INIT_METHOD")
+        if "MASTER_ADDR" in os.environ and "MASTER_PORT" in os.environ:
+            init_method = "env://"
+            os.environ.setdefault("WORLD_SIZE", str(world))
+        kwargs = {"device_id": dev} if (use_cuda and backend == "nccl") else {}
+        dist.init_process_group(backend=backend, init_method=init_method, rank=rank,
+                                world_size=world, **kwargs)
+    _state["initialised"] = True
+    return rank, world, dev
+
+
+def mark_first_step(extra: Optional[Dict[str, float]] = None) -> None:
+    """Tell the launcher the first training step finished (submit-to-first-step latency).
+
+    Writes ``<TONY_B200_MARK_DIR>/first_step.<JOB_NAME>.<TASK_INDEX>`` with the wall time;
+    the TaskExecutor forwards it as a metric.  A no-op outside a launched task.
+    """
+    if _state["first_step_marked"]:
+        return
+    _state["first_step_marked"] = True
+    d = os.environ.get("TONY_B200_MARK_DIR")
+    if not d:
+        return
+    name = f"first_step.{os.environ.get('JOB_NAME', 'task')}.{os.environ.get('TASK_INDEX', '0')}"
+    try:
+        os.makedirs(d, exist_ok=True)
+        tmp = os.path.join(d, name + ".tmp")
+        with open(tmp, "w") as f:
+            f.write(f"{time.time():.6f}\n")
+            for k, v in (extra or {}).items():
+                f.write(f"{k}={v}\n")
+        os.replace(tmp, os.path.join(d, name))
+    except OSError:
+        pass
+
+
+class Trainer:
+    """model + fused optimizer + host<->device batch plumbing, one call per step."""
+
+    def __init__(self, model, *, lr: float = 1e-4, optimizer: str = "adamw", weight_decay: float = 0.01,
+                 betas=(0.9, 0.999), eps: float = 1e-8, momentum: float = 0.9, bucket_mb: float = 64.0,
+                 overlap: bool = True, comm_ctas: int = 32, device=None, group=None,
+                 broadcast: bool = True, generic_hooks: bool = False):
+        import torch
+
+        from ..parallel.flat import FlatParamStore, FusedOptimizer
+
+        self.torch = torch
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.model = model.to(self.device)
+        self.store = FlatParamStore(model.named_parameters(), self.device, group=group,
+                                    bucket_mb=bucket_mb, no_decay=("bias", "ln", "LayerNorm", "norm"))
+        for p, uses in getattr(model, "shared_params", {}).items():
+            self.store.mark_shared(p, uses)
+        if generic_hooks:
+            self.store.register_autograd_hooks()
+        self.opt = FusedOptimizer(self.store, optimizer=optimizer, lr=lr, betas=betas, eps=eps,
+                                  weight_decay=weight_decay, momentum=momentum, overlap=overlap,
+                                  comm_ctas=comm_ctas, broadcast=broadcast)
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self.steps = 0
+
+    def to_device(self, batch_cpu: Dict[str, "object"]):
+        """Async H2D of a (pinned) host batch on the current stream."""
+        return {k: v.to(self.device, non_blocking=True) for k, v in batch_cpu.items()}
+
+    def step_device(self, batch_dev) -> "object":
+        """One optimisation step on device-resident inputs; returns the loss tensor (no sync)."""
+        loss = self.model(**batch_dev)
+        loss.backward()
+        self.opt.step()
+        self.steps += 1
+        return loss
+
+    def step(self, batch_cpu) -> float:
+        """The end-to-end user call: pinned host batch in, Python float loss out."""
+        loss = self.step_device(self.to_device(batch_cpu))
+        value = float(loss.item())  # D2H read of the step's result; also the host sync point
+        if self.steps == 1:
+            mark_first_step()
+        return value
+
+    def check(self):
+        self.store.comm.check_status()
