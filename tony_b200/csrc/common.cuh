@@ -165,8 +165,9 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                  : "memory");
 }
 
-// 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread.
-__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+// 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread (r must be a fully
+// unrolled register array: every index below is a compile-time constant).
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t* r) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
         "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -278,13 +279,43 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
     return __bfloat1622float2(v);
 }
 
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, const uint4& v) {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z),
+                 "r"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "r"(addr)
+                 : "memory");
+    return v;
+}
+
+// erf-based GELU with one ex2 and one rcp per element (Abramowitz-Stegun 7.1.26,
+// |error| < 1.5e-7, far below bf16 resolution): the epilogue must stay cheaper than
+// the tile's MMA time.  e = exp(-x^2/2) is shared between the cdf and the pdf.
+__device__ __forceinline__ void gelu_erf_parts(float x, float& cdf, float& e) {
+    const float z = fabsf(x) * 0.70710678118654752f;
+    const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+    e = __expf(-z * z);
+    float poly = fmaf(t, 1.061405429f, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    const float erf_abs = 1.0f - poly * t * e;            // erf(|x|/sqrt2)
+    cdf = 0.5f * (1.0f + copysignf(erf_abs, x));
+}
 __device__ __forceinline__ float gelu_erf(float x) {
-    return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
+    float cdf, e;
+    gelu_erf_parts(x, cdf, e);
+    return x * cdf;
 }
 __device__ __forceinline__ float dgelu_erf(float x) {
-    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-    const float pdf = 0.39894228040143268f * __expf(-0.5f * x * x);
-    return cdf + x * pdf;
+    float cdf, e;
+    gelu_erf_parts(x, cdf, e);
+    return fmaf(x * 0.39894228040143268f, e, cdf);
 }
 __device__ __forceinline__ float gelu_tanh(float x) {
     const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);

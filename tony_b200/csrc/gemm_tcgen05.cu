@@ -2,12 +2,13 @@
 //
 //   C[m,n] = epilogue( alpha * sum_k A(m,k) * B(n,k) )
 //
-// * persistent kernel, one CTA per SM, 192 threads = 6 warps, warp-specialised:
+// * persistent kernel, one CTA per SM, 320 threads = 10 warps, warp-specialised:
 //     warp 0      TMA producer (one elected lane): global -> 128B-swizzled smem ring
 //     warp 1      TMEM allocator + tcgen05.mma issuer (one lane), commits to mbarriers
-//     warps 2..5  epilogue: tcgen05.ld (TMEM -> registers) -> bias/activation/residual
-//                 -> 16-byte global stores; runs concurrently with the next tile's MMAs
-//                 because the accumulator is double-buffered in TMEM (2 x BLOCK_N columns)
+//     warps 2..9  epilogue: tcgen05.ld (TMEM -> registers) -> bias/activation/residual
+//                 -> smem transpose -> fully coalesced 16-byte global stores; runs
+//                 concurrently with the next tile's MMAs because the accumulator is
+//                 double-buffered in TMEM (2 x BLOCK_N columns)
 // * both operands may be K-major (reduction dim contiguous) or MN-major (the other
 //   dim contiguous), selected at run time; this is what lets forward (X.W^T), dgrad
 //   (dY.W) and wgrad (dY^T.X) of a Linear layer run without any transpose copy.
@@ -31,7 +32,9 @@ namespace tony {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 320;   // TMA warp + MMA warp + 8 epilogue warps
+constexpr int EPI_WARPS = 8;
+constexpr int EPI_STAGING_BYTES = EPI_WARPS * 4096;
 constexpr int CHUNK_BYTES = BLOCK_K * 128;  // one [64 x 128B] MN-major chunk = 8 KB
 
 struct GemmParams {
@@ -120,98 +123,128 @@ __device__ __forceinline__ void allgather_copy_role(const GemmParams& p) {
     }
 }
 
-template <int BLOCK_N>
-__device__ __forceinline__ void gemm_epilogue_chunk(const GemmParams& p, uint32_t (&r)[32], int row,
-                                                    int col0, int split) {
-    if (row >= p.M || col0 >= p.N) return;
-    if (p.splits > 1) {
-        float* dst = p.workspace + (static_cast<size_t>(split) * p.M + row) * p.N + col0;
+// ---- epilogue --------------------------------------------------------------------------
+// Each epilogue warp owns 32 accumulator rows (its TMEM lane quarter) and walks 64-column
+// chunks.  TMEM hands every lane one ROW; global memory wants every store instruction to
+// cover whole 128-byte lines.  A per-warp 4 KB staging tile ([32 rows][128 B], 16-byte
+// units XOR-swizzled by row so both access patterns are bank-conflict free) transposes
+// between the two: every global load/store below moves 4 full rows x 128 B per instruction.
+__device__ __forceinline__ uint32_t stg_addr(uint32_t base, int row, int unit) {
+    return base + row * 128 + ((unit ^ (row & 7)) << 4);
+}
+
+// global [32 x 64] bf16 tile -> this lane's row as 32 packed bf16x2 words
+__device__ __forceinline__ void load_tile_rows(const __nv_bfloat16* g, long long ld, int row0, int col0,
+                                               int M, int N, uint32_t stg, int lane, uint32_t (&out)[32]) {
+    const int unit = lane & 7;
+    const int gc = col0 + unit * 8;
 #pragma unroll
-        for (int g = 0; g < 8; ++g) {
-            if (col0 + g * 4 < p.N) {
-                float4 v = make_float4(__uint_as_float(r[g * 4 + 0]), __uint_as_float(r[g * 4 + 1]),
-                                       __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]));
-                *reinterpret_cast<float4*>(dst + g * 4) = v;
-            }
-        }
-        return;
+    for (int i = 0; i < 8; ++i) {
+        const int row = i * 4 + (lane >> 3);
+        const int gr = row0 + row;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (gr < M && gc < N) v = ld_global_v4(g + static_cast<size_t>(gr) * ld + gc);
+        st_shared_v4(stg_addr(stg, row, unit), v);
     }
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        const uint4 v = ld_shared_v4(stg_addr(stg, lane, u));
+        out[4 * u] = v.x;
+        out[4 * u + 1] = v.y;
+        out[4 * u + 2] = v.z;
+        out[4 * u + 3] = v.w;
+    }
+    __syncwarp();
+}
+
+// this lane's row (32 packed words) -> global [32 x 64] bf16 tile, coalesced
+__device__ __forceinline__ void store_tile_rows(__nv_bfloat16* g, long long ld, int row0, int col0, int M,
+                                                int N, uint32_t stg, int lane, const uint32_t (&in)[32]) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+        st_shared_v4(stg_addr(stg, lane, u), make_uint4(in[4 * u], in[4 * u + 1], in[4 * u + 2], in[4 * u + 3]));
+    __syncwarp();
+    const int unit = lane & 7;
+    const int gc = col0 + unit * 8;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int row = i * 4 + (lane >> 3);
+        const int gr = row0 + row;
+        const uint4 v = ld_shared_v4(stg_addr(stg, row, unit));
+        if (gr < M && gc < N) st_global_v4(g + static_cast<size_t>(gr) * ld + gc, v);
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ void epilogue_chunk64(const GemmParams& p, float (&v)[64], int row0, int col0,
+                                                 uint32_t stg, int lane) {
     const uint32_t flags = p.flags;
+    if (flags & TONY_EPI_BIAS) {
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {  // 8 columns (16 bytes of bf16) at a time
-        const int col = col0 + g * 8;
-        if (col >= p.N) break;
-        float v[8];
+        for (int u = 0; u < 8; ++u) {
+            if (col0 + u * 8 < p.N) {
+                const uint4 b = __ldg(reinterpret_cast<const uint4*>(p.bias + col0 + u * 8));
+                const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]) * p.alpha;
-        if (flags & TONY_EPI_BIAS) {
-            const uint4 b = __ldg(reinterpret_cast<const uint4*>(p.bias + col));
-            const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float2 f = unpack_bf16x2(bw[j]);
-                v[2 * j] += f.x;
-                v[2 * j + 1] += f.y;
-            }
-        }
-        if (flags & (TONY_EPI_RESIDUAL | TONY_EPI_DGELU_ERF | TONY_EPI_DGELU_TANH | TONY_EPI_DRELU)) {
-            const uint4 a =
-                ld_global_nc_v4(p.aux + static_cast<size_t>(row) * p.ld_aux + col);
-            const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float2 f = unpack_bf16x2(aw[j]);
-                if (flags & TONY_EPI_RESIDUAL) {
-                    v[2 * j] += f.x;
-                    v[2 * j + 1] += f.y;
-                } else if (flags & TONY_EPI_DGELU_ERF) {
-                    v[2 * j] *= dgelu_erf(f.x);
-                    v[2 * j + 1] *= dgelu_erf(f.y);
-                } else if (flags & TONY_EPI_DGELU_TANH) {
-                    v[2 * j] *= dgelu_tanh(f.x);
-                    v[2 * j + 1] *= dgelu_tanh(f.y);
-                } else {
-                    v[2 * j] = f.x > 0.f ? v[2 * j] : 0.f;
-                    v[2 * j + 1] = f.y > 0.f ? v[2 * j + 1] : 0.f;
+                for (int j = 0; j < 4; ++j) {
+                    const float2 f = unpack_bf16x2(bw[j]);
+                    v[u * 8 + 2 * j] += f.x;
+                    v[u * 8 + 2 * j + 1] += f.y;
                 }
             }
         }
-        if (flags & TONY_EPI_SAVE_PREACT) {
-            uint4 o;
-            o.x = pack_bf16x2(v[0], v[1]);
-            o.y = pack_bf16x2(v[2], v[3]);
-            o.z = pack_bf16x2(v[4], v[5]);
-            o.w = pack_bf16x2(v[6], v[7]);
-            st_global_v4(p.aux_out + static_cast<size_t>(row) * p.ldc + col, o);
-        }
-        if (flags & TONY_EPI_GELU_ERF) {
+    }
+    if (flags & (TONY_EPI_RESIDUAL | TONY_EPI_DGELU_ERF | TONY_EPI_DGELU_TANH | TONY_EPI_DRELU)) {
+        uint32_t a[32];
+        load_tile_rows(p.aux, p.ld_aux, row0, col0, p.M, p.N, stg, lane, a);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = gelu_erf(v[j]);
-        } else if (flags & TONY_EPI_GELU_TANH) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
-        } else if (flags & TONY_EPI_RELU) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
-        }
-        __nv_bfloat16* cptr = p.C + static_cast<size_t>(row) * p.ldc + col;
-        if (flags & TONY_EPI_ACCUMULATE) {
-            const uint4 c = ld_global_v4(cptr);
-            const uint32_t cw[4] = {c.x, c.y, c.z, c.w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float2 f = unpack_bf16x2(cw[j]);
+        for (int j = 0; j < 32; ++j) {
+            const float2 f = unpack_bf16x2(a[j]);
+            if (flags & TONY_EPI_RESIDUAL) {
                 v[2 * j] += f.x;
                 v[2 * j + 1] += f.y;
+            } else if (flags & TONY_EPI_DGELU_ERF) {
+                v[2 * j] *= dgelu_erf(f.x);
+                v[2 * j + 1] *= dgelu_erf(f.y);
+            } else if (flags & TONY_EPI_DGELU_TANH) {
+                v[2 * j] *= dgelu_tanh(f.x);
+                v[2 * j + 1] *= dgelu_tanh(f.y);
+            } else {
+                v[2 * j] = f.x > 0.f ? v[2 * j] : 0.f;
+                v[2 * j + 1] = f.y > 0.f ? v[2 * j + 1] : 0.f;
             }
         }
-        uint4 o;
-        o.x = pack_bf16x2(v[0], v[1]);
-        o.y = pack_bf16x2(v[2], v[3]);
-        o.z = pack_bf16x2(v[4], v[5]);
-        o.w = pack_bf16x2(v[6], v[7]);
-        st_global_v4(cptr, o);
     }
+    uint32_t o[32];
+    if (flags & TONY_EPI_SAVE_PREACT) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) o[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+        store_tile_rows(p.aux_out, p.ldc, row0, col0, p.M, p.N, stg, lane, o);
+    }
+    if (flags & TONY_EPI_GELU_ERF) {
+#pragma unroll
+        for (int j = 0; j < 64; ++j) v[j] = gelu_erf(v[j]);
+    } else if (flags & TONY_EPI_GELU_TANH) {
+#pragma unroll
+        for (int j = 0; j < 64; ++j) v[j] = gelu_tanh(v[j]);
+    } else if (flags & TONY_EPI_RELU) {
+#pragma unroll
+        for (int j = 0; j < 64; ++j) v[j] = fmaxf(v[j], 0.f);
+    }
+    if (flags & TONY_EPI_ACCUMULATE) {
+        uint32_t c[32];
+        load_tile_rows(p.C, p.ldc, row0, col0, p.M, p.N, stg, lane, c);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const float2 f = unpack_bf16x2(c[j]);
+            v[2 * j] += f.x;
+            v[2 * j + 1] += f.y;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) o[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+    store_tile_rows(p.C, p.ldc, row0, col0, p.M, p.N, stg, lane, o);
 }
 
 template <int BLOCK_N, int STAGES>
@@ -226,7 +259,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+    uint8_t* staging = smem + STAGES * STAGE_BYTES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + EPI_STAGING_BYTES);
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full_bar = empty_bar + STAGES;
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;
@@ -244,7 +278,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tmem_full_bar[s], 1);
-            mbar_init(&tmem_empty_bar[s], 4);  // one arrive per epilogue warp
+            mbar_init(&tmem_empty_bar[s], EPI_WARPS);  // one arrive per epilogue warp
         }
         fence_barrier_init();
     }
@@ -353,8 +387,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 }
             }
         } else {
-            // ------------------------------------------------ epilogue warps (2..5)
-            const int quarter = warp_idx & 3;  // TMEM lane quarter this warp may access
+            // ------------------------------------------------ epilogue warps (2..9)
+            // TMEM lane quarter = warp_idx % 4 (hardware rule); two warps share a quarter and
+            // split its 64-column chunks between them (even / odd).
+            const int quarter = warp_idx & 3;
+            const int half = (warp_idx - 2) >> 2;
+            const uint32_t stg = smem_u32(staging + (warp_idx - 2) * 4096);
             int iter = 0;
             for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
                 const int tile = unit / p.splits;
@@ -365,15 +403,35 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const uint32_t aphase = (iter >> 1) & 1;
                 mbar_wait(&tmem_full_bar[as], aphase);
                 tcgen05_fence_after();
-                const int row = m_blk * BLOCK_M + quarter * 32 + lane;
+                const int row0 = m_blk * BLOCK_M + quarter * 32;
                 const uint32_t taddr0 =
                     tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BLOCK_N;
 #pragma unroll 1
-                for (int c = 0; c < BLOCK_N / 32; ++c) {
-                    uint32_t r[32];
-                    tmem_ld_32x32(taddr0 + c * 32, r);
+                for (int c = half; c < BLOCK_N / 64; c += 2) {
+                    uint32_t r[64];
+                    tmem_ld_32x32(taddr0 + c * 64, r);
+                    tmem_ld_32x32(taddr0 + c * 64 + 32, r + 32);
                     tmem_ld_wait();
-                    gemm_epilogue_chunk<BLOCK_N>(p, r, row, n_blk * BLOCK_N + c * 32, split);
+                    const int col0 = n_blk * BLOCK_N + c * 64;
+                    if (col0 >= p.N || row0 >= p.M) continue;  // warp-uniform
+                    if (p.splits > 1) {
+                        const int row = row0 + lane;
+                        if (row < p.M) {
+                            float* dst = p.workspace + (static_cast<size_t>(split) * p.M + row) * p.N + col0;
+#pragma unroll
+                            for (int g = 0; g < 16; ++g) {
+                                if (col0 + g * 4 < p.N)
+                                    *reinterpret_cast<float4*>(dst + g * 4) = make_float4(
+                                        __uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]),
+                                        __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]));
+                            }
+                        }
+                        continue;
+                    }
+                    float v[64];
+#pragma unroll
+                    for (int j = 0; j < 64; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+                    epilogue_chunk64(p, v, row0, col0, stg, lane);
                 }
                 tcgen05_fence_before();
                 __syncwarp();
@@ -381,7 +439,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             }
         }
     }
-
     else {
         allgather_copy_role<BLOCK_N>(p);
     }
@@ -522,7 +579,8 @@ int device_sm_count() {
 template <int BLOCK_N, int STAGES>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
                        cudaStream_t stream) {
-    constexpr size_t SMEM = static_cast<size_t>(STAGES) * (BLOCK_M + BLOCK_N) * BLOCK_K * 2 + 1024 + 256;
+    constexpr size_t SMEM =
+        static_cast<size_t>(STAGES) * (BLOCK_M + BLOCK_N) * BLOCK_K * 2 + EPI_STAGING_BYTES + 1024 + 256;
     static bool configured[64] = {false};
     int dev = 0;
     TONY_CUDA_CHECK(cudaGetDevice(&dev));

@@ -320,9 +320,11 @@ static int launch_fused(const OptHyper& h, FusedArgs& a, int num_ctas, void* str
     a.timeout_ns = comm_timeout_ns();
     const int threads = 512;
     const size_t nvec = a.count / a.comm.world / 8;
-    int grid = num_ctas > 0 ? num_ctas : 32;
+    // world == 1 is pure HBM streaming: fill the machine.  With peers the kernel is NVLink
+    // bound and shares the GPU with backward, so it stays on the caller's CTA budget.
+    int grid = a.comm.world == 1 ? device_sm_count() * 4 : (num_ctas > 0 ? num_ctas : 32);
     grid = static_cast<int>(std::min<size_t>(grid, std::max<size_t>(1, (nvec + threads - 1) / threads)));
-    grid = std::min(grid, device_sm_count());  // phase C needs every CTA eventually resident
+    if (a.comm.world > 1) grid = std::min(grid, device_sm_count());
     fused_reduce_optim_kernel<<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(h, a);
     count_launch();
     TONY_CUDA_CHECK(cudaGetLastError());
