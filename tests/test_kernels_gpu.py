@@ -220,3 +220,23 @@ def test_gemm_from_fresh_thread():
     t.join()
     assert not err, err
     _close(out, A.float() @ B.float().t())
+
+
+def test_packed_attention_matches_sdpa():
+    from tony_b200.ops import functional as F
+
+    B, S, nh, hd = 2, 128, 4, 64
+    qkv = _rand(B, S, 3, nh, hd).requires_grad_(True)
+    ref_in = qkv.detach().clone().requires_grad_(True)
+    g = _rand(B, S, nh * hd)
+    for causal in (False, True):
+        qkv.grad = None
+        ref_in.grad = None
+        out = F.packed_attention(qkv, causal)
+        out.backward(g)
+        q, k, v = (ref_in[:, :, i].transpose(1, 2) for i in range(3))
+        ref = torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=causal)
+        ref = ref.transpose(1, 2).reshape(B, S, nh * hd)
+        ref.backward(g)
+        _close(out, ref)
+        _close(qkv.grad, ref_in.grad)

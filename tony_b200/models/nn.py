@@ -93,9 +93,7 @@ class SelfAttention(nn.Module):
     def forward(self, x, residual=None):
         B, S, H = x.shape
         qkv = self.qkv(x).view(B, S, 3, self.heads, self.head_dim)
-        q, k, v = (qkv[:, :, i].transpose(1, 2) for i in range(3))
-        o = torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=self.causal)
-        o = o.transpose(1, 2).reshape(B, S, H)
+        o = F.packed_attention(qkv, self.causal)
         return self.out(o, residual=residual)
 
 

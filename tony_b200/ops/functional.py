@@ -438,3 +438,45 @@ class _BroadcastAddParamFn(torch.autograd.Function):
 
 def add_broadcast_param(x, p):
     return _BroadcastAddParamFn.apply(x, p)
+
+
+# ---------------------------------------------------------------------------------------
+class _PackedSdpaFn(torch.autograd.Function):
+    """Attention over a packed ``qkv`` activation ``[B, S, 3, heads, head_dim]``.
+
+    The attention core is the library flash kernel (``scaled_dot_product_attention``); this
+    wrapper only removes the layout traffic stock autograd adds around it: q/k/v go in as
+    strided views of the packed projection output, the context comes back already in
+    ``[B, S, H]`` order, and backward writes dq/dk/dv straight into one packed gradient
+    (three strided copies) instead of three zero-filled ``select_backward`` tensors + adds.
+    """
+
+    @staticmethod
+    def forward(ctx, qkv, causal):
+        B, S, three, nh, hd = qkv.shape
+        base = qkv.detach()
+        with torch.enable_grad():
+            q, k, v = (base[:, :, i].transpose(1, 2).requires_grad_() for i in range(3))
+            o = torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=causal)
+        ctx.graph = (q, k, v, o)
+        ctx.shape = (B, S, nh, hd)
+        out = o.detach().transpose(1, 2)
+        return out.reshape(B, S, nh * hd)
+
+    @staticmethod
+    def backward(ctx, dout):
+        q, k, v, o = ctx.graph
+        ctx.graph = None
+        B, S, nh, hd = ctx.shape
+        do = dout.reshape(B, S, nh, hd).transpose(1, 2)
+        dq, dk, dv = torch.autograd.grad(o, (q, k, v), do)
+        dqkv = torch.empty((B, S, 3, nh, hd), dtype=dout.dtype, device=dout.device)
+        dqkv[:, :, 0].copy_(dq.transpose(1, 2))
+        dqkv[:, :, 1].copy_(dk.transpose(1, 2))
+        dqkv[:, :, 2].copy_(dv.transpose(1, 2))
+        return dqkv, None
+
+
+def packed_attention(qkv, causal: bool = False):
+    """``qkv``: ``[B, S, 3, heads, head_dim]`` -> context ``[B, S, heads*head_dim]``."""
+    return _PackedSdpaFn.apply(qkv, causal)
