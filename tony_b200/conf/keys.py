@@ -178,6 +178,7 @@ DEFAULTS = [
     (APPLICATION_NAME, "TensorFlowApplication", "Display name of the application."),
     (APPLICATION_TYPE, "TONY", "Application type tag."),
     (APPLICATION_TAGS, "", "Comma-separated application tags."),
+    (APPLICATION_NODE_LABEL, "", "Node label for the whole application (recorded only on the local cluster)."),
     (ENABLE_PREPROCESS, "false", "Run the AM command first as a preprocessing job."),
     (APPLICATION_TIMEOUT, "0", "Whole-application timeout in ms; 0 disables it."),
     (FRAMEWORK, "tensorflow", "tensorflow | pytorch | horovod | mxnet | standalone."),
@@ -209,6 +210,9 @@ DEFAULTS = [
     (FAIL_ON_WORKER_FAILURE, "false", "Fail the application on the first failing tracked task."),
     (DOCKER_ENABLED, "false", "Launch tasks through the docker container runtime."),
     (SECURITY_ENABLED, "true", "Authenticate RPC peers with the per-application secret."),
+    (HDFS_CONF_PATH, "", "Extra hdfs-site.xml (recorded only: the local cluster has no HDFS)."),
+    (YARN_CONF_PATH, "", "Extra yarn-site.xml (recorded only: the local cluster has no YARN)."),
+    (MAPRED_CONF_PATH, "", "Extra mapred-site.xml (recorded only)."),
     (PORTAL_URL, "https://localhost:19886", "Base URL of the history portal."),
     (HISTORY_LOCATION, "/path/to/tony-history", "Root of the job-history tree."),
     (HISTORY_INTERMEDIATE, "/path/to/tony-history/intermediate", "Where running jobs write history."),
@@ -244,8 +248,7 @@ DEFAULTS_MAP = {k: v for k, v, _ in DEFAULTS}
 
 # keys that exist without a default in tony-default.xml (TestTonyConfigurationFields skip list)
 KEYS_WITHOUT_DEFAULT = (
-    APPLICATION_NODE_LABEL, PREPARE_STAGE, TRAINING_STAGE, HDFS_CONF_PATH, YARN_CONF_PATH,
-    MAPRED_CONF_PATH, HADOOP_LOCATION, HADOOP_CLASSPATH, TENSORBOARD_LOG_DIR, AM_COMMAND,
+    PREPARE_STAGE, TRAINING_STAGE, HADOOP_LOCATION, HADOOP_CLASSPATH, TENSORBOARD_LOG_DIR, AM_COMMAND,
     CONTAINERS_RESOURCES, CONTAINERS_COMMAND, CONTAINERS_ENVS, EXECUTION_ENVS,
     DOCKER_CONTAINERS_IMAGE, DOCKER_CONTAINERS_MOUNT, GPU_EXEC_PATH, PYTHON_EXEC_PATH,
 )
