@@ -1,0 +1,114 @@
+"""Multi-rank worker (launched by torchrun) validating the fused collective kernels against
+torch.distributed/NCCL + a plain fp32 AdamW reference.  Prints 'MP_OK' on rank 0 on success."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch
+import torch.distributed as dist
+
+from tony_b200 import runtime
+from tony_b200.ops import _lib
+from tony_b200.parallel.symm import SymmComm
+
+
+def main():
+    rank, world, dev = runtime.init()
+    torch.manual_seed(1234 + rank)
+    n = world * 8 * 1000 * 37          # odd-ish size, multiple of world*8
+    comm = SymmComm(n, dev)
+
+    # ---- 1. symmetric all-reduce vs NCCL -------------------------------------------------
+    g = (torch.randn(n, device=dev) * 0.5).to(torch.bfloat16)
+    comm.grad.copy_(g)
+    ref = g.float().clone()
+    dist.all_reduce(ref)
+    torch.cuda.synchronize()
+    dist.barrier()
+    comm.allreduce_(0, n, scale=1.0 / world, num_ctas=16)
+    torch.cuda.synchronize()
+    comm.check_status()
+    err = (comm.param.float() - ref / world).abs().max().item()
+    assert err <= 2e-2 * (ref / world).abs().max().item() + 1e-3, f"allreduce err {err}"
+
+    # partial range with offset
+    comm.param.zero_()
+    dist.barrier()
+    lo, cnt = world * 8 * 100, world * 8 * 500
+    comm.allreduce_(lo, cnt, scale=1.0, num_ctas=4)
+    torch.cuda.synchronize()
+    assert (comm.param[:lo].abs().max().item() == 0) and (comm.param[lo + cnt:].abs().max().item() == 0)
+    err = (comm.param[lo:lo + cnt].float() - ref[lo:lo + cnt]).abs().max().item()
+    assert err <= 2e-2 * ref.abs().max().item() + 1e-3, f"ranged allreduce err {err}"
+
+    # ---- 2. device barrier, many epochs ------------------------------------------------------
+    for _ in range(50):
+        comm.barrier()
+    torch.cuda.synchronize()
+    comm.check_status()
+
+    # ---- 3. fused reduce + sharded AdamW + broadcast vs reference ---------------------------
+    import ctypes
+
+    torch.manual_seed(7)                       # same initial params on every rank
+    p0 = torch.randn(n, device=dev) * 0.1
+    comm.param.copy_(p0.to(torch.bfloat16))
+    chunk = n // world
+    master = comm.param[rank * chunk:(rank + 1) * chunk].float().clone()
+    m = torch.zeros_like(master)
+    v = torch.zeros_like(master)
+    ref_p = comm.param.float().clone().requires_grad_(True)
+    opt = torch.optim.AdamW([ref_p], lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.01)
+    lib = _lib.lib()
+    for step in range(1, 4):
+        torch.manual_seed(100 * step + rank)
+        g = (torch.randn(n, device=dev) * 0.3).to(torch.bfloat16)
+        comm.grad.copy_(g)
+        gsum = g.float().clone()
+        dist.all_reduce(gsum)
+        ref_p.grad = gsum / world
+        opt.step()
+        torch.cuda.synchronize()
+        dist.barrier()
+        _lib.check(lib.tony_fused_reduce_optim(
+            ctypes.byref(comm.c), 0, n, _lib.ptr(master), _lib.ptr(m), _lib.ptr(v), 0, _lib.OPT_ADAMW,
+            1e-2, 0.9, 0.95, 1e-8, 0.01, 1 - 0.9 ** step, 1 - 0.95 ** step, 1.0 / world, None, 1,
+            comm.next_epoch(), 16, _lib.cur_stream()), "fused")
+        torch.cuda.synchronize()
+        comm.check_status()
+        err = (comm.param.float() - ref_p.detach()).abs().max().item()
+        tol = 1.5e-2 * ref_p.detach().abs().max().item() + 2e-3
+        assert err <= tol, f"step {step}: fused param err {err} > {tol}"
+    # every rank holds identical parameters
+    mine = comm.param.float().sum()
+    lo_, hi_ = mine.clone(), mine.clone()
+    dist.all_reduce(lo_, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi_, op=dist.ReduceOp.MAX)
+    assert lo_.item() == hi_.item(), "ranks diverged"
+
+    # ---- 4. end-to-end: Trainer with overlap on a tiny BERT, loss identical across ranks -------
+    from tony_b200.models import bert
+
+    torch.manual_seed(0)
+    cfg = bert.BertConfig.tiny()
+    model = bert.BertForPreTraining(cfg, device=dev)
+    tr = runtime.Trainer(model, lr=1e-3, device=dev, bucket_mb=0.5, overlap=True, comm_ctas=8)
+    batch = bert.synthetic_batch(cfg, 4, 128, pin=True, seed=rank)
+    losses = [tr.step(batch) for _ in range(5)]
+    tr.check()
+    assert losses[-1] < losses[0], losses
+    chk = tr.store.param_buf.float().sum()
+    a, b = chk.clone(), chk.clone()
+    dist.all_reduce(a, op=dist.ReduceOp.MIN)
+    dist.all_reduce(b, op=dist.ReduceOp.MAX)
+    assert a.item() == b.item(), "trainer params diverged across ranks"
+
+    dist.barrier()
+    if rank == 0:
+        print("MP_OK", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
