@@ -97,6 +97,20 @@ size_t tony_colsum_scratch_bytes(int cols);
 int tony_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out, float* scratch,
                      size_t scratch_bytes, int accumulate, void* stream);
 
+/* Same result as tony_colsum_bf16, but the partial-sum scratch is a fixed 2 MiB device
+ * array built into the library, so the call performs no allocation and needs no scratch
+ * pointer.  For host programs that cannot allocate device memory themselves: a framework
+ * that has already reserved the whole GPU for its own pool (a cudaMalloc from a dlopen'ed
+ * helper then fails), or a hot path where the implicit device synchronisation of
+ * cudaMalloc is not acceptable.  cols <= TONY_COLSUM_STATIC_MAX_COLS, otherwise
+ * TONY_ERR_TOO_LARGE.  All calls on a GPU share that one array: issue them in order on a
+ * single stream; calls that overlap on the GPU race.  The first call on each device also
+ * resolves the array's device address — make that call before starting a stream capture.
+ * This entry point has no counterpart in the reference (which has no device code). */
+#define TONY_COLSUM_STATIC_MAX_COLS 8192
+int tony_colsum_bf16_static(const void* x, int rows, int cols, long long ld, void* out,
+                            int accumulate, void* stream);
+
 /* ---- optimizers on flat buffers ------------------------------------------------------ */
 /* AdamW / Adam over n elements: fp32 master weights + moments, bf16 gradients in, bf16
  * weights out.  wd_mask (optional) has one byte per 256 elements: 0 = no weight decay.

@@ -8,6 +8,7 @@
 #include "tony_b200_kernels.h"
 
 #include <algorithm>
+#include <mutex>
 
 namespace tony {
 
@@ -76,6 +77,94 @@ extern "C" int tony_colsum_bf16(const void* x, int rows, int cols, long long ld,
         set_last_error("tony_colsum_bf16", "scratch too small (see tony_colsum_scratch_bytes)");
         return TONY_ERR_INVALID;
     }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int col_tiles = (cols + 255) / 256;
+    int slabs = std::max(1, std::min(CS_MAX_SLABS, (device_sm_count() * 4) / col_tiles));
+    slabs = std::min(slabs, std::max(1, rows / 32));
+    const int rows_per_slab = (rows + slabs - 1) / slabs;
+    slabs = (rows + rows_per_slab - 1) / rows_per_slab;
+    colsum_partial_kernel<<<dim3(col_tiles, slabs), CS_THREADS, 0, s>>>(
+        static_cast<const __nv_bfloat16*>(x), rows, cols, ld, rows_per_slab, scratch);
+    TONY_CUDA_CHECK(cudaGetLastError());
+    colsum_finalize_kernel<<<(cols + 255) / 256, 256, 0, s>>>(
+        scratch, slabs, cols, static_cast<__nv_bfloat16*>(out), accumulate);
+    count_launch(2);
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant.
+//
+// Who needs it: a host program whose GPU memory is already spoken for.  TonY launches
+// TensorFlow, MXNet and Horovod jobs as well as PyTorch ones, and several of those
+// runtimes reserve almost the whole device for their own pool the moment they start.
+// A helper library loaded into such a process (ctypes / dlopen) that then calls
+// cudaMalloc for its scratch gets cudaErrorMemoryAllocation — there is nothing left
+// outside the pool — and it has no way to ask the framework's pool for memory through a
+// C ABI.  The same holds for callers that are forbidden to allocate on their hot path
+// because cudaMalloc synchronises the device.  For them the partial-sum scratch lives in
+// the library image itself: a file-scope device array that every GPU which loads this
+// library carries until the process exits.
+//
+// Limit: TONY_COLSUM_STATIC_MAX_COLS columns (scratch = 64 slabs x 8192 cols x 4 B = 2 MiB
+// per GPU).  Wider matrices are refused with TONY_ERR_TOO_LARGE; use tony_colsum_bf16 with
+// caller-provided scratch for those.
+//
+// Sharing: there is ONE array per GPU and every call uses it.  It still holds whatever
+// the previous call left, but nothing here depends on a zeroed start: the first kernel
+// overwrites every word the second kernel goes on to read, so no clearing is needed.
+// Two calls that overlap on the same GPU (different streams, or different host threads
+// on different streams) would write the same words and race; keep calls to this entry
+// point ordered on one stream per GPU.
+//
+// Set-up: in host code the array's name is only a stand-in, not an address a kernel can
+// use, so the first call on each device asks the runtime for the real device address
+// (cudaGetSymbolAddress, with that device current) and caches it.  That first call does
+// a little more work than later ones; make it before you begin capturing a stream.
+namespace tony {
+
+static __device__ __align__(256) float g_colsum_static_scratch[CS_MAX_SLABS * TONY_COLSUM_STATIC_MAX_COLS];
+
+static std::mutex g_colsum_static_mu;
+static float* g_colsum_static_ptr[64] = {nullptr};
+
+// Device address of the static scratch on the current device (resolved once per device).
+static int colsum_static_scratch(float** out) {
+    int dev = 0;
+    TONY_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        set_last_error("tony_colsum_bf16_static", "device ordinal out of range");
+        return TONY_ERR_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(g_colsum_static_mu);
+    if (g_colsum_static_ptr[dev] == nullptr) {
+        float* p = nullptr;
+        TONY_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_colsum_static_scratch));
+        g_colsum_static_ptr[dev] = p;
+    }
+    *out = g_colsum_static_ptr[dev];
+    return TONY_OK;
+}
+
+}  // namespace tony
+
+extern "C" int tony_colsum_bf16_static(const void* x, int rows, int cols, long long ld, void* out,
+                                       int accumulate, void* stream) {
+    if (!x || !out || rows <= 0 || cols <= 0) return TONY_ERR_INVALID;
+    if ((cols % 8) != 0 || (ld % 8) != 0 || (reinterpret_cast<uintptr_t>(x) & 15)) {
+        set_last_error("tony_colsum_bf16_static", "cols and ld must be multiples of 8; x 16B aligned");
+        return TONY_ERR_INVALID;
+    }
+    if (cols > TONY_COLSUM_STATIC_MAX_COLS) {
+        set_last_error("tony_colsum_bf16_static",
+                       "cols exceeds TONY_COLSUM_STATIC_MAX_COLS (8192): the built-in scratch is 2 MiB; "
+                       "call tony_colsum_bf16 with your own scratch instead");
+        return TONY_ERR_TOO_LARGE;
+    }
+    float* scratch = nullptr;
+    int rc = colsum_static_scratch(&scratch);
+    if (rc) return rc;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int col_tiles = (cols + 255) / 256;
     int slabs = std::max(1, std::min(CS_MAX_SLABS, (device_sm_count() * 4) / col_tiles));
