@@ -292,3 +292,16 @@ def test_limits_are_enforced_at_init(cluster):
     with pytest.raises(RuntimeError):
         client.init(["--executes", "x.py", "--conf", "tony.worker.instances=3", "--conf", "tony.worker.gpus=2",
                      "--conf", "tony.task.max-total-gpus=4"])
+
+
+def test_mnist_pytorch_two_workers_gloo(cluster):
+    """BASELINE config #1: mnist-pytorch distributed, 2 workers on CPU/gloo, launched from tony.xml."""
+    repo = os.path.dirname(os.path.dirname(SCRIPTS))
+    ex = os.path.join(repo, "examples", "mnist-pytorch")
+    client = cluster.new_client()
+    assert client.init(["--conf_file", os.path.join(ex, "tony.xml"), "--executes", os.path.join(ex, "mnist_distributed.py"),
+                        "--python_binary_path", PY, "--task_params", "--epochs 2",
+                        "--shell_env", f"TONY_REPO={repo}", "--conf", "tony.am.wait-client-signal-stop-timeout-sec=2"])
+    assert client.start() == 0
+    assert statuses(client) == {"worker:0": TaskStatus.SUCCEEDED, "worker:1": TaskStatus.SUCCEEDED}
+    assert client.submit_to_first_step_ms is not None

@@ -88,3 +88,81 @@ def test_trainer_matches_torch_adamw_one_step():
     opt.step()
     err = (p.detach().float() - ref.detach()).abs().max().item()
     assert err <= 1e-2 * ref.detach().abs().max().item() + 1e-3, err
+
+
+def test_widedeep_ps_mode_single_gpu_trains():
+    """PS path at world=1: per-weight sharded buckets + all-gather-fused GEMM (copy CTAs idle)."""
+    from tony_b200 import runtime
+    from tony_b200.models import widedeep
+    from tony_b200.parallel.ps import ps_parameters
+
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    cfg = widedeep.WideDeepConfig.tiny()
+    model = widedeep.WideDeep(cfg, device=dev)
+    tr = runtime.Trainer(model, lr=3e-3, device=dev, bucket_mb=0.25, ps_sharded=ps_parameters(model))
+    assert sum(b.ps_sharded for b in tr.store.buckets) == len(cfg.hidden)
+    batch = widedeep.synthetic_batch(cfg, 512, pin=True)
+    losses = [tr.step(batch) for _ in range(8)]
+    tr.check()
+    assert losses[-1] < losses[0] - 0.05, losses
+
+
+def test_allgather_gemm_matches_plain_gemm_single_gpu():
+    from tony_b200.ops import functional as F
+    from tony_b200.parallel.ps import ShardedLinear
+    from tony_b200 import runtime
+
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    lin = ShardedLinear(512, 1024, act="relu", device=dev)
+    lin.weight.data.normal_(0, 0.05)
+    tr = runtime.Trainer(lin, lr=1e-3, device=dev, ps_sharded=[lin.weight])
+    x = (torch.randn(300, 512, device=dev)).to(torch.bfloat16)
+    for _ in range(3):   # repeated calls exercise the per-slab epoch flags
+        y = lin(x)
+    ref = torch.relu(x.float() @ lin.weight.float().t() + lin.bias.float())
+    err = (y.float() - ref).abs().max().item()
+    assert err <= 2e-2 * ref.abs().max().item() + 1e-3, err
+
+
+def test_resnet50_conv1x1_and_generic_ddp_hooks():
+    from tony_b200.models import resnet
+    from tony_b200.parallel.ddp import DistributedDataParallel
+
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    model = DistributedDataParallel(resnet.ResNet50(num_classes=16, device=dev), device=dev, optimizer="sgd",
+                                    lr=0.05, momentum=0.9, weight_decay=1e-4, bucket_mb=8.0)
+    batch = resnet.synthetic_batch(8, dev, size=64, classes=16)
+    losses = []
+    for _ in range(6):
+        loss = model(**batch)
+        loss.backward()
+        model.step()
+        losses.append(loss.item())
+    model.store.comm.check_status()
+    assert all(l == l for l in losses) and losses[-1] < losses[0], losses
+
+
+def test_checkpoint_roundtrip(tmp_path):
+    from tony_b200 import runtime
+    from tony_b200.models import gpt2
+    from tony_b200.runtime import checkpoint
+
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    cfg = gpt2.GPT2Config.tiny()
+    tr = runtime.Trainer(gpt2.GPT2LMHead(cfg, device=dev), lr=1e-3, device=dev, bucket_mb=0.5)
+    batch = gpt2.synthetic_batch(cfg, 2, 64, pin=True)
+    for _ in range(3):
+        tr.step(batch)
+    checkpoint.save(str(tmp_path), tr)
+    want_params = tr.store.param_buf.clone()
+    want_m = tr.opt.state1.clone()
+    next_loss = tr.step(batch)
+    tr.store.param_buf.zero_()
+    tr.opt.state1.zero_()
+    assert checkpoint.load_latest(str(tmp_path), tr) == 3
+    assert torch.equal(tr.store.param_buf, want_params) and torch.equal(tr.opt.state1, want_m)
+    assert abs(tr.step(batch) - next_loss) < 1e-3

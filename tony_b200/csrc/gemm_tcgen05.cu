@@ -785,8 +785,11 @@ extern "C" int tony_allgather_gemm_bf16(const void* X, const void* const* w_shar
     ag.rank = rank;
     ag.rows_per_rank = N / world;
     // every copy CTA bumps a slab's flag once per call, so call #epoch completes at epoch*copy_ctas
+    // the tile width must be a function of N alone: the per-slab flags count calls, so every
+    // call on the same weight has to walk the same set of slabs
+    const int block_n = N >= 256 ? 256 : 128;
     return gemm_host(X, w_full, Y, M, N, K, 0, 0, K, K, N, flags, 1.0f, bias, nullptr, 0, aux_out,
-                     nullptr, 0, 0, 1, ready_flags, epoch * static_cast<unsigned int>(copy_ctas),
+                     nullptr, 0, block_n, 1, ready_flags, epoch * static_cast<unsigned int>(copy_ctas),
                      copy_ctas, 0, &ag, stream);
 }
 

@@ -1,0 +1,94 @@
+"""ResNet-50 (v1.5) for the DDP configuration.
+
+BASELINE.json config "ResNet-50 PyTorch DDP bf16, 8 workers x 1 B200 each".  Honest status
+(DESIGN.md, K8): the 3x3 / 7x7 / strided convolutions and BatchNorm still run on cuDNN / ATen in
+bf16 channels-last — no hand-written implicit-GEMM convolution yet.  What *is* ours on this
+model: every stride-1 1x1 convolution (2 of the 3 convs in each of the 16 bottlenecks, plus the
+classifier) runs as a tcgen05 GEMM over the NHWC activation viewed as [N*H*W, C] with no layout
+copy, the loss is the fused softmax-cross-entropy kernel, and gradients go through the fused
+reduce + sharded SGD-momentum + broadcast kernel via ``parallel.ddp.DistributedDataParallel``.
+"""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from ..ops import functional as F
+from .nn import Linear, _param
+
+
+class Conv1x1(nn.Module):
+    """Stride-1 pointwise convolution on channels-last activations == a GEMM."""
+
+    def __init__(self, cin: int, cout: int, device=None):
+        super().__init__()
+        self.weight = _param(cout, cin, std=(2.0 / cin) ** 0.5, device=device)
+
+    def forward(self, x):                       # x: [N, C, H, W] in channels_last memory format
+        n, c, h, w = x.shape
+        x2 = x.permute(0, 2, 3, 1).reshape(n * h * w, c)      # a view for channels_last tensors
+        y = F.linear(x2, self.weight)
+        return y.view(n, h, w, -1).permute(0, 3, 1, 2)        # still channels_last
+
+
+def _conv(cin, cout, k, stride=1, device=None):
+    return nn.Conv2d(cin, cout, k, stride=stride, padding=k // 2, bias=False, device=device, dtype=torch.bfloat16)
+
+
+def _bn(c, device=None, zero=False):
+    bn = nn.BatchNorm2d(c, device=device, dtype=torch.bfloat16)
+    if zero:
+        nn.init.zeros_(bn.weight)
+    return bn
+
+
+class Bottleneck(nn.Module):
+    def __init__(self, cin, mid, stride, device=None):
+        super().__init__()
+        cout = mid * 4
+        self.conv1, self.bn1 = Conv1x1(cin, mid, device), _bn(mid, device)
+        self.conv2, self.bn2 = _conv(mid, mid, 3, stride, device), _bn(mid, device)
+        self.conv3, self.bn3 = Conv1x1(mid, cout, device), _bn(cout, device, zero=True)
+        self.down = None
+        if stride != 1 or cin != cout:
+            proj = Conv1x1(cin, cout, device) if stride == 1 else _conv(cin, cout, 1, stride, device)
+            self.down = nn.Sequential(proj, _bn(cout, device))
+
+    def forward(self, x):
+        idt = x if self.down is None else self.down(x)
+        y = torch.relu(self.bn1(self.conv1(x)))
+        y = torch.relu(self.bn2(self.conv2(y)))
+        y = self.bn3(self.conv3(y))
+        return torch.relu(y + idt)
+
+
+class ResNet50(nn.Module):
+    def __init__(self, num_classes: int = 1000, device=None):
+        super().__init__()
+        self.stem = nn.Sequential(_conv(3, 64, 7, 2, device), _bn(64, device), nn.ReLU(inplace=True),
+                                  nn.MaxPool2d(3, 2, 1))
+        blocks, cin = [], 64
+        for mid, n, stride in ((64, 3, 1), (128, 4, 2), (256, 6, 2), (512, 3, 2)):
+            for i in range(n):
+                blocks.append(Bottleneck(cin, mid, stride if i == 0 else 1, device))
+                cin = mid * 4
+        self.blocks = nn.Sequential(*blocks)
+        self.fc = Linear(2048, (num_classes + 7) // 8 * 8, device=device)
+        self.num_classes = num_classes
+
+    def forward(self, images, labels):
+        x = images.contiguous(memory_format=torch.channels_last)
+        x = self.blocks(self.stem(x))
+        x = x.mean(dim=(2, 3))
+        return F.softmax_cross_entropy(self.fc(x), labels, vocab=self.num_classes)
+
+
+def synthetic_batch(batch: int, device="cpu", pin: bool = False, seed: int = 0, size: int = 224, classes: int = 1000):
+    g = torch.Generator().manual_seed(seed)
+    out = {"images": torch.randn(batch, 3, size, size, generator=g).to(torch.bfloat16),
+           "labels": torch.randint(0, classes, (batch,), generator=g)}
+    if pin:
+        out = {k: v.pin_memory() for k, v in out.items()}
+    if device != "cpu":
+        out = {k: v.to(device, non_blocking=True) for k, v in out.items()}
+    return out

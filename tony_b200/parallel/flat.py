@@ -41,6 +41,7 @@ class Bucket:
     slots: List["ParamSlot"] = field(default_factory=list)
     pending: int = 0
     launched: bool = False
+    ps_sharded: bool = False  # parameter-server bucket: weights stay sharded (no broadcast)
 
 
 class ParamSlot:
@@ -72,7 +73,8 @@ class ParamSlot:
 
 class FlatParamStore:
     def __init__(self, params: Iterable[Tuple[str, torch.nn.Parameter]], device, group=None,
-                 bucket_mb: float = 64.0, no_decay: Optional[Sequence[str]] = None):
+                 bucket_mb: float = 64.0, no_decay: Optional[Sequence[str]] = None,
+                 ps_sharded: Optional[Iterable[torch.nn.Parameter]] = None):
         named = []
         seen = set()
         for name, p in params:
@@ -93,25 +95,38 @@ class FlatParamStore:
         self.slots: List[ParamSlot] = []
         self.buckets: List[Bucket] = []
         self._by_param: Dict[int, ParamSlot] = {}
+        ps_ids = {id(p) for p in (ps_sharded or [])}
         offset = 0
         cur = Bucket(0, 0, 0)
+
+        def close_bucket():
+            nonlocal offset, cur
+            if not cur.slots:
+                return
+            offset = cur.begin + _round_up(offset - cur.begin, bucket_align)
+            cur.count = offset - cur.begin
+            self.buckets.append(cur)
+            cur = Bucket(len(self.buckets), offset, 0)
+
         for name, p in reversed(named):
             n = p.numel()
+            if id(p) in ps_ids:
+                # a parameter-server weight is a bucket of its own: rank r's 1/world shard of
+                # the bucket is exactly rows [r*N/world, (r+1)*N/world) of the [N, K] matrix
+                if p.dim() != 2 or n % bucket_align or p.shape[0] % self.world:
+                    raise ValueError(f"{name}: a ps-sharded weight must be 2-D with rows % world == 0 "
+                                     f"and numel % {bucket_align} == 0")
+                close_bucket()
+                cur.ps_sharded = True
             slot = ParamSlot(self, name, offset, n, tuple(p.shape))
             slot.bucket = cur
             cur.slots.append(slot)
             self.slots.append(slot)
             self._by_param[id(p)] = slot
             offset += _round_up(n, ALIGN)
-            if offset - cur.begin >= bucket_elems:
-                offset = cur.begin + _round_up(offset - cur.begin, bucket_align)
-                cur.count = offset - cur.begin
-                self.buckets.append(cur)
-                cur = Bucket(len(self.buckets), offset, 0)
-        if cur.slots:
-            offset = cur.begin + _round_up(offset - cur.begin, bucket_align)
-            cur.count = offset - cur.begin
-            self.buckets.append(cur)
+            if cur.ps_sharded or offset - cur.begin >= bucket_elems:
+                close_bucket()
+        close_bucket()
         self.numel = offset
 
         self.comm = SymmComm(self.numel, device, group)
@@ -244,7 +259,7 @@ class FusedOptimizer:
             ctypes.byref(comm.c), b.begin, b.count, _lib.ptr(self.master), _lib.ptr(self.state1),
             _lib.ptr(self.state2), b.begin // st.world, self.kind, self.lr, b1, b2, self.eps,
             self.weight_decay, bc1, bc2, self.grad_scale / st.world, _lib.ptr(st.wd_mask),
-            int(self.broadcast), comm.next_epoch(), num_ctas,
+            int(self.broadcast and not b.ps_sharded), comm.next_epoch(), num_ctas,
             ctypes.c_void_p(stream.cuda_stream)), "tony_fused_reduce_optim")
         b.launched = True
 

@@ -85,7 +85,7 @@ class Trainer:
     def __init__(self, model, *, lr: float = 1e-4, optimizer: str = "adamw", weight_decay: float = 0.01,
                  betas=(0.9, 0.999), eps: float = 1e-8, momentum: float = 0.9, bucket_mb: float = 64.0,
                  overlap: bool = True, comm_ctas: int = 32, device=None, group=None,
-                 broadcast: bool = True, generic_hooks: bool = False):
+                 broadcast: bool = True, generic_hooks: bool = False, ps_sharded=None):
         import torch
 
         from ..parallel.flat import FlatParamStore, FusedOptimizer
@@ -94,7 +94,8 @@ class Trainer:
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.model = model.to(self.device)
         self.store = FlatParamStore(model.named_parameters(), self.device, group=group,
-                                    bucket_mb=bucket_mb, no_decay=("bias", "ln", "LayerNorm", "norm"))
+                                    bucket_mb=bucket_mb, no_decay=("bias", "ln", "LayerNorm", "norm", "bn"),
+                                    ps_sharded=ps_sharded)
         for p, uses in getattr(model, "shared_params", {}).items():
             self.store.mark_shared(p, uses)
         if generic_hooks:
