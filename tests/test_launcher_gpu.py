@@ -1,0 +1,71 @@
+"""Launcher -> GPU job, end to end: tony.xml-style submission through the mini cluster places one
+task per GPU (CUDA_VISIBLE_DEVICES), the tasks build symmetric memory across processes, train
+with the fused data plane, report the first-step marker; plus BASELINE config #5's path: the
+chief dies mid-training, the whole session is retried and resumes from the sharded checkpoint."""
+import os
+import sys
+
+import pytest
+import torch
+
+from tony_b200.am.session import TaskStatus
+from tony_b200.cluster.mini import MiniCluster
+
+pytestmark = pytest.mark.gpu
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EX = os.path.join(REPO, "examples")
+
+
+def _submit(cluster, script, params, confs):
+    client = cluster.new_client()
+    argv = ["--executes", os.path.join(EX, script), "--python_binary_path", sys.executable,
+            "--task_params", params, "--shell_env", f"TONY_REPO={REPO}",
+            "--shell_env", "TONY_B200_COMM_TIMEOUT_MS=30000",
+            "--conf", "tony.am.wait-client-signal-stop-timeout-sec=2"]
+    for c in confs:
+        argv += ["--conf", c]
+    assert client.init(argv)
+    rc = client.start()
+    return rc, client
+
+
+def _logs(client):
+    out = []
+    cdir = os.path.join(client.app_dir, "containers")
+    for c in sorted(os.listdir(cdir)) if os.path.isdir(cdir) else []:
+        for f in ("stdout", "stderr"):
+            p = os.path.join(cdir, c, f)
+            if os.path.exists(p):
+                out.append(f"--- {c}/{f}\n" + open(p, errors="replace").read()[-1500:])
+    return "\n".join(out)
+
+
+def test_horovod_bert_tiny_through_launcher():
+    os.environ["TONY_B200_QUIET"] = "1"
+    os.environ.pop("TONY_B200_FAKE_GPUS", None)
+    n = min(2, torch.cuda.device_count())
+    with MiniCluster() as cluster:
+        rc, client = _submit(cluster, "bert-large-hvd/bert_pretrain.py", "--tiny --steps 6 --batch 4",
+                             ["tony.application.framework=horovod", f"tony.worker.instances={n}",
+                              "tony.worker.gpus=1"])
+        assert rc == 0, _logs(client)
+        st = {f"{t.name}:{t.index}": t.status for t in client.task_infos}
+        assert all(st[f"worker:{i}"] == TaskStatus.SUCCEEDED for i in range(n)), st
+        assert client.submit_to_first_step_ms is not None
+        print(f"submit_to_first_step_ms={client.submit_to_first_step_ms:.0f} (n={n})")
+        text = _logs(client)
+        assert "samples/s" in text
+
+
+def test_gpt2_chief_failure_restart_resumes_from_checkpoint(tmp_path):
+    os.environ["TONY_B200_QUIET"] = "1"
+    os.environ.pop("TONY_B200_FAKE_GPUS", None)
+    n = min(2, torch.cuda.device_count())
+    with MiniCluster() as cluster:
+        rc, client = _submit(cluster, "gpt2-medium-ddp/gpt2_train.py",
+                             f"--tiny --steps 12 --batch 2 --seq 64 --ckpt_every 4 --crash_at 6 --ckpt_dir {tmp_path}",
+                             ["tony.application.framework=pytorch", f"tony.worker.instances={n}",
+                              "tony.worker.gpus=1", "tony.am.retry-count=1"])
+        assert rc == 0, _logs(client)
+        text = _logs(client)
+        assert "simulating a crash" in text and "resumed from step 4" in text, text[-3000:]

@@ -120,9 +120,12 @@ class HorovodAMAdapter(AMAdapter):
             return worker_list
         if not self.driver_ready:
             return None
+        # workerAddrs is an addition to the reference's HorovodClusterSpec: the registered
+        # host:port of every worker, so the torch env:// rendezvous can be exported as well
+        addrs = [t.host_port for t in self.session.job_tasks.get(K.WORKER_JOB_NAME, []) if t is not None]
         return json.dumps({"slotInfos": self.slot_infos, "port": self.rendezvous_port,
-                           "amHost": self.rendezvous_host, "sameHostTaskIndexList": same},
-                          separators=(",", ":"))
+                           "amHost": self.rendezvous_host, "sameHostTaskIndexList": same,
+                           "workerAddrs": addrs}, separators=(",", ":"))
 
     def receive_task_callback_info(self, task_id: str, callback_info: str) -> bool:
         if not self._is_driver(task_id):
@@ -344,6 +347,11 @@ def set_horovod_run_env(env: Dict[str, str], spec: dict, task_index: int, host: 
     env["HOROVOD_RANK"] = str(slot["rank"])
     env["HOROVOD_HOSTNAME"] = str(slot["hostname"])
     # torch env:// names too, so a job using our hvd shim over torch.distributed just works
+    addrs = spec.get("workerAddrs") or []
+    if addrs and addrs[0]:
+        host0, port0 = addrs[0].rsplit(":", 1)
+        env.setdefault("MASTER_ADDR", host0)
+        env.setdefault("MASTER_PORT", port0)
     env.setdefault("RANK", str(slot["rank"]))
     env.setdefault("WORLD_SIZE", str(slot["size"]))
     env.setdefault("LOCAL_RANK", "0" if os.environ.get("CUDA_VISIBLE_DEVICES") else str(slot["localRank"]))
