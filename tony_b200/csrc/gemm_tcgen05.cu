@@ -2,10 +2,10 @@
 //
 //   C[m,n] = epilogue( alpha * sum_k A(m,k) * B(n,k) )
 //
-// * persistent kernel, one CTA per SM, 320 threads = 10 warps, warp-specialised:
+// * persistent kernel, one CTA per SM, 576 threads = 18 warps, warp-specialised:
 //     warp 0      TMA producer (one elected lane): global -> 128B-swizzled smem ring
 //     warp 1      TMEM allocator + tcgen05.mma issuer (one lane), commits to mbarriers
-//     warps 2..9  epilogue: tcgen05.ld (TMEM -> registers) -> bias/activation/residual
+//     warps 2..17 epilogue: tcgen05.ld (TMEM -> registers) -> bias/activation/residual
 //                 -> smem transpose -> fully coalesced 16-byte global stores; runs
 //                 concurrently with the next tile's MMAs because the accumulator is
 //                 double-buffered in TMEM (2 x BLOCK_N columns)
@@ -32,9 +32,9 @@ namespace tony {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int GEMM_THREADS = 320;   // TMA warp + MMA warp + 8 epilogue warps
-constexpr int EPI_WARPS = 8;
-constexpr int EPI_STAGING_BYTES = EPI_WARPS * 4096;
+constexpr int GEMM_THREADS = 576;   // TMA warp + MMA warp + 16 epilogue warps
+constexpr int EPI_WARPS = 16;
+constexpr int EPI_STAGING_BYTES = EPI_WARPS * 2048;
 constexpr int CHUNK_BYTES = BLOCK_K * 128;  // one [64 x 128B] MN-major chunk = 8 KB
 
 struct GemmParams {
@@ -124,23 +124,24 @@ __device__ __forceinline__ void allgather_copy_role(const GemmParams& p) {
 }
 
 // ---- epilogue --------------------------------------------------------------------------
-// Each epilogue warp owns 32 accumulator rows (its TMEM lane quarter) and walks 64-column
+// Each epilogue warp owns 32 accumulator rows (its TMEM lane quarter) and walks 32-column
 // chunks.  TMEM hands every lane one ROW; global memory wants every store instruction to
-// cover whole 128-byte lines.  A per-warp 4 KB staging tile ([32 rows][128 B], 16-byte
-// units XOR-swizzled by row so both access patterns are bank-conflict free) transposes
-// between the two: every global load/store below moves 4 full rows x 128 B per instruction.
+// cover whole sectors of consecutive rows.  A per-warp 2 KB staging tile ([32 rows][64 B],
+// 16-byte units XOR-swizzled by row pair so both access patterns are bank-conflict free)
+// transposes between the two: every global load/store below moves 8 rows x 64 B per
+// instruction.  Sixteen such warps (four per SM sub-partition) hide each other's latency.
 __device__ __forceinline__ uint32_t stg_addr(uint32_t base, int row, int unit) {
-    return base + row * 128 + ((unit ^ (row & 7)) << 4);
+    return base + row * 64 + ((unit ^ ((row >> 1) & 3)) << 4);
 }
 
-// global [32 x 64] bf16 tile -> this lane's row as 32 packed bf16x2 words
+// global [32 x 32] bf16 tile -> this lane's row as 16 packed bf16x2 words
 __device__ __forceinline__ void load_tile_rows(const __nv_bfloat16* g, long long ld, int row0, int col0,
-                                               int M, int N, uint32_t stg, int lane, uint32_t (&out)[32]) {
-    const int unit = lane & 7;
+                                               int M, int N, uint32_t stg, int lane, uint32_t (&out)[16]) {
+    const int unit = lane & 3;
     const int gc = col0 + unit * 8;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int row = i * 4 + (lane >> 3);
+    for (int i = 0; i < 4; ++i) {
+        const int row = i * 8 + (lane >> 2);
         const int gr = row0 + row;
         uint4 v = make_uint4(0, 0, 0, 0);
         if (gr < M && gc < N) v = ld_global_v4(g + static_cast<size_t>(gr) * ld + gc);
@@ -148,7 +149,7 @@ __device__ __forceinline__ void load_tile_rows(const __nv_bfloat16* g, long long
     }
     __syncwarp();
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
+    for (int u = 0; u < 4; ++u) {
         const uint4 v = ld_shared_v4(stg_addr(stg, lane, u));
         out[4 * u] = v.x;
         out[4 * u + 1] = v.y;
@@ -158,18 +159,18 @@ __device__ __forceinline__ void load_tile_rows(const __nv_bfloat16* g, long long
     __syncwarp();
 }
 
-// this lane's row (32 packed words) -> global [32 x 64] bf16 tile, coalesced
+// this lane's row (16 packed words) -> global [32 x 32] bf16 tile, coalesced
 __device__ __forceinline__ void store_tile_rows(__nv_bfloat16* g, long long ld, int row0, int col0, int M,
-                                                int N, uint32_t stg, int lane, const uint32_t (&in)[32]) {
+                                                int N, uint32_t stg, int lane, const uint32_t (&in)[16]) {
 #pragma unroll
-    for (int u = 0; u < 8; ++u)
+    for (int u = 0; u < 4; ++u)
         st_shared_v4(stg_addr(stg, lane, u), make_uint4(in[4 * u], in[4 * u + 1], in[4 * u + 2], in[4 * u + 3]));
     __syncwarp();
-    const int unit = lane & 7;
+    const int unit = lane & 3;
     const int gc = col0 + unit * 8;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int row = i * 4 + (lane >> 3);
+    for (int i = 0; i < 4; ++i) {
+        const int row = i * 8 + (lane >> 2);
         const int gr = row0 + row;
         const uint4 v = ld_shared_v4(stg_addr(stg, row, unit));
         if (gr < M && gc < N) st_global_v4(g + static_cast<size_t>(gr) * ld + gc, v);
@@ -177,29 +178,32 @@ __device__ __forceinline__ void store_tile_rows(__nv_bfloat16* g, long long ld, 
     __syncwarp();
 }
 
-__device__ __forceinline__ void epilogue_chunk64(const GemmParams& p, float (&v)[64], int row0, int col0,
-                                                 uint32_t stg, int lane) {
+__device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, const uint32_t (&r)[32], int row0,
+                                                 int col0, uint32_t stg, int lane) {
     const uint32_t flags = p.flags;
+    float v[32];
     if (flags & TONY_EPI_BIAS) {
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            if (col0 + u * 8 < p.N) {
-                const uint4 b = __ldg(reinterpret_cast<const uint4*>(p.bias + col0 + u * 8));
-                const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+        for (int u = 0; u < 4; ++u) {
+            uint4 b = make_uint4(0, 0, 0, 0);
+            if (col0 + u * 8 < p.N) b = __ldg(reinterpret_cast<const uint4*>(p.bias + col0 + u * 8));
+            const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float2 f = unpack_bf16x2(bw[j]);
-                    v[u * 8 + 2 * j] += f.x;
-                    v[u * 8 + 2 * j + 1] += f.y;
-                }
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(bw[j]);
+                v[u * 8 + 2 * j] = fmaf(__uint_as_float(r[u * 8 + 2 * j]), p.alpha, f.x);
+                v[u * 8 + 2 * j + 1] = fmaf(__uint_as_float(r[u * 8 + 2 * j + 1]), p.alpha, f.y);
             }
         }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
     }
     if (flags & (TONY_EPI_RESIDUAL | TONY_EPI_DGELU_ERF | TONY_EPI_DGELU_TANH | TONY_EPI_DRELU)) {
-        uint32_t a[32];
+        uint32_t a[16];
         load_tile_rows(p.aux, p.ld_aux, row0, col0, p.M, p.N, stg, lane, a);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
+        for (int j = 0; j < 16; ++j) {
             const float2 f = unpack_bf16x2(a[j]);
             if (flags & TONY_EPI_RESIDUAL) {
                 v[2 * j] += f.x;
@@ -216,34 +220,34 @@ __device__ __forceinline__ void epilogue_chunk64(const GemmParams& p, float (&v)
             }
         }
     }
-    uint32_t o[32];
+    uint32_t o[16];
     if (flags & TONY_EPI_SAVE_PREACT) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) o[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+        for (int j = 0; j < 16; ++j) o[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
         store_tile_rows(p.aux_out, p.ldc, row0, col0, p.M, p.N, stg, lane, o);
     }
     if (flags & TONY_EPI_GELU_ERF) {
 #pragma unroll
-        for (int j = 0; j < 64; ++j) v[j] = gelu_erf(v[j]);
+        for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
     } else if (flags & TONY_EPI_GELU_TANH) {
 #pragma unroll
-        for (int j = 0; j < 64; ++j) v[j] = gelu_tanh(v[j]);
+        for (int j = 0; j < 32; ++j) v[j] = gelu_tanh(v[j]);
     } else if (flags & TONY_EPI_RELU) {
 #pragma unroll
-        for (int j = 0; j < 64; ++j) v[j] = fmaxf(v[j], 0.f);
+        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
     }
     if (flags & TONY_EPI_ACCUMULATE) {
-        uint32_t c[32];
+        uint32_t c[16];
         load_tile_rows(p.C, p.ldc, row0, col0, p.M, p.N, stg, lane, c);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
+        for (int j = 0; j < 16; ++j) {
             const float2 f = unpack_bf16x2(c[j]);
             v[2 * j] += f.x;
             v[2 * j + 1] += f.y;
         }
     }
 #pragma unroll
-    for (int j = 0; j < 32; ++j) o[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+    for (int j = 0; j < 16; ++j) o[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
     store_tile_rows(p.C, p.ldc, row0, col0, p.M, p.N, stg, lane, o);
 }
 
@@ -387,12 +391,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 }
             }
         } else {
-            // ------------------------------------------------ epilogue warps (2..9)
-            // TMEM lane quarter = warp_idx % 4 (hardware rule); two warps share a quarter and
-            // split its 64-column chunks between them (even / odd).
+            // ------------------------------------------------ epilogue warps (2..17)
+            // TMEM lane quarter = warp_idx % 4 (hardware rule); four warps share a quarter and
+            // deal its 32-column chunks round-robin.
             const int quarter = warp_idx & 3;
-            const int half = (warp_idx - 2) >> 2;
-            const uint32_t stg = smem_u32(staging + (warp_idx - 2) * 4096);
+            const int group = (warp_idx - 2) >> 2;
+            const uint32_t stg = smem_u32(staging + (warp_idx - 2) * 2048);
             int iter = 0;
             for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
                 const int tile = unit / p.splits;
@@ -407,19 +411,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const uint32_t taddr0 =
                     tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BLOCK_N;
 #pragma unroll 1
-                for (int c = half; c < BLOCK_N / 64; c += 2) {
-                    uint32_t r[64];
-                    tmem_ld_32x32(taddr0 + c * 64, r);
-                    tmem_ld_32x32(taddr0 + c * 64 + 32, r + 32);
+                for (int c = group; c < BLOCK_N / 32; c += EPI_WARPS / 4) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(taddr0 + c * 32, r);
                     tmem_ld_wait();
-                    const int col0 = n_blk * BLOCK_N + c * 64;
+                    const int col0 = n_blk * BLOCK_N + c * 32;
                     if (col0 >= p.N || row0 >= p.M) continue;  // warp-uniform
                     if (p.splits > 1) {
                         const int row = row0 + lane;
                         if (row < p.M) {
                             float* dst = p.workspace + (static_cast<size_t>(split) * p.M + row) * p.N + col0;
 #pragma unroll
-                            for (int g = 0; g < 16; ++g) {
+                            for (int g = 0; g < 8; ++g) {
                                 if (col0 + g * 4 < p.N)
                                     *reinterpret_cast<float4*>(dst + g * 4) = make_float4(
                                         __uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]),
@@ -428,10 +431,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                         }
                         continue;
                     }
-                    float v[64];
-#pragma unroll
-                    for (int j = 0; j < 64; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
-                    epilogue_chunk64(p, v, row0, col0, stg, lane);
+                    epilogue_chunk32(p, r, row0, col0, stg, lane);
                 }
                 tcgen05_fence_before();
                 __syncwarp();
