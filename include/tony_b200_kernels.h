@@ -111,6 +111,13 @@ int tony_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out,
 int tony_colsum_bf16_static(const void* x, int rows, int cols, long long ld, void* out,
                             int accumulate, void* stream);
 
+/* ---- packing ------------------------------------------------------------------------- */
+/* out[r, 0..2, :] = (a[r,:], b[r,:], c[r,:]): interleave the dq/dk/dv of a library attention
+ * backward into the packed gradient of a fused QKV projection in one launch (strides in
+ * elements).  Replaces three zero-filled select_backward tensors + adds of stock autograd. */
+int tony_pack3_rows(const void* a, const void* b, const void* c, long long lda, long long ldb,
+                    long long ldc, void* out, int rows, int row_elems, void* stream);
+
 /* ---- optimizers on flat buffers ------------------------------------------------------ */
 /* AdamW / Adam over n elements: fp32 master weights + moments, bf16 gradients in, bf16
  * weights out.  wd_mask (optional) has one byte per 256 elements: 0 = no weight decay.

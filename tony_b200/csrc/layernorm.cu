@@ -78,8 +78,11 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
     }
 }
 
+// Registers are the occupancy limit here (per-lane dgamma/dbeta accumulators alone are
+// 16*NV floats), so x / dy / gamma stay packed as bf16 and are unpacked twice (statistics
+// pass, then dx pass) instead of being held as fp32: 2 CTAs x 8 warps per SM for H <= 1024.
 template <int NV>
-__global__ void __launch_bounds__(LN_WARPS * 32)
+__global__ void __launch_bounds__(LN_WARPS * 32, (NV <= 4) ? 2 : 1)
 layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean,
                      const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
@@ -87,30 +90,37 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     constexpr int H = NV * 256;
     __shared__ float red[2][H];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float g[NV][8], dg[NV][8], db[NV][8];
+    uint4 gq[NV];
+    float dg[NV][8], db[NV][8];
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
-        unpack8(__ldg(reinterpret_cast<const uint4*>(gamma + (i * 32 + lane) * 8)), g[i]);
+        gq[i] = __ldg(reinterpret_cast<const uint4*>(gamma + (i * 32 + lane) * 8));
 #pragma unroll
         for (int j = 0; j < 8; ++j) dg[i][j] = db[i][j] = 0.f;
     }
     for (int row = blockIdx.x * LN_WARPS + warp; row < rows; row += gridDim.x * LN_WARPS) {
         const size_t off = static_cast<size_t>(row) * H;
         const float mu = mean[row], rs = rstd[row];
-        float xh[NV][8], wdy[NV][8];
+        uint4 xq[NV], dq[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            xq[i] = ld_global_nc_v4(x + off + (i * 32 + lane) * 8);
+            dq[i] = ld_global_nc_v4(dy + off + (i * 32 + lane) * 8);
+        }
         float c1 = 0.f, c2 = 0.f;
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
-            float xv[8], dv[8];
-            unpack8(ld_global_nc_v4(x + off + (i * 32 + lane) * 8), xv);
-            unpack8(ld_global_nc_v4(dy + off + (i * 32 + lane) * 8), dv);
+            float xv[8], dv[8], gv[8];
+            unpack8(xq[i], xv);
+            unpack8(dq[i], dv);
+            unpack8(gq[i], gv);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                xh[i][j] = (xv[j] - mu) * rs;
-                wdy[i][j] = dv[j] * g[i][j];
-                c1 += xh[i][j] * wdy[i][j];
-                c2 += wdy[i][j];
-                dg[i][j] += dv[j] * xh[i][j];
+                const float xh = (xv[j] - mu) * rs;
+                const float wdy = dv[j] * gv[j];
+                c1 = fmaf(xh, wdy, c1);
+                c2 += wdy;
+                dg[i][j] = fmaf(dv[j], xh, dg[i][j]);
                 db[i][j] += dv[j];
             }
         }
@@ -118,9 +128,15 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         c2 = warp_sum(c2) * (1.0f / H);
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
-            float o[8];
+            float xv[8], dv[8], gv[8], o[8];
+            unpack8(xq[i], xv);
+            unpack8(dq[i], dv);
+            unpack8(gq[i], gv);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) o[j] = (wdy[i][j] - (xh[i][j] * c1 + c2)) * rs;
+            for (int j = 0; j < 8; ++j) {
+                const float xh = (xv[j] - mu) * rs;
+                o[j] = (dv[j] * gv[j] - fmaf(xh, c1, c2)) * rs;
+            }
             st_global_v4(dx + off + (i * 32 + lane) * 8, pack8(o));
         }
     }
@@ -186,7 +202,7 @@ static int launch_bwd(const void* dy, const void* x, const void* gamma, const fl
                       const float* rstd, void* dx, void* dgamma, void* dbeta, int rows, float* scratch,
                       int accumulate, cudaStream_t s) {
     constexpr int H = NV * 256;
-    const int grid = std::min({(rows + LN_WARPS - 1) / LN_WARPS, device_sm_count() * 2, LN_MAX_PARTIALS});
+    const int grid = std::min({(rows + LN_WARPS - 1) / LN_WARPS, device_sm_count() * (NV <= 4 ? 2 : 1), LN_MAX_PARTIALS});
     layernorm_bwd_kernel<NV><<<grid, LN_WARPS * 32, 0, s>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
         static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<__nv_bfloat16*>(dx),

@@ -108,9 +108,7 @@ def _declare(lib) -> None:
     lib.tony_symm_barrier.argtypes = [POINTER(FusedComm), c_uint, vp]
     lib.tony_allgather_gemm_bf16.argtypes = [vp, POINTER(c_void_p), vp, vp, c_int, c_int, c_int,
                                              c_int, c_int, c_uint, vp, vp, vp, c_uint, c_int, vp]
-    for name in ("tony_embedding_fwd", "tony_embedding_bwd"):
-        if hasattr(lib, name):
-            getattr(lib, name).restype = c_int
+    lib.tony_pack3_rows.argtypes = [vp, vp, vp, c_longlong, c_longlong, c_longlong, vp, c_int, c_int, vp]
 
 
 def lib():

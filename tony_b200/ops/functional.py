@@ -471,9 +471,22 @@ class _PackedSdpaFn(torch.autograd.Function):
         do = dout.reshape(B, S, nh, hd).transpose(1, 2)
         dq, dk, dv = torch.autograd.grad(o, (q, k, v), do)
         dqkv = torch.empty((B, S, 3, nh, hd), dtype=dout.dtype, device=dout.device)
-        dqkv[:, :, 0].copy_(dq.transpose(1, 2))
-        dqkv[:, :, 1].copy_(dk.transpose(1, 2))
-        dqkv[:, :, 2].copy_(dv.transpose(1, 2))
+        parts = [t.transpose(1, 2) for t in (dq, dk, dv)]          # [B, S, nh, hd] views
+        H = nh * hd
+
+        def rows_view(t):
+            # (row stride in elements) if t is [B*S rows] x [H contiguous elements], else None
+            ok = t.stride(3) == 1 and t.stride(2) == hd and t.stride(0) == S * t.stride(1)
+            return t.stride(1) if ok and t.stride(1) % 8 == 0 and t.data_ptr() % 16 == 0 else None
+
+        strides = [rows_view(t) for t in parts]
+        if dout.dtype == torch.bfloat16 and H % 8 == 0 and all(s is not None for s in strides):
+            check(_lib.lib().tony_pack3_rows(ptr(parts[0]), ptr(parts[1]), ptr(parts[2]), strides[0],
+                                             strides[1], strides[2], ptr(dqkv), B * S, H, cur_stream()),
+                  "tony_pack3_rows")
+        else:
+            for i, t in enumerate(parts):
+                dqkv[:, :, i].copy_(t)
         return dqkv, None
 
 
