@@ -25,6 +25,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 namespace tony {
@@ -452,6 +453,207 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
 }
 
+// ----------------------------------------------------------------------------------------
+// CTA-pair variant: two SMs (one cluster of 2) compute one 256 x 256 tile.
+//   * each CTA TMA-loads only ITS half of both operands (128 rows of A, 128 rows of B), so
+//     a k-block costs 32 KB of L2->smem traffic per SM instead of 48 KB, and the smem ring is
+//     6 deep instead of 4;
+//   * the leader CTA issues tcgen05.mma.cta_group::2 (M = 256, N = 256): the tensor cores of
+//     both SMs read A/B halves from both shared memories; each CTA's TMEM receives its 128
+//     rows x 256 columns of the accumulator;
+//   * TMA completions of both CTAs are credited to the leader's `full` barrier; the leader's
+//     tcgen05.commit multicasts the `empty` / `tmem_full` arrivals to both CTAs; the epilogue
+//     warps of both CTAs arrive remotely on the leader's `tmem_empty` barrier.
+// Per-CTA shared-memory layout and descriptors are exactly those of the 128 x 128 1-CTA kernel.
+template <int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                              const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
+    constexpr int HALF_N = 128;                       // B rows held by each CTA
+    constexpr int TILE_N = 256;
+    constexpr int TILE_M = 256;
+    constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;
+    constexpr uint32_t B_BYTES = HALF_N * BLOCK_K * 2;
+    constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+    constexpr uint32_t TMEM_COLS = 2 * TILE_N;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(
+        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    uint8_t* staging = smem + STAGES * STAGE_BYTES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + EPI_STAGING_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+    const int warp_idx = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t cta_rank = cluster_ctarank();
+    const bool leader = cta_rank == 0;
+
+    if (warp_idx == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);    // leader's producer arrive.expect_tx (both CTAs' bytes)
+            mbar_init(&empty_bar[s], 1);   // multicast commit from the leader's MMA thread
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full_bar[s], 1);
+            mbar_init(&tmem_empty_bar[s], 2 * EPI_WARPS);  // epilogue warps of BOTH CTAs
+        }
+        fence_barrier_init();
+    }
+    if (warp_idx == 1) tmem_alloc_2cta<TMEM_COLS>(tmem_base_slot);
+    tcgen05_fence_before();
+    cluster_sync_all();   // peer barriers initialised before any remote arrive / TMA credit
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_base_slot;
+
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks;   // blocks of 256 x 256 here
+    const int num_units = num_tiles * p.splits;
+    const int cluster_id = static_cast<int>(blockIdx.x >> 1);
+    const int num_clusters = static_cast<int>(gridDim.x >> 1);
+
+    if (warp_idx == 0) {
+        // ---------------------------------------------------- TMA producer (both CTAs)
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int unit = cluster_id; unit < num_units; unit += num_clusters) {
+                const int tile = unit / p.splits;
+                const int split = unit - tile * p.splits;
+                int m_blk, n_blk;
+                tile_coords(p, tile, m_blk, n_blk);
+                const int m0 = m_blk * TILE_M + static_cast<int>(cta_rank) * BLOCK_M;
+                const int n0 = n_blk * TILE_N + static_cast<int>(cta_rank) * HALF_N;
+                const int kb0 = split * p.kb_per_split;
+                const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * STAGE_BYTES;
+                    uint8_t* sb = sa + A_BYTES;
+                    const uint32_t bar = mapa_u32(smem_u32(&full_bar[stage]), 0);  // leader's barrier
+                    if (leader) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+                    if (!p.a_mn_major) {
+                        tma_load_2d_2cta(&tmap_a, bar, sa, kb * BLOCK_K, m0);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BLOCK_M / 64; ++c)
+                            tma_load_2d_2cta(&tmap_a, bar, sa + c * CHUNK_BYTES, m0 + c * 64, kb * BLOCK_K);
+                    }
+                    if (!p.b_mn_major) {
+                        tma_load_2d_2cta(&tmap_b, bar, sb, kb * BLOCK_K, n0);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < HALF_N / 64; ++c)
+                            tma_load_2d_2cta(&tmap_b, bar, sb + c * CHUNK_BYTES, n0 + c * 64, kb * BLOCK_K);
+                    }
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp_idx == 1) {
+        // ---------------------------------------------------- MMA issuer (leader CTA only)
+        if (leader && lane == 0) {
+            const uint32_t idesc = make_idesc_bf16(TILE_M, TILE_N, p.a_mn_major, p.b_mn_major);
+            const uint32_t a_lbo = p.a_mn_major ? CHUNK_BYTES : 16;
+            const uint32_t b_lbo = p.b_mn_major ? CHUNK_BYTES : 16;
+            const uint32_t a_kstep = p.a_mn_major ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+            const uint32_t b_kstep = p.b_mn_major ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+            int stage = 0;
+            uint32_t phase = 0;
+            int iter = 0;
+            for (int unit = cluster_id; unit < num_units; unit += num_clusters, ++iter) {
+                const int tile = unit / p.splits;
+                const int split = unit - tile * p.splits;
+                const int as = iter & 1;
+                const uint32_t aphase = (iter >> 1) & 1;
+                mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
+                tcgen05_fence_after();
+                const uint32_t d_tmem = tmem_base + as * TILE_N;
+                const int kb0 = split * p.kb_per_split;
+                const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tcgen05_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+                    const uint32_t sb = sa + A_BYTES;
+                    const uint64_t da = make_umma_desc_sw128(sa, a_lbo, 1024);
+                    const uint64_t db = make_umma_desc_sw128(sb, b_lbo, 1024);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        umma_bf16_2cta(d_tmem, da + k * a_kstep, db + k * b_kstep, idesc,
+                                       (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit_2cta(&empty_bar[stage], 3);   // frees the slot in both CTAs
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                umma_commit_2cta(&tmem_full_bar[as], 3);      // accumulators complete in both CTAs
+            }
+        }
+    } else {
+        // ---------------------------------------------------- epilogue warps (both CTAs)
+        const int quarter = warp_idx & 3;
+        const int group = (warp_idx - 2) >> 2;
+        const uint32_t stg = smem_u32(staging + (warp_idx - 2) * 2048);
+        int iter = 0;
+        for (int unit = cluster_id; unit < num_units; unit += num_clusters, ++iter) {
+            const int tile = unit / p.splits;
+            const int split = unit - tile * p.splits;
+            int m_blk, n_blk;
+            tile_coords(p, tile, m_blk, n_blk);
+            const int as = iter & 1;
+            const uint32_t aphase = (iter >> 1) & 1;
+            mbar_wait(&tmem_full_bar[as], aphase);
+            tcgen05_fence_after();
+            const int row0 = m_blk * TILE_M + static_cast<int>(cta_rank) * BLOCK_M + quarter * 32;
+            const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * TILE_N;
+#pragma unroll 1
+            for (int c = group; c < TILE_N / 32; c += EPI_WARPS / 4) {
+                uint32_t r[32];
+                tmem_ld_32x32(taddr0 + c * 32, r);
+                tmem_ld_wait();
+                const int col0 = n_blk * TILE_N + c * 32;
+                if (col0 >= p.N || row0 >= p.M) continue;  // warp-uniform
+                if (p.splits > 1) {
+                    const int row = row0 + lane;
+                    if (row < p.M) {
+                        float* dst = p.workspace + (static_cast<size_t>(split) * p.M + row) * p.N + col0;
+#pragma unroll
+                        for (int g = 0; g < 8; ++g) {
+                            if (col0 + g * 4 < p.N)
+                                *reinterpret_cast<float4*>(dst + g * 4) = make_float4(
+                                    __uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]),
+                                    __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]));
+                        }
+                    }
+                    continue;
+                }
+                epilogue_chunk32(p, r, row0, col0, stg, lane);
+            }
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tmem_empty_bar[as]), 0));
+        }
+    }
+
+    __syncwarp();
+    tcgen05_fence_before();
+    cluster_sync_all();   // both CTAs done with TMEM and with each other's barriers
+    if (warp_idx == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc_2cta<TMEM_COLS>(tmem_base);
+    }
+}
+
 // out = alpha * sum_s ws[s] (+ old out) (+ bias), fp32 partials -> bf16
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, int M, int N,
                                      __nv_bfloat16* __restrict__ C, long long ldc, float alpha,
@@ -596,6 +798,36 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
     return TONY_OK;
 }
 
+template <int STAGES>
+static int launch_gemm_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
+                            cudaStream_t stream) {
+    constexpr size_t SMEM =
+        static_cast<size_t>(STAGES) * (BLOCK_M + 128) * BLOCK_K * 2 + EPI_STAGING_BYTES + 1024 + 256;
+    static bool configured[64] = {false};
+    int dev = 0;
+    TONY_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        TONY_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_2cta_kernel<STAGES>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             static_cast<int>(SMEM)));
+        configured[dev] = true;
+    }
+    gemm_bf16_tcgen05_2cta_kernel<STAGES><<<grid, GEMM_THREADS, SMEM, stream>>>(ta, tb, p);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}
+
+// TONY_B200_GEMM_2CTA=0 disables the CTA-pair kernel (A/B testing); default on
+static int two_cta_mode() {
+    static int mode = -1;
+    if (mode < 0) {
+        const char* e = getenv("TONY_B200_GEMM_2CTA");
+        mode = e ? atoi(e) : 1;
+    }
+    return mode;
+}
+
 static double wave_efficiency(long long units, int sms) {
     const long long waves = (units + sms - 1) / sms;
     return static_cast<double>(units) / static_cast<double>(waves * sms);
@@ -641,10 +873,27 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
     if (max_ctas > 0) workers = std::min(workers, max_ctas - copy_ctas);
     if (workers <= 0) return TONY_ERR_INVALID;
 
-    const int num_m = (M + BLOCK_M - 1) / BLOCK_M;
+    int num_m = (M + BLOCK_M - 1) / BLOCK_M;
     const int num_k = (K + BLOCK_K - 1) / BLOCK_K;
     int block_n = force_block_n;
-    if (block_n != 128 && block_n != 256) {
+    // CTA-pair kernel (256 x 256 tiles over 2 SMs): force_block_n == 512 forces it, 0 lets the
+    // heuristic decide, 128 / 256 force the 1-CTA kernels.
+    bool use_2cta = false;
+    if (!ag && copy_ctas == 0 && b_ready == nullptr && two_cta_mode() > 0 && (workers % 2) == 0) {
+        if (force_block_n == 512) {
+            use_2cta = true;
+        } else if (force_block_n == 0 && N >= 256 && M >= 256) {
+            // measured on BERT-large (profiles/): the pair kernel wins on every such shape,
+            // even where its wave quantisation is worse, because each SM moves a third less
+            // operand traffic and the smem ring is 6 deep
+            use_2cta = true;
+        }
+    }
+    if (use_2cta) {
+        block_n = 256;
+        num_m = (M + 255) / 256;
+        workers /= 2;  // clusters
+    } else if (block_n != 128 && block_n != 256) {
         const long long t256 = static_cast<long long>(num_m) * ((N + 255) / 256);
         const long long t128 = static_cast<long long>(num_m) * ((N + 127) / 128);
         block_n = (N <= 128 || wave_efficiency(t128, workers) > 1.12 * wave_efficiency(t256, workers))
@@ -683,7 +932,7 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
     CUtensorMap ta, tb;
     int rc = make_operand_tmap(&ta, A, M, K, lda, a_mn_major, BLOCK_M);
     if (rc) return rc;
-    rc = make_operand_tmap(&tb, B, N, K, ldb, b_mn_major, block_n);
+    rc = make_operand_tmap(&tb, B, N, K, ldb, b_mn_major, use_2cta ? 128 : block_n);
     if (rc) return rc;
 
     GemmParams p;
@@ -724,7 +973,9 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
 
     const long long units = tiles * splits;
     const int grid = static_cast<int>(std::min<long long>(units, workers)) + copy_ctas;
-    if (block_n == 256)
+    if (use_2cta)
+        rc = launch_gemm_2cta<6>(ta, tb, p, grid * 2, stream);
+    else if (block_n == 256)
         rc = launch_gemm<256, 4>(ta, tb, p, grid, stream);
     else
         rc = launch_gemm<128, 6>(ta, tb, p, grid, stream);

@@ -83,6 +83,7 @@ static T* to_dev(const std::vector<T>& h) {
 }
 
 static int g_fail = 0;
+static int g_force_block_n = 0;  // 0 auto, 128/256 1-CTA kernels, 512 CTA-pair kernel
 
 struct Case {
     const char* name;
@@ -117,8 +118,8 @@ static bool run_case(const Case& c) {
     ref_gemm<<<dim3((N + 127) / 128, M), 128>>>(dA, dB, dref, M, N, K, c.a_mn, c.b_mn, lda, ldb, c.flags,
                                                 c.alpha, dbias, daux, dCold, dpre_ref);
     CK(cudaGetLastError());
-    int rc = tony_gemm_bf16(dA, dB, dC, M, N, K, c.a_mn, c.b_mn, lda, ldb, N, c.flags, c.alpha, dbias,
-                            daux, N, dpre, ws, ws_bytes, nullptr);
+    int rc = tony_gemm_bf16_ex(dA, dB, dC, M, N, K, c.a_mn, c.b_mn, lda, ldb, N, c.flags, c.alpha, dbias,
+                               daux, N, dpre, ws, ws_bytes, g_force_block_n, 0, nullptr, 0, 0, 0, nullptr);
     if (rc != 0) {
         printf("[FAIL] %-34s rc=%d (%s)\n", c.name, rc, tony_last_error());
         g_fail++;
@@ -262,8 +263,8 @@ static void perf_case(const char* name, int M, int N, int K, int a_mn, int b_mn,
     for (int it = 0; it < iters + 3; ++it) {
         CK(cudaMemsetAsync(flush, it, flush_bytes));
         CK(cudaEventRecord(e0));
-        int rc = tony_gemm_bf16(dA, dB, dC, M, N, K, a_mn, b_mn, lda, ldb, N, flags, 1.0f, dbias, dC, N, dpre,
-                                ws, ws_bytes, nullptr);
+        int rc = tony_gemm_bf16_ex(dA, dB, dC, M, N, K, a_mn, b_mn, lda, ldb, N, flags, 1.0f, dbias, dC, N, dpre,
+                                   ws, ws_bytes, g_force_block_n, 0, nullptr, 0, 0, 0, nullptr);
         CK(cudaEventRecord(e1));
         if (rc) { printf("perf %s rc=%d %s\n", name, rc, tony_last_error()); return; }
         CK(cudaEventSynchronize(e1));
@@ -279,10 +280,11 @@ static void perf_case(const char* name, int M, int N, int K, int a_mn, int b_mn,
 }
 
 int main(int argc, char** argv) {
-    bool perf = false, want_probe = false;
+    bool perf = false, want_probe = false, skip_2cta = false;
     for (int i = 1; i < argc; ++i) {
         if (!strcmp(argv[i], "--perf")) perf = true;
         if (!strcmp(argv[i], "--probe")) want_probe = true;
+        if (!strcmp(argv[i], "--no-2cta")) skip_2cta = true;
     }
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, 0));
@@ -330,7 +332,16 @@ int main(int argc, char** argv) {
             printf("  (K-major baseline failing: probes skipped, fix that first)\n");
         }
     }
+    if (!skip_2cta) {
+        printf("---- CTA-pair kernel forced (force_block_n = 512) ----\n");
+        g_force_block_n = 512;
+        for (const Case& c : cases) run_case(c);
+        g_force_block_n = 0;
+    }
     if (perf && g_fail == 0) {
+        for (int pass = 0; pass < (skip_2cta ? 1 : 2); ++pass) {
+        g_force_block_n = pass == 0 ? 256 : 512;
+        printf("---- perf with force_block_n = %d (%s) ----\n", g_force_block_n, pass ? "CTA pair" : "1 CTA, 128x256");
         // BERT-large (tokens = 16 x 512 = 8192) and GPT-2 medium shapes: fwd, dgrad, wgrad
         perf_case("fwd qkv", 8192, 3072, 1024, 0, 0, TONY_EPI_BIAS, 0);
         perf_case("fwd attn_out(+res)", 8192, 1024, 1024, 0, 0, TONY_EPI_BIAS | TONY_EPI_RESIDUAL, 0);
@@ -344,6 +355,8 @@ int main(int argc, char** argv) {
         perf_case("wgrad qkv", 3072, 1024, 8192, 1, 1, 0, 1);
         perf_case("square 8192", 8192, 8192, 8192, 0, 0, 0, 0);
         perf_case("square 4096", 4096, 4096, 4096, 0, 0, 0, 0);
+        }
+        g_force_block_n = 0;
     }
     printf("%s: %d failing case(s)\n", g_fail ? "SELFTEST FAILED" : "SELFTEST PASSED", g_fail);
     return g_fail ? 1 : 0;
