@@ -1,8 +1,7 @@
 // tony_b200 — LayerNorm forward / backward for sm_100a (memory-bound: one pass over HBM).
 //
 // One warp per row, 16-byte vector loads (8 bf16 per lane per load), fp32 statistics.
-// Backward is two-stage for dgamma/dbeta: per-lane register accumulators over a CTA's
-// rows -> smem -> per-CTA partial rows in caller scratch -> a finalize kernel.
+// Backward = a dx kernel + a column-reduction kernel for dgamma/dbeta (see below).
 // Replaces ATen layer_norm / native_layer_norm_backward in the launched jobs
 // (the reference itself has no device code: SURVEY.md §2.4).
 #include "common.cuh"
@@ -78,26 +77,22 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
     }
 }
 
-// Registers are the occupancy limit here (per-lane dgamma/dbeta accumulators alone are
-// 16*NV floats), so x / dy / gamma stay packed as bf16 and are unpacked twice (statistics
-// pass, then dx pass) instead of being held as fp32: 2 CTAs x 8 warps per SM for H <= 1024.
+// Backward is split in two light kernels instead of one register-heavy one:
+//   * layernorm_bwd_dx_kernel: warp per row, no per-column state -> few registers, high
+//     occupancy, streams x and dy once from HBM and writes dx;
+//   * layernorm_bwd_dgdb_kernel: column reduction of dy*xhat and dy.  Each thread owns 8
+//     columns and walks a slab of rows (x / dy are re-read, but 2 x 32 MB has just been
+//     streamed and sits in the 126 MB L2); partial rows go to caller scratch and the last
+//     CTA of each column tile folds them (counter in the first 4 KB of scratch).
+// (A single kernel keeping 16*NV per-lane accumulators needed 192 registers -> one CTA per SM,
+// or spilled at 128: 40-45 us for 16384 x 1024 against a 15 us HBM floor.)
 template <int NV>
-__global__ void __launch_bounds__(LN_WARPS * 32, (NV <= 4) ? 2 : 1)
-layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                     const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean,
-                     const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
-                     float* __restrict__ partials, int rows) {
+__global__ void __launch_bounds__(LN_WARPS * 32)
+layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                        const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean,
+                        const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx, int rows) {
     constexpr int H = NV * 256;
-    __shared__ float red[2][H];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint4 gq[NV];
-    float dg[NV][8], db[NV][8];
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-        gq[i] = __ldg(reinterpret_cast<const uint4*>(gamma + (i * 32 + lane) * 8));
-#pragma unroll
-        for (int j = 0; j < 8; ++j) dg[i][j] = db[i][j] = 0.f;
-    }
     for (int row = blockIdx.x * LN_WARPS + warp; row < rows; row += gridDim.x * LN_WARPS) {
         const size_t off = static_cast<size_t>(row) * H;
         const float mu = mean[row], rs = rstd[row];
@@ -113,15 +108,12 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
             float xv[8], dv[8], gv[8];
             unpack8(xq[i], xv);
             unpack8(dq[i], dv);
-            unpack8(gq[i], gv);
+            unpack8(__ldg(reinterpret_cast<const uint4*>(gamma + (i * 32 + lane) * 8)), gv);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                const float xh = (xv[j] - mu) * rs;
                 const float wdy = dv[j] * gv[j];
-                c1 = fmaf(xh, wdy, c1);
+                c1 = fmaf((xv[j] - mu) * rs, wdy, c1);
                 c2 += wdy;
-                dg[i][j] = fmaf(dv[j], xh, dg[i][j]);
-                db[i][j] += dv[j];
             }
         }
         c1 = warp_sum(c1) * (1.0f / H);
@@ -131,7 +123,7 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
             float xv[8], dv[8], gv[8], o[8];
             unpack8(xq[i], xv);
             unpack8(dq[i], dv);
-            unpack8(gq[i], gv);
+            unpack8(__ldg(reinterpret_cast<const uint4*>(gamma + (i * 32 + lane) * 8)), gv);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const float xh = (xv[j] - mu) * rs;
@@ -140,48 +132,97 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
             st_global_v4(dx + off + (i * 32 + lane) * 8, pack8(o));
         }
     }
-    // CTA reduction of the per-lane accumulators: warps take turns adding into smem
-    for (int w = 0; w < LN_WARPS; ++w) {
-        if (warp == w) {
-#pragma unroll
-            for (int i = 0; i < NV; ++i)
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const int c = (i * 32 + lane) * 8 + j;
-                    if (w == 0) {
-                        red[0][c] = dg[i][j];
-                        red[1][c] = db[i][j];
-                    } else {
-                        red[0][c] += dg[i][j];
-                        red[1][c] += db[i][j];
-                    }
-                }
-        }
-        __syncthreads();
-    }
-    float* out = partials + static_cast<size_t>(blockIdx.x) * 2 * H;
-    for (int c = threadIdx.x; c < 2 * H; c += blockDim.x) out[c] = red[c / H][c % H];
 }
 
-// dgamma/dbeta[c] (+)= sum_p partials[p][which][c]
-__global__ void layernorm_bwd_finalize_kernel(const float* __restrict__ partials, int num_partials,
-                                              int H, __nv_bfloat16* __restrict__ dgamma,
-                                              __nv_bfloat16* __restrict__ dbeta, int accumulate) {
-    __shared__ float red[8][33];
-    const int c = blockIdx.x * 32 + threadIdx.x;
-    const int which = blockIdx.y;
-    float s = 0.f;
-    for (int p = threadIdx.y; p < num_partials; p += 8)
-        s += partials[(static_cast<size_t>(p) * 2 + which) * H + c];
-    red[threadIdx.y][threadIdx.x] = s;
-    __syncthreads();
-    if (threadIdx.y == 0) {
+constexpr int LN_RED_THREADS = 256;  // 8 warps x 32 lanes x 8 columns = 256 columns per CTA
+
+__global__ void __launch_bounds__(LN_RED_THREADS)
+layernorm_bwd_dgdb_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                          const float* __restrict__ mean, const float* __restrict__ rstd, int rows, int H,
+                          int rows_per_slab, float* __restrict__ partials, unsigned int* __restrict__ counters,
+                          __nv_bfloat16* __restrict__ dgamma, __nv_bfloat16* __restrict__ dbeta,
+                          int accumulate) {
+    __shared__ float red[2][LN_RED_THREADS / 32][256];
+    __shared__ unsigned int is_last;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int col = blockIdx.x * 256 + lane * 8;
+    const int r0 = blockIdx.y * rows_per_slab;
+    const int r1 = min(rows, r0 + rows_per_slab);
+    float ag[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float ab[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    constexpr int W = LN_RED_THREADS / 32;
+    int r = r0 + warp;
+    for (; r + W < r1; r += 2 * W) {  // two rows in flight per warp
+        const uint4 xa = ld_global_nc_v4(x + static_cast<size_t>(r) * H + col);
+        const uint4 da = ld_global_nc_v4(dy + static_cast<size_t>(r) * H + col);
+        const uint4 xb = ld_global_nc_v4(x + static_cast<size_t>(r + W) * H + col);
+        const uint4 db = ld_global_nc_v4(dy + static_cast<size_t>(r + W) * H + col);
+        const float mua = mean[r], rsa = rstd[r], mub = mean[r + W], rsb = rstd[r + W];
+        float xv[8], dv[8];
+        unpack8(xa, xv);
+        unpack8(da, dv);
 #pragma unroll
-        for (int k = 1; k < 8; ++k) s += red[k][threadIdx.x];
-        __nv_bfloat16* out = which == 0 ? dgamma : dbeta;
-        if (accumulate) s += __bfloat162float(out[c]);
-        out[c] = __float2bfloat16(s);
+        for (int j = 0; j < 8; ++j) {
+            ag[j] = fmaf(dv[j], (xv[j] - mua) * rsa, ag[j]);
+            ab[j] += dv[j];
+        }
+        unpack8(xb, xv);
+        unpack8(db, dv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            ag[j] = fmaf(dv[j], (xv[j] - mub) * rsb, ag[j]);
+            ab[j] += dv[j];
+        }
     }
+    for (; r < r1; r += W) {
+        float xv[8], dv[8];
+        unpack8(ld_global_nc_v4(x + static_cast<size_t>(r) * H + col), xv);
+        unpack8(ld_global_nc_v4(dy + static_cast<size_t>(r) * H + col), dv);
+        const float mu = mean[r], rs = rstd[r];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            ag[j] = fmaf(dv[j], (xv[j] - mu) * rs, ag[j]);
+            ab[j] += dv[j];
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        red[0][warp][lane * 8 + j] = ag[j];
+        red[1][warp][lane * 8 + j] = ab[j];
+    }
+    __syncthreads();
+    const int c = threadIdx.x;
+    float sg = 0.f, sb = 0.f;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+        sg += red[0][w][c];
+        sb += red[1][w][c];
+    }
+    const int gc = blockIdx.x * 256 + c;
+    float* my = partials + static_cast<size_t>(blockIdx.y) * 2 * H;
+    my[gc] = sg;
+    my[H + gc] = sb;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int prev = atomicAdd(&counters[blockIdx.x], 1u);
+        is_last = (prev == gridDim.y - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    float tg = 0.f, tb = 0.f;
+    for (int k = 0; k < static_cast<int>(gridDim.y); ++k) {
+        tg += __ldcg(partials + static_cast<size_t>(k) * 2 * H + gc);
+        tb += __ldcg(partials + static_cast<size_t>(k) * 2 * H + H + gc);
+    }
+    if (accumulate) {
+        tg += __bfloat162float(dgamma[gc]);
+        tb += __bfloat162float(dbeta[gc]);
+    }
+    dgamma[gc] = __float2bfloat16(tg);
+    dbeta[gc] = __float2bfloat16(tb);
+    if (threadIdx.x == 0) counters[blockIdx.x] = 0;
 }
 
 template <int NV>
@@ -202,15 +243,23 @@ static int launch_bwd(const void* dy, const void* x, const void* gamma, const fl
                       const float* rstd, void* dx, void* dgamma, void* dbeta, int rows, float* scratch,
                       int accumulate, cudaStream_t s) {
     constexpr int H = NV * 256;
-    const int grid = std::min({(rows + LN_WARPS - 1) / LN_WARPS, device_sm_count() * (NV <= 4 ? 2 : 1), LN_MAX_PARTIALS});
-    layernorm_bwd_kernel<NV><<<grid, LN_WARPS * 32, 0, s>>>(
+    const int sms = device_sm_count();
+    const int grid = std::min((rows + LN_WARPS - 1) / LN_WARPS, sms * 8);
+    layernorm_bwd_dx_kernel<NV><<<grid, LN_WARPS * 32, 0, s>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
-        static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<__nv_bfloat16*>(dx),
-        scratch, rows);
+        static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<__nv_bfloat16*>(dx), rows);
     TONY_CUDA_CHECK(cudaGetLastError());
-    layernorm_bwd_finalize_kernel<<<dim3(H / 32, 2), dim3(32, 8), 0, s>>>(
-        scratch, grid, H, static_cast<__nv_bfloat16*>(dgamma), static_cast<__nv_bfloat16*>(dbeta),
-        accumulate);
+    // scratch: [4 KB counters][partials: slabs x 2 x H floats]
+    const int col_tiles = H / 256;
+    int slabs = std::max(1, std::min({LN_MAX_PARTIALS, (sms * 4) / col_tiles, std::max(1, rows / 16)}));
+    const int rows_per_slab = (rows + slabs - 1) / slabs;
+    slabs = (rows + rows_per_slab - 1) / rows_per_slab;
+    unsigned int* counters = reinterpret_cast<unsigned int*>(scratch);
+    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, static_cast<size_t>(col_tiles) * 4, s));
+    layernorm_bwd_dgdb_kernel<<<dim3(col_tiles, slabs), LN_RED_THREADS, 0, s>>>(
+        static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x), mean, rstd, rows, H,
+        rows_per_slab, scratch + 1024, counters, static_cast<__nv_bfloat16*>(dgamma),
+        static_cast<__nv_bfloat16*>(dbeta), accumulate);
     count_launch(2);
     TONY_CUDA_CHECK(cudaGetLastError());
     return TONY_OK;
@@ -241,7 +290,7 @@ extern "C" int tony_layernorm_fwd(const void* x, const void* gamma, const void* 
 }
 
 extern "C" size_t tony_layernorm_bwd_scratch_bytes(int H) {
-    return static_cast<size_t>(LN_MAX_PARTIALS) * 2 * static_cast<size_t>(H) * sizeof(float);
+    return 4096 + static_cast<size_t>(LN_MAX_PARTIALS) * 2 * static_cast<size_t>(H) * sizeof(float);
 }
 
 extern "C" int tony_layernorm_bwd(const void* dy, const void* x, const void* gamma,
@@ -263,8 +312,9 @@ extern "C" int tony_layernorm_bwd(const void* dy, const void* x, const void* gam
         case 1280: return launch_bwd<5>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
         case 1536: return launch_bwd<6>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
         case 2048: return launch_bwd<8>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
+        case 4096: return launch_bwd<16>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
         default:
-            set_last_error("tony_layernorm_bwd", "H must be one of 256,512,768,1024,1280,1536,2048");
+            set_last_error("tony_layernorm_bwd", "H must be one of 256,512,768,1024,1280,1536,2048,4096");
             return TONY_ERR_UNSUPPORTED;
     }
 }
