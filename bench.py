@@ -106,7 +106,7 @@ def parse_args(argv=None):
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "stock", "reference"])
-    ap.add_argument("--model", default="bert-large", choices=["bert-large", "bert-tiny", "gpt2-medium"])
+    ap.add_argument("--model", default="bert-large", choices=["bert-large", "bert-tiny", "gpt2-medium", "resnet50", "widedeep"])
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default 32 BERT / 8 GPT-2)")
     ap.add_argument("--seq", type=int, default=0)
     ap.add_argument("--no-overlap", action="store_true")
@@ -130,6 +130,26 @@ def build(args, device):
         model = bert.BertForPreTraining(cfg, device=device) if args.impl == "ours" else stock.StockBertForPreTraining(cfg)
         metric = "bert_large_pretrain_samples_per_sec" if args.model == "bert-large" else "bert_tiny_samples_per_sec"
         name = "BERT-large (24L/1024H/16A, vocab 30522, MLM 80 preds + NSP)" if args.model == "bert-large" else "BERT-tiny"
+    elif args.model == "resnet50":
+        from tony_b200.models import resnet
+
+        batch = args.batch or 256
+        make = lambda seed, pin=False, dev="cpu": resnet.synthetic_batch(batch, dev, pin, seed)
+        flops = 3 * 4.1e9 * 2 / 2  # ~4.1 GMACs forward per 224x224 image, x3 for fwd+bwd
+        model = resnet.ResNet50(device=device) if args.impl == "ours" else resnet.stock_resnet50(device=device)
+        return model, make, batch, 224, flops, "resnet50_train_img_per_sec", \
+            "ResNet-50 v1.5, 224x224, bf16 channels-last (3x3/7x7 convs + BN on cuDNN in both arms)"
+    elif args.model == "widedeep":
+        from tony_b200.models import widedeep
+
+        cfg = widedeep.WideDeepConfig()
+        batch = args.batch or 16384
+        make = lambda seed, pin=False, dev="cpu": widedeep.synthetic_batch(cfg, batch, dev, pin, seed)
+        dims = [26 * 128 + 16] + cfg.hidden
+        flops = 6.0 * sum(a * b for a, b in zip(dims[:-1], dims[1:]))
+        model = widedeep.WideDeep(cfg, device=device) if args.impl == "ours" else widedeep.StockWideDeep(cfg)
+        return model, make, batch, 1, flops, "widedeep_ps_samples_per_sec", \
+            "wide&deep recommender (26 x 100k-row tables, tower 3344-4096-4096-2048-1024)"
     else:
         cfg = gpt2.GPT2Config.medium()
         seq = args.seq or 1024
@@ -145,23 +165,27 @@ def build(args, device):
 class StockTrainer:
     """Baseline arm: autocast-bf16 + DDP(NCCL) + fused AdamW, same step contract as Trainer."""
 
-    def __init__(self, model, device, world):
+    def __init__(self, model, device, world, sgd=False, autocast=True):
         import torch
 
         self.torch = torch
         self.device = device
+        self.autocast = autocast
         self.model = model.to(device)
         if world > 1:
             from torch.nn.parallel import DistributedDataParallel as DDP
 
             self.model = DDP(self.model, device_ids=[device.index], gradient_as_bucket_view=True)
-        self.opt = torch.optim.AdamW(self.model.parameters(), lr=1e-4, weight_decay=0.01, fused=True)
+        if sgd:
+            self.opt = torch.optim.SGD(self.model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4, fused=True)
+        else:
+            self.opt = torch.optim.AdamW(self.model.parameters(), lr=1e-4, weight_decay=0.01, fused=True)
 
     def to_device(self, b):
         return {k: v.to(self.device, non_blocking=True) for k, v in b.items()}
 
     def step_device(self, b):
-        with self.torch.autocast("cuda", dtype=self.torch.bfloat16):
+        with self.torch.autocast("cuda", dtype=self.torch.bfloat16, enabled=self.autocast):
             loss = self.model(**b)
         loss.backward()
         self.opt.step()
@@ -196,11 +220,20 @@ def main(argv=None) -> int:
     if args.impl == "ours":
         from tony_b200.ops import _lib
 
-        trainer = runtime.Trainer(model, lr=1e-4, weight_decay=0.01, overlap=not args.no_overlap,
-                                  bucket_mb=args.bucket_mb, comm_ctas=args.comm_ctas, device=device)
+        kw = dict(overlap=not args.no_overlap, bucket_mb=args.bucket_mb, comm_ctas=args.comm_ctas, device=device)
+        if args.model == "resnet50":
+            model = model.to(device=device, dtype=torch.bfloat16)
+            trainer = runtime.Trainer(model, lr=0.1, optimizer="sgd", weight_decay=1e-4, generic_hooks=True, **kw)
+        elif args.model == "widedeep":
+            from tony_b200.parallel.ps import ps_parameters
+
+            trainer = runtime.Trainer(model, lr=1e-3, weight_decay=0.0, ps_sharded=ps_parameters(model), **kw)
+        else:
+            trainer = runtime.Trainer(model, lr=1e-4, weight_decay=0.01, **kw)
         launches = _lib.launch_count
     else:
-        trainer = StockTrainer(model, device, world)
+        trainer = StockTrainer(model, device, world, sgd=(args.model == "resnet50"),
+                               autocast=(args.model != "resnet50"))
         launches = lambda: 0
 
     def sync_all():
@@ -264,7 +297,7 @@ def main(argv=None) -> int:
         tflops = value / world * flops_per_sample / 1e12
         denom = peaks.get("bf16_tflops_sustained") or 1400.0
         out = {
-            "metric": metric, "value": round(value, 2), "unit": "samples/s", "n_gpus": world,
+            "metric": metric, "value": round(value, 2), "unit": "img/s" if args.model == "resnet50" else "samples/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_total / args.steps, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic (random token ids, random-init weights)", "impl": args.impl,

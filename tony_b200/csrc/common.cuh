@@ -185,6 +185,16 @@ __device__ __forceinline__ void tmem_ld_wait() {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// ---- programmatic dependent launch -------------------------------------------------------
+// A kernel launched with the programmatic-stream-serialization attribute may start while the
+// previous kernel in the stream is still draining; it must not touch global memory before
+// pdl_wait() (returns at once when the kernel was launched normally).  pdl_launch_dependents()
+// lets the NEXT kernel's CTAs be scheduled as soon as every CTA of this grid has called it.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 // ---- CTA-pair (cta_group::2) variants ----------------------------------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;

@@ -292,6 +292,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_base_slot;
+    pdl_launch_dependents();  // the next kernel may start its own prologue on idle SMs
 
     const int num_tiles = p.num_m_blocks * p.num_n_blocks;
     const int num_units = num_tiles * p.splits;
@@ -304,6 +305,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             if (lane == 0) {
                 int stage = 0;
                 uint32_t phase = 0;
+                pdl_wait();  // everything above overlapped the previous kernel's tail
                 for (int unit = worker; unit < num_units; unit += num_workers) {
                     const int tile = unit / p.splits;
                     const int split = unit - tile * p.splits;
@@ -441,6 +443,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
     }
     else {
+        pdl_wait();
         allgather_copy_role<BLOCK_N>(p);
     }
 
@@ -510,6 +513,7 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
     cluster_sync_all();   // peer barriers initialised before any remote arrive / TMA credit
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_base_slot;
+    pdl_launch_dependents();
 
     const int num_tiles = p.num_m_blocks * p.num_n_blocks;   // blocks of 256 x 256 here
     const int num_units = num_tiles * p.splits;
@@ -521,6 +525,7 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            pdl_wait();
             for (int unit = cluster_id; unit < num_units; unit += num_clusters) {
                 const int tile = unit / p.splits;
                 const int split = unit - tile * p.splits;
@@ -778,6 +783,29 @@ int device_sm_count() {
     return cached[dev];
 }
 
+// Launch with programmatic stream serialization: the kernel may begin (prologue only, see
+// pdl_wait) before the previous kernel in the stream has fully drained.  TONY_B200_PDL=0 disables.
+template <typename Kern>
+static cudaError_t launch_pdl(Kern kern, int grid, size_t smem, cudaStream_t stream, const CUtensorMap& ta,
+                              const CUtensorMap& tb, const GemmParams& p) {
+    static int pdl = -1;
+    if (pdl < 0) {
+        const char* e = getenv("TONY_B200_PDL");
+        pdl = e ? atoi(e) : 1;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, ta, tb, p);
+}
+
 template <int BLOCK_N, int STAGES>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
                        cudaStream_t stream) {
@@ -792,9 +820,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
                                              static_cast<int>(SMEM)));
         configured[dev] = true;
     }
-    gemm_bf16_tcgen05_kernel<BLOCK_N, STAGES><<<grid, GEMM_THREADS, SMEM, stream>>>(ta, tb, p);
+    TONY_CUDA_CHECK(launch_pdl(gemm_bf16_tcgen05_kernel<BLOCK_N, STAGES>, grid, SMEM, stream, ta, tb, p));
     count_launch();
-    TONY_CUDA_CHECK(cudaGetLastError());
     return TONY_OK;
 }
 
@@ -812,9 +839,8 @@ static int launch_gemm_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const 
                                              static_cast<int>(SMEM)));
         configured[dev] = true;
     }
-    gemm_bf16_tcgen05_2cta_kernel<STAGES><<<grid, GEMM_THREADS, SMEM, stream>>>(ta, tb, p);
+    TONY_CUDA_CHECK(launch_pdl(gemm_bf16_tcgen05_2cta_kernel<STAGES>, grid, SMEM, stream, ta, tb, p));
     count_launch();
-    TONY_CUDA_CHECK(cudaGetLastError());
     return TONY_OK;
 }
 
@@ -910,7 +936,7 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
     if (splittable) {
         if (force_splits > 1) {
             splits = force_splits;
-        } else if (force_splits == 0 && tiles * 2 <= workers) {
+        } else if (force_splits == 0 && (tiles * 2 <= workers || wave_efficiency(tiles, workers) < 0.75)) {
             double best = wave_efficiency(tiles, workers);
             for (int s = 2; s <= 16; ++s) {
                 if (num_k / s < 8) break;  // keep >= 512 reduction elements per split

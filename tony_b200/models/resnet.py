@@ -1,20 +1,27 @@
 """ResNet-50 (v1.5) for the DDP configuration.
 
 BASELINE.json config "ResNet-50 PyTorch DDP bf16, 8 workers x 1 B200 each".  Honest status
-(DESIGN.md, K8): the 3x3 / 7x7 / strided convolutions and BatchNorm still run on cuDNN / ATen in
-bf16 channels-last — no hand-written implicit-GEMM convolution yet.  What *is* ours on this
-model: every stride-1 1x1 convolution (2 of the 3 convs in each of the 16 bottlenecks, plus the
-classifier) runs as a tcgen05 GEMM over the NHWC activation viewed as [N*H*W, C] with no layout
-copy, the loss is the fused softmax-cross-entropy kernel, and gradients go through the fused
-reduce + sharded SGD-momentum + broadcast kernel via ``parallel.ddp.DistributedDataParallel``.
+(DESIGN.md, K8): the convolutions and BatchNorm still run on cuDNN / ATen in bf16
+channels-last — no hand-written implicit-GEMM convolution yet.  Stride-1 1x1 convolutions CAN
+run as a tcgen05 GEMM over the NHWC activation viewed as [N*H*W, C] (no layout copy), but the
+measured crossover (profiles/r1_call23_*) says cuDNN wins for every reduction depth in this
+network (4494 img/s with all of them on the GEMM, 4741 with none), so by default only the
+2048-channel ones do (``TONY_B200_RESNET_GEMM_MIN_CIN``).  Ours on this model: the classifier
+GEMM, the fused softmax-cross-entropy kernel, and the fused reduce + sharded SGD-momentum +
+broadcast kernel fed by bucketed gradient hooks (``Trainer(generic_hooks=True)``).
 """
 from __future__ import annotations
+
+import os
 
 import torch
 from torch import nn
 
 from ..ops import functional as F
 from .nn import Linear, _param
+
+
+STOCK = {"on": False}   # set by stock_resnet50(): build the cuDNN-only twin for the baseline arm
 
 
 class Conv1x1(nn.Module):
@@ -46,12 +53,19 @@ class Bottleneck(nn.Module):
     def __init__(self, cin, mid, stride, device=None):
         super().__init__()
         cout = mid * 4
-        self.conv1, self.bn1 = Conv1x1(cin, mid, device), _bn(mid, device)
+        # a pointwise conv becomes a tcgen05 GEMM only when its reduction dim is deep enough to
+        # amortise the per-tile epilogue (measured crossover, see profiles/); shallower ones stay on cuDNN
+        min_cin = int(os.environ.get("TONY_B200_RESNET_GEMM_MIN_CIN", "1024"))
+
+        def C1(i, o, d):
+            return _conv(i, o, 1, 1, d) if (STOCK["on"] or i < min_cin) else Conv1x1(i, o, d)
+
+        self.conv1, self.bn1 = C1(cin, mid, device), _bn(mid, device)
         self.conv2, self.bn2 = _conv(mid, mid, 3, stride, device), _bn(mid, device)
-        self.conv3, self.bn3 = Conv1x1(mid, cout, device), _bn(cout, device, zero=True)
+        self.conv3, self.bn3 = C1(mid, cout, device), _bn(cout, device, zero=True)
         self.down = None
         if stride != 1 or cin != cout:
-            proj = Conv1x1(cin, cout, device) if stride == 1 else _conv(cin, cout, 1, stride, device)
+            proj = C1(cin, cout, device) if stride == 1 else _conv(cin, cout, 1, stride, device)
             self.down = nn.Sequential(proj, _bn(cout, device))
 
     def forward(self, x):
@@ -73,14 +87,27 @@ class ResNet50(nn.Module):
                 blocks.append(Bottleneck(cin, mid, stride if i == 0 else 1, device))
                 cin = mid * 4
         self.blocks = nn.Sequential(*blocks)
-        self.fc = Linear(2048, (num_classes + 7) // 8 * 8, device=device)
+        self.stock = STOCK["on"]
+        self.fc = (nn.Linear(2048, num_classes, device=device, dtype=torch.bfloat16) if self.stock
+                   else Linear(2048, (num_classes + 7) // 8 * 8, device=device))
         self.num_classes = num_classes
 
     def forward(self, images, labels):
         x = images.contiguous(memory_format=torch.channels_last)
         x = self.blocks(self.stem(x))
         x = x.mean(dim=(2, 3))
+        if self.stock:
+            return torch.nn.functional.cross_entropy(self.fc(x).float(), labels)
         return F.softmax_cross_entropy(self.fc(x), labels, vocab=self.num_classes)
+
+
+def stock_resnet50(num_classes: int = 1000, device=None) -> "ResNet50":
+    """The baseline twin: every layer on cuDNN / ATen (bf16, channels-last), ATen cross-entropy."""
+    STOCK["on"] = True
+    try:
+        return ResNet50(num_classes, device)
+    finally:
+        STOCK["on"] = False
 
 
 def synthetic_batch(batch: int, device="cpu", pin: bool = False, seed: int = 0, size: int = 224, classes: int = 1000):

@@ -89,3 +89,27 @@ def synthetic_batch(c: WideDeepConfig, batch: int, device="cpu", pin: bool = Fal
     if device != "cpu":
         out = {k: v.to(device, non_blocking=True) for k, v in out.items()}
     return out
+
+
+class StockWideDeep(nn.Module):
+    """Baseline twin on stock PyTorch modules (fp32 params, bf16 autocast, replicated weights)."""
+
+    def __init__(self, c: WideDeepConfig):
+        super().__init__()
+        self.config = c
+        self.deep_tables = nn.ModuleList(nn.Embedding(c.vocab_per_field, c.embed_dim) for _ in range(c.num_fields))
+        self.wide_tables = nn.ModuleList(nn.Embedding(c.vocab_per_field, 2) for _ in range(c.num_fields))
+        prev = c.num_fields * c.embed_dim + c.dense_features
+        layers = []
+        for h in c.hidden:
+            layers += [nn.Linear(prev, h), nn.ReLU()]
+            prev = h
+        self.tower = nn.Sequential(*layers)
+        self.head = nn.Linear(prev, 2)
+
+    def forward(self, sparse_ids, dense, labels):
+        deep = [t(sparse_ids[:, i]) for i, t in enumerate(self.deep_tables)]
+        x = torch.cat(deep + [dense.float()], dim=1)
+        logits = self.head(self.tower(x))
+        wide = sum(t(sparse_ids[:, i]) for i, t in enumerate(self.wide_tables))
+        return torch.nn.functional.cross_entropy((logits + wide).float(), labels)

@@ -183,22 +183,38 @@ class FlatParamStore:
             self._ready_cb(b)
 
     def register_autograd_hooks(self) -> None:
-        """Generic path for parameters whose gradients come from stock autograd ops: copy
-        ``p.grad`` into the bucket slot as soon as it has been accumulated."""
+        """Generic path for parameters whose gradients come from stock autograd ops: collect
+        ``p.grad`` as it is accumulated and move a whole bucket into the flat gradient buffer
+        with ONE multi-tensor copy when its last gradient arrives."""
+        pending: Dict[int, list] = {}
+
         for name, p in self.named:
             slot = self._by_param[id(p)]
 
             def hook(param, slot=slot):
                 if param.grad is None:
                     return
-                if slot.begin_write():
-                    slot.grad_view.add_(param.grad.to(torch.bfloat16))
-                else:
-                    slot.grad_view.copy_(param.grad)
+                g = param.grad
                 param.grad = None
-                slot.end_write()
+                if slot.begin_write() or slot.expected != 1:
+                    # shared / multiply-used parameter: accumulate immediately
+                    if slot.begin_write():
+                        slot.grad_view.add_(g.to(torch.bfloat16))
+                    else:
+                        slot.grad_view.copy_(g)
+                    slot.end_write()
+                    return
+                b = slot.bucket
+                lst = pending.setdefault(b.index, [])
+                lst.append((slot, g))
+                if len(lst) == sum(1 for s_ in b.slots if s_.expected == 1 and s_.written == 0):
+                    torch._foreach_copy_([s_.grad_view for s_, _ in lst], [g_ for _, g_ in lst])
+                    pending[b.index] = []
+                    for s_, _ in lst:
+                        s_.end_write()
 
             p.register_post_accumulate_grad_hook(hook)
+        self._pending_hook_grads = pending
 
     def shard_range(self, b: Bucket) -> Tuple[int, int]:
         chunk = b.count // self.world
@@ -273,6 +289,14 @@ class FusedOptimizer:
         """Finish the step: launch whatever backward did not, then join the comm stream."""
         st = self.store
         cur = torch.cuda.current_stream()
+        leftovers = getattr(st, "_pending_hook_grads", None)
+        if leftovers:
+            for idx, lst in leftovers.items():
+                if lst:
+                    torch._foreach_copy_([s_.grad_view for s_, _ in lst], [g_ for _, g_ in lst])
+                    for s_, _ in lst:
+                        s_.written += 1
+                    leftovers[idx] = []
         for b in st.buckets:
             if b.launched:
                 continue
