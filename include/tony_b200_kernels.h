@@ -181,6 +181,47 @@ int tony_symm_allreduce_bf16(const tony_fused_comm* comm, size_t begin, size_t c
 /* All-rank barrier on the GPU (arrive + wait on flag words). */
 int tony_symm_barrier(const tony_fused_comm* comm, unsigned int epoch, void* stream);
 
+/* ---- NVLS (in-switch) form of the fused kernel ----------------------------------------- */
+/* Symmetric heap on CUDA VMM + NVSwitch multicast (csrc/symm_vmm.cu).  Allocation protocol:
+ * tony_vmm_granularity -> tony_vmm_alloc (returns an exportable fd) -> exchange fds ->
+ * tony_vmm_import / tony_vmm_map for peers -> rank 0 tony_mc_create, others tony_vmm_import
+ * of its fd -> every rank tony_mc_add_device -> barrier -> tony_mc_bind -> barrier ->
+ * tony_vmm_map(mc handle) gives the multicast address. */
+int tony_nvls_supported(void);
+int tony_vmm_granularity(int world, size_t bytes, size_t* padded_out);
+int tony_vmm_alloc(size_t padded_bytes, unsigned long long* handle_out, int* fd_out);
+int tony_vmm_import(int fd, unsigned long long* handle_out);
+int tony_vmm_map(unsigned long long handle, size_t padded_bytes, void** ptr_out);
+int tony_vmm_unmap(void* ptr, size_t padded_bytes);
+int tony_vmm_release(unsigned long long handle);
+int tony_mc_create(size_t padded_bytes, int world, unsigned long long* handle_out, int* fd_out);
+int tony_mc_add_device(unsigned long long mc_handle);
+int tony_mc_bind(unsigned long long mc_handle, unsigned long long mem_handle, size_t padded_bytes);
+
+typedef struct tony_nvls_comm {
+    int rank, world;
+    const void* grad_mc;        /* multicast address of the bf16 gradient buffers          */
+    void* param_mc;             /* multicast address of the bf16 parameter buffers         */
+    void* param_local;          /* this rank's own parameter buffer (unicast)              */
+    unsigned int* flags_mc;     /* multicast address of the flag block (>= 64 words)       */
+    unsigned int* flags_local;  /* this rank's copy of the flag block                      */
+    unsigned int* counter;      /* local: one word, zero-initialised                       */
+    int* status;                /* local: set to TONY_ERR_TIMEOUT if a peer never came     */
+} tony_nvls_comm;
+
+/* Same contract as tony_fused_reduce_optim, but the reduction happens INSIDE the NVSwitch:
+ * each rank issues multimem.ld_reduce (fp32 accumulation in the switch) over its shard of the
+ * multicast gradient address, updates its optimizer shard, and publishes the new bf16 weights
+ * to every rank with one multimem.st; arrivals are counted with multimem.red on a multicast
+ * flag word.  `call_index` = 1, 2, 3, ... counts NVLS collectives on this comm (all ranks must
+ * agree).  optimizer = -1 gives a plain all-reduce (sum * grad_scale written to param). */
+int tony_fused_reduce_optim_nvls(const tony_nvls_comm* comm, size_t begin, size_t count, float* master,
+                                 float* state1, float* state2, size_t state_offset, int optimizer,
+                                 float lr, float beta1_or_momentum, float beta2, float eps,
+                                 float weight_decay, float bc1, float bc2, float grad_scale,
+                                 const unsigned char* wd_mask, int broadcast, unsigned int call_index,
+                                 int num_ctas, void* stream);
+
 /* ---- all-gather fused into a GEMM (K3) ---------------------------------------------- */
 /* Y = epi(X . W^T) where W [N,K] is row-sharded over `world` ranks (rows
  * [r*N/world, (r+1)*N/world) live on rank r at w_shard[r]).  Copy CTAs pull the remote

@@ -163,6 +163,9 @@ def main():
 
     dist.barrier()
     if rank == 0:
+        from tony_b200.parallel.symm import symm_mode
+
+        print(f"symm_mode={symm_mode()} nvls={'on' if comm.nvls is not None else 'off'}", flush=True)
         print("MP_OK", flush=True)
     dist.destroy_process_group()
 

@@ -240,3 +240,62 @@ def test_packed_attention_matches_sdpa():
         ref.backward(g)
         _close(out, ref)
         _close(qkv.grad, ref_in.grad)
+
+
+@pytest.mark.parametrize("force", [128, 256, 512])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True)])
+def test_gemm_every_kernel_variant(force, a_mn, b_mn):
+    """1-CTA 128x128 / 128x256 kernels and the CTA-pair 256x256 kernel, forced through the _ex ABI."""
+    import ctypes
+
+    from tony_b200.ops import _lib
+    from tony_b200.ops._lib import EPI_BIAS, EPI_RESIDUAL
+
+    M, N, K = 640, 776, 328
+    A, B, bias, res = _rand(M, K), _rand(N, K), _rand(N), _rand(M, N)
+    a = A.t().contiguous() if a_mn else A
+    b = B.t().contiguous() if b_mn else B
+    out = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    rc = _lib.lib().tony_gemm_bf16_ex(
+        _lib.ptr(a), _lib.ptr(b), _lib.ptr(out), M, N, K, int(a_mn), int(b_mn), a.stride(0), b.stride(0), N,
+        EPI_BIAS | EPI_RESIDUAL, 1.0, _lib.ptr(bias), _lib.ptr(res), N, None, None, 0, force, 1, None, 0, 0, 0,
+        _lib.cur_stream())
+    _lib.check(rc, "tony_gemm_bf16_ex")
+    _close(out, A.float() @ B.float().t() + bias.float() + res.float())
+
+
+def test_pack3_rows():
+    from tony_b200.ops import _lib
+
+    rows, H = 1000, 1024
+    a, b, c = _rand(rows, H), _rand(rows, 2 * H)[:, :H], _rand(rows, H)
+    out = torch.empty(rows, 3, H, device=DEV, dtype=torch.bfloat16)
+    _lib.check(_lib.lib().tony_pack3_rows(_lib.ptr(a), _lib.ptr(b), _lib.ptr(c), a.stride(0), b.stride(0),
+                                          c.stride(0), _lib.ptr(out), rows, H, _lib.cur_stream()), "pack3")
+    assert torch.equal(out[:, 0], a) and torch.equal(out[:, 1], b) and torch.equal(out[:, 2], c)
+
+
+def test_layernorm_bwd_h4096_and_accumulate():
+    from tony_b200.ops import _lib
+    from tony_b200.ops import functional as F
+
+    rows, H = 300, 4096
+    x, dy = _rand(rows, H, scale=2.0), _rand(rows, H)
+    g = (_rand(H, scale=0.2).float() + 1).to(torch.bfloat16)
+    xr, gr = x.float().requires_grad_(True), g.float().requires_grad_(True)
+    br = torch.zeros(H, device=DEV, requires_grad=True)
+    torch.nn.functional.layer_norm(xr, (H,), gr, br, 1e-5).backward(dy.float())
+    mean = x.float().mean(1)
+    rstd = (x.float().var(1, unbiased=False) + 1e-5).rsqrt()
+    dx = torch.empty_like(x)
+    dg0, db0 = _rand(H), _rand(H)
+    dg, db = dg0.clone(), db0.clone()
+    lib = _lib.lib()
+    nb = int(lib.tony_layernorm_bwd_scratch_bytes(H))
+    scratch = F.workspace("ln_bwd", nb, x.device)
+    _lib.check(lib.tony_layernorm_bwd(_lib.ptr(dy), _lib.ptr(x), _lib.ptr(g), _lib.ptr(mean), _lib.ptr(rstd),
+                                      _lib.ptr(dx), _lib.ptr(dg), _lib.ptr(db), rows, H, _lib.ptr(scratch), nb, 1,
+                                      _lib.cur_stream()), "ln_bwd")
+    _close(dx, xr.grad)
+    _close(dg, gr.grad + dg0.float())
+    _close(db, br.grad + db0.float())

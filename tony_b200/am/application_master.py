@@ -78,9 +78,16 @@ class ApplicationMaster:
         self.started_ms = int(time.time() * 1000)
         self.submit_time = float(os.environ.get("TONY_B200_SUBMIT_TIME", "0") or 0) or time.time()
         self.host = U.local_hostname()
+        self.timeline: List[dict] = []   # (event, seconds since submit) for submit-to-first-step analysis
         self.rm: Optional[LocalResourceManager] = None
         self.hb: Optional[LivelinessMonitor] = None
         self.events: Optional[EventHandler] = None
+
+    def mark(self, event: str, **extra) -> None:
+        """Launcher timeline: monotonic milestones relative to the client's submit time."""
+        row = {"event": event, "t_ms": round(1000.0 * (time.time() - self.submit_time), 1)}
+        row.update(extra)
+        self.timeline.append(row)
 
     # ================================================================== init / prepare
     def init(self) -> bool:
@@ -107,6 +114,7 @@ class ApplicationMaster:
         return True
 
     def prepare(self) -> None:
+        self.mark("am_started")
         self.app_rpc = RpcServer(self, APPLICATION_RPC_METHODS, self.secret).start()
         self.metrics_rpc = RpcServer(self, METRICS_RPC_METHODS, self.secret).start()
         self.container_env[K.AM_HOST] = self.host
@@ -164,6 +172,9 @@ class ApplicationMaster:
                 session.registered.add(worker)
                 self.hb.register(worker)
                 log(f"registered {worker} at {spec} ({session.num_registered()}/{session.num_expected_tasks})")
+                self.mark("task_registered", task=worker)
+                if session.num_registered() == session.num_expected_tasks:
+                    self.mark("gang_barrier_open")
                 self._kill_chief_worker_if_testing(worker)
                 self.lock.notify_all()
             while True:
@@ -223,6 +234,8 @@ class ApplicationMaster:
         with self.lock:
             if taskId not in self.first_step:
                 self.first_step[taskId] = float(timestamp)
+                self.timeline.append({"event": "first_step", "task": taskId,
+                                      "t_ms": round(1000.0 * (timestamp - self.submit_time), 1)})
                 log(f"first step of {taskId}: {1000.0 * (timestamp - self.submit_time):.0f} ms after submit")
         return None
 
@@ -295,6 +308,7 @@ class ApplicationMaster:
         with self.lock:
             task.status = TaskStatus.RUNNING
             log(f"launched {task.id} in {container.container_id} gpus={container.gpu_ids}")
+            self.mark("task_launched", task=task.id)
             self.events.emit(ev.task_started(task.job_name, task.index, container.host, container.container_id))
             self.lock.notify_all()
 
@@ -551,7 +565,8 @@ class ApplicationMaster:
             self.events.stop(self.final_status)
         with open(os.path.join(self.app_dir, "final_status.json.tmp"), "w") as f:
             json.dump({"status": self.final_status, "message": message, "sessionId": self.session_id,
-                       "firstStep": self.first_step, "submitTime": self.submit_time}, f)
+                       "firstStep": self.first_step, "submitTime": self.submit_time,
+                       "timeline": self.timeline}, f)
         os.replace(os.path.join(self.app_dir, "final_status.json.tmp"),
                    os.path.join(self.app_dir, "final_status.json"))
         # wait for the client's finishApplication so it can read final task states
@@ -567,6 +582,11 @@ class ApplicationMaster:
         for srv in ("app_rpc", "metrics_rpc"):
             if hasattr(self, srv):
                 getattr(self, srv).stop()
+        try:
+            with open(os.path.join(self.app_dir, "timeline.json"), "w") as f:
+                json.dump(self.timeline, f, indent=1)
+        except OSError:
+            pass
         log(f"application finished: {self.final_status} ({message})")
 
 

@@ -34,6 +34,7 @@ SOURCES = [
     "colsum.cu",
     "optim.cu",
     "embedding.cu",
+    "symm_vmm.cu",
 ]
 
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]

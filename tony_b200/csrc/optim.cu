@@ -222,6 +222,100 @@ fused_reduce_optim_kernel(OptHyper h, FusedArgs a) {
     }
 }
 
+// ---- NVLS variant ---------------------------------------------------------------------------
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc_addr) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(mc_addr)
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st_bf16x8(void* mc_addr, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "r"(v.x),
+                 "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ void multimem_red_add_release(unsigned int* mc_addr, unsigned int v) {
+    asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(mc_addr), "r"(v) : "memory");
+}
+
+struct NvlsArgs {
+    tony_nvls_comm comm;
+    size_t begin, count, state_offset;
+    float* master;
+    float* s1;
+    float* s2;
+    const unsigned char* wd_mask;
+    int broadcast;
+    uint32_t target;  // world * call_index: every rank added 1 per call to the multicast flag
+    unsigned long long timeout_ns;
+};
+
+constexpr int NVLS_FLAG_A = 40, NVLS_FLAG_B = 41;  // words of the flag block used by this path
+
+__global__ void __launch_bounds__(512)
+fused_reduce_optim_nvls_kernel(OptHyper h, NvlsArgs a) {
+    __shared__ int sh_flag;
+    const int world = a.comm.world, rank = a.comm.rank;
+    const int tid = threadIdx.x;
+    // ---- A: all ranks' buckets complete: one multicast add, everyone polls its own copy ----
+    if (tid == 0) {
+        sh_flag = 1;
+        if (blockIdx.x == 0) {
+            __threadfence_system();
+            multimem_red_add_release(a.comm.flags_mc + NVLS_FLAG_A, 1u);
+        }
+        if (!wait_flag_sys(a.comm.flags_local + NVLS_FLAG_A, a.target, a.timeout_ns)) {
+            *a.comm.status = TONY_ERR_TIMEOUT;
+            sh_flag = 0;
+        }
+    }
+    __syncthreads();
+    if (!sh_flag) return;
+
+    // ---- B: in-switch reduction of my shard, optimizer, multicast store of the new weights ---
+    const size_t chunk = a.count / world;
+    const size_t my_begin = a.begin + static_cast<size_t>(rank) * chunk;
+    const size_t nvec = chunk / 8;
+    const __nv_bfloat16* gmc = static_cast<const __nv_bfloat16*>(a.comm.grad_mc);
+    for (size_t v = blockIdx.x * static_cast<size_t>(blockDim.x) + tid; v < nvec;
+         v += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const size_t idx = my_begin + v * 8;
+        const uint4 sum = multimem_ld_reduce_bf16x8(gmc + idx);
+        float g[8];
+        unpack8f(sum, g);
+        uint4 w;
+        if (h.optimizer >= 0) {
+            const float wd = (a.wd_mask == nullptr || a.wd_mask[idx >> 8]) ? h.weight_decay : 0.f;
+            w = optim_update8(h, a.master, a.s1, a.s2, a.state_offset + v * 8, g, wd);
+        } else {
+            w.x = pack_bf16x2(g[0] * h.grad_scale, g[1] * h.grad_scale);
+            w.y = pack_bf16x2(g[2] * h.grad_scale, g[3] * h.grad_scale);
+            w.z = pack_bf16x2(g[4] * h.grad_scale, g[5] * h.grad_scale);
+            w.w = pack_bf16x2(g[6] * h.grad_scale, g[7] * h.grad_scale);
+        }
+        if (a.broadcast)
+            multimem_st_bf16x8(static_cast<__nv_bfloat16*>(a.comm.param_mc) + idx, w);
+        else
+            st_global_v4(static_cast<__nv_bfloat16*>(a.comm.param_local) + idx, w);
+    }
+
+    // ---- C: last CTA out publishes "done" and waits for every rank's "done" ------------------
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned int prev = atomicAdd(a.comm.counter, 1u);
+        if (prev == gridDim.x - 1) {
+            __threadfence_system();
+            *a.comm.counter = 0;
+            multimem_red_add_release(a.comm.flags_mc + NVLS_FLAG_B, 1u);
+            if (!wait_flag_sys(a.comm.flags_local + NVLS_FLAG_B, a.target, a.timeout_ns))
+                *a.comm.status = TONY_ERR_TIMEOUT;
+        }
+    }
+}
+
 __global__ void symm_barrier_kernel(FusedArgs a) {
     __threadfence_system();
     arrive_and_wait_all(a, 0, threadIdx.x);
@@ -403,6 +497,50 @@ extern "C" int tony_symm_barrier(const tony_fused_comm* comm, unsigned int epoch
     a.ar_scale = 1.f;
     a.timeout_ns = comm_timeout_ns();
     symm_barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(a);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}
+
+
+extern "C" int tony_fused_reduce_optim_nvls(const tony_nvls_comm* comm, size_t begin, size_t count,
+                                            float* master, float* state1, float* state2,
+                                            size_t state_offset, int optimizer, float lr,
+                                            float beta1_or_momentum, float beta2, float eps,
+                                            float weight_decay, float bc1, float bc2, float grad_scale,
+                                            const unsigned char* wd_mask, int broadcast,
+                                            unsigned int call_index, int num_ctas, void* stream) {
+    if (!comm || comm->world < 2 || comm->world > TONY_MAX_RANKS || comm->rank < 0 || comm->rank >= comm->world ||
+        !comm->grad_mc || !comm->param_mc || !comm->param_local || !comm->flags_mc || !comm->flags_local ||
+        !comm->counter || !comm->status || call_index == 0) {
+        set_last_error("tony_fused_reduce_optim_nvls", "bad comm descriptor (needs world >= 2 and multicast mappings)");
+        return TONY_ERR_INVALID;
+    }
+    if (count == 0 || (count % (static_cast<size_t>(comm->world) * 8)) != 0 || (begin % 8) != 0 ||
+        (state_offset % 8) != 0) {
+        set_last_error("tony_fused_reduce_optim_nvls", "count must be a multiple of world*8; begin/state_offset of 8");
+        return TONY_ERR_INVALID;
+    }
+    if (optimizer >= 0 && (!master || !state1 || (optimizer == TONY_OPT_ADAMW && !state2))) return TONY_ERR_INVALID;
+    NvlsArgs a;
+    a.comm = *comm;
+    a.begin = begin;
+    a.count = count;
+    a.state_offset = state_offset;
+    a.master = master;
+    a.s1 = state1;
+    a.s2 = state2;
+    a.wd_mask = wd_mask;
+    a.broadcast = broadcast;
+    a.target = static_cast<uint32_t>(comm->world) * call_index;
+    a.timeout_ns = comm_timeout_ns();
+    const int threads = 512;
+    const size_t nvec = count / comm->world / 8;
+    int grid = num_ctas > 0 ? num_ctas : 32;
+    grid = static_cast<int>(std::min<size_t>(grid, std::max<size_t>(1, (nvec + threads - 1) / threads)));
+    grid = std::min(grid, device_sm_count());
+    fused_reduce_optim_nvls_kernel<<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+        make_hyper(optimizer, lr, beta1_or_momentum, beta2, eps, weight_decay, bc1, bc2, grad_scale, 0), a);
     count_launch();
     TONY_CUDA_CHECK(cudaGetLastError());
     return TONY_OK;

@@ -50,6 +50,22 @@ class KernelError(RuntimeError):
     pass
 
 
+class NvlsComm(Structure):
+    """Mirror of ``tony_nvls_comm``."""
+
+    _fields_ = [
+        ("rank", c_int),
+        ("world", c_int),
+        ("grad_mc", c_void_p),
+        ("param_mc", c_void_p),
+        ("param_local", c_void_p),
+        ("flags_mc", c_void_p),
+        ("flags_local", c_void_p),
+        ("counter", c_void_p),
+        ("status", c_void_p),
+    ]
+
+
 class FusedComm(Structure):
     """Mirror of ``tony_fused_comm``."""
 
@@ -108,6 +124,20 @@ def _declare(lib) -> None:
     lib.tony_symm_barrier.argtypes = [POINTER(FusedComm), c_uint, vp]
     lib.tony_allgather_gemm_bf16.argtypes = [vp, POINTER(c_void_p), vp, vp, c_int, c_int, c_int,
                                              c_int, c_int, c_uint, vp, vp, vp, c_uint, c_int, vp]
+    ull_p = POINTER(c_ulonglong)
+    lib.tony_nvls_supported.restype = c_int
+    lib.tony_vmm_granularity.argtypes = [c_int, c_size_t, POINTER(c_size_t)]
+    lib.tony_vmm_alloc.argtypes = [c_size_t, ull_p, POINTER(c_int)]
+    lib.tony_vmm_import.argtypes = [c_int, ull_p]
+    lib.tony_vmm_map.argtypes = [c_ulonglong, c_size_t, POINTER(c_void_p)]
+    lib.tony_vmm_unmap.argtypes = [vp, c_size_t]
+    lib.tony_vmm_release.argtypes = [c_ulonglong]
+    lib.tony_mc_create.argtypes = [c_size_t, c_int, ull_p, POINTER(c_int)]
+    lib.tony_mc_add_device.argtypes = [c_ulonglong]
+    lib.tony_mc_bind.argtypes = [c_ulonglong, c_ulonglong, c_size_t]
+    lib.tony_fused_reduce_optim_nvls.argtypes = [POINTER(NvlsComm), c_size_t, c_size_t, vp, vp, vp, c_size_t,
+                                                 c_int, c_float, c_float, c_float, c_float, c_float, c_float,
+                                                 c_float, c_float, vp, c_int, c_uint, c_int, vp]
     lib.tony_pack3_rows.argtypes = [vp, vp, vp, c_longlong, c_longlong, c_longlong, vp, c_int, c_int, vp]
 
 

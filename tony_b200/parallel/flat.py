@@ -271,6 +271,16 @@ class FusedOptimizer:
         else:
             b1, b2, bc1, bc2 = self.momentum, 0.0, 1.0, 1.0
         comm = st.comm
+        if comm.nvls is not None:
+            # in-switch reduction (multimem.ld_reduce) + multicast weight store
+            check(_lib.lib().tony_fused_reduce_optim_nvls(
+                ctypes.byref(comm.nvls), b.begin, b.count, _lib.ptr(self.master), _lib.ptr(self.state1),
+                _lib.ptr(self.state2), b.begin // st.world, self.kind, self.lr, b1, b2, self.eps,
+                self.weight_decay, bc1, bc2, self.grad_scale / st.world, _lib.ptr(st.wd_mask),
+                int(self.broadcast and not b.ps_sharded), comm.next_nvls_call(), num_ctas,
+                ctypes.c_void_p(stream.cuda_stream)), "tony_fused_reduce_optim_nvls")
+            b.launched = True
+            return
         check(_lib.lib().tony_fused_reduce_optim(
             ctypes.byref(comm.c), b.begin, b.count, _lib.ptr(self.master), _lib.ptr(self.state1),
             _lib.ptr(self.state2), b.begin // st.world, self.kind, self.lr, b1, b2, self.eps,

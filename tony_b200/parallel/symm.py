@@ -11,12 +11,17 @@ The reference has no data plane; this replaces what NCCL would
 from __future__ import annotations
 
 import ctypes
+import os
+import socket
+import tempfile
+import threading
+import uuid
 from typing import List, Optional
 
 import torch
 
 from ..ops import _lib
-from ..ops._lib import MAX_RANKS, FusedComm, KernelError, check
+from ..ops._lib import MAX_RANKS, FusedComm, KernelError, NvlsComm, check
 
 _DTYPE_STR = {torch.bfloat16: None, torch.float32: "<f4", torch.uint8: "|u1", torch.int32: "<i4",
               torch.uint16: "<u2", torch.int16: "<i2"}
@@ -38,8 +43,149 @@ def tensor_from_ptr(ptr: int, nbytes: int, dtype: torch.dtype, device, owner=Non
     return raw.view(dtype)
 
 
+def symm_mode() -> str:
+    """``ipc`` (cudaMalloc + CUDA IPC) or ``vmm`` (cuMemCreate + fd exchange + NVLS multicast).
+    TONY_B200_SYMM=ipc|vmm|auto; auto picks vmm when the device supports multicast."""
+    mode = os.environ.get("TONY_B200_SYMM", "auto").lower()
+    if mode == "auto":
+        try:
+            mode = "vmm" if _lib.lib().tony_nvls_supported() else "ipc"
+        except Exception:  # noqa: BLE001
+            mode = "ipc"
+    return mode
+
+
+def _exchange_fds(my_fd: Optional[int], rank: int, world: int, group, only_from: Optional[int] = None):
+    """Pass POSIX fds between the ranks of one node over unix sockets (SCM_RIGHTS).
+    Returns ``fds[r]`` = a duplicate of rank r's fd valid in this process (own slot = my_fd).
+    With ``only_from=k`` only rank k serves its fd."""
+    import torch.distributed as dist
+
+    token = [uuid.uuid4().hex if rank == 0 else None]
+    dist.broadcast_object_list(token, src=0, group=group)
+    base = os.path.join(tempfile.gettempdir(), f"tony_symm_{token[0]}")
+    serving = my_fd is not None and (only_from is None or only_from == rank)
+    srv = None
+    if serving:
+        srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        srv.bind(f"{base}.{rank}")
+        srv.listen(world)
+    dist.barrier(group=group)
+
+    def serve():
+        for _ in range(world - 1):
+            conn, _ = srv.accept()
+            socket.send_fds(conn, [b"f"], [my_fd])
+            conn.close()
+
+    t = None
+    if serving and world > 1:
+        t = threading.Thread(target=serve, daemon=True)
+        t.start()
+    fds = [-1] * world
+    fds[rank] = my_fd if my_fd is not None else -1
+    sources = range(world) if only_from is None else [only_from]
+    for r in sources:
+        if r == rank:
+            continue
+        c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        c.connect(f"{base}.{r}")
+        _, got, _, _ = socket.recv_fds(c, 16, 1)
+        c.close()
+        fds[r] = got[0]
+    if t is not None:
+        t.join()
+    dist.barrier(group=group)
+    if srv is not None:
+        srv.close()
+        try:
+            os.unlink(f"{base}.{rank}")
+        except OSError:
+            pass
+    return fds
+
+
+class VmmBuffer:
+    """Symmetric allocation on CUDA VMM: unicast mapping of every rank's copy + one NVLS
+    multicast mapping (``mc_ptr``) of all copies.  Same attributes as :class:`SymmBuffer`."""
+
+    def __init__(self, nbytes: int, dtype: torch.dtype, device, group=None):
+        import torch.distributed as dist
+
+        self.device = torch.device(device)
+        self.dtype = dtype
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        lib = _lib.lib()
+        with torch.cuda.device(self.device):
+            padded = ctypes.c_size_t()
+            check(lib.tony_vmm_granularity(self.world, int(nbytes), ctypes.byref(padded)), "tony_vmm_granularity")
+            self.padded = int(padded.value)
+            self.nbytes = int(nbytes)
+            h, fd = ctypes.c_ulonglong(), ctypes.c_int()
+            check(lib.tony_vmm_alloc(self.padded, ctypes.byref(h), ctypes.byref(fd)), "tony_vmm_alloc")
+            self.handle = int(h.value)
+            fds = _exchange_fds(int(fd.value), self.rank, self.world, group)
+            self.peer_ptrs: List[int] = [0] * self.world
+            self._handles = {}
+            for r in range(self.world):
+                hr = self.handle
+                if r != self.rank:
+                    hh = ctypes.c_ulonglong()
+                    check(lib.tony_vmm_import(fds[r], ctypes.byref(hh)), f"tony_vmm_import(rank {r})")
+                    hr = int(hh.value)
+                    os.close(fds[r])
+                    self._handles[r] = hr
+                p = ctypes.c_void_p()
+                check(lib.tony_vmm_map(hr, self.padded, ctypes.byref(p)), f"tony_vmm_map(rank {r})")
+                self.peer_ptrs[r] = int(p.value)
+            os.close(int(fd.value))
+            self.ptr = self.peer_ptrs[self.rank]
+            # multicast object: created by rank 0, imported by the others
+            mch, mcfd = ctypes.c_ulonglong(), ctypes.c_int(-1)
+            if self.rank == 0:
+                check(lib.tony_mc_create(self.padded, self.world, ctypes.byref(mch), ctypes.byref(mcfd)), "tony_mc_create")
+            mfds = _exchange_fds(int(mcfd.value) if self.rank == 0 else None, self.rank, self.world, group, only_from=0)
+            if self.rank != 0:
+                check(lib.tony_vmm_import(mfds[0], ctypes.byref(mch)), "tony_vmm_import(multicast)")
+                os.close(mfds[0])
+            else:
+                os.close(int(mcfd.value))
+            self.mc_handle = int(mch.value)
+            check(lib.tony_mc_add_device(self.mc_handle), "tony_mc_add_device")
+            dist.barrier(group=group)
+            check(lib.tony_mc_bind(self.mc_handle, self.handle, self.padded), "tony_mc_bind")
+            dist.barrier(group=group)
+            q = ctypes.c_void_p()
+            check(lib.tony_vmm_map(self.mc_handle, self.padded, ctypes.byref(q)), "tony_vmm_map(multicast)")
+            self.mc_ptr = int(q.value)
+        self.local = tensor_from_ptr(self.ptr, self.nbytes, dtype, self.device, owner=self)
+        self.local.zero_()
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=group)
+
+    def peer_tensor(self, r: int) -> torch.Tensor:
+        return tensor_from_ptr(self.peer_ptrs[r], self.nbytes, self.dtype, self.device, owner=self)
+
+    def close(self):
+        lib = _lib.lib()
+        if getattr(self, "mc_ptr", 0):
+            lib.tony_vmm_unmap(ctypes.c_void_p(self.mc_ptr), self.padded)
+            self.mc_ptr = 0
+        for p in getattr(self, "peer_ptrs", []):
+            if p:
+                lib.tony_vmm_unmap(ctypes.c_void_p(p), self.padded)
+        self.peer_ptrs = []
+        for h in list(getattr(self, "_handles", {}).values()) + [getattr(self, "mc_handle", 0), getattr(self, "handle", 0)]:
+            if h:
+                lib.tony_vmm_release(h)
+        self._handles, self.mc_handle, self.handle = {}, 0, 0
+
+
 class SymmBuffer:
     """One symmetric allocation: ``local`` tensor + ``peer_ptrs[r]`` for every rank."""
+
+    mc_ptr = 0  # the IPC path has no multicast mapping
 
     def __init__(self, nbytes: int, dtype: torch.dtype, device, group=None):
         import torch.distributed as dist
@@ -103,10 +249,13 @@ class SymmComm:
         self.rank = dist.get_rank(group) if self.world > 1 else 0
         self.numel = int(numel)
         self.epoch = 0
+        self.nvls = None
+        self.nvls_calls = 0
         if self.world > 1:
-            self.grad_buf = SymmBuffer(self.numel * 2, torch.bfloat16, device, group)
-            self.param_buf = SymmBuffer(self.numel * 2, torch.bfloat16, device, group)
-            self.flag_buf = SymmBuffer(self.FLAG_BYTES, torch.int32, device, group)
+            Buf = VmmBuffer if symm_mode() == "vmm" else SymmBuffer
+            self.grad_buf = Buf(self.numel * 2, torch.bfloat16, device, group)
+            self.param_buf = Buf(self.numel * 2, torch.bfloat16, device, group)
+            self.flag_buf = Buf(self.FLAG_BYTES, torch.int32, device, group)
             self.grad = self.grad_buf.local
             self.param = self.param_buf.local
             flags_local = self.flag_buf.ptr
@@ -128,6 +277,13 @@ class SymmComm:
         c.status = flags_local + 2 * MAX_RANKS * 4 + 64
         self.c = c
         self._status_view = tensor_from_ptr(int(c.status), 4, torch.int32, self.device, owner=self)
+        if self.world > 1 and self.grad_buf.mc_ptr and os.environ.get("TONY_B200_NVLS", "1") != "0":
+            n = NvlsComm()
+            n.rank, n.world = self.rank, self.world
+            n.grad_mc, n.param_mc, n.param_local = self.grad_buf.mc_ptr, self.param_buf.mc_ptr, self.param_buf.ptr
+            n.flags_mc, n.flags_local = self.flag_buf.mc_ptr, self.flag_buf.ptr
+            n.counter, n.status = c.counter, c.status
+            self.nvls = n
         if self.world > 1:
             dist.barrier(group=group)  # every rank has mapped every peer before first use
 
@@ -147,9 +303,18 @@ class SymmComm:
         s = ctypes.c_void_p(stream.cuda_stream) if stream is not None else _lib.cur_stream()
         check(_lib.lib().tony_symm_barrier(ctypes.byref(self.c), self.next_epoch(), s), "tony_symm_barrier")
 
+    def next_nvls_call(self) -> int:
+        self.nvls_calls += 1
+        return self.nvls_calls
+
     def allreduce_(self, begin: int, count: int, scale: float = 1.0, num_ctas: int = 0, stream=None):
         """param[begin:begin+count] on every rank = scale * sum_r grad_r[begin:begin+count]."""
         s = ctypes.c_void_p(stream.cuda_stream) if stream is not None else _lib.cur_stream()
+        if self.nvls is not None:
+            check(_lib.lib().tony_fused_reduce_optim_nvls(
+                ctypes.byref(self.nvls), begin, count, None, None, None, 0, -1, 0.0, 0.0, 0.0, 0.0, 0.0, 1.0, 1.0,
+                scale, None, 1, self.next_nvls_call(), num_ctas, s), "tony_fused_reduce_optim_nvls(allreduce)")
+            return
         check(_lib.lib().tony_symm_allreduce_bf16(ctypes.byref(self.c), begin, count, scale,
                                                   self.next_epoch(), num_ctas, s),
               "tony_symm_allreduce_bf16")

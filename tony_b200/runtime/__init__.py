@@ -112,9 +112,16 @@ class Trainer:
 
     def step_device(self, batch_dev) -> "object":
         """One optimisation step on device-resident inputs; returns the loss tensor (no sync)."""
+        nvtx = self.torch.cuda.nvtx
+        nvtx.range_push("tony.forward")
         loss = self.model(**batch_dev)
+        nvtx.range_pop()
+        nvtx.range_push("tony.backward+fused_reduce_optim")
         loss.backward()
+        nvtx.range_pop()
+        nvtx.range_push("tony.optimizer_join")
         self.opt.step()
+        nvtx.range_pop()
         self.steps += 1
         return loss
 
@@ -122,6 +129,10 @@ class Trainer:
         """The end-to-end user call: pinned host batch in, Python float loss out."""
         loss = self.step_device(self.to_device(batch_cpu))
         value = float(loss.item())  # D2H read of the step's result; also the host sync point
+        if self.store.world > 1:
+            # GPU-side hang detection: a fused collective that gave up waiting for a dead peer
+            # set the status word; fail the task so the launcher's failure policy takes over
+            self.store.comm.check_status()
         if self.steps == 1:
             mark_first_step()
         return value
