@@ -305,3 +305,42 @@ def test_mnist_pytorch_two_workers_gloo(cluster):
     assert client.start() == 0
     assert statuses(client) == {"worker:0": TaskStatus.SUCCEEDED, "worker:1": TaskStatus.SUCCEEDED}
     assert client.submit_to_first_step_ms is not None
+
+
+def _example(cluster, rel, script, extra_conf=()):
+    repo = os.path.dirname(os.path.dirname(SCRIPTS))
+    ex = os.path.join(repo, "examples", rel)
+    client = cluster.new_client()
+    argv = ["--conf_file", os.path.join(ex, "tony.xml"), "--executes", os.path.join(ex, script),
+            "--python_binary_path", PY, "--conf", "tony.am.wait-client-signal-stop-timeout-sec=2"]
+    for c in extra_conf:
+        argv += ["--conf", c]
+    assert client.init(argv)
+    return client.start(), client
+
+
+def test_example_tensorflow_ps_worker(cluster):
+    rc, client = _example(cluster, "mnist-tensorflow", "mnist_ps_worker.py")
+    assert rc == 0
+    st = statuses(client)
+    assert st["worker:0"] == st["worker:1"] == TaskStatus.SUCCEEDED and st["ps:0"] == TaskStatus.FINISHED
+
+
+def test_example_mxnet_dmlc_roles(cluster):
+    rc, client = _example(cluster, "linearregression-mxnet", "dmlc_linear_regression.py")
+    assert rc == 0
+
+
+def test_example_custom_job_types_head_worker(cluster):
+    rc, client = _example(cluster, "ray-on-tony", "discovery.py")
+    assert rc == 0
+    assert statuses(client)["head:0"] == TaskStatus.SUCCEEDED
+
+
+def test_timeline_is_recorded(cluster):
+    rc, client = run(cluster, "exit_0.py", ["tony.worker.instances=2"])
+    assert rc == 0
+    tl = json.load(open(os.path.join(client.app_dir, "timeline.json")))
+    events = [e["event"] for e in tl]
+    assert events[0] == "am_started" and "gang_barrier_open" in events and events.count("task_registered") == 2
+    assert all(a["t_ms"] <= b["t_ms"] for a, b in zip(tl, tl[1:]))

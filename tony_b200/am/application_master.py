@@ -296,6 +296,7 @@ class ApplicationMaster:
         try:
             self._localize(task.job_name, container_dir)
             cmd = [sys.executable, "-m", "tony_b200.executor.task_executor"]
+            docker_util.write_env_file(self.conf, env, container_dir)
             cmd = docker_util.wrap_command(self.conf, task.job_name, cmd, container, container_dir)
             self.rm.start_container(container, cmd, env, container_dir)
         except Exception as exc:  # noqa: BLE001

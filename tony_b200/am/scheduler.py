@@ -57,9 +57,7 @@ class TaskScheduler:
 
     def _schedule(self, req: JobContainerRequest) -> None:
         self.scheduled.append(req.job_name)
-        # the gang barrier only counts tracked types that have been released so far
-        if self.session.is_tracked(req.job_name) or req.job_name in self.session.untracked:
-            pass
+        # the gang barrier only counts job types the DAG has released so far
         self.session.num_expected_tasks += req.num_instances
         self.request_containers(req)
 

@@ -70,3 +70,36 @@ def is_port_available(port: int) -> bool:
 
 def reserve(reuse: bool) -> ServerPort:
     return ReusablePort.create() if reuse else EphemeralPort.create()
+
+
+def main(argv=None) -> int:
+    """``python -m tony_b200.executor.ports -p PORT [-d SECONDS]``: hold PORT with SO_REUSEPORT and
+    create ``<PORT>___PORT___`` in the working directory once it is held — the contract of the
+    reference's reserve_reusable_port.py (resources/reserve_reusable_port.py:52-89) for callers
+    that want the reservation to live in a separate process."""
+    import argparse
+    import os
+    import time
+
+    ap = argparse.ArgumentParser()
+    ap.add_argument("-p", "--port", type=int, required=True)
+    ap.add_argument("-d", "--duration", type=float, default=3600.0)
+    a = ap.parse_args(argv)
+    port = ReusablePort.create(a.port)
+    marker = f"{port.port}___PORT___"
+    open(marker, "w").close()
+    try:
+        time.sleep(a.duration)
+    except KeyboardInterrupt:
+        pass
+    finally:
+        port.close()
+        try:
+            os.unlink(marker)
+        except OSError:
+            pass
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

@@ -364,7 +364,24 @@ _TASK = {"tensorflow": TFTaskAdapter, "pytorch": PyTorchTaskAdapter, "mxnet": MX
          "horovod": HorovodTaskAdapter, "standalone": StandaloneTaskAdapter}
 
 
+def register_framework(name: str, am_adapter_cls, task_adapter_cls) -> None:
+    """Plug in a runtime for ``tony.application.framework=<name>`` (the reference discovers
+    AbstractFrameworkRuntime implementations through java.util.ServiceLoader:
+    FrameworkRuntimeProvider.java:29-46).  Also loaded from the entry-point style env var
+    ``TONY_B200_FRAMEWORK_PLUGINS=module1,module2``: each module is imported and may call this."""
+    _AM[name.lower()] = am_adapter_cls
+    _TASK[name.lower()] = task_adapter_cls
+
+
+def _load_plugins() -> None:
+    import importlib
+
+    for mod in filter(None, os.environ.get("TONY_B200_FRAMEWORK_PLUGINS", "").split(",")):
+        importlib.import_module(mod.strip())
+
+
 def get_am_adapter(framework: str) -> AMAdapter:
+    _load_plugins()
     try:
         return _AM[framework.lower()]()
     except KeyError:
@@ -372,6 +389,7 @@ def get_am_adapter(framework: str) -> AMAdapter:
 
 
 def get_task_adapter(framework: str, executor) -> TaskAdapter:
+    _load_plugins()
     try:
         return _TASK[framework.lower()](executor)
     except KeyError:

@@ -56,3 +56,16 @@ def wrap_command(conf: TonyConfiguration, job: str, cmd: List[str], container, c
             out += ["-v", m if len(parts) >= 2 else f"{m}:{m}"]
     out += ["--env-file", os.path.join(container_dir, "docker.env"), image] + cmd
     return out
+
+
+def write_env_file(conf: TonyConfiguration, env: Dict[str, str], container_dir: str) -> Optional[str]:
+    """``docker run --env-file`` input: the task's environment contract, one KEY=VALUE per line."""
+    if not conf.get_bool(K.DOCKER_ENABLED, False):
+        return None
+    os.makedirs(container_dir, exist_ok=True)
+    path = os.path.join(container_dir, "docker.env")
+    with open(path, "w") as f:
+        for k, v in env.items():
+            if "\n" not in v:
+                f.write(f"{k}={v}\n")
+    return path
