@@ -111,6 +111,20 @@ int tony_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out,
 int tony_colsum_bf16_static(const void* x, int rows, int cols, long long ld, void* out,
                             int accumulate, void* stream);
 
+/* ---- fused attention on a packed QKV activation (tcgen05 + TMA, head_dim 64) ------------ */
+/* qkv: [batch*seq, 3, heads, 64] bf16 (the fused QKV projection's output, read in place);
+ * out: [batch*seq, heads*64] bf16; lse: [batch*heads, seq] fp32 log2-sum-exp saved for backward.
+ * seq must be a multiple of 128.  Replaces the library attention core (cuDNN / flash kernels
+ * behind scaled_dot_product_attention) of the stock PyTorch jobs the reference launches; no
+ * reference counterpart. */
+int tony_attention_fwd_bf16(const void* qkv, void* out, float* lse, int batch, int seq, int heads,
+                            int head_dim, int causal, float scale, void* stream);
+/* dqkv: packed gradient [batch*seq, 3, heads, 64], every element written (no atomics, no
+ * zero-fill); delta: [batch*heads, seq] fp32 scratch.  Three launches: delta, dq, dk+dv. */
+int tony_attention_bwd_bf16(const void* qkv, const void* out, const void* dout, const float* lse,
+                            float* delta, void* dqkv, int batch, int seq, int heads, int head_dim,
+                            int causal, float scale, void* stream);
+
 /* ---- packing ------------------------------------------------------------------------- */
 /* out[r, 0..2, :] = (a[r,:], b[r,:], c[r,:]): interleave the dq/dk/dv of a library attention
  * backward into the packed gradient of a fused QKV projection in one launch (strides in

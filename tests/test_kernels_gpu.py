@@ -1,6 +1,10 @@
 """Numerics of every sm_100a kernel against a plain PyTorch fp32 reference (SURVEY.md §4 tier 4)."""
+import math
+
 import pytest
 import torch
+
+from tony_b200.ops import functional as F
 
 pytestmark = pytest.mark.gpu
 
@@ -299,3 +303,54 @@ def test_layernorm_bwd_h4096_and_accumulate():
     _close(dx, xr.grad)
     _close(dg, gr.grad + dg0.float())
     _close(db, br.grad + db0.float())
+
+
+def _attention_reference(qkv, causal):
+    q, k, v = (qkv[:, :, i].transpose(1, 2).float() for i in range(3))       # [B, nh, S, hd]
+    s = q @ k.transpose(-1, -2) / math.sqrt(q.shape[-1])
+    if causal:
+        S = s.shape[-1]
+        s = s.masked_fill(torch.triu(torch.ones(S, S, dtype=torch.bool, device=s.device), 1), float("-inf"))
+    o = torch.softmax(s, -1) @ v
+    return o.transpose(1, 2).reshape(qkv.shape[0], qkv.shape[1], -1)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("B,S,nh,gain", [(2, 256, 4, 1.0), (1, 512, 2, 1.0), (1, 384, 3, 6.0)])
+def test_fused_attention_matches_fp32_reference(B, S, nh, gain, causal):
+    """tcgen05 attention forward + backward vs. plain fp32 softmax(QK^T)V and its autograd.
+    ``gain`` 6 makes the row max grow by far more than 2^8 between key blocks, which exercises
+    the lazy rescale of the TMEM-resident output."""
+    torch.manual_seed(7)
+    dev = torch.device("cuda")
+    qkv = (torch.randn(B, S, 3, nh, 64, device=dev) * gain).to(torch.bfloat16)
+    if gain > 1:
+        qkv[:, :, 2] = qkv[:, :, 2] / gain        # keep V O(1)
+        # put the largest keys late in the sequence so every row's max keeps moving
+        qkv[:, :, 1] = qkv[:, :, 1] * torch.linspace(0.2, 1.0, S, device=dev).view(1, S, 1, 1).to(torch.bfloat16)
+    a = qkv.clone().requires_grad_()
+    b = qkv.float().requires_grad_()
+    out = F.packed_attention(a, causal)
+    ref = _attention_reference(b, causal)
+    assert out.shape == ref.shape
+    err = (out.float() - ref).abs().max().item()
+    assert err < 3e-2 * max(1.0, ref.abs().max().item()), err
+    g = torch.randn_like(ref)
+    out.backward(g.to(torch.bfloat16))
+    ref.backward(g)
+    for i, name in enumerate(("dq", "dk", "dv")):
+        got, want = a.grad[:, :, i].float(), b.grad[:, :, i]
+        scale = want.abs().max().item()
+        e = (got - want).abs().max().item()
+        assert e < 4e-2 * scale + 1e-3, (name, e, scale)
+        # the mean error must be far smaller than the worst element (catches a wrong tile)
+        assert (got - want).abs().mean().item() < 6e-3 * scale + 1e-4, name
+
+
+def test_fused_attention_library_switch(monkeypatch):
+    torch.manual_seed(1)
+    qkv = torch.randn(1, 128, 3, 2, 64, device="cuda").to(torch.bfloat16)
+    ours = F.packed_attention(qkv)
+    monkeypatch.setenv("TONY_B200_ATTENTION", "library")
+    lib_out = F.packed_attention(qkv)
+    assert (ours.float() - lib_out.float()).abs().max().item() < 2e-2

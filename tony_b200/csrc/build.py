@@ -35,6 +35,7 @@ SOURCES = [
     "optim.cu",
     "embedding.cu",
     "symm_vmm.cu",
+    "attention.cu",
 ]
 
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]

@@ -770,6 +770,35 @@ int make_operand_tmap(CUtensorMap* map, const void* ptr, int mn_extent, int k_ex
     return TONY_OK;
 }
 
+// Generic 2-D bf16 map with 128-byte swizzle: `inner` is the contiguous dimension.
+int make_tmap_2d_bf16(CUtensorMap* map, const void* ptr, long long inner_extent, long long outer_extent,
+                      long long ld, int box_inner, int box_outer) {
+    static thread_local bool tls_ctx_bound = false;
+    if (!tls_ctx_bound) {
+        cudaFree(nullptr);
+        tls_ctx_bound = true;
+    }
+    PFN_encodeTiled enc = get_encode_fn();
+    if (!enc) {
+        set_last_error("cuTensorMapEncodeTiled", "driver entry point not found");
+        return TONY_ERR_UNSUPPORTED;
+    }
+    cuuint64_t gdim[2] = {static_cast<cuuint64_t>(inner_extent), static_cast<cuuint64_t>(outer_extent)};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
+    cuuint64_t gstride[1] = {static_cast<cuuint64_t>(ld) * 2};
+    cuuint32_t estride[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride,
+                     box, estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[64];
+        snprintf(buf, sizeof(buf), "CUresult %d", static_cast<int>(r));
+        set_last_error("cuTensorMapEncodeTiled", buf);
+        return TONY_ERR_CUDA;
+    }
+    return TONY_OK;
+}
+
 int device_sm_count() {
     static int cached[64] = {0};
     int dev = 0;

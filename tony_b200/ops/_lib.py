@@ -139,6 +139,9 @@ def _declare(lib) -> None:
                                                  c_int, c_float, c_float, c_float, c_float, c_float, c_float,
                                                  c_float, c_float, vp, c_int, c_uint, c_int, vp]
     lib.tony_pack3_rows.argtypes = [vp, vp, vp, c_longlong, c_longlong, c_longlong, vp, c_int, c_int, vp]
+    lib.tony_attention_fwd_bf16.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_float, vp]
+    lib.tony_attention_bwd_bf16.argtypes = [vp, vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int,
+                                            c_float, vp]
 
 
 def lib():

@@ -13,6 +13,8 @@ dense layers in tony-examples/horovod-on-tony/tensorflow2_mnist.py), re-designed
 """
 from __future__ import annotations
 
+import math
+import os
 from typing import Optional
 
 import torch
@@ -490,6 +492,47 @@ class _PackedSdpaFn(torch.autograd.Function):
         return dqkv, None
 
 
+class _FusedAttentionFn(torch.autograd.Function):
+    """tcgen05 attention on the packed ``qkv`` activation (csrc/attention.cu): one forward
+    launch, three backward launches (delta, dq, dk+dv); q/k/v are read in place through a tensor
+    map and dq/dk/dv land directly in the packed gradient of the QKV projection."""
+
+    @staticmethod
+    def forward(ctx, qkv, causal):
+        B, S, _, nh, hd = qkv.shape
+        qkv = qkv.contiguous()
+        out = torch.empty((B, S, nh * hd), dtype=qkv.dtype, device=qkv.device)
+        lse = torch.empty((B * nh, S), dtype=torch.float32, device=qkv.device)
+        scale = 1.0 / math.sqrt(hd)
+        check(_lib.lib().tony_attention_fwd_bf16(ptr(qkv), ptr(out), ptr(lse), B, S, nh, hd, int(causal),
+                                                 scale, cur_stream()), "tony_attention_fwd_bf16")
+        ctx.save_for_backward(qkv, out, lse)
+        ctx.meta = (B, S, nh, hd, int(causal), scale)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, out, lse = ctx.saved_tensors
+        B, S, nh, hd, causal, scale = ctx.meta
+        dout = dout.contiguous()
+        delta = torch.empty_like(lse)
+        dqkv = torch.empty_like(qkv)
+        check(_lib.lib().tony_attention_bwd_bf16(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(delta),
+                                                 ptr(dqkv), B, S, nh, hd, causal, scale, cur_stream()),
+              "tony_attention_bwd_bf16")
+        return dqkv, None
+
+
+def fused_attention_supported(qkv) -> bool:
+    return (qkv.is_cuda and qkv.dtype == torch.bfloat16 and qkv.dim() == 5 and qkv.shape[4] == 64
+            and qkv.shape[1] % 128 == 0)
+
+
 def packed_attention(qkv, causal: bool = False):
-    """``qkv``: ``[B, S, 3, heads, head_dim]`` -> context ``[B, S, heads*head_dim]``."""
+    """``qkv``: ``[B, S, 3, heads, head_dim]`` -> context ``[B, S, heads*head_dim]``.
+
+    head_dim 64 with a sequence length that is a multiple of 128 runs on the tcgen05 kernels of
+    csrc/attention.cu; other shapes (and ``TONY_B200_ATTENTION=library``) use the library core."""
+    if fused_attention_supported(qkv) and os.environ.get("TONY_B200_ATTENTION", "tcgen05") != "library":
+        return _FusedAttentionFn.apply(qkv, causal)
     return _PackedSdpaFn.apply(qkv, causal)
