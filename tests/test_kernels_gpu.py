@@ -5,6 +5,7 @@ import pytest
 import torch
 
 from tony_b200.ops import functional as F
+from tony_b200.ops._lib import launch_count
 
 pytestmark = pytest.mark.gpu
 
@@ -317,10 +318,11 @@ def _attention_reference(qkv, causal):
 
 @pytest.mark.parametrize("causal", [False, True])
 @pytest.mark.parametrize("B,S,nh,gain", [(2, 256, 4, 1.0), (1, 512, 2, 1.0), (1, 384, 3, 6.0)])
-def test_fused_attention_matches_fp32_reference(B, S, nh, gain, causal):
+def test_fused_attention_matches_fp32_reference(B, S, nh, gain, causal, monkeypatch):
     """tcgen05 attention forward + backward vs. plain fp32 softmax(QK^T)V and its autograd.
     ``gain`` 6 makes the row max grow by far more than 2^8 between key blocks, which exercises
     the lazy rescale of the TMEM-resident output."""
+    monkeypatch.setenv("TONY_B200_ATTENTION", "tcgen05")
     torch.manual_seed(7)
     dev = torch.device("cuda")
     qkv = (torch.randn(B, S, 3, nh, 64, device=dev) * gain).to(torch.bfloat16)
@@ -350,7 +352,11 @@ def test_fused_attention_matches_fp32_reference(B, S, nh, gain, causal):
 def test_fused_attention_library_switch(monkeypatch):
     torch.manual_seed(1)
     qkv = torch.randn(1, 128, 3, 2, 64, device="cuda").to(torch.bfloat16)
+    monkeypatch.setenv("TONY_B200_ATTENTION", "tcgen05")
+    before = launch_count()
     ours = F.packed_attention(qkv)
+    assert launch_count() == before + 1          # the own forward kernel really ran
     monkeypatch.setenv("TONY_B200_ATTENTION", "library")
     lib_out = F.packed_attention(qkv)
+    assert launch_count() == before + 1
     assert (ours.float() - lib_out.float()).abs().max().item() < 2e-2

@@ -1,22 +1,33 @@
 // Fused multi-head attention for sm_100a on a PACKED qkv activation.
 //
 // Input is the output of the fused QKV projection, [tokens, 3, heads, 64] bf16, read in place
-// through ONE tensor map (no q/k/v split or transposes); the context comes back as
+// through tensor maps (no q/k/v split or transposes); the context comes back as
 // [tokens, heads*64], the layout the output projection's GEMM consumes.
 //
-// Forward, one CTA per (batch, head, 128 query rows), two CTAs resident per SM:
-//   warp 0     TMA producer: Q tile once, then K_j / V_j tiles (128 keys x 64) through a ring of
-//              three 16 KB slots
-//   warp 1     tcgen05.mma issuer: S = Q K_j^T (M128 N128 K64, fp32 in TMEM columns [0,128)),
-//              O += P_j V_j (M128 N64 K128, TMEM columns [128,192)); V is consumed as an
-//              MN-major B operand straight from its row-major tile
-//   warps 2-5  softmax: one thread per query row (= one TMEM lane), two passes over S with
-//              tcgen05.ld (row max, then exp2 / row sum), P written as bf16 into the 128B-
-//              swizzled K-major layout the second MMA reads.  The running max is only advanced
-//              when it grows by more than 2^8 (exact: the stale offset cancels in O / l), so
-//              the TMEM-resident O is rescaled (tcgen05.ld -> mul -> tcgen05.st) only then.
-// S(j+1) is issued before P_j V_j, so the tensor pipe computes the next scores while the
-// softmax warps of this CTA are still busy; the second resident CTA fills the remaining gaps.
+// Forward: a persistent kernel, two CTAs resident per SM, each looping over work items
+// (batch, head, 128 query rows); all pipelines run across item boundaries, so the loads and
+// the first score MMAs of the next item overlap the epilogue of the current one.
+//   warp 0     TMA producer: Q tile per item, K_j / V_j tiles (64 keys x 64) through two rings of
+//              three 8 KB slots
+//   warp 1     tcgen05.mma issuer, an event loop over two cursors: S = Q K_j^T (M128 N64 K64)
+//              into one of TWO 64-column TMEM buffers, up to two blocks ahead of the softmax;
+//              O += P_j V_j (M128 N64 K64) with P read FROM TENSOR MEMORY as the A operand and
+//              V consumed as an MN-major B operand straight from its row-major tile.  Whichever
+//              MMA has its inputs ready is issued, so neither waits behind the other's barrier.
+//   warps 2-5  softmax: one thread per query row (= one TMEM lane).  A block's 64 scores are
+//              pulled into registers with two tcgen05.ld and the TMEM buffer is handed back at
+//              once.  P goes back to TMEM as bf16 pairs (tcgen05.st, 32 columns, double
+//              buffered): the probabilities never touch shared memory.  The running max only
+//              advances when it grows by more than 2^8 (exact: the stale offset cancels in
+//              O / l), so the TMEM-resident O is rescaled (tcgen05.ld -> mul -> tcgen05.st)
+//              only then.
+// TMEM columns per CTA: S0 [0,64) S1 [64,128) | O [128,192) | P0 [192,224) P1 [224,256).
+// The causal mask is applied only in the (at most two) diagonal blocks, which run a separate
+// instantiation of the block body; blocks above the diagonal are never loaded, and causal work
+// items are handed out heaviest first.
+// Measured (profiles/r1_attention_tcgen05_vs_library.md): correct against fp32, 430 TFLOP/s
+// forward on B200 vs 575 for the cuDNN sm_100 kernel, so ops/functional.py keeps the library
+// core as the default and this path is opt-in (TONY_B200_ATTENTION=tcgen05).
 //
 // The reference (zuston/TonY) has no device code; this replaces the attention
 // core that stock PyTorch jobs launched by the reference run through a library kernel.
@@ -25,75 +36,103 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
+
+#include <type_traits>
 
 #include "common.cuh"
 
 namespace tony {
 
-constexpr int ATT_BM = 128;        // query rows per CTA
-constexpr int ATT_BN = 128;        // keys per block
+constexpr int ATT_BM = 128;        // rows per CTA (queries in fwd / dq, keys in dkdv)
+constexpr int ATT_BK = 64;         // streamed block (keys in fwd / dq, queries in dkdv)
 constexpr int ATT_D = 64;          // head dim
-constexpr int ATT_THREADS = 192;   // TMA warp, MMA warp, 4 softmax warps
-constexpr int ATT_SLOTS = 3;
-constexpr uint32_t ATT_TILE_BYTES = ATT_BN * ATT_D * 2;   // 16 KB
-constexpr uint32_t ATT_P_BYTES = ATT_BM * ATT_BN * 2;     // 32 KB
-constexpr uint32_t ATT_FWD_SMEM = (1 + ATT_SLOTS) * ATT_TILE_BYTES + ATT_P_BYTES + 128 + 1024;
+constexpr int ATT_THREADS = 192;   // backward: TMA warp, MMA warp, 4 elementwise warps
+constexpr uint32_t ATT_TILE_BYTES = ATT_BM * ATT_D * 2;   // 16 KB
+constexpr uint32_t ATT_HALF_BYTES = ATT_BK * ATT_D * 2;   // 8 KB
+constexpr int ATT_FWD_SLOTS = 3;   // depth of the K ring and of the V ring
+constexpr uint32_t ATT_FWD_SMEM =
+    ATT_TILE_BYTES + 2 * ATT_FWD_SLOTS * ATT_HALF_BYTES + ATT_TILE_BYTES + 256 + 1024;
 constexpr float ATT_RESCALE_THRESHOLD = 8.0f;
 
 struct AttnFwdParams {
     int batch, seq, heads, hidden;
     int causal;
+    int num_items;                  // batch * heads * (seq / 128)
     float scale_log2;               // softmax scale * log2(e)
     __nv_bfloat16* out;             // [tokens, hidden]
     float* lse;                     // [batch*heads, seq], log2 domain
 };
 
-// byte offset of 16-byte unit `u` (0..15, eight keys each) of row `row` in a [128 x 128] bf16
-// K-major operand stored as two [128 rows x 128 B] swizzle-128B panels
-__device__ __forceinline__ uint32_t p_unit_offset(int row, int u) {
-    return static_cast<uint32_t>((u >> 3) * 16384 + row * 128 + (((u & 7) ^ (row & 7)) << 4));
+// 16-byte unit `u` (0..7) of row `row` in a [128 x 64] bf16 K-major swizzle-128B panel
+__device__ __forceinline__ uint32_t panel_unit_offset(int row, int u) {
+    return static_cast<uint32_t>(row * 128 + ((u ^ (row & 7)) << 4));
+}
+
+struct AttnItem {
+    int bh, qt, nblk;
+};
+
+__device__ __forceinline__ AttnItem attn_item(const AttnFwdParams& p, int w) {
+    const int nq = p.seq / ATT_BM;
+    AttnItem it;
+    if (p.causal) {   // heaviest query tiles first, heads interleaved
+        const int nbh = p.batch * p.heads;
+        it.qt = nq - 1 - w / nbh;
+        it.bh = w - (w / nbh) * nbh;
+        it.nblk = (it.qt + 1) * (ATT_BM / ATT_BK);
+    } else {          // tiles of one head back to back: its K/V stay hot in L2
+        it.bh = w / nq;
+        it.qt = w - it.bh * nq;
+        it.nblk = p.seq / ATT_BK;
+    }
+    return it;
 }
 
 __global__ void __launch_bounds__(ATT_THREADS, 2)
-attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnFwdParams p) {
+attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
+                     const __grid_constant__ CUtensorMap tmap_qkv64, const AttnFwdParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     uint8_t* sQ = smem;
-    uint8_t* sRing = sQ + ATT_TILE_BYTES;
-    uint8_t* sP = sRing + ATT_SLOTS * ATT_TILE_BYTES;
-    uint64_t* q_full = reinterpret_cast<uint64_t*>(sP + ATT_P_BYTES);
-    uint64_t* ring_full = q_full + 1;
-    uint64_t* ring_empty = ring_full + ATT_SLOTS;
-    uint64_t* s_full = ring_empty + ATT_SLOTS;
-    uint64_t* s_free = s_full + 1;
-    uint64_t* p_full = s_free + 1;
-    uint64_t* o_done = p_full + 1;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 1);
+    uint8_t* sK = sQ + ATT_TILE_BYTES;                               // ring of 8 KB key tiles
+    uint8_t* sV = sK + ATT_FWD_SLOTS * ATT_HALF_BYTES;               // ring of 8 KB value tiles
+    uint8_t* sStage = sV + ATT_FWD_SLOTS * ATT_HALF_BYTES;           // 16 KB epilogue staging
+    uint64_t* q_full = reinterpret_cast<uint64_t*>(sStage + ATT_TILE_BYTES);
+    uint64_t* q_empty = q_full + 1;
+    uint64_t* k_full = q_empty + 1;
+    uint64_t* k_empty = k_full + ATT_FWD_SLOTS;
+    uint64_t* v_full = k_empty + ATT_FWD_SLOTS;
+    uint64_t* v_empty = v_full + ATT_FWD_SLOTS;
+    uint64_t* s_full = v_empty + ATT_FWD_SLOTS;      // [2]
+    uint64_t* s_free = s_full + 2;                   // [2]
+    uint64_t* p_full = s_free + 2;                   // [2]
+    uint64_t* pv_done = p_full + 2;                  // [2]
+    uint64_t* o_free = pv_done + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_free + 1);
 
     const int warp_idx = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
-    const int nq = p.seq / ATT_BM;
-    const int bh = static_cast<int>(blockIdx.x) / nq;
-    const int qt = nq - 1 - (static_cast<int>(blockIdx.x) - bh * nq);   // heavy causal tiles first
-    const int b = bh / p.heads;
-    const int h = bh - b * p.heads;
-    const int q0 = qt * ATT_BM;
-    const int row_base = b * p.seq;
-    const int nblk = p.causal ? qt + 1 : p.seq / ATT_BN;
-
     if (warp_idx == 0 && lane == 0) {
-        tma_prefetch_desc(&tmap_qkv);
+        tma_prefetch_desc(&tmap_qkv128);
+        tma_prefetch_desc(&tmap_qkv64);
         mbar_init(q_full, 1);
-        for (int s = 0; s < ATT_SLOTS; ++s) {
-            mbar_init(&ring_full[s], 1);
-            mbar_init(&ring_empty[s], 1);
+        mbar_init(q_empty, 1);
+        for (int s = 0; s < ATT_FWD_SLOTS; ++s) {
+            mbar_init(&k_full[s], 1);
+            mbar_init(&k_empty[s], 1);
+            mbar_init(&v_full[s], 1);
+            mbar_init(&v_empty[s], 1);
         }
-        mbar_init(s_full, 1);
-        mbar_init(s_free, 4);
-        mbar_init(p_full, 4);
-        mbar_init(o_done, 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&s_full[s], 1);
+            mbar_init(&s_free[s], 4);
+            mbar_init(&p_full[s], 4);
+            mbar_init(&pv_done[s], 1);
+        }
+        mbar_init(o_free, 4);
         fence_barrier_init();
     }
     if (warp_idx == 1) tmem_alloc<256>(tmem_slot);
@@ -101,100 +140,145 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnFwd
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t tS = tmem_base;
-    const uint32_t tO = tmem_base + ATT_BN;
+    // TMEM columns: S0 [0,64) S1 [64,128) fp32 scores | O [128,192) fp32 | P0 [192,224) P1 [224,256) bf16x2
+    const uint32_t tO = tmem_base + 2 * ATT_BK;
+    const uint32_t tP = tmem_base + 2 * ATT_BK + ATT_D;
+    const int stride = static_cast<int>(gridDim.x);
 
     if (warp_idx == 0) {
         if (lane == 0) {
-            mbar_expect_tx(q_full, ATT_TILE_BYTES);
-            tma_load_2d(&tmap_qkv, q_full, sQ, h * ATT_D, row_base + q0);
-            for (int i = 0; i < 2 * nblk; ++i) {
-                const int slot = i % ATT_SLOTS;
-                const uint32_t use = static_cast<uint32_t>(i / ATT_SLOTS);
-                mbar_wait(&ring_empty[slot], (use & 1) ^ 1);
-                mbar_expect_tx(&ring_full[slot], ATT_TILE_BYTES);
-                const int col = ((i & 1) ? 2 * p.hidden : p.hidden) + h * ATT_D;   // K then V
-                tma_load_2d(&tmap_qkv, &ring_full[slot], sRing + slot * ATT_TILE_BYTES, col,
-                            row_base + (i >> 1) * ATT_BN);
+            uint32_t g = 0;   // running block index across work items
+            uint32_t n = 0;
+            for (int w = blockIdx.x; w < p.num_items; w += stride, ++n) {
+                const AttnItem a = attn_item(p, w);
+                const int b = a.bh / p.heads, h = a.bh - b * p.heads;
+                const int row_base = b * p.seq;
+                mbar_wait_relaxed(q_empty, (n & 1) ^ 1);   // every S of the previous item has retired
+                mbar_expect_tx(q_full, ATT_TILE_BYTES);
+                tma_load_2d(&tmap_qkv128, q_full, sQ, h * ATT_D, row_base + a.qt * ATT_BM);
+                for (int j = 0; j < a.nblk; ++j, ++g) {
+                    const uint32_t slot = g % ATT_FWD_SLOTS;
+                    const uint32_t par = ((g / ATT_FWD_SLOTS) & 1) ^ 1;
+                    mbar_wait_relaxed(&k_empty[slot], par);
+                    mbar_expect_tx(&k_full[slot], ATT_HALF_BYTES);
+                    tma_load_2d(&tmap_qkv64, &k_full[slot], sK + slot * ATT_HALF_BYTES,
+                                p.hidden + h * ATT_D, row_base + j * ATT_BK);
+                    mbar_wait_relaxed(&v_empty[slot], par);
+                    mbar_expect_tx(&v_full[slot], ATT_HALF_BYTES);
+                    tma_load_2d(&tmap_qkv64, &v_full[slot], sV + slot * ATT_HALF_BYTES,
+                                2 * p.hidden + h * ATT_D, row_base + j * ATT_BK);
+                }
             }
         }
     } else if (warp_idx == 1) {
         if (lane == 0) {
-            const uint32_t idesc_s = make_idesc_bf16(ATT_BM, ATT_BN, 0, 0);
+            // Event loop over two cursors on the flattened (item, block) sequence: the score
+            // MMAs run up to two blocks ahead of the P V MMAs; whichever has all its inputs
+            // ready is issued, so neither waits behind the other's barrier.
+            const uint32_t idesc_s = make_idesc_bf16(ATT_BM, ATT_BK, 0, 0);
             const uint32_t idesc_o = make_idesc_bf16(ATT_BM, ATT_D, 0, 1);   // B = V, MN-major
             const uint64_t dq = make_umma_desc_sw128(smem_u32(sQ), 16, 1024);
-            const uint64_t dp0 = make_umma_desc_sw128(smem_u32(sP), 16, 1024);
-            auto issue_s = [&](int j) {
-                const int i = 2 * j;
-                const int slot = i % ATT_SLOTS;
-                mbar_wait(&ring_full[slot], static_cast<uint32_t>(i / ATT_SLOTS) & 1);
-                tcgen05_fence_after();
-                const uint64_t dk =
-                    make_umma_desc_sw128(smem_u32(sRing + slot * ATT_TILE_BYTES), 16, 1024);
+            int ws = blockIdx.x, js = 0;
+            uint32_t ns = 0, gs = 0;
+            int nblk_s = ws < p.num_items ? attn_item(p, ws).nblk : 0;
+            int wp = blockIdx.x, jp = 0;
+            uint32_t np = 0, gp = 0;
+            int nblk_p = nblk_s;
+            while (nblk_p) {
+                bool progressed = false;
+                if (nblk_s && gs < gp + 2) {
+                    const uint32_t slot = gs % ATT_FWD_SLOTS;
+                    bool ok = gs < 2 || mbar_test_wait(&s_free[gs & 1], ((gs - 2) >> 1) & 1);
+                    if (ok && js == 0) ok = mbar_test_wait(q_full, ns & 1);
+                    if (ok) ok = mbar_test_wait(&k_full[slot], (gs / ATT_FWD_SLOTS) & 1);
+                    if (ok) {
+                        tcgen05_fence_after();
+                        const uint64_t dk = make_umma_desc_sw128(smem_u32(sK + slot * ATT_HALF_BYTES), 16, 1024);
+                        const uint32_t tS = tmem_base + (gs & 1) * ATT_BK;
 #pragma unroll
-                for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tS, dq + k * 2, dk + k * 2, idesc_s, k > 0);
-                umma_commit(&ring_empty[slot]);
-                umma_commit(s_full);
-            };
-            mbar_wait(q_full, 0);
-            issue_s(0);
-            for (int j = 0; j < nblk; ++j) {
-                if (j + 1 < nblk) {
-                    mbar_wait(s_free, j & 1);   // softmax has read S_j out of TMEM
-                    tcgen05_fence_after();
-                    issue_s(j + 1);
+                        for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tS, dq + k * 2, dk + k * 2, idesc_s, k > 0);
+                        umma_commit(&k_empty[slot]);
+                        umma_commit(&s_full[gs & 1]);
+                        progressed = true;
+                        ++gs;
+                        if (++js == nblk_s) {
+                            umma_commit(q_empty);   // Q may be replaced once these MMAs retire
+                            js = 0;
+                            ++ns;
+                            ws += stride;
+                            nblk_s = ws < p.num_items ? attn_item(p, ws).nblk : 0;
+                        }
+                    }
                 }
-                const int i = 2 * j + 1;
-                const int slot = i % ATT_SLOTS;
-                mbar_wait(&ring_full[slot], static_cast<uint32_t>(i / ATT_SLOTS) & 1);
-                mbar_wait(p_full, j & 1);
-                tcgen05_fence_after();
-                const uint64_t dv =
-                    make_umma_desc_sw128(smem_u32(sRing + slot * ATT_TILE_BYTES), 8192, 1024);
+                {
+                    const uint32_t bsel = gp & 1;
+                    const uint32_t slot = gp % ATT_FWD_SLOTS;
+                    bool ok = mbar_test_wait(&p_full[bsel], (gp >> 1) & 1);
+                    if (ok) ok = mbar_test_wait(&v_full[slot], (gp / ATT_FWD_SLOTS) & 1);
+                    if (ok && jp == 0 && np > 0) ok = mbar_test_wait(o_free, (np - 1) & 1);   // previous O read out
+                    if (ok) {
+                        tcgen05_fence_after();
+                        const uint64_t dv = make_umma_desc_sw128(smem_u32(sV + slot * ATT_HALF_BYTES), 8192, 1024);
 #pragma unroll
-                for (int k = 0; k < ATT_BN / 16; ++k) {
-                    // A: panel k/4 (16 KB apart), 32 B per k-step inside the swizzle row
-                    // B: 16 key rows = 2048 B per k-step
-                    umma_bf16(tO, dp0 + (k >> 2) * 1024 + (k & 3) * 2, dv + k * 128, idesc_o,
-                              (j > 0 || k > 0) ? 1u : 0u);
+                        for (int k = 0; k < ATT_BK / 16; ++k)   // A: P from TMEM, 8 columns per k-step; B: 16 key rows = 2048 B
+                            umma_bf16_ts(tO, tP + bsel * (ATT_BK / 2) + k * 8, dv + k * 128, idesc_o,
+                                         (jp > 0 || k > 0) ? 1u : 0u);
+                        umma_commit(&v_empty[slot]);
+                        umma_commit(&pv_done[bsel]);
+                        progressed = true;
+                        ++gp;
+                        if (++jp == nblk_p) {
+                            jp = 0;
+                            ++np;
+                            wp += stride;
+                            nblk_p = wp < p.num_items ? attn_item(p, wp).nblk : 0;
+                        }
+                    }
                 }
-                umma_commit(&ring_empty[slot]);
-                umma_commit(o_done);
+                if (!progressed) __nanosleep(40);   // keep the poll off the softmax warps' issue slots
             }
         }
     } else {
         const int quarter = warp_idx & 3;
         const int row = quarter * 32 + lane;
         const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
-        const uint32_t sP_u32 = smem_u32(sP);
-        const float NEG_INF = -INFINITY;
-        float m_used = NEG_INF;
-        float l = 0.f;
-        for (int j = 0; j < nblk; ++j) {
-            const bool diag = p.causal && j == nblk - 1;
-            mbar_wait(s_full, j & 1);
+        const uint32_t stage = smem_u32(sStage);
+        uint32_t g = 0;   // running block index across work items
+        uint32_t n = 0;
+        float m_used = 0.f, l = 0.f;
+        int q0 = 0;
+#ifdef ATT_PROFILE
+        long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        long long tprev = clock64();
+#define ATT_T(k) { long long _t = clock64(); tacc[k] += _t - tprev; tprev = _t; }
+#else
+#define ATT_T(k)
+#endif
+
+        auto block = [&](int j, auto masked_tag) {
+            constexpr bool MASKED = decltype(masked_tag)::value;
+            const uint32_t bsel = g & 1;
+            const uint32_t ph = (g >> 1) & 1;
+            const int rel = q0 + row - j * ATT_BK;   // keys with column index > rel are masked
+            ATT_T(0);
+            mbar_wait(&s_full[bsel], ph);
+            ATT_T(1);
             tcgen05_fence_after();
-            // ---- pass 1: row max of the raw scores
-            float mx = NEG_INF;
-#pragma unroll 1
-            for (int c2 = 0; c2 < 2; ++c2) {
-                uint32_t r0[32], r1[32];
-                tmem_ld_32x32(tS + lane_addr + c2 * 64, r0);
-                tmem_ld_32x32(tS + lane_addr + c2 * 64 + 32, r1);
-                tmem_ld_wait();
-                if (diag) {
+            uint32_t r[64];
+            tmem_ld_32x32(tmem_base + lane_addr + bsel * ATT_BK, r);
+            tmem_ld_32x32(tmem_base + lane_addr + bsel * ATT_BK + 32, r + 32);
+            tmem_ld_wait();
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_free[bsel]);
+            ATT_T(2);
+            float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        if (c2 * 64 + i <= row) mx = fmaxf(mx, __uint_as_float(r0[i]));
-                        if (c2 * 64 + 32 + i <= row) mx = fmaxf(mx, __uint_as_float(r1[i]));
-                    }
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        mx = fmaxf(mx, fmaxf(__uint_as_float(r0[i]), __uint_as_float(r1[i])));
-                }
+            for (int i = 0; i < 64; ++i) {
+                if (MASKED && i > rel) r[i] = __float_as_uint(-INFINITY);
+                mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(r[i]));
             }
-            const float m_new = fmaxf(m_used, mx * p.scale_log2);
+            const float m_new = fmaxf(m_used, fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * p.scale_log2);
             float alpha = 1.f;
             bool need = false;
             if (j == 0) {
@@ -204,80 +288,102 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnFwd
                 alpha = ex2_approx(m_used - m_new);
                 m_used = m_new;
             }
-            const bool any = __any_sync(0xffffffffu, need);
-            if (j > 0) {
-                mbar_wait(o_done, (j - 1) & 1);   // P_{j-1} V_{j-1} retired: sP and O are ours
+            if (__any_sync(0xffffffffu, need)) {
+                mbar_wait(&pv_done[bsel ^ 1], ((g - 1) >> 1) & 1);   // previous P V retired
                 tcgen05_fence_after();
-            }
-            if (any) {
 #pragma unroll 1
                 for (int c = 0; c < 2; ++c) {
-                    uint32_t r[32];
-                    tmem_ld_32x32(tO + lane_addr + c * 32, r);
+                    uint32_t o[32];
+                    tmem_ld_32x32(tO + lane_addr + c * 32, o);
                     tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-                    tmem_st_32x32(tO + lane_addr + c * 32, r);
+                    for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                    tmem_st_32x32(tO + lane_addr + c * 32, o);
                 }
                 tmem_st_wait();
                 l *= alpha;
             }
-            // ---- pass 2: p = exp2(s * scale - m), row sum, bf16 P into the MMA layout
-            float sum = 0.f;
             const float neg_m = -m_used;
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                uint32_t r[32];
-                tmem_ld_32x32(tS + lane_addr + c * 32, r);
-                tmem_ld_wait();
-                uint32_t w[16];
+            float sum[4] = {0.f, 0.f, 0.f, 0.f};
+            ATT_T(3);
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    float a = ex2_approx(fmaf(__uint_as_float(r[2 * i]), p.scale_log2, neg_m));
-                    float bq = ex2_approx(fmaf(__uint_as_float(r[2 * i + 1]), p.scale_log2, neg_m));
-                    if (diag) {
-                        if (c * 32 + 2 * i > row) a = 0.f;
-                        if (c * 32 + 2 * i + 1 > row) bq = 0.f;
-                    }
-                    sum += a + bq;
-                    w[i] = pack_bf16x2(a, bq);
-                }
-#pragma unroll
-                for (int v = 0; v < 4; ++v)
-                    st_shared_v4(sP_u32 + p_unit_offset(row, c * 4 + v),
-                                 make_uint4(w[4 * v], w[4 * v + 1], w[4 * v + 2], w[4 * v + 3]));
+            for (int i = 0; i < 32; ++i) {   // packed P overwrites the scores it was made from
+                const float a = ex2_approx(fmaf(__uint_as_float(r[2 * i]), p.scale_log2, neg_m));
+                const float c = ex2_approx(fmaf(__uint_as_float(r[2 * i + 1]), p.scale_log2, neg_m));
+                sum[i & 1] += a;
+                sum[2 + (i & 1)] += c;
+                r[i] = pack_bf16x2(a, c);
             }
-            l += sum;
+            l += (sum[0] + sum[1]) + (sum[2] + sum[3]);
+            ATT_T(4);
+            if (g >= 2) mbar_wait(&pv_done[bsel], ph ^ 1);
+            ATT_T(5);   // P V two blocks back retired: its P columns are free
+            tcgen05_fence_after();
+            // P stays in tensor memory (32 columns of bf16 pairs): the second MMA reads its A
+            // operand from there, so the probabilities never touch shared memory
+            tmem_st_32x32(tP + lane_addr + bsel * (ATT_BK / 2), r);
+            tmem_st_wait();
             tcgen05_fence_before();
-            fence_proxy_async();   // generic-proxy P stores -> async-proxy MMA operand reads
             __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(s_free);
-                mbar_arrive(p_full);
+            if (lane == 0) mbar_arrive(&p_full[bsel]);
+            ATT_T(6);
+        };
+
+        for (int w = blockIdx.x; w < p.num_items; w += stride, ++n) {
+            const AttnItem a = attn_item(p, w);
+            const int b = a.bh / p.heads, h = a.bh - b * p.heads;
+            const int row_base = b * p.seq;
+            q0 = a.qt * ATT_BM;
+            m_used = -INFINITY;
+            l = 0.f;
+            for (int j = 0; j < a.nblk; ++j, ++g) {
+                if (p.causal && (j * ATT_BK + ATT_BK - 1 > q0))
+                    block(j, std::true_type{});
+                else
+                    block(j, std::false_type{});
             }
-        }
-        // ---- epilogue: O / l -> bf16 context rows, log2-sum-exp for backward
-        mbar_wait(o_done, (nblk - 1) & 1);
-        tcgen05_fence_after();
-        const float inv = 1.f / l;
-        const size_t token = static_cast<size_t>(row_base + q0 + row);
-        __nv_bfloat16* orow = p.out + token * p.hidden + h * ATT_D;
-#pragma unroll 1
-        for (int c = 0; c < 2; ++c) {
-            uint32_t r[32];
-            tmem_ld_32x32(tO + lane_addr + c * 32, r);
+            ATT_T(7);
+            // ---- item epilogue: O / l -> bf16 context rows (staged through this warp's 32 rows of a
+            // swizzled panel so every global store covers whole 128-byte rows), log2-sum-exp
+            const uint32_t gl = g - 1;
+            mbar_wait(&pv_done[gl & 1], (gl >> 1) & 1);
+            tcgen05_fence_after();
+            uint32_t o[64];
+            tmem_ld_32x32(tO + lane_addr, o);
+            tmem_ld_32x32(tO + lane_addr + 32, o + 32);
             tmem_ld_wait();
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(o_free);   // the next item's first P V may overwrite O
+            const float inv = 1.f / l;
 #pragma unroll
-            for (int v = 0; v < 4; ++v) {
-                uint4 o;
-                o.x = pack_bf16x2(__uint_as_float(r[8 * v]) * inv, __uint_as_float(r[8 * v + 1]) * inv);
-                o.y = pack_bf16x2(__uint_as_float(r[8 * v + 2]) * inv, __uint_as_float(r[8 * v + 3]) * inv);
-                o.z = pack_bf16x2(__uint_as_float(r[8 * v + 4]) * inv, __uint_as_float(r[8 * v + 5]) * inv);
-                o.w = pack_bf16x2(__uint_as_float(r[8 * v + 6]) * inv, __uint_as_float(r[8 * v + 7]) * inv);
-                st_global_v4(orow + c * 32 + v * 8, o);
+            for (int u = 0; u < 8; ++u) {
+                uint4 q;
+                q.x = pack_bf16x2(__uint_as_float(o[8 * u]) * inv, __uint_as_float(o[8 * u + 1]) * inv);
+                q.y = pack_bf16x2(__uint_as_float(o[8 * u + 2]) * inv, __uint_as_float(o[8 * u + 3]) * inv);
+                q.z = pack_bf16x2(__uint_as_float(o[8 * u + 4]) * inv, __uint_as_float(o[8 * u + 5]) * inv);
+                q.w = pack_bf16x2(__uint_as_float(o[8 * u + 6]) * inv, __uint_as_float(o[8 * u + 7]) * inv);
+                st_shared_v4(stage + panel_unit_offset(row, u), q);
             }
+            __syncwarp();
+            __nv_bfloat16* obase =
+                p.out + static_cast<size_t>(row_base + q0 + quarter * 32) * p.hidden + h * ATT_D;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int rr = i * 4 + (lane >> 3);
+                const uint4 v = ld_shared_v4(stage + panel_unit_offset(quarter * 32 + rr, lane & 7));
+                st_global_v4(obase + static_cast<size_t>(rr) * p.hidden + (lane & 7) * 8, v);
+            }
+            __syncwarp();   // the staging rows are rewritten by this warp's next epilogue
+            p.lse[static_cast<size_t>(a.bh) * p.seq + q0 + row] = m_used + lg2_approx(l);
+            ATT_T(0);
         }
-        p.lse[static_cast<size_t>(bh) * p.seq + q0 + row] = m_used + lg2_approx(l);
+#ifdef ATT_PROFILE
+        if (lane == 0 && blockIdx.x < 4) {
+            for (int k = 0; k < 8; ++k)
+                reinterpret_cast<long long*>(p.lse)[(blockIdx.x * 4 + (warp_idx - 2)) * 8 + k] = tacc[k];
+        }
+#endif
     }
 
     __syncwarp();
@@ -301,8 +407,6 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnFwd
 // P is recomputed from the forward's log2-sum-exp.  Every "second" MMA takes the row-major
 // K_j / Q_i / dO_i tile as an MN-major B operand, so no tile is ever transposed in memory.
 // TMEM: 192 (dq) / 256 (dkdv) columns per CTA, two CTAs per SM.
-constexpr int ATT_BK = 64;
-constexpr uint32_t ATT_HALF_BYTES = ATT_BK * ATT_D * 2;   // 8 KB
 constexpr int ATT_BWD_SLOTS = 6;    // dq kernel: three key blocks of K_j / V_j in flight
 constexpr int ATT_KV_SLOTS = 5;     // dkdv kernel (two CTAs per SM leave room for five)
 constexpr uint32_t ATT_DQ_SMEM = 2 * ATT_TILE_BYTES + ATT_BWD_SLOTS * ATT_HALF_BYTES + ATT_TILE_BYTES + 128 + 1024;
@@ -347,11 +451,6 @@ __global__ void attention_bwd_delta_kernel(const __nv_bfloat16* __restrict__ out
         const int s = static_cast<int>(token - b * seq);
         delta[(b * heads + h) * seq + s] = acc;
     }
-}
-
-// 16-byte unit `u` (0..7) of row `row` in a [128 x 64] bf16 K-major swizzle-128B panel
-__device__ __forceinline__ uint32_t panel_unit_offset(int row, int u) {
-    return static_cast<uint32_t>(row * 128 + ((u ^ (row & 7)) << 4));
 }
 
 __global__ void __launch_bounds__(ATT_THREADS, 2)
@@ -792,8 +891,10 @@ extern "C" int tony_attention_fwd_bf16(const void* qkv, void* out, float* lse, i
     }
     const int hidden = heads * ATT_D;
     const long long tokens = static_cast<long long>(batch) * seq;
-    CUtensorMap tmap;
-    rc = make_tmap_2d_bf16(&tmap, qkv, 3LL * hidden, tokens, 3LL * hidden, ATT_D, ATT_BM);
+    CUtensorMap tmap128, tmap64;
+    rc = make_tmap_2d_bf16(&tmap128, qkv, 3LL * hidden, tokens, 3LL * hidden, ATT_D, ATT_BM);
+    if (rc != TONY_OK) return rc;
+    rc = make_tmap_2d_bf16(&tmap64, qkv, 3LL * hidden, tokens, 3LL * hidden, ATT_D, ATT_BK);
     if (rc != TONY_OK) return rc;
     rc = set_smem_once(reinterpret_cast<const void*>(attention_fwd_kernel), ATT_FWD_SMEM, 0);
     if (rc != TONY_OK) return rc;
@@ -806,8 +907,9 @@ extern "C" int tony_attention_fwd_bf16(const void* qkv, void* out, float* lse, i
     p.scale_log2 = scale * 1.4426950408889634f;
     p.out = static_cast<__nv_bfloat16*>(out);
     p.lse = lse;
-    const int grid = batch * heads * (seq / ATT_BM);
-    attention_fwd_kernel<<<grid, ATT_THREADS, ATT_FWD_SMEM, static_cast<cudaStream_t>(stream)>>>(tmap, p);
+    p.num_items = batch * heads * (seq / ATT_BM);
+    const int grid = p.num_items < 2 * device_sm_count() ? p.num_items : 2 * device_sm_count();
+    attention_fwd_kernel<<<grid, ATT_THREADS, ATT_FWD_SMEM, static_cast<cudaStream_t>(stream)>>>(tmap128, tmap64, p);
     TONY_CUDA_CHECK(cudaGetLastError());
     count_launch();
     return TONY_OK;

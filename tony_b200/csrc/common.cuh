@@ -88,9 +88,30 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     return ok != 0;
 }
 
+// Non-blocking probe (no hardware suspend): for issuers that poll several barriers.
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
     }
+}
+
+// For producer / issuer threads whose wake-up latency is not critical: sleep between probes so
+// the spin does not compete with the math warps for issue slots and the MIO queue.
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity, uint32_t ns = 64) {
+    while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
 }
 
 // Make mbarrier.init visible to the async proxy (TMA / tcgen05.commit).
@@ -102,6 +123,12 @@ __device__ __forceinline__ void fence_barrier_init() {
 // reads (TMA loads) issued by this thread.
 __device__ __forceinline__ void fence_proxy_async() {
     asm volatile("fence.proxy.async;" ::: "memory");
+}
+
+// Same, restricted to this CTA's shared memory (st.shared operand tiles -> tcgen05.mma reads);
+// does not wait for outstanding global stores.
+__device__ __forceinline__ void fence_proxy_async_smem() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
 // ----------------------------------------------------------------------------
@@ -158,6 +185,21 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
         "}\n"
         :
         : "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+// Same with the A operand read from tensor memory (M = 128 lanes, 16 bf16 = 8 columns per
+// instruction): D[tmem] (+)= A[tmem] * B[smem desc].
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b,
+                                             uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+        "}\n"
+        :
+        : "r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
 

@@ -531,8 +531,10 @@ def fused_attention_supported(qkv) -> bool:
 def packed_attention(qkv, causal: bool = False):
     """``qkv``: ``[B, S, 3, heads, head_dim]`` -> context ``[B, S, heads*head_dim]``.
 
-    head_dim 64 with a sequence length that is a multiple of 128 runs on the tcgen05 kernels of
-    csrc/attention.cu; other shapes (and ``TONY_B200_ATTENTION=library``) use the library core."""
-    if fused_attention_supported(qkv) and os.environ.get("TONY_B200_ATTENTION", "tcgen05") != "library":
+    ``TONY_B200_ATTENTION=tcgen05`` runs head_dim 64 / seq % 128 == 0 on the hand-written
+    kernels of csrc/attention.cu.  The default is the library core: on B200 it is the cuDNN
+    sm_100 flash kernel, which the own kernels do not beat yet (profiles/r1_attention_*.md has
+    the measured comparison), and the default follows the measurement."""
+    if fused_attention_supported(qkv) and os.environ.get("TONY_B200_ATTENTION", "library") == "tcgen05":
         return _FusedAttentionFn.apply(qkv, causal)
     return _PackedSdpaFn.apply(qkv, causal)
