@@ -360,3 +360,32 @@ def test_fused_attention_library_switch(monkeypatch):
     lib_out = F.packed_attention(qkv)
     assert launch_count() == before + 1
     assert (ours.float() - lib_out.float()).abs().max().item() < 2e-2
+
+
+def test_residual_blocks_match_unfused_composition():
+    """attention_block / mlp(residual=x) fuse the residual branch's gradient into the last dgrad
+    GEMM; they must match the same block built from separate linear / attention calls."""
+    torch.manual_seed(3)
+    B, S, H, nh = 2, 128, 256, 4
+    x = _rand(B, S, H)
+    wqkv, bqkv = _rand(3 * H, H, scale=0.05), _rand(3 * H, scale=0.1)
+    wo, bo = _rand(H, H, scale=0.05), _rand(H, scale=0.1)
+    w1, b1 = _rand(4 * H, H, scale=0.05), _rand(4 * H, scale=0.1)
+    w2, b2 = _rand(H, 4 * H, scale=0.05), _rand(H, scale=0.1)
+    g = _rand(B, S, H)
+
+    def run(fused):
+        leaves = [t.clone().requires_grad_() for t in (x, wqkv, bqkv, wo, bo, w1, b1, w2, b2)]
+        xi, a, ab, o, ob, f1, f1b, f2, f2b = leaves
+        if fused:
+            y = F.attention_block(xi, a, ab, o, ob, nh)
+            z = F.mlp(y, f1, f1b, f2, f2b, residual=y)
+        else:
+            qkv = F.linear(xi, a, ab).view(B, S, 3, nh, H // nh)
+            y = F.linear(F.packed_attention(qkv), o, ob) + xi
+            z = F.mlp(y, f1, f1b, f2, f2b) + y
+        z.backward(g)
+        return [z] + [t.grad for t in leaves]
+
+    for got, want in zip(run(True), run(False)):
+        _close(got, want, rel=3e-2)

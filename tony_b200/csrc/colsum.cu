@@ -12,7 +12,8 @@
 
 namespace tony {
 
-constexpr int CS_MAX_SLABS = 64;
+constexpr int CS_MAX_SLABS = 64;         // static-scratch variant (fixed 2 MiB array)
+constexpr int CS_MAX_SLABS_FUSED = 160;  // single-launch variant: enough for 4 CTAs per SM on one column tile
 constexpr int CS_THREADS = 256;  // 8 warps: 32 lanes x 8 columns = 256 columns per CTA
 
 __global__ void __launch_bounds__(CS_THREADS)
@@ -75,13 +76,13 @@ colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, lon
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (col < cols) {
         int r = r0 + warp;
-        for (; r + 3 * (CS_THREADS / 32) < r1; r += 4 * (CS_THREADS / 32)) {  // 4 loads in flight
-            uint4 u[4];
+        for (; r + 7 * (CS_THREADS / 32) < r1; r += 8 * (CS_THREADS / 32)) {  // 8 loads in flight
+            uint4 u[8];
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < 8; ++k)
                 u[k] = ld_global_nc_v4(x + static_cast<size_t>(r + k * (CS_THREADS / 32)) * ld + col);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
+            for (int k = 0; k < 8; ++k) {
                 const uint32_t w[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -120,10 +121,9 @@ colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, lon
     __syncthreads();
     if (!is_last) return;
     __threadfence();
+    float t = fold_partials_256(partials, static_cast<size_t>(cols), static_cast<int>(gridDim.y),
+                                blockIdx.x * 256, cols, red);
     if (gc < cols) {
-        float t = 0.f;
-        for (int k = 0; k < static_cast<int>(gridDim.y); ++k)
-            t += __ldcg(partials + static_cast<size_t>(k) * cols + gc);
         if (accumulate) t += __bfloat162float(out[gc]);
         out[gc] = __float2bfloat16(t);
     }
@@ -135,7 +135,7 @@ colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, lon
 using namespace tony;
 
 static size_t colsum_partials_bytes(int cols) {
-    return static_cast<size_t>(CS_MAX_SLABS) * static_cast<size_t>(cols) * sizeof(float);
+    return static_cast<size_t>(CS_MAX_SLABS_FUSED) * static_cast<size_t>(cols) * sizeof(float);
 }
 
 extern "C" size_t tony_colsum_scratch_bytes(int cols) {
@@ -157,8 +157,8 @@ extern "C" int tony_colsum_bf16(const void* x, int rows, int cols, long long ld,
     }
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int col_tiles = (cols + 255) / 256;
-    int slabs = std::max(1, std::min(CS_MAX_SLABS, (device_sm_count() * 4) / col_tiles));
-    slabs = std::min(slabs, std::max(1, rows / 32));
+    int slabs = std::max(1, std::min(CS_MAX_SLABS_FUSED, (device_sm_count() * 4) / col_tiles));
+    slabs = std::min(slabs, std::max(1, rows / 64));
     const int rows_per_slab = (rows + slabs - 1) / slabs;
     slabs = (rows + rows_per_slab - 1) / rows_per_slab;
     // scratch layout: [4 KB of per-column-tile counters][partial rows].  The counters are

@@ -482,6 +482,43 @@ __device__ __forceinline__ float dgelu_tanh(float x) {
     return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * du;
 }
 
+// Tail of the single-launch column reductions: the last CTA of a 256-column tile folds `nparts`
+// fp32 partial rows (`stride` floats apart) with ALL of its 8 warps — warp w takes parts w, w+8,
+// ..., lane l the columns [8l, 8l+8) with two 16-byte L2 loads per part, two parts in flight —
+// and a shared-memory pass adds the 8 warp sums.  (One thread per column walking every part in
+// turn was a chain of ~150 dependent L2 round trips: 10+ us for a 5 us reduction.)
+// Returns the total for column `col0 + threadIdx.x`; `red` is [8][256] floats, 256 threads.
+__device__ __forceinline__ float fold_partials_256(const float* __restrict__ partials, size_t stride,
+                                                   int nparts, int col0, int cols, float (*red)[256]) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c = col0 + lane * 8;
+    float t[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (c < cols) {
+        int k = warp;
+        for (; k + 8 < nparts; k += 16) {
+            const float4* p0 = reinterpret_cast<const float4*>(partials + static_cast<size_t>(k) * stride + c);
+            const float4* p1 = reinterpret_cast<const float4*>(partials + static_cast<size_t>(k + 8) * stride + c);
+            const float4 a0 = __ldcg(p0), a1 = __ldcg(p0 + 1), b0 = __ldcg(p1), b1 = __ldcg(p1 + 1);
+            t[0] += a0.x + b0.x; t[1] += a0.y + b0.y; t[2] += a0.z + b0.z; t[3] += a0.w + b0.w;
+            t[4] += a1.x + b1.x; t[5] += a1.y + b1.y; t[6] += a1.z + b1.z; t[7] += a1.w + b1.w;
+        }
+        for (; k < nparts; k += 8) {
+            const float4* p0 = reinterpret_cast<const float4*>(partials + static_cast<size_t>(k) * stride + c);
+            const float4 a0 = __ldcg(p0), a1 = __ldcg(p0 + 1);
+            t[0] += a0.x; t[1] += a0.y; t[2] += a0.z; t[3] += a0.w;
+            t[4] += a1.x; t[5] += a1.y; t[6] += a1.z; t[7] += a1.w;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = t[j];
+    __syncthreads();
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += red[w][threadIdx.x];
+    __syncthreads();
+    return s;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

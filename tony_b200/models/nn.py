@@ -78,9 +78,8 @@ class MLP(nn.Module):
 class SelfAttention(nn.Module):
     """Fused QKV projection -> SDPA -> output projection with the residual in its epilogue.
 
-    The attention core itself is ``torch.nn.functional.scaled_dot_product_attention``
-    (library flash kernel): attention is not among the ops the project's spec names for
-    hand-written kernels, and both bench arms use the same call.
+    The attention core is ``functional.packed_attention``: the library flash kernel by default,
+    the hand-written tcgen05 kernels of csrc/attention.cu with ``TONY_B200_ATTENTION=tcgen05``.
     """
 
     def __init__(self, hidden: int, heads: int, causal: bool = False, std: float = 0.02,
@@ -92,6 +91,10 @@ class SelfAttention(nn.Module):
 
     def forward(self, x, residual=None):
         B, S, H = x.shape
+        if residual is x and x.is_cuda and x.dtype == torch.bfloat16:
+            # post-LN block: one autograd node, residual gradient fused into the last dgrad GEMM
+            return F.attention_block(x, self.qkv.weight, self.qkv.bias, self.out.weight, self.out.bias,
+                                     self.heads, self.causal)
         qkv = self.qkv(x).view(B, S, 3, self.heads, self.head_dim)
         o = F.packed_attention(qkv, self.causal)
         return self.out(o, residual=residual)

@@ -201,7 +201,7 @@ class _MlpFn(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, x, w1, b1, w2, b2, residual, act):
+    def forward(ctx, x, w1, b1, w2, b2, residual, act, self_residual=False):
         K = w1.shape[1]
         x2 = x.reshape(-1, K)
         if not x2.is_contiguous():
@@ -210,13 +210,16 @@ class _MlpFn(torch.autograd.Function):
         N = w2.shape[0]
         pre = torch.empty((x2.shape[0], F), dtype=torch.bfloat16, device=x.device)
         h = gemm(x2, w1, flags=EPI_BIAS | _ACT_FWD[act] | EPI_SAVE_PREACT, bias=b1, aux_out=pre)
-        res2 = residual.reshape(-1, N) if residual is not None else None
-        y = gemm(h, w2, flags=EPI_BIAS | (EPI_RESIDUAL if residual is not None else 0), bias=b2,
-                 aux=res2)
+        if self_residual:        # y = x + FFN(x): the block input is its own residual
+            res2 = x2
+        else:
+            res2 = residual.reshape(-1, N) if residual is not None else None
+        y = gemm(h, w2, flags=EPI_BIAS | (EPI_RESIDUAL if res2 is not None else 0), bias=b2, aux=res2)
         ctx.save_for_backward(x2, w1, w2, pre, h)
         ctx.b1, ctx.b2, ctx.act = b1, b2, act
         ctx.x_shape = x.shape
         ctx.has_res = residual is not None
+        ctx.self_residual = self_residual
         return y.view(*x.shape[:-1], N)
 
     @staticmethod
@@ -231,12 +234,21 @@ class _MlpFn(torch.autograd.Function):
         dpre = gemm(dy2, w2, b_mn=True, flags=_ACT_BWD[ctx.act], aux=pre)  # (dY.W2) * act'(pre)
         dw1 = _weight_grad(dpre, x2, w1)
         db1 = _bias_grad(dpre, ctx.b1)
-        dx = gemm(dpre, w1, b_mn=True).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
-        return dx, dw1, db1, dw2, db2, (dy if ctx.has_res else None), None
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if ctx.self_residual:
+                # d(x + FFN(x)) = dY + dpre . W1: the residual branch's gradient rides in the last
+                # dgrad GEMM's epilogue instead of a separate elementwise add over the activation
+                dx = gemm(dpre, w1, b_mn=True, flags=EPI_RESIDUAL, aux=dy2).view(ctx.x_shape)
+            else:
+                dx = gemm(dpre, w1, b_mn=True).view(ctx.x_shape)
+        return dx, dw1, db1, dw2, db2, (dy if ctx.has_res else None), None, None
 
 
 def mlp(x, w1, b1, w2, b2, residual=None, act="gelu"):
-    return _MlpFn.apply(x, w1, b1, w2, b2, residual, act)
+    if residual is x and x.shape[-1] == w2.shape[0]:
+        return _MlpFn.apply(x, w1, b1, w2, b2, None, act, True)
+    return _MlpFn.apply(x, w1, b1, w2, b2, residual, act, False)
 
 
 class _LinearActFn(torch.autograd.Function):
@@ -526,6 +538,105 @@ class _FusedAttentionFn(torch.autograd.Function):
 def fused_attention_supported(qkv) -> bool:
     return (qkv.is_cuda and qkv.dtype == torch.bfloat16 and qkv.dim() == 5 and qkv.shape[4] == 64
             and qkv.shape[1] % 128 == 0)
+
+
+def _attention_core_forward(qkv, causal):
+    """-> (context [B, S, H], saved state for ``_attention_core_backward``)."""
+    if fused_attention_supported(qkv) and os.environ.get("TONY_B200_ATTENTION", "library") == "tcgen05":
+        B, S, _, nh, hd = qkv.shape
+        out = torch.empty((B, S, nh * hd), dtype=qkv.dtype, device=qkv.device)
+        lse = torch.empty((B * nh, S), dtype=torch.float32, device=qkv.device)
+        scale = 1.0 / math.sqrt(hd)
+        check(_lib.lib().tony_attention_fwd_bf16(ptr(qkv), ptr(out), ptr(lse), B, S, nh, hd, int(causal),
+                                                 scale, cur_stream()), "tony_attention_fwd_bf16")
+        return out, ("tcgen05", qkv, out, lse, (B, S, nh, hd, int(causal), scale))
+    B, S, _, nh, hd = qkv.shape
+    with torch.enable_grad():
+        q, k, v = (qkv[:, :, i].transpose(1, 2).detach().requires_grad_() for i in range(3))
+        o = torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=causal)
+    return o.detach().transpose(1, 2).reshape(B, S, nh * hd), ("library", q, k, v, o, (B, S, nh, hd))
+
+
+def _attention_core_backward(saved, dout):
+    """-> packed gradient ``[B, S, 3, heads, head_dim]``."""
+    if saved[0] == "tcgen05":
+        _, qkv, out, lse, (B, S, nh, hd, causal, scale) = saved
+        dout = dout.contiguous()
+        delta = torch.empty_like(lse)
+        dqkv = torch.empty_like(qkv)
+        check(_lib.lib().tony_attention_bwd_bf16(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(delta),
+                                                 ptr(dqkv), B, S, nh, hd, causal, scale, cur_stream()),
+              "tony_attention_bwd_bf16")
+        return dqkv
+    _, q, k, v, o, (B, S, nh, hd) = saved
+    do = dout.reshape(B, S, nh, hd).transpose(1, 2)
+    dq, dk, dv = torch.autograd.grad(o, (q, k, v), do)
+    dqkv = torch.empty((B, S, 3, nh, hd), dtype=dout.dtype, device=dout.device)
+    parts = [t.transpose(1, 2) for t in (dq, dk, dv)]          # [B, S, nh, hd] views
+    H = nh * hd
+
+    def rows_view(t):
+        ok = t.stride(3) == 1 and t.stride(2) == hd and t.stride(0) == S * t.stride(1)
+        return t.stride(1) if ok and t.stride(1) % 8 == 0 and t.data_ptr() % 16 == 0 else None
+
+    strides = [rows_view(t) for t in parts]
+    if dout.dtype == torch.bfloat16 and H % 8 == 0 and all(st is not None for st in strides):
+        check(_lib.lib().tony_pack3_rows(ptr(parts[0]), ptr(parts[1]), ptr(parts[2]), strides[0],
+                                         strides[1], strides[2], ptr(dqkv), B * S, H, cur_stream()),
+              "tony_pack3_rows")
+    else:
+        for i, t in enumerate(parts):
+            dqkv[:, :, i].copy_(t)
+    return dqkv
+
+
+class _AttentionBlockFn(torch.autograd.Function):
+    """y = x + Wo . attention(Wqkv x + bqkv) + bo as ONE autograd node (post-LN transformer block).
+
+    Besides the epilogue fusions of the two projections, owning the whole block lets backward
+    add the residual branch's gradient in the epilogue of the LAST dgrad GEMM
+    (dx = dqkv . Wqkv + dy), so autograd never runs an elementwise add over the activation to
+    merge the two branches."""
+
+    @staticmethod
+    def forward(ctx, x, wqkv, bqkv, wo, bo, heads, causal):
+        B, S, H = x.shape
+        x2 = x.reshape(B * S, H)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        qkv = gemm(x2, wqkv, flags=EPI_BIAS if bqkv is not None else 0, bias=bqkv)
+        o, saved = _attention_core_forward(qkv.view(B, S, 3, heads, H // heads), causal)
+        o2 = o.reshape(B * S, H)
+        y = gemm(o2, wo, flags=(EPI_BIAS if bo is not None else 0) | EPI_RESIDUAL, bias=bo, aux=x2)
+        ctx.save_for_backward(x2, wqkv, wo, o2)
+        ctx.saved_core = saved
+        ctx.bqkv, ctx.bo = bqkv, bo
+        ctx.shape = (B, S, H)
+        return y.view(B, S, H)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, wqkv, wo, o2 = ctx.saved_tensors
+        B, S, H = ctx.shape
+        dy2 = dy.reshape(B * S, H)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dwo = _weight_grad(dy2, o2, wo)
+        dbo = _bias_grad(dy2, ctx.bo)
+        do = gemm(dy2, wo, b_mn=True)
+        dqkv = _attention_core_backward(ctx.saved_core, do.view(B, S, H)).view(B * S, 3 * H)
+        ctx.saved_core = None
+        dwqkv = _weight_grad(dqkv, x2, wqkv)
+        dbqkv = _bias_grad(dqkv, ctx.bqkv)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm(dqkv, wqkv, b_mn=True, flags=EPI_RESIDUAL, aux=dy2).view(B, S, H)
+        return dx, dwqkv, dbqkv, dwo, dbo, None, None
+
+
+def attention_block(x, wqkv, bqkv, wo, bo, heads: int, causal: bool = False):
+    """``x + out_proj(attention(qkv_proj(x)))`` for bf16 CUDA tensors (see ``_AttentionBlockFn``)."""
+    return _AttentionBlockFn.apply(x, wqkv, bqkv, wo, bo, heads, causal)
 
 
 def packed_attention(qkv, causal: bool = False):
