@@ -132,6 +132,20 @@ int tony_attention_bwd_bf16(const void* qkv, const void* out, const void* dout, 
 int tony_pack3_rows(const void* a, const void* b, const void* c, long long lda, long long ldb,
                     long long ldc, void* out, int rows, int row_elems, void* stream);
 
+/* ---- fused input embedding (word + token-type + position) ------------------------------ */
+/* out[t,:] = word[ids[t],:] (+ type[tt[t],:]) (+ pos[t mod seq,:]); type / pos may be NULL.
+ * ids / tt are int64.  Replaces three gathers + two adds of a stock embedding stack. */
+int tony_embedding_sum_fwd(const void* word, const long long* ids, const void* type, const long long* tt,
+                           const void* pos, void* out, long long tokens, int seq, int H, void* stream);
+/* One pass over dy -> all three gradients.  dword (may be NULL): bf16x2 reductions into
+ * [vocab_rows, H], zero-filled first unless word_accumulate; dtype (may be NULL, n_types <= 4):
+ * masked column sums through `scratch`; dpos (may be NULL): [seq, H] sums over the batch. */
+size_t tony_embedding_bwd_scratch_bytes(int seq, int n_types, int H);
+int tony_embedding_sum_bwd(const void* dy, const long long* ids, const long long* tt, void* dword,
+                           long long vocab_rows, int word_accumulate, void* dtype, int n_types,
+                           int type_accumulate, void* dpos, int pos_accumulate, float* scratch,
+                           size_t scratch_bytes, int batch, int seq, int H, void* stream);
+
 /* ---- optimizers on flat buffers ------------------------------------------------------ */
 /* AdamW / Adam over n elements: fp32 master weights + moments, bf16 gradients in, bf16
  * weights out.  wd_mask (optional) has one byte per 256 elements: 0 = no weight decay.

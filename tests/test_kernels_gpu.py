@@ -389,3 +389,29 @@ def test_residual_blocks_match_unfused_composition():
 
     for got, want in zip(run(True), run(False)):
         _close(got, want, rel=3e-2)
+
+
+@pytest.mark.parametrize("with_type", [True, False])
+def test_embedding_sum_forward_backward(with_type):
+    """Fused word + type + position embedding vs. fp32 gathers; small vocabulary so many tokens
+    collide on the same word row (exercises the bf16x2 reductions)."""
+    torch.manual_seed(5)
+    B, S, H, V, P = 4, 128, 512, 97, 160
+    ids = torch.randint(0, V, (B, S), device=DEV)
+    tt = torch.randint(0, 2, (B, S), device=DEV) if with_type else None
+    word, typ, pos = _rand(V, H), (_rand(2, H) if with_type else None), _rand(P, H)
+    leaves = [t.clone().requires_grad_() for t in (word, typ, pos) if t is not None]
+    w, ty, ps = (leaves[0], leaves[1], leaves[2]) if with_type else (leaves[0], None, leaves[1])
+    out = F.embedding_sum(ids, tt, w, ty, ps)
+    ref_leaves = [t.float().requires_grad_() for t in (word, typ, pos) if t is not None]
+    rw, rty, rps = (ref_leaves[0], ref_leaves[1], ref_leaves[2]) if with_type else (ref_leaves[0], None, ref_leaves[1])
+    ref = rw[ids] + rps[:S].unsqueeze(0)
+    if with_type:
+        ref = ref + rty[tt]
+    _close(out, ref, rel=1e-2)
+    g = _rand(B, S, H, scale=0.1)
+    out.backward(g)
+    ref.backward(g.float())
+    for got, want in zip(leaves, ref_leaves):
+        _close(got.grad, want.grad, rel=2e-2)
+    assert ps.grad[S:].abs().max().item() == 0.0

@@ -80,9 +80,13 @@ class BertForPreTraining(nn.Module):
     def forward(self, input_ids, token_type_ids, masked_positions, masked_labels, nsp_labels):
         """Returns the summed MLM + NSP loss (scalar, fp32)."""
         B, S = input_ids.shape
-        pos_ids = torch.arange(S, device=input_ids.device)
-        x = self.word(input_ids) + self.tok_type(token_type_ids)
-        x = x + self.pos(pos_ids)
+        if F.embedding_sum_supported(self.word.weight, self.tok_type.weight) and input_ids.dtype == torch.int64:
+            x = F.embedding_sum(input_ids, token_type_ids, self.word.weight, self.tok_type.weight,
+                                self.pos.weight)
+        else:
+            pos_ids = torch.arange(S, device=input_ids.device)
+            x = self.word(input_ids) + self.tok_type(token_type_ids)
+            x = x + self.pos(pos_ids)
         x = self.emb_ln(x)
         for layer in self.layers:
             x = layer(x)

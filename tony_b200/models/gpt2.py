@@ -68,7 +68,10 @@ class GPT2LMHead(nn.Module):
 
     def forward(self, input_ids, labels):
         B, S = input_ids.shape
-        x = self.wte(input_ids) + self.wpe(torch.arange(S, device=input_ids.device))
+        if F.embedding_sum_supported(self.wte.weight) and input_ids.dtype == torch.int64:
+            x = F.embedding_sum(input_ids, None, self.wte.weight, None, self.wpe.weight)
+        else:
+            x = self.wte(input_ids) + self.wpe(torch.arange(S, device=input_ids.device))
         for blk in self.blocks:
             x = blk(x)
         x = self.ln_f(x)

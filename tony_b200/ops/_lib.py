@@ -139,6 +139,11 @@ def _declare(lib) -> None:
                                                  c_int, c_float, c_float, c_float, c_float, c_float, c_float,
                                                  c_float, c_float, vp, c_int, c_uint, c_int, vp]
     lib.tony_pack3_rows.argtypes = [vp, vp, vp, c_longlong, c_longlong, c_longlong, vp, c_int, c_int, vp]
+    lib.tony_embedding_sum_fwd.argtypes = [vp, vp, vp, vp, vp, vp, c_longlong, c_int, c_int, vp]
+    lib.tony_embedding_bwd_scratch_bytes.argtypes = [c_int, c_int, c_int]
+    lib.tony_embedding_bwd_scratch_bytes.restype = c_size_t
+    lib.tony_embedding_sum_bwd.argtypes = [vp, vp, vp, vp, c_longlong, c_int, vp, c_int, c_int, vp, c_int, vp,
+                                           c_size_t, c_int, c_int, c_int, vp]
     lib.tony_attention_fwd_bf16.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_float, vp]
     lib.tony_attention_bwd_bf16.argtypes = [vp, vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int,
                                             c_float, vp]

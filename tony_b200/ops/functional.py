@@ -427,6 +427,66 @@ def embedding(weight, idx):
     return _EmbeddingFn.apply(weight, idx)
 
 
+class _EmbeddingSumFn(torch.autograd.Function):
+    """``word[ids] (+ type[tt]) (+ pos[0:S])`` in one kernel; backward makes all three gradients in
+    one pass over dy (csrc/embedding.cu) and writes them straight into the gradient bucket slots."""
+
+    @staticmethod
+    def forward(ctx, ids, tt, word, type_w, pos_w):
+        B, S = ids.shape
+        H = word.shape[1]
+        ids = ids.contiguous()
+        tt = tt.contiguous() if tt is not None else None
+        out = torch.empty((B, S, H), dtype=word.dtype, device=word.device)
+        check(_lib.lib().tony_embedding_sum_fwd(ptr(word), ptr(ids), ptr(type_w) if type_w is not None else None,
+                                                ptr(tt) if tt is not None else None,
+                                                ptr(pos_w) if pos_w is not None else None, ptr(out), B * S, S, H,
+                                                cur_stream()), "tony_embedding_sum_fwd")
+        ctx.save_for_backward(ids, tt) if tt is not None else ctx.save_for_backward(ids)
+        ctx.params = (word, type_w, pos_w)
+        ctx.dims = (B, S, H)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        saved = ctx.saved_tensors
+        ids, tt = saved[0], (saved[1] if len(saved) > 1 else None)
+        word, type_w, pos_w = ctx.params
+        B, S, H = ctx.dims
+        dy = dy.contiguous()
+        dests, bufs, accs = [], [], []
+        for prm in (word, type_w, pos_w):
+            if prm is None:
+                dests.append(None), bufs.append(None), accs.append(0)
+                continue
+            d = _GradDest(prm)
+            buf = d.tensor if d.tensor is not None else torch.empty_like(prm)
+            dests.append(d), bufs.append(buf), accs.append(1 if d.accumulate else 0)
+        if pos_w is not None and not accs[2] and pos_w.shape[0] > S:
+            bufs[2][S:].zero_()          # positions past this batch's length get no gradient
+        n_types = type_w.shape[0] if type_w is not None else 0
+        nbytes = _lib.lib().tony_embedding_bwd_scratch_bytes(S, n_types, H) if type_w is not None else 0
+        scratch = workspace("embedding_bwd", nbytes, dy.device) if nbytes else None
+        check(_lib.lib().tony_embedding_sum_bwd(
+            ptr(dy), ptr(ids), ptr(tt) if tt is not None else None, ptr(bufs[0]), word.shape[0], accs[0],
+            ptr(bufs[1]) if type_w is not None else None, n_types, accs[1],
+            ptr(bufs[2]) if pos_w is not None else None, accs[2],
+            ptr(scratch) if scratch is not None else None, nbytes, B, S, H, cur_stream()),
+            "tony_embedding_sum_bwd")
+        grads = [d.finish(b) if d is not None else None for d, b in zip(dests, bufs)]
+        return None, None, grads[0], grads[1], grads[2]
+
+
+def embedding_sum(ids, tt, word, type_w=None, pos_w=None):
+    """Fused input embedding for ``ids`` ``[B, S]`` (int64): ``word[ids] + type_w[tt] + pos_w[:S]``."""
+    return _EmbeddingSumFn.apply(ids, tt, word, type_w, pos_w)
+
+
+def embedding_sum_supported(word, type_w=None) -> bool:
+    return (word.is_cuda and word.dtype == torch.bfloat16 and word.shape[1] % 8 == 0
+            and (type_w is None or type_w.shape[0] <= 4))
+
+
 class _BroadcastAddParamFn(torch.autograd.Function):
     """x + p where p broadcasts over the leading dims (position embeddings)."""
 
