@@ -10,7 +10,8 @@ For N > 1 launch with ``python -m torch.distributed.run --nproc-per-node N ... b
 Rank 0 prints ONE JSON line.  ``value`` is whole-job samples/s with device-resident inputs,
 timed with CUDA events bracketed by barrier+synchronize, max over ranks; ``e2e`` is the
 same metric through the public ``tony_b200.runtime.Trainer.step`` call, including every
-step's pinned-host -> device input copy and device -> host loss read.
+step's pinned-host -> device input copy and device -> host loss read (both arms read step i's
+loss after step i+1 has been enqueued: ``Trainer.step_async``).
 
 ``--impl stock`` runs the identical model on stock PyTorch (cuBLAS/ATen/NCCL DDP/fused
 AdamW) — the data plane a TonY-launched job uses today.  ``--impl reference`` reports that
@@ -110,6 +111,8 @@ def parse_args(argv=None):
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default 32 BERT / 8 GPT-2)")
     ap.add_argument("--seq", type=int, default=0)
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--cuda-graph", type=int, default=-1,
+                    help="1/0: replay forward+backward as one CUDA graph (default: Trainer's own default)")
     ap.add_argument("--bucket-mb", type=float, default=64.0)
     ap.add_argument("--comm-ctas", type=int, default=32)
     ap.add_argument("--skip-e2e", action="store_true")
@@ -195,6 +198,25 @@ class StockTrainer:
     def step(self, b):
         return float(self.step_device(self.to_device(b)).item())
 
+    def step_async(self, b):
+        """Same one-step-late loss read as Trainer.step_async, so both arms are timed alike."""
+        torch = self.torch
+        loss = self.step_device(self.to_device(b))
+        if not hasattr(self, "_ring"):
+            self._ring, self._n = [torch.empty(1, dtype=torch.float32, pin_memory=True) for _ in range(4)], 0
+        host = self._ring[self._n % 4]
+        self._n += 1
+        host.copy_(loss.detach().reshape(1).float(), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+
+        class _Fut:
+            def result(_self):
+                ev.synchronize()
+                return float(host[0])
+
+        return _Fut()
+
 
 def main(argv=None) -> int:
     args = parse_args(argv)
@@ -220,7 +242,8 @@ def main(argv=None) -> int:
     if args.impl == "ours":
         from tony_b200.ops import _lib
 
-        kw = dict(overlap=not args.no_overlap, bucket_mb=args.bucket_mb, comm_ctas=args.comm_ctas, device=device)
+        kw = dict(overlap=not args.no_overlap, bucket_mb=args.bucket_mb, comm_ctas=args.comm_ctas, device=device,
+                  cuda_graph=None if args.cuda_graph < 0 else bool(args.cuda_graph))
         if args.model == "resnet50":
             model = model.to(device=device, dtype=torch.bfloat16)
             trainer = runtime.Trainer(model, lr=0.1, optimizer="sgd", weight_decay=1e-4, generic_hooks=True, **kw)
@@ -273,8 +296,18 @@ def main(argv=None) -> int:
         h2d = sum(v.numel() * v.element_size() for v in host[0].values())
         sync_all()
         e0.record()
-        for i in range(args.steps):
-            val = trainer.step(host[i % nb])
+        if hasattr(trainer, "step_async"):
+            # public pipelined API: step i's loss is read (D2H, pinned) after step i+1 is enqueued
+            pending = None
+            for i in range(args.steps):
+                fut = trainer.step_async(host[i % nb])
+                if pending is not None:
+                    val = pending.result()
+                pending = fut
+            val = pending.result()
+        else:
+            for i in range(args.steps):
+                val = trainer.step(host[i % nb])
         e1.record()
         sync_all()
         ms2 = torch.tensor([e0.elapsed_time(e1)], device=device)
@@ -306,6 +339,7 @@ def main(argv=None) -> int:
                        "optimizer": "AdamW (fp32 master + moments, sharded 1/N per rank)" if args.impl == "ours"
                        else "torch.optim.AdamW(fused=True), fp32 params + autocast",
                        "dropout": 0.0,
+                       "cuda_graph": bool(getattr(trainer, "cuda_graph", False)),
                        "l2": "no explicit flush: every step streams >0.67 GB of weights plus GBs of "
                              "activations, far larger than the 126 MB L2; 4 distinct input batches rotate"},
             "clocks": clocks,

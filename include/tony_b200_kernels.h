@@ -32,6 +32,9 @@ const char* tony_last_error(void);
 int tony_version(void);
 /* Number of kernels this library has launched in this process (for bench accounting). */
 unsigned long long tony_launch_count(void);
+/* Credit n launches that did not go through this library's host entry points: the replay of a
+ * CUDA graph that captured them (the counter is bench accounting only). */
+void tony_launch_count_add(unsigned long long n);
 
 /* ---- GEMM epilogue flags ------------------------------------------------------------ */
 #define TONY_EPI_BIAS 0x001u        /* + bias[n]                                   */

@@ -41,6 +41,7 @@ extern "C" const char* tony_last_error(void) {
 extern "C" int tony_version(void) { return 100; }
 
 extern "C" unsigned long long tony_launch_count(void) { return g_launches.load(); }
+extern "C" void tony_launch_count_add(unsigned long long n) { g_launches.fetch_add(n); }
 
 extern "C" int tony_symm_alloc(size_t bytes, void** ptr) {
     if (!ptr || bytes == 0) return TONY_ERR_INVALID;

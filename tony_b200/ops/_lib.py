@@ -89,6 +89,8 @@ def _declare(lib) -> None:
     lib.tony_last_error.restype = c_char_p
     lib.tony_version.restype = c_int
     lib.tony_launch_count.restype = c_ulonglong
+    lib.tony_launch_count_add.argtypes = [c_ulonglong]
+    lib.tony_launch_count_add.restype = None
     lib.tony_gemm_bf16.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_longlong,
                                    c_longlong, c_longlong, c_uint, c_float, vp, vp, c_longlong, vp,
                                    vp, c_size_t, vp]

@@ -295,8 +295,10 @@ class FusedOptimizer:
         self.comm_stream.wait_event(ev)
         self._launch(b, self.comm_stream, self.comm_ctas)
 
-    def step(self):
-        """Finish the step: launch whatever backward did not, then join the comm stream."""
+    def step(self, grads_complete: bool = False):
+        """Finish the step: launch whatever backward did not, then join the comm stream.
+        ``grads_complete``: every gradient slot was written by device work the host did not see
+        (a replayed CUDA graph), so the per-slot bookkeeping is skipped."""
         st = self.store
         cur = torch.cuda.current_stream()
         leftovers = getattr(st, "_pending_hook_grads", None)
@@ -311,7 +313,7 @@ class FusedOptimizer:
             if b.launched:
                 continue
             for s in b.slots:
-                if s.written == 0:
+                if s.written == 0 and not grads_complete:
                     s.grad_view.zero_()  # parameter unused this step
             if self.overlap:
                 self._bucket_ready(b)
