@@ -344,3 +344,65 @@ def test_timeline_is_recorded(cluster):
     events = [e["event"] for e in tl]
     assert events[0] == "am_started" and "gang_barrier_open" in events and events.count("task_registered") == 2
     assert all(a["t_ms"] <= b["t_ms"] for a, b in zip(tl, tl[1:]))
+
+
+def test_am_throwing_exception_fails_the_app(cluster):
+    """TestTonyE2E.testAMThrowExceptionCrashTonYShouldFail: an exception inside the AM's monitor
+    loop (not a process crash) must still end the application as FAILED."""
+    rc, _ = run(cluster, "exit_0.py", ["tony.worker.instances=1"], env={"TEST_AM_THROW_EXCEPTION_CRASH": "1"})
+    assert rc == -1
+
+
+def test_horovod_debug_mode_runs_user_driver(cluster):
+    """TestTonyE2E.testTonyHorovodWithDebugModeShouldPass: in driver debug mode the user's own
+    driver command runs instead of the built-in rendezvous driver (same port-file contract)."""
+    import sys
+
+    from tony_b200.runtimes import horovod_driver as hd
+
+    driver_cmd = f"{sys.executable} {os.path.abspath(hd.__file__)} -t -p 9999 -w $CLUSTER_WORKER_LIST -o $DRIVER_OUTPUT_PATH"
+    rc, client = run(cluster, "check_horovod_env.py",
+                     ["tony.application.framework=horovod", "tony.worker.instances=2",
+                      "tony.horovod.driver.mode.debug=true", "tony.driver.command=" + driver_cmd])
+    assert rc == 0
+    assert statuses(client)["driver:0"] == TaskStatus.FINISHED
+    # debug mode without a driver command is rejected up front
+    rc, _ = run(cluster, "check_horovod_env.py",
+                ["tony.application.framework=horovod", "tony.worker.instances=2",
+                 "tony.horovod.driver.mode.debug=true"])
+    assert rc == -1
+
+
+def test_final_conf_is_frozen_for_am_and_tasks(cluster):
+    """TestTonyE2E.testTonyFinalConf: everything the client resolved (CLI --conf included) is in
+    the tony-final.xml of the application directory, which is what the AM and the tasks read."""
+    from tony_b200.conf.configuration import TonyConfiguration
+
+    rc, client = run(cluster, "exit_0.py", ["tony.worker.instances=2", "tony.application.name=final-conf-check",
+                                            "tony.worker.gpus=0"])
+    assert rc == 0
+    final = TonyConfiguration.from_final_xml(os.path.join(client.app_dir, "tony-final.xml"))
+    assert final.get("tony.application.name") == "final-conf-check"
+    assert final.get_int("tony.worker.instances", 0) == 2
+    assert final.get("tony.task.heartbeat-interval-ms") == "100"
+    # a hadoop-classpath style entry that does not exist is recorded, not fatal
+    # (testTonyFinalConfWithNonExistentHDFSClasspath)
+    rc, client = run(cluster, "exit_0.py", ["tony.worker.instances=1",
+                                            "tony.application.hadoop.location=/no/such/hadoop"])
+    assert rc == 0
+    final = TonyConfiguration.from_final_xml(os.path.join(client.app_dir, "tony-final.xml"))
+    assert final.get("tony.application.hadoop.location") == "/no/such/hadoop"
+
+
+def test_client_survives_am_that_never_comes_up(cluster, tmp_path):
+    """TestTonyE2E.testNullAMRpcClient: with no AM endpoint the client's monitor loop must end in
+    failure instead of raising or spinning forever."""
+    client = cluster.new_client()
+    assert client.init(["--python_binary_path", PY, "--executes", os.path.join(SCRIPTS, "exit_0.py"),
+                        "--conf", "tony.worker.instances=1"])
+    os.environ["TEST_AM_NEVER_STARTS"] = "1"
+    try:
+        rc = client.start()
+    finally:
+        os.environ.pop("TEST_AM_NEVER_STARTS", None)
+    assert rc == -1

@@ -265,9 +265,14 @@ class TonyClient:
             self.secret = None
         out = open(os.path.join(self.app_dir, "amstdout.log"), "ab")
         err = open(os.path.join(self.app_dir, "amstderr.log"), "ab")
+        am_cmd = [sys.executable, "-m", "tony_b200.am.application_master", "--app_dir", self.app_dir,
+                  "--app_id", self.app_id, "--user", U.current_user()]
+        if os.environ.get("TEST_AM_NEVER_STARTS"):
+            # fault injection: the AM container dies before it publishes an RPC endpoint
+            # (the client then has no RPC proxy at all: TestTonyE2E.testNullAMRpcClient)
+            am_cmd = [sys.executable, "-c", "import sys; sys.exit(3)"]
         self.am_proc = subprocess.Popen(
-            [sys.executable, "-m", "tony_b200.am.application_master", "--app_dir", self.app_dir,
-             "--app_id", self.app_id, "--user", U.current_user()],
+            am_cmd,
             env=env, cwd=self.app_dir, stdout=out, stderr=err, start_new_session=True)
         out.close()
         err.close()
