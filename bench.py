@@ -224,13 +224,19 @@ def main(argv=None) -> int:
         print(json.dumps({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE}))
         return 0
 
+    # Libraries (NCCL's version banner, cuDNN notices) write to the C-level stdout; the contract is
+    # ONE JSON line there.  Point fd 1 at stderr for the run and keep the real stdout for the result.
+    sys.stdout.flush()
+    result_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     import torch.distributed as dist
 
     from tony_b200 import runtime
 
     if not torch.cuda.is_available():
-        print(json.dumps({"error": "no CUDA device; bench.py needs a B200"}))
+        os.write(result_fd, (json.dumps({"error": "no CUDA device; bench.py needs a B200"}) + "\n").encode())
         return 1
     rank, world, device = runtime.init()
     if world != args.gpus:
@@ -349,7 +355,8 @@ def main(argv=None) -> int:
             "mfu_of_measured_sustained_peak": round(tflops / denom, 3),
             "loss_after_warmup": round(warm_loss, 4), "loss_final": round(final_loss, 4),
         }
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.write(result_fd, (json.dumps(out) + "\n").encode())
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -28,6 +28,8 @@ extern "C" {
 #define TONY_ERR_TOO_LARGE 4
 #define TONY_ERR_TIMEOUT 5
 
+#define TONY_MAX_RANKS 8   /* one NVSwitch domain */
+
 const char* tony_last_error(void);
 int tony_version(void);
 /* Number of kernels this library has launched in this process (for bench accounting). */
@@ -149,6 +151,28 @@ int tony_embedding_sum_bwd(const void* dy, const long long* ids, const long long
                            int type_accumulate, void* dpos, int pos_accumulate, float* scratch,
                            size_t scratch_bytes, int batch, int seq, int H, void* stream);
 
+/* ---- row-sharded embedding bag over peer memory (recommender, ps ownership) ------------- */
+/* Row r of every field lives on rank r % world at local row r / world; `table[r]` / `grad[r]`
+ * are rank r's shard ([fields, rows_per_shard, row_elems] bf16) mapped into this process
+ * (tony_symm_alloc + tony_ipc_open, or the VMM heap).  A row is [deep_elems | rest]. */
+typedef struct {
+    void* table[TONY_MAX_RANKS];
+    void* grad[TONY_MAX_RANKS];
+    int rank, world;
+} tony_embbag_comm;
+/* deep: [batch, fields * deep_elems]; rest: [batch, fields, row_elems - deep_elems].  Rows come
+ * straight from the owners' memory (lookup + dispatch in one kernel).  The caller orders this
+ * after every owner's last table update (tony_symm_barrier). */
+int tony_embbag_gather(const tony_embbag_comm* comm, const long long* ids, long long batch, int fields,
+                       long long rows_per_shard, int row_elems, int deep_elems, void* deep, void* rest,
+                       void* stream);
+/* Adds every gradient row into the owner's gradient shard with system-scope bf16x2 reductions
+ * (combine + sparse accumulation in one kernel).  Shards must be zero before the first scatter of
+ * a step and the owner may read them only after a barrier that follows every rank's scatter. */
+int tony_embbag_scatter(const tony_embbag_comm* comm, const long long* ids, long long batch, int fields,
+                        long long rows_per_shard, int row_elems, int deep_elems, const void* ddeep,
+                        const void* drest, void* stream);
+
 /* ---- optimizers on flat buffers ------------------------------------------------------ */
 /* AdamW / Adam over n elements: fp32 master weights + moments, bf16 gradients in, bf16
  * weights out.  wd_mask (optional) has one byte per 256 elements: 0 = no weight decay.
@@ -175,7 +199,6 @@ int tony_ipc_open(const unsigned char* handle, void** peer_ptr);
 int tony_ipc_close(void* peer_ptr);
 
 /* ---- fused gradient collective + optimizer (K1 / K2 in SURVEY.md section 8) ---------- */
-#define TONY_MAX_RANKS 8
 #define TONY_OPT_ADAMW 0
 #define TONY_OPT_SGD 1
 typedef struct tony_fused_comm {

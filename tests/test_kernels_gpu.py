@@ -415,3 +415,43 @@ def test_embedding_sum_forward_backward(with_type):
     for got, want in zip(leaves, ref_leaves):
         _close(got.grad, want.grad, rel=2e-2)
     assert ps.grad[S:].abs().max().item() == 0.0
+
+
+def test_sharded_embedding_bag_single_gpu():
+    """K9 at world = 1: gather = row lookup into the concatenated activation, scatter = sparse
+    accumulation into the gradient shard, tony_step = AdamW on the shard."""
+    from tony_b200.parallel.ps import ShardedEmbeddingBag
+
+    torch.manual_seed(2)
+    Fd, V, D, R, B = 3, 50, 16, 8, 64
+    bag = ShardedEmbeddingBag(Fd, V, D, R, std=0.5, device=DEV, seed=7)
+    bag.tony_configure(lr=0.1)
+    gen = torch.Generator(device=DEV)
+    full = []
+    for f in range(Fd):
+        gen.manual_seed(7 + f)
+        full.append((torch.randn(V, D + R, generator=gen, device=DEV) * 0.5).to(torch.bfloat16).float())
+    ids = torch.randint(0, V, (B, Fd), device=DEV)
+    deep, rest = bag(ids)
+    ref_deep = torch.cat([full[f][ids[:, f], :D] for f in range(Fd)], dim=1)
+    ref_rest = torch.stack([full[f][ids[:, f], D:] for f in range(Fd)], dim=1)
+    assert torch.equal(deep.float(), ref_deep) and torch.equal(rest.float(), ref_rest)
+    gd, gr = _rand(B, Fd * D, scale=0.1), _rand(B, Fd, R, scale=0.1)
+    torch.autograd.backward([deep, rest], [gd, gr])
+    ref_grad = [torch.zeros(V, D + R, device=DEV) for _ in range(Fd)]
+    for f in range(Fd):
+        ref_grad[f].index_add_(0, ids[:, f], torch.cat([gd[:, f * D:(f + 1) * D], gr[:, f]], dim=1).float())
+    n = Fd * bag.rows_per_shard * bag.row_elems
+    got = bag.grad[:n].view(Fd, V, D + R).float()
+    for f in range(Fd):
+        _close(got[f], ref_grad[f], rel=3e-2)
+    before = bag.full_table(0).float().clone()
+    bag.tony_step()
+    after = bag.full_table(0).float()
+    touched = ref_grad[0].abs().sum(1) > 0
+    assert torch.equal(after[~touched], before[~touched])            # no weight decay: untouched rows stay
+    step = (before - after)[touched]
+    big = ref_grad[0][touched].abs() > 1e-2
+    # first AdamW step moves every coordinate by ~lr in the direction of its gradient
+    assert ((step[big] * torch.sign(ref_grad[0][touched][big])) > 0.05).all()
+    assert bag.grad.abs().max().item() == 0.0                         # shard cleared for the next step

@@ -36,6 +36,7 @@ SOURCES = [
     "embedding.cu",
     "symm_vmm.cu",
     "attention.cu",
+    "embbag.cu",
 ]
 
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]

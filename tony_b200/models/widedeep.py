@@ -35,13 +35,26 @@ class WideDeepConfig:
 
 
 class WideDeep(nn.Module):
-    def __init__(self, c: WideDeepConfig, device=None, sharded: bool = True):
+    """``sparse="bag"`` (default on CUDA) keeps the categorical tables row-sharded across the ranks
+    (:class:`tony_b200.parallel.ps.ShardedEmbeddingBag`: lookups pull rows from their owners over
+    NVLink, gradients are reduced into the owners' shards, each owner updates only its rows);
+    ``sparse="dense"`` is the replicated nn.Embedding-style layout with dense gradients."""
+
+    def __init__(self, c: WideDeepConfig, device=None, sharded: bool = True, sparse: str = "auto"):
         super().__init__()
         self.config = c
-        self.deep_tables = nn.ModuleList(Embedding(c.vocab_per_field, c.embed_dim, std=0.01, device=device)
-                                         for _ in range(c.num_fields))
-        self.wide_tables = nn.ModuleList(Embedding(c.vocab_per_field, 8, std=0.01, device=device)
-                                         for _ in range(c.num_fields))
+        if sparse == "auto":
+            sparse = "bag" if (device is not None and torch.device(device).type == "cuda") else "dense"
+        self.sparse = sparse
+        if sparse == "bag":
+            from ..parallel.ps import ShardedEmbeddingBag
+
+            self.bag = ShardedEmbeddingBag(c.num_fields, c.vocab_per_field, c.embed_dim, 8, std=0.01, device=device)
+        else:
+            self.deep_tables = nn.ModuleList(Embedding(c.vocab_per_field, c.embed_dim, std=0.01, device=device)
+                                             for _ in range(c.num_fields))
+            self.wide_tables = nn.ModuleList(Embedding(c.vocab_per_field, 8, std=0.01, device=device)
+                                             for _ in range(c.num_fields))
         in_dim = c.num_fields * c.embed_dim + c.dense_features
         self.in_dim = (in_dim + 7) // 8 * 8
         layers = []
@@ -56,14 +69,19 @@ class WideDeep(nn.Module):
     def forward(self, sparse_ids, dense, labels):
         """sparse_ids [B, fields] int64, dense [B, dense_features] bf16, labels [B] int64."""
         B = sparse_ids.shape[0]
-        deep = [t(sparse_ids[:, i]) for i, t in enumerate(self.deep_tables)]
-        x = torch.cat(deep + [dense], dim=1)
+        if self.sparse == "bag":
+            deep_cat, rest = self.bag(sparse_ids)
+            x = torch.cat([deep_cat, dense], dim=1)
+            wide = rest.sum(dim=1)                                                   # [B, 8], cols 0..1 used
+        else:
+            deep = [t(sparse_ids[:, i]) for i, t in enumerate(self.deep_tables)]
+            x = torch.cat(deep + [dense], dim=1)
+            wide = sum(t(sparse_ids[:, i]) for i, t in enumerate(self.wide_tables))
         if x.shape[1] < self.in_dim:
             x = torch.nn.functional.pad(x, (0, self.in_dim - x.shape[1]))
         for layer in self.tower:
             x = layer(x)
         logits = self.head(x)
-        wide = sum(t(sparse_ids[:, i]) for i, t in enumerate(self.wide_tables))   # [B, 8], cols 0..1 used
         return F.softmax_cross_entropy(logits + wide, labels, vocab=2)
 
 

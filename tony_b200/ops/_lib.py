@@ -50,6 +50,12 @@ class KernelError(RuntimeError):
     pass
 
 
+class EmbBagComm(Structure):
+    """Mirror of ``tony_embbag_comm``."""
+
+    _fields_ = [("table", c_void_p * MAX_RANKS), ("grad", c_void_p * MAX_RANKS), ("rank", c_int), ("world", c_int)]
+
+
 class NvlsComm(Structure):
     """Mirror of ``tony_nvls_comm``."""
 
@@ -146,6 +152,8 @@ def _declare(lib) -> None:
     lib.tony_embedding_bwd_scratch_bytes.restype = c_size_t
     lib.tony_embedding_sum_bwd.argtypes = [vp, vp, vp, vp, c_longlong, c_int, vp, c_int, c_int, vp, c_int, vp,
                                            c_size_t, c_int, c_int, c_int, vp]
+    lib.tony_embbag_gather.argtypes = [POINTER(EmbBagComm), vp, c_longlong, c_int, c_longlong, c_int, c_int, vp, vp, vp]
+    lib.tony_embbag_scatter.argtypes = [POINTER(EmbBagComm), vp, c_longlong, c_int, c_longlong, c_int, c_int, vp, vp, vp]
     lib.tony_attention_fwd_bf16.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_float, vp]
     lib.tony_attention_bwd_bf16.argtypes = [vp, vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int,
                                             c_float, vp]

@@ -116,3 +116,146 @@ class ShardedLinear(nn.Module):
 def ps_parameters(module: nn.Module):
     """Weights of every ShardedLinear in ``module`` (what to pass as ``ps_sharded``)."""
     return [m.weight for m in module.modules() if isinstance(m, ShardedLinear)]
+
+
+# ---------------------------------------------------------------------------------------
+# Row-sharded embedding bag (K9): ps ownership for the sparse side of the recommender
+# ---------------------------------------------------------------------------------------
+class SymmBarrier:
+    """A device-side barrier of its own (own flag words, own epoch counter) so users of symmetric
+    memory outside the gradient buckets never interleave with the fused optimizer's flag traffic."""
+
+    def __init__(self, device, group=None):
+        import torch.distributed as dist
+
+        from .symm import SymmBuffer, VmmBuffer, symm_mode
+
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.rank = dist.get_rank(group) if self.world > 1 else 0
+        self.epoch = 0
+        if self.world == 1:
+            return
+        Buf = VmmBuffer if symm_mode() == "vmm" else SymmBuffer
+        self._buf = Buf(1024, torch.int32, device, group)
+        self._buf.local.zero_()
+        c = _lib.FusedComm()
+        c.rank, c.world = self.rank, self.world
+        for r in range(self.world):
+            c.flags[r] = self._buf.peer_ptrs[r]
+        c.counter = self._buf.ptr + 2 * _lib.MAX_RANKS * 4
+        c.status = self._buf.ptr + 2 * _lib.MAX_RANKS * 4 + 64
+        self.c = c
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)
+
+    def __call__(self):
+        if self.world == 1:
+            return
+        self.epoch += 1
+        check(_lib.lib().tony_symm_barrier(ctypes.byref(self.c), self.epoch, cur_stream()), "tony_symm_barrier")
+
+
+class _EmbBagFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, anchor, ids, bag):
+        B, Fd = ids.shape
+        ids = ids.contiguous()
+        deep = torch.empty((B, Fd * bag.deep_dim), dtype=torch.bfloat16, device=ids.device)
+        rest = torch.empty((B, Fd, bag.rest_dim), dtype=torch.bfloat16, device=ids.device)
+        check(_lib.lib().tony_embbag_gather(ctypes.byref(bag.comm), ptr(ids), B, Fd, bag.rows_per_shard,
+                                            bag.row_elems, bag.deep_dim, ptr(deep), ptr(rest), cur_stream()),
+              "tony_embbag_gather")
+        ctx.bag, ctx.ids = bag, ids
+        return deep, rest
+
+    @staticmethod
+    def backward(ctx, ddeep, drest):
+        bag, ids = ctx.bag, ctx.ids
+        B, Fd = ids.shape
+        ddeep = ddeep.contiguous()
+        drest = drest.contiguous()
+        check(_lib.lib().tony_embbag_scatter(ctypes.byref(bag.comm), ptr(ids), B, Fd, bag.rows_per_shard,
+                                             bag.row_elems, bag.deep_dim, ptr(ddeep), ptr(drest), cur_stream()),
+              "tony_embbag_scatter")
+        bag._dirty = True
+        return None, None, None
+
+
+class ShardedEmbeddingBag(nn.Module):
+    """``fields`` categorical tables of ``vocab`` rows, each row ``[deep_dim | rest_dim]`` bf16,
+    row ``r`` owned by rank ``r % world`` (csrc/embbag.cu).  ``forward(ids[B, fields])`` returns the
+    concatenated deep activation ``[B, fields*deep_dim]`` and the per-field ``rest`` rows
+    ``[B, fields, rest_dim]`` (the "wide" logit contributions).  The tables are NOT ``nn.Parameter``s:
+    gradients arrive at the owners as NVLink reductions and ``tony_step`` (called by the Trainer after
+    backward) runs AdamW on the local shard only."""
+
+    def __init__(self, fields: int, vocab: int, deep_dim: int, rest_dim: int = 8, std: float = 0.01,
+                 device=None, group=None, seed: int = 1234):
+        super().__init__()
+        import torch.distributed as dist
+
+        from ..ops.optim import FlatAdamW
+        from .symm import SymmBuffer, VmmBuffer, symm_mode
+
+        if deep_dim % 8 or rest_dim % 8:
+            raise ValueError("deep_dim and rest_dim must be multiples of 8")
+        device = torch.device(device or "cuda")
+        self.fields, self.vocab, self.deep_dim, self.rest_dim = fields, vocab, deep_dim, rest_dim
+        self.row_elems = deep_dim + rest_dim
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.rank = dist.get_rank(group) if self.world > 1 else 0
+        self.rows_per_shard = (vocab + self.world - 1) // self.world
+        n = fields * self.rows_per_shard * self.row_elems
+        n_pad = (n + 255) // 256 * 256
+        if self.world > 1:
+            Buf = VmmBuffer if symm_mode() == "vmm" else SymmBuffer
+            self._tbuf = Buf(n_pad * 2, torch.bfloat16, device, group)
+            self._gbuf = Buf(n_pad * 2, torch.bfloat16, device, group)
+            self.table, self.grad = self._tbuf.local, self._gbuf.local
+            tptrs, gptrs = self._tbuf.peer_ptrs, self._gbuf.peer_ptrs
+        else:
+            self.table = torch.empty(n_pad, dtype=torch.bfloat16, device=device)
+            self.grad = torch.empty(n_pad, dtype=torch.bfloat16, device=device)
+            tptrs, gptrs = [self.table.data_ptr()], [self.grad.data_ptr()]
+        self.grad.zero_()
+        comm = _lib.EmbBagComm()
+        comm.rank, comm.world = self.rank, self.world
+        for r in range(self.world):
+            comm.table[r] = tptrs[r]
+            comm.grad[r] = gptrs[r]
+        self.comm = comm
+        # the same full table on every rank (seeded), of which this rank keeps rows rank::world
+        master = torch.zeros(n_pad, dtype=torch.float32, device=device)
+        view = master[:n].view(fields, self.rows_per_shard, self.row_elems)
+        gen = torch.Generator(device=device)
+        for f in range(fields):
+            gen.manual_seed(seed + f)
+            full = torch.randn(vocab, self.row_elems, generator=gen, device=device) * std
+            mine = full[self.rank::self.world]
+            view[f, : mine.shape[0]].copy_(mine)
+        self.table.copy_(master.to(torch.bfloat16))
+        self.opt = FlatAdamW(master, lr=1e-3, weight_decay=0.0)
+        self.barrier = SymmBarrier(device, group)
+        self.anchor = nn.Parameter(torch.zeros(8, dtype=torch.bfloat16, device=device))
+        self._dirty = False
+        self.barrier()
+
+    def tony_configure(self, lr: float, betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0):
+        self.opt.lr, self.opt.betas, self.opt.eps, self.opt.weight_decay = lr, betas, eps, weight_decay
+
+    def forward(self, ids):
+        return _EmbBagFn.apply(self.anchor, ids, self)
+
+    def tony_step(self):
+        """Owner-side update: wait for every rank's gradient reductions, AdamW on the local shard,
+        clear the shard, and release the next step's gathers."""
+        self.barrier()
+        self.opt.step(self.grad, self.table, grad_scale=1.0 / self.world)
+        self.grad.zero_()
+        self.barrier()
+        self._dirty = False
+
+    def full_table(self, field: int) -> torch.Tensor:
+        """Debug / tests: rows of ``field`` held by THIS rank, in global row order rank::world."""
+        n = self.fields * self.rows_per_shard * self.row_elems
+        return self.table[:n].view(self.fields, self.rows_per_shard, self.row_elems)[field]

@@ -126,13 +126,17 @@ class Trainer:
                                   comm_ctas=comm_ctas, broadcast=broadcast)
         self.copy_stream = torch.cuda.Stream(device=self.device)
         self.steps = 0
+        # modules that own state outside the flat parameter store (row-sharded embedding bags)
+        self._step_modules = [m for m in self.model.modules() if hasattr(m, "tony_step")]
+        for m in self._step_modules:
+            m.tony_configure(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
         # CUDA-graph mode: forward + backward (about 600 launches for BERT-large) are captured once
         # and replayed; the fused reduce+optimizer launches stay outside the graph because their
         # arguments change every step (bias corrections, flag epochs).  Needs a model whose
         # gradients are all produced by this package's ops (no autograd hooks) and static shapes.
         if cuda_graph is None:
             cuda_graph = os.environ.get("TONY_B200_CUDA_GRAPH", "0") == "1"
-        self.cuda_graph = bool(cuda_graph) and not generic_hooks and not ps_sharded
+        self.cuda_graph = bool(cuda_graph) and not generic_hooks and not ps_sharded and not self._step_modules
         self._graph = None
         self._graph_kernels = 0
         self._static_in: Optional[Dict[str, "object"]] = None
@@ -190,6 +194,8 @@ class Trainer:
         nvtx.range_pop()
         nvtx.range_push("tony.optimizer_join")
         self.opt.step()
+        for m in self._step_modules:
+            m.tony_step()
         nvtx.range_pop()
         self.steps += 1
         # detached: a caller holding the loss must not keep this step's autograd graph (and the
