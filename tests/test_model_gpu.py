@@ -193,3 +193,29 @@ def test_cuda_graph_mode_matches_eager():
         assert abs(a - b) < 2e-2 * max(1.0, abs(a)), (losses_e, losses_g)
     pe, pg = eager.store.param_buf.float(), graph.store.param_buf.float()
     assert (pe - pg).abs().max().item() < 2e-2 * pe.abs().max().item()
+
+
+def test_checkpoint_roundtrip_includes_sharded_embedding_bag(tmp_path):
+    """save / load_latest must carry the row-sharded tables (state outside the flat store)."""
+    from tony_b200 import runtime
+    from tony_b200.models import widedeep
+    from tony_b200.parallel.ps import ps_parameters
+    from tony_b200.runtime import checkpoint
+
+    dev = torch.device("cuda")
+    cfg = widedeep.WideDeepConfig.tiny()
+
+    def make():
+        torch.manual_seed(0)
+        m = widedeep.WideDeep(cfg, device=dev)
+        return m, runtime.Trainer(m, lr=3e-3, device=dev, bucket_mb=0.25, ps_sharded=ps_parameters(m))
+
+    m1, t1 = make()
+    batch = widedeep.synthetic_batch(cfg, 256, pin=True)
+    for _ in range(3):
+        t1.step(batch)
+    checkpoint.save(str(tmp_path), t1)
+    nxt = t1.step(batch)
+    m2, t2 = make()
+    assert checkpoint.load_latest(str(tmp_path), t2) == 3
+    assert abs(t2.step(batch) - nxt) < 2e-2 * max(1.0, abs(nxt))

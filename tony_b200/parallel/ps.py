@@ -255,6 +255,18 @@ class ShardedEmbeddingBag(nn.Module):
         self.barrier()
         self._dirty = False
 
+    def tony_state_dict(self):
+        """This rank's shard: fp32 master rows + AdamW moments (the bf16 table is re-derived)."""
+        return {"opt": self.opt.state_dict(), "world": self.world, "rank": self.rank}
+
+    def tony_load_state_dict(self, sd):
+        if sd["world"] != self.world or sd["rank"] != self.rank:
+            raise ValueError("embedding-bag shard was saved for a different rank layout")
+        self.opt.load_state_dict(sd["opt"])
+        self.table.copy_(self.opt.master.to(torch.bfloat16))
+        self.grad.zero_()
+        self.barrier()
+
     def full_table(self, field: int) -> torch.Tensor:
         """Debug / tests: rows of ``field`` held by THIS rank, in global row order rank::world."""
         n = self.fields * self.rows_per_shard * self.row_elems

@@ -30,7 +30,12 @@ def save(directory: str, trainer, step: Optional[int] = None) -> str:
     step = trainer.steps if step is None else step
     st = trainer.store
     base = os.path.join(directory, f"step{step:09d}")
-    _atomic_save(trainer.opt.state_dict(), f"{base}.opt.rank{st.rank:03d}of{st.world:03d}.pt")
+    opt_state = trainer.opt.state_dict()
+    # modules with state outside the flat store (row-sharded embedding bags): each rank saves its shard
+    extra = [m.tony_state_dict() for m in getattr(trainer, "_step_modules", []) if hasattr(m, "tony_state_dict")]
+    if extra:
+        opt_state = dict(opt_state, _step_modules=extra)
+    _atomic_save(opt_state, f"{base}.opt.rank{st.rank:03d}of{st.world:03d}.pt")
     if st.rank == 0:
         _atomic_save({"param_buf": st.param_buf, "numel": st.numel, "step": step}, f"{base}.params.pt")
         tmp = f"{base}.meta.json.tmp"
@@ -66,8 +71,14 @@ def load_latest(directory: str, trainer) -> Optional[int]:
     if params["numel"] != st.numel:
         raise ValueError("checkpoint was written for a different model layout")
     st.param_buf.copy_(params["param_buf"])
-    trainer.opt.load_state_dict(torch.load(f"{base}.opt.rank{st.rank:03d}of{st.world:03d}.pt",
-                                           map_location=st.device))
+    opt_state = torch.load(f"{base}.opt.rank{st.rank:03d}of{st.world:03d}.pt", map_location=st.device)
+    extra = opt_state.pop("_step_modules", [])
+    trainer.opt.load_state_dict(opt_state)
+    mods = [m for m in getattr(trainer, "_step_modules", []) if hasattr(m, "tony_load_state_dict")]
+    if len(extra) != len(mods):
+        raise ValueError("checkpoint was written for a different set of sharded modules")
+    for m, sd in zip(mods, extra):
+        m.tony_load_state_dict(sd)
     trainer.steps = step
     torch.cuda.synchronize()
     return step
