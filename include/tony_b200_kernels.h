@@ -173,6 +173,21 @@ int tony_embbag_scatter(const tony_embbag_comm* comm, const long long* ids, long
                         long long rows_per_shard, int row_elems, int deep_elems, const void* ddeep,
                         const void* drest, void* stream);
 
+/* ---- fused BatchNorm (+ residual) (+ ReLU), channels-last bf16, training mode ------------- */
+/* x / y / residual: [M = N*H*W, C] row-major (a channels-last activation); C a power of two in
+ * [8, 2048].  Forward: batch statistics (mean, rstd out, fp32; running_mean / running_var updated
+ * when non-NULL), then y = relu?(gamma*(x-mean)*rstd + beta (+ residual)).  Two launches. */
+size_t tony_bn_scratch_bytes(int C);
+int tony_bn_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+                float* mean, float* rstd, float* running_mean, float* running_var, long long M, int C,
+                float eps, float momentum, int relu, float* scratch, size_t scratch_bytes, void* stream);
+/* Backward of the same: dx, dgamma, dbeta (bf16) and, when dres != NULL, the residual branch's
+ * gradient.  `y` is only needed when relu != 0 AND the forward had a residual (otherwise pass NULL:
+ * the ReLU mask is recomputed from x).  Two launches. */
+int tony_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta,
+                const float* mean, const float* rstd, void* dx, void* dres, void* dgamma, void* dbeta,
+                long long M, int C, int relu, float* scratch, size_t scratch_bytes, void* stream);
+
 /* ---- optimizers on flat buffers ------------------------------------------------------ */
 /* AdamW / Adam over n elements: fp32 master weights + moments, bf16 gradients in, bf16
  * weights out.  wd_mask (optional) has one byte per 256 elements: 0 = no weight decay.

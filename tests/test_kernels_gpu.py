@@ -455,3 +455,40 @@ def test_sharded_embedding_bag_single_gpu():
     # first AdamW step moves every coordinate by ~lr in the direction of its gradient
     assert ((step[big] * torch.sign(ref_grad[0][touched][big])) > 0.05).all()
     assert bag.grad.abs().max().item() == 0.0                         # shard cleared for the next step
+
+
+@pytest.mark.parametrize("C,relu,with_res", [(64, True, False), (256, True, True), (512, False, False),
+                                             (2048, True, True), (128, True, True)])
+def test_fused_batchnorm_matches_aten(C, relu, with_res):
+    """BatchNorm (+ residual) (+ ReLU) forward / backward on a channels-last activation vs. the same
+    computation in fp32 through ATen autograd (training mode, batch statistics)."""
+    torch.manual_seed(4)
+    N, H, W = 8, 7, 9 if C >= 512 else 14
+    x = (torch.randn(N, C, H, W, device=DEV) * 1.5 + 0.3).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    res = _rand(N, C, H, W).contiguous(memory_format=torch.channels_last) if with_res else None
+    gamma, beta = _rand(C, scale=0.5) + 1.0, _rand(C, scale=0.2)
+    rm = torch.zeros(C, device=DEV)
+    rv = torch.ones(C, device=DEV)
+    leaves = [t.clone().requires_grad_() for t in (x, gamma, beta)] + ([res.clone().requires_grad_()] if with_res else [])
+    y = F.batch_norm_act(leaves[0], leaves[1], leaves[2], rm, rv, leaves[3] if with_res else None, relu=relu)
+    ref_leaves = [t.float().requires_grad_() for t in (x, gamma, beta)] + ([res.float().requires_grad_()] if with_res else [])
+    rrm, rrv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+    ref = torch.nn.functional.batch_norm(ref_leaves[0], rrm, rrv, ref_leaves[1], ref_leaves[2], True, 0.1, 1e-5)
+    if with_res:
+        ref = ref + ref_leaves[3]
+    if relu:
+        ref = torch.relu(ref)
+    _close(y, ref, rel=2e-2)
+    assert y.is_contiguous(memory_format=torch.channels_last)
+    _close(rm, rrm, rel=2e-2)
+    _close(rv, rrv, rel=2e-2)
+    g = _rand(N, C, H, W).contiguous(memory_format=torch.channels_last)
+    y.backward(g)
+    ref.backward(g.float())
+    for got, want in zip(leaves, ref_leaves):
+        # elements whose pre-activation is within bf16 rounding of 0 may flip the ReLU mask: compare
+        # in aggregate (mean error) and allow a handful of outliers in the max
+        d = (got.grad.float() - want.grad).abs()
+        scale = want.grad.abs().max().item() + 1e-6
+        assert d.mean().item() < 4e-3 * scale, (d.mean().item(), scale)
+        assert (d > 5e-2 * scale).float().mean().item() < 2e-3

@@ -37,6 +37,7 @@ SOURCES = [
     "symm_vmm.cu",
     "attention.cu",
     "embbag.cu",
+    "batchnorm.cu",
 ]
 
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]

@@ -75,6 +75,37 @@ class MLP(nn.Module):
         return F.mlp(x, self.fc1.weight, self.fc1.bias, self.fc2.weight, self.fc2.bias, residual, self.act)
 
 
+class BatchNormAct(nn.Module):
+    """BatchNorm2d with the following residual add and ReLU fused in (functional.batch_norm_act).
+    Training mode uses the hand-written channels-last kernels; evaluation mode (running statistics)
+    and unsupported shapes use the ATen ops."""
+
+    def __init__(self, channels: int, relu: bool = True, eps: float = 1e-5, momentum: float = 0.1,
+                 zero_init: bool = False, device=None):
+        super().__init__()
+        self.weight = _param(channels, fill=0.0 if zero_init else 1.0, device=device)
+        self.bias = _param(channels, fill=0.0, device=device)
+        self.register_buffer("running_mean", torch.zeros(channels, dtype=torch.float32, device=device))
+        self.register_buffer("running_var", torch.ones(channels, dtype=torch.float32, device=device))
+        self.relu, self.eps, self.momentum = relu, eps, momentum
+
+    def forward(self, x, residual=None):
+        if self.running_mean.dtype != torch.float32:     # model.to(bfloat16) also casts buffers: undo
+            self.running_mean = self.running_mean.float()
+            self.running_var = self.running_var.float()
+        if self.training and F.batch_norm_act_supported(x):
+            return F.batch_norm_act(x, self.weight, self.bias, self.running_mean, self.running_var, residual,
+                                    self.eps, self.momentum, self.relu)
+        rm, rv = self.running_mean.to(x.dtype), self.running_var.to(x.dtype)
+        y = torch.nn.functional.batch_norm(x, rm, rv, self.weight, self.bias, self.training, self.momentum, self.eps)
+        if self.training:
+            self.running_mean.copy_(rm)
+            self.running_var.copy_(rv)
+        if residual is not None:
+            y = y + residual
+        return torch.relu(y) if self.relu else y
+
+
 class SelfAttention(nn.Module):
     """Fused QKV projection -> SDPA -> output projection with the residual in its epilogue.
 

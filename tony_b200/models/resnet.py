@@ -1,8 +1,9 @@
 """ResNet-50 (v1.5) for the DDP configuration.
 
 BASELINE.json config "ResNet-50 PyTorch DDP bf16, 8 workers x 1 B200 each".  Honest status
-(DESIGN.md, K8): the convolutions and BatchNorm still run on cuDNN / ATen in bf16
-channels-last — no hand-written implicit-GEMM convolution yet.  Stride-1 1x1 convolutions CAN
+(DESIGN.md, K8): the convolutions still run on cuDNN in bf16 channels-last — no hand-written
+implicit-GEMM convolution yet.  BatchNorm (+ residual add + ReLU), which is 79 % of the stock step
+on B200, runs on the fused channels-last kernels of csrc/batchnorm.cu.  Stride-1 1x1 convolutions CAN
 run as a tcgen05 GEMM over the NHWC activation viewed as [N*H*W, C] (no layout copy), but the
 measured crossover (profiles/r1_call23_*) says cuDNN wins for every reduction depth in this
 network (4494 img/s with all of them on the GEMM, 4741 with none), so by default only the
@@ -18,7 +19,7 @@ import torch
 from torch import nn
 
 from ..ops import functional as F
-from .nn import Linear, _param
+from .nn import BatchNormAct, Linear, _param
 
 
 STOCK = {"on": False}   # set by stock_resnet50(): build the cuDNN-only twin for the baseline arm
@@ -42,7 +43,11 @@ def _conv(cin, cout, k, stride=1, device=None):
     return nn.Conv2d(cin, cout, k, stride=stride, padding=k // 2, bias=False, device=device, dtype=torch.bfloat16)
 
 
-def _bn(c, device=None, zero=False):
+def _bn(c, device=None, zero=False, relu=True):
+    """Stock twin: nn.BatchNorm2d (the ReLU / add stay separate ATen kernels).  Ours: BatchNormAct,
+    whose forward / backward are the fused channels-last kernels of csrc/batchnorm.cu."""
+    if not STOCK["on"]:
+        return BatchNormAct(c, relu=relu, zero_init=zero, device=device)
     bn = nn.BatchNorm2d(c, device=device, dtype=torch.bfloat16)
     if zero:
         nn.init.zeros_(bn.weight)
@@ -66,10 +71,15 @@ class Bottleneck(nn.Module):
         self.down = None
         if stride != 1 or cin != cout:
             proj = C1(cin, cout, device) if stride == 1 else _conv(cin, cout, 1, stride, device)
-            self.down = nn.Sequential(proj, _bn(cout, device))
+            self.down = nn.Sequential(proj, _bn(cout, device, relu=False))
+        self.fused = not STOCK["on"]
 
     def forward(self, x):
         idt = x if self.down is None else self.down(x)
+        if self.fused:      # ReLU and the residual add ride in the BatchNorm kernels
+            y = self.bn1(self.conv1(x))
+            y = self.bn2(self.conv2(y))
+            return self.bn3(self.conv3(y), residual=idt)
         y = torch.relu(self.bn1(self.conv1(x)))
         y = torch.relu(self.bn2(self.conv2(y)))
         y = self.bn3(self.conv3(y))
@@ -79,8 +89,11 @@ class Bottleneck(nn.Module):
 class ResNet50(nn.Module):
     def __init__(self, num_classes: int = 1000, device=None):
         super().__init__()
-        self.stem = nn.Sequential(_conv(3, 64, 7, 2, device), _bn(64, device), nn.ReLU(inplace=True),
-                                  nn.MaxPool2d(3, 2, 1))
+        if STOCK["on"]:
+            self.stem = nn.Sequential(_conv(3, 64, 7, 2, device), _bn(64, device), nn.ReLU(inplace=True),
+                                      nn.MaxPool2d(3, 2, 1))
+        else:
+            self.stem = nn.Sequential(_conv(3, 64, 7, 2, device), _bn(64, device), nn.MaxPool2d(3, 2, 1))
         blocks, cin = [], 64
         for mid, n, stride in ((64, 3, 1), (128, 4, 2), (256, 6, 2), (512, 3, 2)):
             for i in range(n):

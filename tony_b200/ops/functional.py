@@ -487,6 +487,57 @@ def embedding_sum_supported(word, type_w=None) -> bool:
             and (type_w is None or type_w.shape[0] <= 4))
 
 
+class _BatchNormActFn(torch.autograd.Function):
+    """Training-mode BatchNorm2d (+ residual add) (+ ReLU) on a channels-last bf16 activation:
+    two launches forward, two backward (csrc/batchnorm.cu)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu):
+        N, C, H, W = x.shape
+        x = x.contiguous(memory_format=torch.channels_last)
+        res = residual.contiguous(memory_format=torch.channels_last) if residual is not None else None
+        M = N * H * W
+        y = torch.empty_like(x)
+        mean = torch.empty(C, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(C, dtype=torch.float32, device=x.device)
+        nbytes = _lib.lib().tony_bn_scratch_bytes(C)
+        scratch = workspace("batchnorm", nbytes, x.device)
+        check(_lib.lib().tony_bn_fwd(ptr(x), ptr(res), ptr(gamma), ptr(beta), ptr(y), ptr(mean), ptr(rstd),
+                                     ptr(running_mean), ptr(running_var), M, C, eps, momentum, int(relu),
+                                     ptr(scratch), nbytes, cur_stream()), "tony_bn_fwd")
+        need_y = relu and residual is not None          # otherwise the ReLU mask is recomputed from x
+        ctx.save_for_backward(x, gamma, beta, mean, rstd, y if need_y else None)
+        ctx.meta = (M, C, int(relu), residual is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma, beta, mean, rstd, y = ctx.saved_tensors
+        M, C, relu, has_res = ctx.meta
+        dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = torch.empty_like(x)
+        dres = torch.empty_like(x) if has_res else None
+        dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(beta)
+        nbytes = _lib.lib().tony_bn_scratch_bytes(C)
+        scratch = workspace("batchnorm", nbytes, x.device)
+        check(_lib.lib().tony_bn_bwd(ptr(dy), ptr(x), ptr(y), ptr(gamma), ptr(beta), ptr(mean), ptr(rstd), ptr(dx),
+                                     ptr(dres), ptr(dgamma), ptr(dbeta), M, C, relu, ptr(scratch), nbytes,
+                                     cur_stream()), "tony_bn_bwd")
+        return dx, dgamma, dbeta, dres, None, None, None, None, None
+
+
+def batch_norm_act(x, gamma, beta, running_mean=None, running_var=None, residual=None, eps: float = 1e-5,
+                   momentum: float = 0.1, relu: bool = True):
+    """``relu(batch_norm(x) + residual)`` with batch statistics, for ``x`` ``[N, C, H, W]`` bf16 in
+    channels-last memory format and ``C`` a power of two in [8, 2048]."""
+    return _BatchNormActFn.apply(x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu)
+
+
+def batch_norm_act_supported(x) -> bool:
+    C = x.shape[1]
+    return x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 4 and 8 <= C <= 2048 and (C & (C - 1)) == 0
+
+
 class _BroadcastAddParamFn(torch.autograd.Function):
     """x + p where p broadcasts over the leading dims (position embeddings)."""
 
