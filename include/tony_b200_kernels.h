@@ -188,6 +188,11 @@ int tony_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma,
                 const float* mean, const float* rstd, void* dx, void* dres, void* dgamma, void* dbeta,
                 long long M, int C, int relu, float* scratch, size_t scratch_bytes, void* stream);
 
+/* 3x3 / stride 2 / pad 1 max pooling, channels-last bf16 [N, H, W, C] (C % 8 == 0).  idx: one byte
+ * per output element (position 0..8 of the first maximum), consumed by the gather-style backward. */
+int tony_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, void* stream);
+int tony_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, void* stream);
+
 /* ---- optimizers on flat buffers ------------------------------------------------------ */
 /* AdamW / Adam over n elements: fp32 master weights + moments, bf16 gradients in, bf16
  * weights out.  wd_mask (optional) has one byte per 256 elements: 0 = no weight decay.

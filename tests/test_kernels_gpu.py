@@ -492,3 +492,17 @@ def test_fused_batchnorm_matches_aten(C, relu, with_res):
         scale = want.grad.abs().max().item() + 1e-6
         assert d.mean().item() < 4e-3 * scale, (d.mean().item(), scale)
         assert (d > 5e-2 * scale).float().mean().item() < 2e-3
+
+
+def test_maxpool_3x3_s2_matches_aten():
+    torch.manual_seed(6)
+    x = _rand(4, 64, 30, 23).contiguous(memory_format=torch.channels_last)
+    a = x.clone().requires_grad_()
+    b = x.float().requires_grad_()
+    y = F.max_pool_3x3_s2(a)
+    ref = torch.nn.functional.max_pool2d(b, 3, 2, 1)
+    assert torch.equal(y.float(), ref)
+    g = _rand(*ref.shape).contiguous(memory_format=torch.channels_last)
+    y.backward(g)
+    ref.backward(g.float())
+    _close(a.grad, b.grad, rel=1e-2)

@@ -54,6 +54,11 @@ def _bn(c, device=None, zero=False, relu=True):
     return bn
 
 
+class _MaxPool(nn.Module):
+    def forward(self, x):
+        return F.max_pool_3x3_s2(x)
+
+
 class Bottleneck(nn.Module):
     def __init__(self, cin, mid, stride, device=None):
         super().__init__()
@@ -93,7 +98,15 @@ class ResNet50(nn.Module):
             self.stem = nn.Sequential(_conv(3, 64, 7, 2, device), _bn(64, device), nn.ReLU(inplace=True),
                                       nn.MaxPool2d(3, 2, 1))
         else:
-            self.stem = nn.Sequential(_conv(3, 64, 7, 2, device), _bn(64, device), nn.MaxPool2d(3, 2, 1))
+            # the 3-channel stem convolution lands on slow non-tensor-core cuDNN kernels; padding the
+            # image to 4 / 8 zero channels (the extra filter taps only ever see zeros, so their
+            # gradients stay zero) lets cuDNN pick aligned kernels.  TONY_B200_RESNET_STEM_CPAD=3 disables.
+            self.stem_cin = int(os.environ.get("TONY_B200_RESNET_STEM_CPAD", "3"))
+            conv = _conv(self.stem_cin, 64, 7, 2, device)
+            if self.stem_cin > 3:
+                with torch.no_grad():
+                    conv.weight[:, 3:].zero_()
+            self.stem = nn.Sequential(conv, _bn(64, device), _MaxPool())
         blocks, cin = [], 64
         for mid, n, stride in ((64, 3, 1), (128, 4, 2), (256, 6, 2), (512, 3, 2)):
             for i in range(n):
@@ -106,6 +119,8 @@ class ResNet50(nn.Module):
         self.num_classes = num_classes
 
     def forward(self, images, labels):
+        if not self.stock and self.stem_cin > 3:
+            images = torch.nn.functional.pad(images, (0, 0, 0, 0, 0, self.stem_cin - 3))
         x = images.contiguous(memory_format=torch.channels_last)
         x = self.blocks(self.stem(x))
         x = x.mean(dim=(2, 3))

@@ -538,6 +538,38 @@ def batch_norm_act_supported(x) -> bool:
     return x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 4 and 8 <= C <= 2048 and (C & (C - 1)) == 0
 
 
+class _MaxPool3x3s2Fn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        N, C, H, W = x.shape
+        x = x.contiguous(memory_format=torch.channels_last)
+        OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+        y = torch.empty((N, C, OH, OW), dtype=x.dtype, device=x.device).contiguous(memory_format=torch.channels_last)
+        idx = torch.empty((N, OH, OW, C), dtype=torch.uint8, device=x.device)
+        check(_lib.lib().tony_maxpool3x3s2_fwd(ptr(x), ptr(y), ptr(idx), N, H, W, C, cur_stream()),
+              "tony_maxpool3x3s2_fwd")
+        ctx.save_for_backward(idx)
+        ctx.shape = (N, C, H, W)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        N, C, H, W = ctx.shape
+        dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = torch.empty((N, C, H, W), dtype=dy.dtype, device=dy.device).contiguous(memory_format=torch.channels_last)
+        check(_lib.lib().tony_maxpool3x3s2_bwd(ptr(dy), ptr(idx), ptr(dx), N, H, W, C, cur_stream()),
+              "tony_maxpool3x3s2_bwd")
+        return dx
+
+
+def max_pool_3x3_s2(x):
+    """``max_pool2d(x, 3, stride=2, padding=1)`` for channels-last bf16 ``[N, C, H, W]`` with C % 8 == 0."""
+    if x.is_cuda and x.dtype == torch.bfloat16 and x.shape[1] % 8 == 0:
+        return _MaxPool3x3s2Fn.apply(x)
+    return torch.nn.functional.max_pool2d(x, 3, 2, 1)
+
+
 class _BroadcastAddParamFn(torch.autograd.Function):
     """x + p where p broadcasts over the leading dims (position embeddings)."""
 

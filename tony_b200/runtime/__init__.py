@@ -144,8 +144,19 @@ class Trainer:
         self._eager_before_capture = 2
 
     def to_device(self, batch_cpu: Dict[str, "object"]):
-        """Async H2D of a (pinned) host batch on the current stream."""
-        return {k: v.to(self.device, non_blocking=True) for k, v in batch_cpu.items()}
+        """Async H2D of a (pinned) host batch on the copy stream: the transfer of step i+1's inputs
+        runs under step i's kernels (the host is a step ahead of the GPU); the compute stream only
+        waits for the copy's event."""
+        torch = self.torch
+        cur = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self.copy_stream):
+            out = {k: v.to(self.device, non_blocking=True) for k, v in batch_cpu.items()}
+            ev = torch.cuda.Event()
+            ev.record(self.copy_stream)
+        cur.wait_event(ev)
+        for v in out.values():
+            v.record_stream(cur)
+        return out
 
     def _capture(self, batch_dev) -> None:
         torch = self.torch
