@@ -243,6 +243,9 @@ def main(argv=None) -> int:
         if rank == 0:
             sys.stderr.write(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}; using {world}\n")
     torch.manual_seed(1234)
+    if args.model == "resnet50" and os.environ.get("TONY_B200_CUDNN_BENCHMARK", "1") == "1":
+        # fixed-shape CNN: let cuDNN time its algorithms once (standard practice; BOTH arms)
+        torch.backends.cudnn.benchmark = True
     model, make, batch, seq, flops_per_sample, metric, model_name = build(args, device)
 
     if args.impl == "ours":
