@@ -178,15 +178,15 @@ int tony_embbag_scatter(const tony_embbag_comm* comm, const long long* ids, long
  * [8, 2048].  Forward: batch statistics (mean, rstd out, fp32; running_mean / running_var updated
  * when non-NULL), then y = relu?(gamma*(x-mean)*rstd + beta (+ residual)).  Two launches. */
 size_t tony_bn_scratch_bytes(int C);
-int tony_bn_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+int tony_bn_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y, void* mask,
                 float* mean, float* rstd, float* running_mean, float* running_var, long long M, int C,
                 float eps, float momentum, int relu, float* scratch, size_t scratch_bytes, void* stream);
 /* Backward of the same: dx, dgamma, dbeta (bf16) and, when dres != NULL, the residual branch's
- * gradient.  `y` is only needed when relu != 0 AND the forward had a residual (otherwise pass NULL:
- * the ReLU mask is recomputed from x).  Two launches. */
-int tony_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta,
-                const float* mean, const float* rstd, void* dx, void* dres, void* dgamma, void* dbeta,
-                long long M, int C, int relu, float* scratch, size_t scratch_bytes, void* stream);
+ * gradient.  `mask` is the M*C/8-byte ReLU bit mask the forward wrote (one bit per element;
+ * required when relu != 0, pass it to tony_bn_fwd as well).  Two launches. */
+int tony_bn_bwd(const void* dy, const void* x, const void* mask, const void* gamma, const float* mean,
+                const float* rstd, void* dx, void* dres, void* dgamma, void* dbeta, long long M, int C,
+                int relu, float* scratch, size_t scratch_bytes, void* stream);
 
 /* 3x3 / stride 2 / pad 1 max pooling, channels-last bf16 [N, H, W, C] (C % 8 == 0).  idx: one byte
  * per output element (position 0..8 of the first maximum), consumed by the gather-style backward. */

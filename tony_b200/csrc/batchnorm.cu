@@ -7,7 +7,7 @@
 //             b = beta - mean*a and the running statistics), then ONE elementwise kernel
 //             y = relu(x*a + b + residual);
 //   backward: reduce kernel (dbeta = sum dy_m, dgamma = sum dy_m*xhat with the ReLU mask applied on
-//             the fly: recomputed from x when there is no residual, read from y otherwise), then ONE
+//             the fly from a 1-bit-per-element mask the forward transform wrote), then ONE
 //             elementwise kernel dx = a*(dy_m - dbeta/M - xhat*dgamma/M) that also emits the
 //             residual branch's gradient dy_m.
 // Narrow layers (C < 256) are processed as a [M/k, k*C] matrix (k = 256/C) so that every lane still
@@ -172,7 +172,8 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, const BnDims d, float* __re
 // y = relu(x*a + b (+ residual)); every thread keeps the 8 channels it owns in registers.
 __global__ void __launch_bounds__(BN_THREADS)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ residual,
-                const float* __restrict__ ab, __nv_bfloat16* __restrict__ y, long long M, int C, int relu) {
+                const float* __restrict__ ab, __nv_bfloat16* __restrict__ y, unsigned char* __restrict__ mask,
+                long long M, int C, int relu) {
     const int groups = C / 8;                                    // divides 256 for every supported C
     const long long tid = static_cast<long long>(blockIdx.x) * BN_THREADS + threadIdx.x;
     const int cg = static_cast<int>(tid % groups);
@@ -197,8 +198,13 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
             for (int j = 0; j < 8; ++j) v[j] += rr[j];
         }
         if (relu) {
+            unsigned int bits = 0;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+            for (int j = 0; j < 8; ++j) {
+                bits |= (v[j] > 0.f ? 1u : 0u) << j;
+                v[j] = fmaxf(v[j], 0.f);
+            }
+            if (mask) mask[off >> 3] = static_cast<unsigned char>(bits);   // one bit per element for backward
         }
         st_global_v4(y + off, pack8f(v));
     }
@@ -207,10 +213,8 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
 // Folded-view column sums of dy_m and dy_m * xhat.
 __global__ void __launch_bounds__(BN_THREADS)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                     const __nv_bfloat16* __restrict__ y, const BnDims d, const float* __restrict__ mean,
-                     const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ gamma,
-                     const __nv_bfloat16* __restrict__ beta, int relu,
-                     float* __restrict__ partials, unsigned int* __restrict__ counters,
+                     const unsigned char* __restrict__ mask, const BnDims d, const float* __restrict__ mean,
+                     const float* __restrict__ rstd, int relu, float* __restrict__ partials, unsigned int* __restrict__ counters,
                      __nv_bfloat16* __restrict__ dgamma, __nv_bfloat16* __restrict__ dbeta, float* __restrict__ coef) {
     __shared__ float red[8][256];
     __shared__ unsigned int is_last;
@@ -221,41 +225,40 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     float a1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};   // sum dy_m
     float a2[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};   // sum dy_m * xhat
     if (col < d.Cw) {
-        float mu[8], rs[8], aa[8], bb[8];
+        float mu[8], rs[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int c = (col + j) % d.C;
             mu[j] = mean[c];
             rs[j] = rstd[c];
-            aa[j] = __bfloat162float(gamma[c]) * rs[j];            // same a / b as the forward transform
-            bb[j] = __bfloat162float(beta[c]) - mu[j] * aa[j];
         }
-        for (long long r = r0 + warp; r < r1; r += 16) {     // two rows in flight per warp
-            const bool two = r + 8 < r1;
-            const size_t o0 = static_cast<size_t>(r) * d.Cw + col, o1 = o0 + static_cast<size_t>(8) * d.Cw;
-            const uint4 g0 = ld_global_nc_v4(dy + o0), x0 = ld_global_nc_v4(x + o0);
-            uint4 g1 = make_uint4(0, 0, 0, 0), x1 = g1, y0 = g1, y1 = g1;
-            if (two) {
-                g1 = ld_global_nc_v4(dy + o1);
-                x1 = ld_global_nc_v4(x + o1);
-            }
-            if (relu && y) {
-                y0 = ld_global_nc_v4(y + o0);
-                if (two) y1 = ld_global_nc_v4(y + o1);
+        for (long long r = r0 + warp; r < r1; r += 32) {     // four rows in flight per warp
+            uint4 g[4], xx[4];
+            unsigned int mb[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const long long rr = r + q * 8;
+                if (rr < r1) {
+                    const size_t o = static_cast<size_t>(rr) * d.Cw + col;
+                    g[q] = ld_global_nc_v4(dy + o);
+                    xx[q] = ld_global_nc_v4(x + o);
+                    mb[q] = relu ? mask[o >> 3] : 0xffu;
+                } else {
+                    g[q] = make_uint4(0, 0, 0, 0);
+                    xx[q] = g[q];
+                    mb[q] = 0;
+                }
             }
 #pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                if (q == 1 && !two) break;
-                float gv[8], xv[8], yv[8];
-                unpack8f(q ? g1 : g0, gv);
-                unpack8f(q ? x1 : x0, xv);
-                if (relu && y) unpack8f(q ? y1 : y0, yv);
+            for (int q = 0; q < 4; ++q) {
+                float gv[8], xv[8];
+                unpack8f(g[q], gv);
+                unpack8f(xx[q], xv);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    const bool on = !relu || (y ? yv[j] > 0.f : fmaf(xv[j], aa[j], bb[j]) > 0.f);
-                    const float g = on ? gv[j] : 0.f;
-                    a1[j] += g;
-                    a2[j] = fmaf(g, (xv[j] - mu[j]) * rs[j], a2[j]);
+                    const float gm = ((mb[q] >> j) & 1u) ? gv[j] : 0.f;
+                    a1[j] += gm;
+                    a2[j] = fmaf(gm, (xv[j] - mu[j]) * rs[j], a2[j]);
                 }
             }
         }
@@ -292,35 +295,34 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 // dx = a * (dy_m - dbeta/M - xhat * dgamma/M); optionally dres = dy_m.
 __global__ void __launch_bounds__(BN_THREADS)
 bn_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                 const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+                 const unsigned char* __restrict__ mask, const float* __restrict__ mean,
                  const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ gamma,
-                 const __nv_bfloat16* __restrict__ beta, const float* __restrict__ coef, int relu, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, long long M, int C) {
+                 const float* __restrict__ coef, int relu, __nv_bfloat16* __restrict__ dx,
+                 __nv_bfloat16* __restrict__ dres, long long M, int C) {
     const int groups = C / 8;
     const long long tid = static_cast<long long>(blockIdx.x) * BN_THREADS + threadIdx.x;
     const int cg = static_cast<int>(tid % groups);
     const long long row0 = tid / groups;
     const long long row_stride = static_cast<long long>(gridDim.x) * BN_THREADS / groups;
-    float mu[8], rs[8], aa[8], bb[8], c1[8], c2[8];
+    float mu[8], rs[8], aa[8], c1[8], c2[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const int c = cg * 8 + j;
         mu[j] = mean[c];
         rs[j] = rstd[c];
         aa[j] = __bfloat162float(gamma[c]) * rs[j];
-        bb[j] = __bfloat162float(beta[c]) - mu[j] * aa[j];
         c1[j] = coef[c];
         c2[j] = coef[C + c];
     }
     for (long long r = row0; r < M; r += row_stride) {
         const size_t off = static_cast<size_t>(r) * C + cg * 8;
-        float gv[8], xv[8], yv[8], o[8];
+        float gv[8], xv[8], o[8];
         unpack8f(ld_global_nc_v4(dy + off), gv);
         unpack8f(ld_global_nc_v4(x + off), xv);
-        if (relu && y) unpack8f(ld_global_nc_v4(y + off), yv);
+        const unsigned int mb = relu ? mask[off >> 3] : 0xffu;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const bool on = !relu || (y ? yv[j] > 0.f : fmaf(xv[j], aa[j], bb[j]) > 0.f);
-            const float g = on ? gv[j] : 0.f;
+            const float g = ((mb >> j) & 1u) ? gv[j] : 0.f;
             gv[j] = g;
             o[j] = aa[j] * (g - c1[j] - (xv[j] - mu[j]) * rs[j] * c2[j]);
         }
@@ -373,7 +375,7 @@ extern "C" size_t tony_bn_scratch_bytes(int C) {
 }
 
 extern "C" int tony_bn_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
-                           float* mean, float* rstd, float* running_mean, float* running_var, long long M,
+                           void* mask, float* mean, float* rstd, float* running_mean, float* running_var, long long M,
                            int C, float eps, float momentum, int relu, float* scratch, size_t scratch_bytes,
                            void* stream) {
     if (!x || !gamma || !beta || !y || !mean || !rstd || !scratch) return TONY_ERR_INVALID;
@@ -397,16 +399,16 @@ extern "C" int tony_bn_fwd(const void* x, const void* residual, const void* gamm
     TONY_CUDA_CHECK(cudaGetLastError());
     bn_apply_kernel<<<elementwise_grid(M, C), BN_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(residual), ab,
-        static_cast<__nv_bfloat16*>(y), M, C, relu);
+        static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(mask), M, C, relu);
     TONY_CUDA_CHECK(cudaGetLastError());
     count_launch(2);
     return TONY_OK;
 }
 
-extern "C" int tony_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta,
+extern "C" int tony_bn_bwd(const void* dy, const void* x, const void* mask, const void* gamma,
                            const float* mean, const float* rstd, void* dx, void* dres, void* dgamma, void* dbeta, long long M,
                            int C, int relu, float* scratch, size_t scratch_bytes, void* stream) {
-    if (!dy || !x || !gamma || !beta || !mean || !rstd || !dx || !dgamma || !dbeta || !scratch)
+    if (!dy || !x || !gamma || !mean || !rstd || !dx || !dgamma || !dbeta || !scratch || (relu && !mask))
         return TONY_ERR_INVALID;
     BnDims d;
     int rc = make_dims("tony_bn_bwd", M, C, &d);
@@ -418,22 +420,21 @@ extern "C" int tony_bn_bwd(const void* dy, const void* x, const void* y, const v
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     unsigned int* counters = reinterpret_cast<unsigned int*>(scratch);
     float* partials = scratch + 1024;
-    // a = gamma * rstd and b = beta - mean * a (ReLU-mask recomputation, dx scale) are rebuilt from the
-    // saved statistics in the kernels: the scratch may have served other layers since the forward.
+    // a = gamma * rstd (dx scale) is rebuilt from the saved statistics in the kernel: the scratch may
+    // have served other layers since the forward.  The ReLU mask comes from the forward's bit mask.
     float* coef = partials + static_cast<size_t>(BN_MAX_SLABS) * 2 * (C < 256 ? 256 : C) + 2 * C;
     const int col_tiles = (d.Cw + 255) / 256;
     const int slabs = static_cast<int>((d.Mv + d.rows_per_slab - 1) / d.rows_per_slab);
     TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, static_cast<size_t>(col_tiles) * 4, s));
     bn_bwd_reduce_kernel<<<dim3(col_tiles, slabs), BN_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
-        static_cast<const __nv_bfloat16*>(y), d, mean, rstd, static_cast<const __nv_bfloat16*>(gamma),
-        static_cast<const __nv_bfloat16*>(beta), relu, partials, counters,
+        static_cast<const unsigned char*>(mask), d, mean, rstd, relu, partials, counters,
         static_cast<__nv_bfloat16*>(dgamma), static_cast<__nv_bfloat16*>(dbeta), coef);
     TONY_CUDA_CHECK(cudaGetLastError());
     bn_bwd_dx_kernel<<<elementwise_grid(M, C), BN_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
-        static_cast<const __nv_bfloat16*>(y), mean, rstd, static_cast<const __nv_bfloat16*>(gamma),
-        static_cast<const __nv_bfloat16*>(beta), coef, relu, static_cast<__nv_bfloat16*>(dx),
+        static_cast<const unsigned char*>(mask), mean, rstd, static_cast<const __nv_bfloat16*>(gamma), coef, relu,
+        static_cast<__nv_bfloat16*>(dx),
         static_cast<__nv_bfloat16*>(dres), M, C);
     TONY_CUDA_CHECK(cudaGetLastError());
     count_launch(2);

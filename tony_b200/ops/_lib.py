@@ -156,9 +156,9 @@ def _declare(lib) -> None:
     lib.tony_embbag_scatter.argtypes = [POINTER(EmbBagComm), vp, c_longlong, c_int, c_longlong, c_int, c_int, vp, vp, vp]
     lib.tony_bn_scratch_bytes.argtypes = [c_int]
     lib.tony_bn_scratch_bytes.restype = c_size_t
-    lib.tony_bn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, c_longlong, c_int, c_float, c_float, c_int,
+    lib.tony_bn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_longlong, c_int, c_float, c_float, c_int,
                                 vp, c_size_t, vp]
-    lib.tony_bn_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_longlong, c_int, c_int, vp, c_size_t, vp]
+    lib.tony_bn_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_longlong, c_int, c_int, vp, c_size_t, vp]
     lib.tony_maxpool3x3s2_fwd.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, vp]
     lib.tony_maxpool3x3s2_bwd.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, vp]
     lib.tony_attention_fwd_bf16.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_float, vp]

@@ -500,27 +500,28 @@ class _BatchNormActFn(torch.autograd.Function):
         y = torch.empty_like(x)
         mean = torch.empty(C, dtype=torch.float32, device=x.device)
         rstd = torch.empty(C, dtype=torch.float32, device=x.device)
+        # one bit per element: backward applies the ReLU mask without re-reading y or the residual
+        mask = torch.empty(M * C // 8, dtype=torch.uint8, device=x.device) if relu else None
         nbytes = _lib.lib().tony_bn_scratch_bytes(C)
         scratch = workspace("batchnorm", nbytes, x.device)
-        check(_lib.lib().tony_bn_fwd(ptr(x), ptr(res), ptr(gamma), ptr(beta), ptr(y), ptr(mean), ptr(rstd),
-                                     ptr(running_mean), ptr(running_var), M, C, eps, momentum, int(relu),
-                                     ptr(scratch), nbytes, cur_stream()), "tony_bn_fwd")
-        need_y = relu and residual is not None          # otherwise the ReLU mask is recomputed from x
-        ctx.save_for_backward(x, gamma, beta, mean, rstd, y if need_y else None)
+        check(_lib.lib().tony_bn_fwd(ptr(x), ptr(res), ptr(gamma), ptr(beta), ptr(y), ptr(mask), ptr(mean),
+                                     ptr(rstd), ptr(running_mean), ptr(running_var), M, C, eps, momentum,
+                                     int(relu), ptr(scratch), nbytes, cur_stream()), "tony_bn_fwd")
+        ctx.save_for_backward(x, gamma, mean, rstd, mask)
         ctx.meta = (M, C, int(relu), residual is not None)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, gamma, beta, mean, rstd, y = ctx.saved_tensors
+        x, gamma, mean, rstd, mask = ctx.saved_tensors
         M, C, relu, has_res = ctx.meta
         dy = dy.contiguous(memory_format=torch.channels_last)
         dx = torch.empty_like(x)
         dres = torch.empty_like(x) if has_res else None
-        dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(beta)
+        dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(gamma)
         nbytes = _lib.lib().tony_bn_scratch_bytes(C)
         scratch = workspace("batchnorm", nbytes, x.device)
-        check(_lib.lib().tony_bn_bwd(ptr(dy), ptr(x), ptr(y), ptr(gamma), ptr(beta), ptr(mean), ptr(rstd), ptr(dx),
+        check(_lib.lib().tony_bn_bwd(ptr(dy), ptr(x), ptr(mask), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx),
                                      ptr(dres), ptr(dgamma), ptr(dbeta), M, C, relu, ptr(scratch), nbytes,
                                      cur_stream()), "tony_bn_bwd")
         return dx, dgamma, dbeta, dres, None, None, None, None, None
