@@ -25,7 +25,14 @@
 namespace tony {
 
 constexpr int BN_THREADS = 256;
-constexpr int BN_MAX_SLABS = 160;
+// Partial rows: slabs * column tiles <= 4 CTAs per SM, so every SM gets the same number of CTAs (a
+// cap of 160 slabs left 12 SMs with twice the work for every layer narrower than 1024 channels).
+constexpr int BN_CTAS_PER_SM = 4;
+constexpr int BN_MAX_SMS = 256;
+
+static size_t bn_partials_floats() {   // slabs * 2 * Cw  <=  4 * SMs * 2 * 256
+    return static_cast<size_t>(BN_CTAS_PER_SM) * BN_MAX_SMS * 2 * 256;
+}
 
 __device__ __forceinline__ void unpack8f(const uint4& u, float (&v)[8]) {
     const uint32_t w[4] = {u.x, u.y, u.z, u.w};
@@ -350,7 +357,7 @@ static int make_dims(const char* what, long long M, int C, BnDims* d) {
     d->Mv = M / k;
     d->Cw = C * k;
     const int col_tiles = (d->Cw + 255) / 256;
-    long long slabs = std::max(1, std::min(BN_MAX_SLABS, (device_sm_count() * 4) / col_tiles));
+    long long slabs = std::max(1, (std::min(device_sm_count(), BN_MAX_SMS) * BN_CTAS_PER_SM) / col_tiles);
     slabs = std::min<long long>(slabs, std::max<long long>(1, d->Mv / 32));
     d->rows_per_slab = static_cast<int>((d->Mv + slabs - 1) / slabs);
     return TONY_OK;
@@ -371,7 +378,8 @@ using namespace tony;
 extern "C" size_t tony_bn_scratch_bytes(int C) {
     const int Cw = C < 256 ? 256 : C;
     // [4 KB counters][partials: slabs x 2 x Cw][ab: 2 x C][coef: 2 x C]
-    return 4096 + (static_cast<size_t>(BN_MAX_SLABS) * 2 * Cw + 4 * static_cast<size_t>(C)) * sizeof(float);
+    (void)Cw;
+    return 4096 + (bn_partials_floats() + 4 * static_cast<size_t>(C)) * sizeof(float);
 }
 
 extern "C" int tony_bn_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
@@ -389,7 +397,7 @@ extern "C" int tony_bn_fwd(const void* x, const void* residual, const void* gamm
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     unsigned int* counters = reinterpret_cast<unsigned int*>(scratch);
     float* partials = scratch + 1024;
-    float* ab = partials + static_cast<size_t>(BN_MAX_SLABS) * 2 * (C < 256 ? 256 : C);
+    float* ab = partials + bn_partials_floats();
     const int col_tiles = (d.Cw + 255) / 256;
     const int slabs = static_cast<int>((d.Mv + d.rows_per_slab - 1) / d.rows_per_slab);
     TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, static_cast<size_t>(col_tiles) * 4, s));
@@ -422,7 +430,7 @@ extern "C" int tony_bn_bwd(const void* dy, const void* x, const void* mask, cons
     float* partials = scratch + 1024;
     // a = gamma * rstd (dx scale) is rebuilt from the saved statistics in the kernel: the scratch may
     // have served other layers since the forward.  The ReLU mask comes from the forward's bit mask.
-    float* coef = partials + static_cast<size_t>(BN_MAX_SLABS) * 2 * (C < 256 ? 256 : C) + 2 * C;
+    float* coef = partials + bn_partials_floats() + 2 * C;
     const int col_tiles = (d.Cw + 255) / 256;
     const int slabs = static_cast<int>((d.Mv + d.rows_per_slab - 1) / d.rows_per_slab);
     TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, static_cast<size_t>(col_tiles) * 4, s));
