@@ -599,84 +599,26 @@ def add_broadcast_param(x, p):
 
 
 # ---------------------------------------------------------------------------------------
-class _PackedSdpaFn(torch.autograd.Function):
-    """Attention over a packed ``qkv`` activation ``[B, S, 3, heads, head_dim]``.
+class _PackedAttentionFn(torch.autograd.Function):
+    """Attention over a packed ``qkv`` activation ``[B, S, 3, heads, head_dim]`` -> ``[B, S, H]``.
 
-    The attention core is the library flash kernel (``scaled_dot_product_attention``); this
-    wrapper only removes the layout traffic stock autograd adds around it: q/k/v go in as
-    strided views of the packed projection output, the context comes back already in
-    ``[B, S, H]`` order, and backward writes dq/dk/dv straight into one packed gradient
-    (three strided copies) instead of three zero-filled ``select_backward`` tensors + adds.
-    """
-
-    @staticmethod
-    def forward(ctx, qkv, causal):
-        B, S, three, nh, hd = qkv.shape
-        base = qkv.detach()
-        with torch.enable_grad():
-            q, k, v = (base[:, :, i].transpose(1, 2).requires_grad_() for i in range(3))
-            o = torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=causal)
-        ctx.graph = (q, k, v, o)
-        ctx.shape = (B, S, nh, hd)
-        out = o.detach().transpose(1, 2)
-        return out.reshape(B, S, nh * hd)
-
-    @staticmethod
-    def backward(ctx, dout):
-        q, k, v, o = ctx.graph
-        ctx.graph = None
-        B, S, nh, hd = ctx.shape
-        do = dout.reshape(B, S, nh, hd).transpose(1, 2)
-        dq, dk, dv = torch.autograd.grad(o, (q, k, v), do)
-        dqkv = torch.empty((B, S, 3, nh, hd), dtype=dout.dtype, device=dout.device)
-        parts = [t.transpose(1, 2) for t in (dq, dk, dv)]          # [B, S, nh, hd] views
-        H = nh * hd
-
-        def rows_view(t):
-            # (row stride in elements) if t is [B*S rows] x [H contiguous elements], else None
-            ok = t.stride(3) == 1 and t.stride(2) == hd and t.stride(0) == S * t.stride(1)
-            return t.stride(1) if ok and t.stride(1) % 8 == 0 and t.data_ptr() % 16 == 0 else None
-
-        strides = [rows_view(t) for t in parts]
-        if dout.dtype == torch.bfloat16 and H % 8 == 0 and all(s is not None for s in strides):
-            check(_lib.lib().tony_pack3_rows(ptr(parts[0]), ptr(parts[1]), ptr(parts[2]), strides[0],
-                                             strides[1], strides[2], ptr(dqkv), B * S, H, cur_stream()),
-                  "tony_pack3_rows")
-        else:
-            for i, t in enumerate(parts):
-                dqkv[:, :, i].copy_(t)
-        return dqkv, None
-
-
-class _FusedAttentionFn(torch.autograd.Function):
-    """tcgen05 attention on the packed ``qkv`` activation (csrc/attention.cu): one forward
-    launch, three backward launches (delta, dq, dk+dv); q/k/v are read in place through a tensor
-    map and dq/dk/dv land directly in the packed gradient of the QKV projection."""
+    The core is chosen by ``_attention_core_forward``: the library flash kernel behind
+    ``scaled_dot_product_attention`` by default, or the tcgen05 kernels of csrc/attention.cu.  In
+    both cases q/k/v are read as strided views of the packed projection output, the context comes
+    back already in ``[B, S, H]`` order and backward produces ONE packed gradient (the library path
+    interleaves dq/dk/dv with ``tony_pack3_rows`` instead of three zero-filled ``select_backward``
+    tensors + adds)."""
 
     @staticmethod
     def forward(ctx, qkv, causal):
-        B, S, _, nh, hd = qkv.shape
-        qkv = qkv.contiguous()
-        out = torch.empty((B, S, nh * hd), dtype=qkv.dtype, device=qkv.device)
-        lse = torch.empty((B * nh, S), dtype=torch.float32, device=qkv.device)
-        scale = 1.0 / math.sqrt(hd)
-        check(_lib.lib().tony_attention_fwd_bf16(ptr(qkv), ptr(out), ptr(lse), B, S, nh, hd, int(causal),
-                                                 scale, cur_stream()), "tony_attention_fwd_bf16")
-        ctx.save_for_backward(qkv, out, lse)
-        ctx.meta = (B, S, nh, hd, int(causal), scale)
+        out, saved = _attention_core_forward(qkv.detach().contiguous(), causal)
+        ctx.saved_core = saved
         return out
 
     @staticmethod
     def backward(ctx, dout):
-        qkv, out, lse = ctx.saved_tensors
-        B, S, nh, hd, causal, scale = ctx.meta
-        dout = dout.contiguous()
-        delta = torch.empty_like(lse)
-        dqkv = torch.empty_like(qkv)
-        check(_lib.lib().tony_attention_bwd_bf16(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(delta),
-                                                 ptr(dqkv), B, S, nh, hd, causal, scale, cur_stream()),
-              "tony_attention_bwd_bf16")
-        return dqkv, None
+        saved, ctx.saved_core = ctx.saved_core, None
+        return _attention_core_backward(saved, dout), None
 
 
 def fused_attention_supported(qkv) -> bool:
@@ -790,6 +732,4 @@ def packed_attention(qkv, causal: bool = False):
     kernels of csrc/attention.cu.  The default is the library core: on B200 it is the cuDNN
     sm_100 flash kernel, which the own kernels do not beat yet (profiles/r1_attention_*.md has
     the measured comparison), and the default follows the measurement."""
-    if fused_attention_supported(qkv) and os.environ.get("TONY_B200_ATTENTION", "library") == "tcgen05":
-        return _FusedAttentionFn.apply(qkv, causal)
-    return _PackedSdpaFn.apply(qkv, causal)
+    return _PackedAttentionFn.apply(qkv, causal)
