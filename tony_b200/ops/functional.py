@@ -545,7 +545,7 @@ class _MaxPool3x3s2Fn(torch.autograd.Function):
         N, C, H, W = x.shape
         x = x.contiguous(memory_format=torch.channels_last)
         OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
-        y = torch.empty((N, C, OH, OW), dtype=x.dtype, device=x.device).contiguous(memory_format=torch.channels_last)
+        y = torch.empty((N, C, OH, OW), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
         idx = torch.empty((N, OH, OW, C), dtype=torch.uint8, device=x.device)
         check(_lib.lib().tony_maxpool3x3s2_fwd(ptr(x), ptr(y), ptr(idx), N, H, W, C, cur_stream()),
               "tony_maxpool3x3s2_fwd")
@@ -558,7 +558,7 @@ class _MaxPool3x3s2Fn(torch.autograd.Function):
         (idx,) = ctx.saved_tensors
         N, C, H, W = ctx.shape
         dy = dy.contiguous(memory_format=torch.channels_last)
-        dx = torch.empty((N, C, H, W), dtype=dy.dtype, device=dy.device).contiguous(memory_format=torch.channels_last)
+        dx = torch.empty((N, C, H, W), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
         check(_lib.lib().tony_maxpool3x3s2_bwd(ptr(dy), ptr(idx), ptr(dx), N, H, W, C, cur_stream()),
               "tony_maxpool3x3s2_bwd")
         return dx
