@@ -63,6 +63,17 @@ int tony_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, i
                    float alpha, const void* bias, const void* aux, long long ld_aux, void* aux_out,
                    void* workspace, size_t workspace_bytes, void* stream);
 
+/* tony_gemm_bf16 that ALSO produces rowsum_out[m] = sum_k A(m,k) (bf16 [M], optionally added to
+ * its previous contents): in a weight-gradient GEMM dW = dY^T X the A operand is dY^T, so this is
+ * the bias gradient, computed by one extra N=16 MMA per k-step against a shared-memory tile of ones
+ * instead of a separate pass over dY.  Only the CTA-pair kernel carries it (M >= 256 and N >= 256);
+ * other shapes return TONY_ERR_UNSUPPORTED and the caller runs tony_colsum_bf16. */
+int tony_gemm_bf16_rowsum(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                          int b_mn_major, long long lda, long long ldb, long long ldc, unsigned int flags,
+                          float alpha, const void* bias, const void* aux, long long ld_aux, void* aux_out,
+                          void* workspace, size_t workspace_bytes, void* rowsum_out, int rowsum_accumulate,
+                          void* stream);
+
 /* Extended form: tile/split overrides (0 = auto; force_splits = 1 disables split-K),
  * B-readiness flags and reserved copy CTAs used by the all-gather-fused GEMM,
  * and an SM budget (max_ctas, 0 = all SMs) so the GEMM can share the GPU with a

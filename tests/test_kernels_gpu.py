@@ -556,3 +556,20 @@ def test_batchnorm_kernels_stay_inside_their_buffers(M, C):
         assert (buf[:G].float() == fill).all() and (buf[-G:].float() == fill).all(), "write outside the buffer"
     assert (mbuf[:G] == 0xAB).all() and (mbuf[-G:] == 0xAB).all(), "mask written outside its buffer"
     assert torch.isfinite(dx.float()).all()
+
+
+@pytest.mark.parametrize("M,N,K,acc", [(1024, 1024, 16384, False), (4096, 1024, 4096, True), (3072, 1024, 2048, False),
+                                       (520, 264, 1000, True)])
+def test_wgrad_gemm_carries_the_bias_gradient(M, N, K, acc):
+    """dW = dY^T X with rowsum_out = colsum(dY) produced inside the GEMM (ones-tile MMA), including
+    split-K shapes, ragged edges and accumulation into existing gradients."""
+    torch.manual_seed(9)
+    dy, x = _rand(K, M, scale=0.5), _rand(K, N, scale=0.5)        # dY [tokens, out], X [tokens, in]
+    dw0, db0 = _rand(M, N), _rand(M)
+    dw, db = dw0.clone(), db0.clone()
+    F.gemm(dy, x, a_mn=True, b_mn=True, out=dw, flags=F.EPI_ACCUMULATE if acc else 0, rowsum_out=db,
+           rowsum_accumulate=acc)
+    ref_w = dy.float().t() @ x.float() + (dw0.float() if acc else 0)
+    ref_b = dy.float().sum(0) + (db0.float() if acc else 0)
+    _close(dw, ref_w, rel=2e-2)
+    _close(db, ref_b, rel=2e-2)

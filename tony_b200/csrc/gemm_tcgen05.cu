@@ -61,6 +61,11 @@ struct GemmParams {
     uint32_t* ag_flags;
     int ag_rows_per_rank;
     int n_rot;                     // n-block sweep starts here (the local shard)
+    // CTA-pair kernel only: rowsum[m] = sum_k A(m,k) (the bias gradient when A = dY^T in a wgrad
+    // GEMM), produced by one extra N=16 MMA per k-step against a tile of ones
+    __nv_bfloat16* rowsum_out;     // nullptr = off
+    int rowsum_accumulate;
+    float* rowsum_ws;              // split-K: partial row sums [splits][M]
 };
 
 __device__ __forceinline__ void tile_coords(const GemmParams& p, int tile, int& m_blk, int& n_blk) {
@@ -468,7 +473,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
 //     tcgen05.commit multicasts the `empty` / `tmem_full` arrivals to both CTAs; the epilogue
 //     warps of both CTAs arrive remotely on the leader's `tmem_empty` barrier.
 // Per-CTA shared-memory layout and descriptors are exactly those of the 128 x 128 1-CTA kernel.
-template <int STAGES>
+template <int STAGES, bool ROWSUM>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
                               const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
@@ -484,7 +489,9 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
     uint8_t* smem = reinterpret_cast<uint8_t*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     uint8_t* staging = smem + STAGES * STAGE_BYTES;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + EPI_STAGING_BYTES);
+    // ROWSUM only: 8 rows x 128 B of bf16 1.0 (this CTA's half of a 16 x 64 operand of ones)
+    uint8_t* ones_tile = staging + EPI_STAGING_BYTES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(ones_tile + (ROWSUM ? 1024 : 0));
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full_bar = empty_bar + STAGES;
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;
@@ -494,6 +501,16 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int lane = threadIdx.x & 31;
     const uint32_t cta_rank = cluster_ctarank();
     const bool leader = cta_rank == 0;
+    // Row-sum mode keeps ONE accumulator stage (columns [0,256)) and puts the 16-column row-sum
+    // accumulator at column 256; the reduction is so long in the GEMMs that use it (wgrad, K = tokens)
+    // that the lost epilogue overlap is noise.
+    constexpr bool rowsum = ROWSUM;      // a separate instantiation: the plain kernel's code is untouched
+    constexpr int nstage = ROWSUM ? 1 : 2;
+    if (ROWSUM && warp_idx == 2) {
+        reinterpret_cast<uint4*>(ones_tile)[lane] = make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);
+        reinterpret_cast<uint4*>(ones_tile)[lane + 32] = make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);
+        fence_proxy_async();   // generic-proxy stores -> tensor-core (async proxy) reads
+    }
 
     if (warp_idx == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
@@ -570,17 +587,22 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
             const uint32_t b_lbo = p.b_mn_major ? CHUNK_BYTES : 16;
             const uint32_t a_kstep = p.a_mn_major ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
             const uint32_t b_kstep = p.b_mn_major ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+            const uint32_t idesc_ones = make_idesc_bf16(TILE_M, 16, p.a_mn_major, 0);
+            const uint64_t d_ones = make_umma_desc_sw128(smem_u32(ones_tile), 16, 1024);
             int stage = 0;
             uint32_t phase = 0;
             int iter = 0;
             for (int unit = cluster_id; unit < num_units; unit += num_clusters, ++iter) {
                 const int tile = unit / p.splits;
                 const int split = unit - tile * p.splits;
-                const int as = iter & 1;
-                const uint32_t aphase = (iter >> 1) & 1;
+                const int as = iter % nstage;
+                const uint32_t aphase = (iter / nstage) & 1;
                 mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
                 tcgen05_fence_after();
                 const uint32_t d_tmem = tmem_base + as * TILE_N;
+                int m_blk_i, n_blk_i;
+                tile_coords(p, tile, m_blk_i, n_blk_i);
+                const bool do_rowsum = rowsum && n_blk_i == 0;   // one column of tiles owns the row sums
                 const int kb0 = split * p.kb_per_split;
                 const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
                 for (int kb = kb0; kb < kb1; ++kb) {
@@ -594,6 +616,13 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
                         umma_bf16_2cta(d_tmem, da + k * a_kstep, db + k * b_kstep, idesc,
                                        (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    if (do_rowsum) {
+                        // D2[256 x 16] += A_tile[256 x 64] . ones[64 x 16]: every column is the row sum
+#pragma unroll
+                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                            umma_bf16_2cta(tmem_base + TILE_N, da + k * a_kstep, d_ones, idesc_ones,
+                                           (kb > kb0 || k > 0) ? 1u : 0u);
                     }
                     umma_commit_2cta(&empty_bar[stage], 3);   // frees the slot in both CTAs
                     if (++stage == STAGES) {
@@ -615,8 +644,8 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
             const int split = unit - tile * p.splits;
             int m_blk, n_blk;
             tile_coords(p, tile, m_blk, n_blk);
-            const int as = iter & 1;
-            const uint32_t aphase = (iter >> 1) & 1;
+            const int as = iter % nstage;
+            const uint32_t aphase = (iter / nstage) & 1;
             mbar_wait(&tmem_full_bar[as], aphase);
             tcgen05_fence_after();
             const int row0 = m_blk * TILE_M + static_cast<int>(cta_rank) * BLOCK_M + quarter * 32;
@@ -644,6 +673,23 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 }
                 epilogue_chunk32(p, r, row0, col0, stg, lane);
             }
+            if (rowsum && n_blk == 0 && group == 0) {
+                // one warp per TMEM lane quarter: column 0 of the row-sum accumulator is this lane's row
+                uint32_t r[32];
+                tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + TILE_N, r);
+                tmem_ld_wait();
+                const int row = row0 + lane;
+                if (row < p.M) {
+                    const float v = __uint_as_float(r[0]);
+                    if (p.splits > 1) {
+                        p.rowsum_ws[static_cast<size_t>(split) * p.M + row] = v;
+                    } else {
+                        float t = v;
+                        if (p.rowsum_accumulate) t += __bfloat162float(p.rowsum_out[row]);
+                        p.rowsum_out[row] = __float2bfloat16(t);
+                    }
+                }
+            }
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tmem_empty_bar[as]), 0));
@@ -662,7 +708,18 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
 // out = alpha * sum_s ws[s] (+ old out) (+ bias), fp32 partials -> bf16
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, int M, int N,
                                      __nv_bfloat16* __restrict__ C, long long ldc, float alpha,
-                                     uint32_t flags, const __nv_bfloat16* __restrict__ bias) {
+                                     uint32_t flags, const __nv_bfloat16* __restrict__ bias,
+                                     const float* __restrict__ rowsum_ws, __nv_bfloat16* __restrict__ rowsum_out,
+                                     int rowsum_accumulate) {
+    if (rowsum_out) {   // partial row sums of the split-K units (see GemmParams::rowsum_out)
+        for (size_t r = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; r < static_cast<size_t>(M);
+             r += static_cast<size_t>(gridDim.x) * blockDim.x) {
+            float t = 0.f;
+            for (int sp = 0; sp < splits; ++sp) t += rowsum_ws[static_cast<size_t>(sp) * M + r];
+            if (rowsum_accumulate) t += __bfloat162float(rowsum_out[r]);
+            rowsum_out[r] = __float2bfloat16(t);
+        }
+    }
     const size_t total4 = static_cast<size_t>(M) * N / 4;
     const size_t plane = static_cast<size_t>(M) * N;
     for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total4;
@@ -854,21 +911,21 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
     return TONY_OK;
 }
 
-template <int STAGES>
+template <int STAGES, bool ROWSUM>
 static int launch_gemm_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
                             cudaStream_t stream) {
-    constexpr size_t SMEM =
-        static_cast<size_t>(STAGES) * (BLOCK_M + 128) * BLOCK_K * 2 + EPI_STAGING_BYTES + 1024 + 256;
+    constexpr size_t SMEM = static_cast<size_t>(STAGES) * (BLOCK_M + 128) * BLOCK_K * 2 + EPI_STAGING_BYTES +
+                            (ROWSUM ? 1024 : 0) + 1024 + 256;
     static bool configured[64] = {false};
     int dev = 0;
     TONY_CUDA_CHECK(cudaGetDevice(&dev));
     if (dev >= 0 && dev < 64 && !configured[dev]) {
-        TONY_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_2cta_kernel<STAGES>,
+        TONY_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_2cta_kernel<STAGES, ROWSUM>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              static_cast<int>(SMEM)));
         configured[dev] = true;
     }
-    TONY_CUDA_CHECK(launch_pdl(gemm_bf16_tcgen05_2cta_kernel<STAGES>, grid, SMEM, stream, ta, tb, p));
+    TONY_CUDA_CHECK(launch_pdl(gemm_bf16_tcgen05_2cta_kernel<STAGES, ROWSUM>, grid, SMEM, stream, ta, tb, p));
     count_launch();
     return TONY_OK;
 }
@@ -905,7 +962,7 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
                      long long ld_aux, void* aux_out, void* workspace, size_t workspace_bytes,
                      int force_block_n, int force_splits, const unsigned int* b_ready,
                      unsigned int b_ready_epoch, int copy_ctas, int max_ctas, const AgHost* ag,
-                     void* stream_v) {
+                     void* stream_v, void* rowsum_out = nullptr, int rowsum_accumulate = 0) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
     if (!A || !B || !C || M <= 0 || N <= 0 || K <= 0) {
         set_last_error("tony_gemm_bf16", "null pointer or non-positive dimension");
@@ -944,6 +1001,10 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
             use_2cta = true;
         }
     }
+    if (rowsum_out && !use_2cta) {
+        set_last_error("tony_gemm_bf16_rowsum", "row sums ride only in the CTA-pair kernel (M, N >= 256)");
+        return TONY_ERR_UNSUPPORTED;
+    }
     if (use_2cta) {
         block_n = 256;
         num_m = (M + 255) / 256;
@@ -978,7 +1039,7 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
         }
         splits = std::min(splits, num_k);
         while (splits > 1 &&
-               static_cast<size_t>(splits) * M * static_cast<size_t>(N) * 4 > workspace_bytes)
+               static_cast<size_t>(splits) * M * (static_cast<size_t>(N) + (rowsum_out ? 1 : 0)) * 4 > workspace_bytes)
             --splits;
     }
     int kb_per_split = (num_k + splits - 1) / splits;
@@ -1018,6 +1079,12 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
     p.ag_flags = nullptr;
     p.ag_rows_per_rank = 1;
     p.n_rot = 0;
+    p.rowsum_out = static_cast<__nv_bfloat16*>(rowsum_out);
+    p.rowsum_accumulate = rowsum_accumulate;
+    // split-K partial row sums live behind the [splits][M][N] partial products
+    p.rowsum_ws = (rowsum_out && splits > 1)
+                      ? static_cast<float*>(workspace) + static_cast<size_t>(splits) * M * static_cast<size_t>(N)
+                      : nullptr;
     if (ag) {
         for (int r = 0; r < ag->world; ++r) p.ag_src[r] = static_cast<const __nv_bfloat16*>(ag->src[r]);
         p.ag_dst = static_cast<__nv_bfloat16*>(ag->dst);
@@ -1029,7 +1096,8 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
     const long long units = tiles * splits;
     const int grid = static_cast<int>(std::min<long long>(units, workers)) + copy_ctas;
     if (use_2cta)
-        rc = launch_gemm_2cta<6>(ta, tb, p, grid * 2, stream);
+        rc = rowsum_out ? launch_gemm_2cta<6, true>(ta, tb, p, grid * 2, stream)
+                        : launch_gemm_2cta<6, false>(ta, tb, p, grid * 2, stream);
     else if (block_n == 256)
         rc = launch_gemm<256, 4>(ta, tb, p, grid, stream);
     else
@@ -1043,7 +1111,8 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
                                                              static_cast<size_t>(sms) * 8));
         splitk_reduce_kernel<<<blocks, threads, 0, stream>>>(
             static_cast<const float*>(workspace), splits, M, N, static_cast<__nv_bfloat16*>(C), ldc,
-            alpha, flags, static_cast<const __nv_bfloat16*>(bias));
+            alpha, flags, static_cast<const __nv_bfloat16*>(bias), p.rowsum_ws,
+            static_cast<__nv_bfloat16*>(rowsum_out), rowsum_accumulate);
         count_launch();
         TONY_CUDA_CHECK(cudaGetLastError());
     }
@@ -1107,4 +1176,15 @@ extern "C" int tony_gemm_bf16(const void* A, const void* B, void* C, int M, int 
     return gemm_host(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, flags, alpha, bias, aux,
                      ld_aux, aux_out, workspace, workspace_bytes, 0, 0, nullptr, 0, 0, 0, nullptr,
                      stream);
+}
+
+extern "C" int tony_gemm_bf16_rowsum(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                                     int b_mn_major, long long lda, long long ldb, long long ldc,
+                                     unsigned int flags, float alpha, const void* bias, const void* aux,
+                                     long long ld_aux, void* aux_out, void* workspace, size_t workspace_bytes,
+                                     void* rowsum_out, int rowsum_accumulate, void* stream) {
+    if (!rowsum_out) return TONY_ERR_INVALID;
+    return gemm_host(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, flags, alpha, bias, aux, ld_aux,
+                     aux_out, workspace, workspace_bytes, 0, 0, nullptr, 0, 0, 0, nullptr, stream, rowsum_out,
+                     rowsum_accumulate);
 }

@@ -100,6 +100,9 @@ def _declare(lib) -> None:
     lib.tony_gemm_bf16.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_longlong,
                                    c_longlong, c_longlong, c_uint, c_float, vp, vp, c_longlong, vp,
                                    vp, c_size_t, vp]
+    lib.tony_gemm_bf16_rowsum.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_longlong, c_longlong,
+                                          c_longlong, c_uint, c_float, vp, vp, c_longlong, vp, vp, c_size_t, vp,
+                                          c_int, vp]
     lib.tony_gemm_bf16_ex.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_longlong,
                                       c_longlong, c_longlong, c_uint, c_float, vp, vp, c_longlong,
                                       vp, vp, c_size_t, c_int, c_int, vp, c_uint, c_int, c_int, vp]

@@ -64,7 +64,8 @@ def _check_bf16(*tensors):
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
          out: Optional[torch.Tensor] = None, flags: int = 0, bias: Optional[torch.Tensor] = None,
          aux: Optional[torch.Tensor] = None, aux_out: Optional[torch.Tensor] = None,
-         alpha: float = 1.0, allow_splitk: bool = True) -> torch.Tensor:
+         alpha: float = 1.0, allow_splitk: bool = True, rowsum_out: Optional[torch.Tensor] = None,
+         rowsum_accumulate: bool = False) -> torch.Tensor:
     """``out[m,n] = epi(alpha * sum_k A(m,k) B(n,k))`` on the tcgen05 tensor cores.
 
     ``a`` is ``[M,K]`` (``a_mn=False``) or ``[K,M]`` (``a_mn=True``); ``b`` is ``[N,K]`` or
@@ -88,6 +89,15 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     elif out.shape != (M, N) or out.stride(1) != 1:
         raise ValueError("bad out tensor")
     ws = workspace("splitk", SPLITK_WORKSPACE_BYTES, a.device) if allow_splitk else None
+    if rowsum_out is not None:
+        # rowsum_out[m] = sum_k A(m,k) rides in the GEMM (bias gradient of a wgrad GEMM)
+        rc = _lib.lib().tony_gemm_bf16_rowsum(
+            ptr(a), ptr(b), ptr(out), M, N, K, int(a_mn), int(b_mn), a.stride(0), b.stride(0),
+            out.stride(0), flags, float(alpha), ptr(bias), ptr(aux),
+            aux.stride(0) if aux is not None else 0, ptr(aux_out), ptr(ws),
+            ws.numel() if ws is not None else 0, ptr(rowsum_out), int(rowsum_accumulate), cur_stream())
+        check(rc, "tony_gemm_bf16_rowsum")
+        return out
     rc = _lib.lib().tony_gemm_bf16(
         ptr(a), ptr(b), ptr(out), M, N, K, int(a_mn), int(b_mn), a.stride(0), b.stride(0),
         out.stride(0), flags, float(alpha), ptr(bias), ptr(aux),
@@ -144,6 +154,37 @@ def _weight_grad(dy2: torch.Tensor, x2: torch.Tensor, weight: torch.Tensor):
     return dest.finish(out)
 
 
+def rowsum_gemm_supported(m: int, n: int) -> bool:
+    """Shapes for which the wgrad GEMM can carry the bias gradient (CTA-pair kernel, ROWSUM
+    instantiation).  Off by default: measured on BERT-large it is 1.5 % SLOWER than the separate
+    column-sum kernels (736.4 vs 747.9 samples/s) — the N=16 row-sum MMA still reads the whole A tile
+    from shared memory (about 32 clk next to the main MMA's 64), only the first column of tiles pays
+    it, and in these single-wave GEMMs the slowest tile sets the time.  TONY_B200_GEMM_ROWSUM=1
+    enables it; spreading the row-sum k-blocks over all column tiles is the open follow-up."""
+    return m >= 256 and n >= 256 and os.environ.get("TONY_B200_GEMM_ROWSUM", "0") == "1" \
+        and os.environ.get("TONY_B200_GEMM_2CTA", "1") != "0"
+
+
+def _weight_bias_grad(dy2: torch.Tensor, x2: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]):
+    """dW = dY^T X and db = colsum(dY).  When the shape allows it db is produced INSIDE the wgrad
+    GEMM (dY^T is its A operand: one extra N=16 MMA per k-step against a tile of ones), so dY is
+    not read a second time by a column-sum kernel."""
+    if bias is None or not rowsum_gemm_supported(weight.shape[0], weight.shape[1]):
+        return _weight_grad(dy2, x2, weight), _bias_grad(dy2, bias)
+    wdest, bdest = _GradDest(weight), _GradDest(bias)
+    db = bdest.tensor if bdest.tensor is not None else torch.empty_like(bias)
+    wflags = EPI_ACCUMULATE if wdest.accumulate else 0
+    try:
+        out = gemm(dy2, x2, a_mn=True, b_mn=True, out=wdest.tensor, flags=wflags, rowsum_out=db,
+                   rowsum_accumulate=bdest.accumulate)
+    except _lib.KernelError as e:
+        if "code 3" not in str(e):          # TONY_ERR_UNSUPPORTED: this launch did not take the pair kernel
+            raise
+        out = gemm(dy2, x2, a_mn=True, b_mn=True, out=wdest.tensor, flags=wflags)
+        colsum(dy2, out=db, accumulate=bdest.accumulate)
+    return wdest.finish(out), bdest.finish(db)
+
+
 def _bias_grad(dy2: torch.Tensor, bias: Optional[torch.Tensor]):
     if bias is None:
         return None
@@ -181,8 +222,7 @@ class _LinearFn(torch.autograd.Function):
         dx = None
         if ctx.needs_input_grad[0]:
             dx = gemm(dy2, weight, b_mn=True).view(ctx.x_shape)  # dX = dY . W
-        dw = _weight_grad(dy2, x2, weight)
-        db = _bias_grad(dy2, ctx.bias)
+        dw, db = _weight_bias_grad(dy2, x2, weight, ctx.bias)
         return dx, dw, db, (dy if ctx.has_res else None)
 
 
@@ -229,11 +269,9 @@ class _MlpFn(torch.autograd.Function):
         dy2 = dy.reshape(-1, N)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        dw2 = _weight_grad(dy2, h, w2)
-        db2 = _bias_grad(dy2, ctx.b2)
+        dw2, db2 = _weight_bias_grad(dy2, h, w2, ctx.b2)
         dpre = gemm(dy2, w2, b_mn=True, flags=_ACT_BWD[ctx.act], aux=pre)  # (dY.W2) * act'(pre)
-        dw1 = _weight_grad(dpre, x2, w1)
-        db1 = _bias_grad(dpre, ctx.b1)
+        dw1, db1 = _weight_bias_grad(dpre, x2, w1, ctx.b1)
         dx = None
         if ctx.needs_input_grad[0]:
             if ctx.self_residual:
@@ -707,13 +745,11 @@ class _AttentionBlockFn(torch.autograd.Function):
         dy2 = dy.reshape(B * S, H)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        dwo = _weight_grad(dy2, o2, wo)
-        dbo = _bias_grad(dy2, ctx.bo)
+        dwo, dbo = _weight_bias_grad(dy2, o2, wo, ctx.bo)
         do = gemm(dy2, wo, b_mn=True)
         dqkv = _attention_core_backward(ctx.saved_core, do.view(B, S, H)).view(B * S, 3 * H)
         ctx.saved_core = None
-        dwqkv = _weight_grad(dqkv, x2, wqkv)
-        dbqkv = _bias_grad(dqkv, ctx.bqkv)
+        dwqkv, dbqkv = _weight_bias_grad(dqkv, x2, wqkv, ctx.bqkv)
         dx = None
         if ctx.needs_input_grad[0]:
             dx = gemm(dqkv, wqkv, b_mn=True, flags=EPI_RESIDUAL, aux=dy2).view(B, S, H)
