@@ -177,7 +177,7 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, const BnDims d, float* __re
 }
 
 // y = relu(x*a + b (+ residual)); every thread keeps the 8 channels it owns in registers.
-__global__ void __launch_bounds__(BN_THREADS)
+__global__ void __launch_bounds__(BN_THREADS, 4)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ residual,
                 const float* __restrict__ ab, __nv_bfloat16* __restrict__ y, unsigned char* __restrict__ mask,
                 long long M, int C, int relu) {
@@ -192,33 +192,47 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
         a[j] = ab[cg * 8 + j];
         b[j] = ab[C + cg * 8 + j];
     }
-    for (long long r = row0; r < M; r += row_stride) {
-        const size_t off = static_cast<size_t>(r) * C + cg * 8;
-        float v[8];
-        unpack8f(ld_global_nc_v4(x + off), v);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], a[j], b[j]);
+    for (long long r = row0; r < M; r += 2 * row_stride) {      // two rows in flight
+        const long long r2 = r + row_stride;
+        const bool two = r2 < M;
+        const size_t off0 = static_cast<size_t>(r) * C + cg * 8;
+        const size_t off1 = static_cast<size_t>(two ? r2 : r) * C + cg * 8;
+        const uint4 x0 = ld_global_nc_v4(x + off0), x1 = ld_global_nc_v4(x + off1);
+        uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
         if (residual) {
-            float rr[8];
-            unpack8f(ld_global_nc_v4(residual + off), rr);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] += rr[j];
+            q0 = ld_global_nc_v4(residual + off0);
+            q1 = ld_global_nc_v4(residual + off1);
         }
-        if (relu) {
-            unsigned int bits = 0;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                bits |= (v[j] > 0.f ? 1u : 0u) << j;
-                v[j] = fmaxf(v[j], 0.f);
+        for (int q = 0; q < 2; ++q) {
+            if (q == 1 && !two) break;
+            const size_t off = q ? off1 : off0;
+            float v[8];
+            unpack8f(q ? x1 : x0, v);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], a[j], b[j]);
+            if (residual) {
+                float rr[8];
+                unpack8f(q ? q1 : q0, rr);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] += rr[j];
             }
-            if (mask) mask[off >> 3] = static_cast<unsigned char>(bits);   // one bit per element for backward
+            if (relu) {
+                unsigned int bits = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    bits |= (v[j] > 0.f ? 1u : 0u) << j;
+                    v[j] = fmaxf(v[j], 0.f);
+                }
+                if (mask) mask[off >> 3] = static_cast<unsigned char>(bits);   // one bit per element for backward
+            }
+            st_global_v4(y + off, pack8f(v));
         }
-        st_global_v4(y + off, pack8f(v));
     }
 }
 
 // Folded-view column sums of dy_m and dy_m * xhat.
-__global__ void __launch_bounds__(BN_THREADS)
+__global__ void __launch_bounds__(BN_THREADS, 3)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const unsigned char* __restrict__ mask, const BnDims d, const float* __restrict__ mean,
                      const float* __restrict__ rstd, int relu, float* __restrict__ partials, unsigned int* __restrict__ counters,
@@ -232,13 +246,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     float a1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};   // sum dy_m
     float a2[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};   // sum dy_m * xhat
     if (col < d.Cw) {
-        float mu[8], rs[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int c = (col + j) % d.C;
-            mu[j] = mean[c];
-            rs[j] = rstd[c];
-        }
+        // a2 accumulates sum dy_m * x; the fold turns it into sum dy_m * xhat = rstd * (a2 - mean * a1),
+        // so the streaming loop carries no per-channel statistics
         for (long long r = r0 + warp; r < r1; r += 32) {     // four rows in flight per warp
             uint4 g[4], xx[4];
             unsigned int mb[4];
@@ -265,7 +274,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                 for (int j = 0; j < 8; ++j) {
                     const float gm = ((mb[q] >> j) & 1u) ? gv[j] : 0.f;
                     a1[j] += gm;
-                    a2[j] = fmaf(gm, (xv[j] - mu[j]) * rs[j], a2[j]);
+                    a2[j] = fmaf(gm, xv[j], a2[j]);
                 }
             }
         }
@@ -290,6 +299,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                                  blockIdx.x * 256, d.Cw, red);
     int c;
     if (combine_groups(d, s1, s2, red, c)) {
+        s2 = rstd[c] * (s2 - mean[c] * s1);
         dbeta[c] = __float2bfloat16(s1);
         dgamma[c] = __float2bfloat16(s2);
         const float inv_m = 1.0f / static_cast<float>(d.M);
@@ -300,7 +310,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 }
 
 // dx = a * (dy_m - dbeta/M - xhat * dgamma/M); optionally dres = dy_m.
-__global__ void __launch_bounds__(BN_THREADS)
+__global__ void __launch_bounds__(BN_THREADS, 4)
 bn_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                  const unsigned char* __restrict__ mask, const float* __restrict__ mean,
                  const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ gamma,
@@ -311,30 +321,43 @@ bn_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __re
     const int cg = static_cast<int>(tid % groups);
     const long long row0 = tid / groups;
     const long long row_stride = static_cast<long long>(gridDim.x) * BN_THREADS / groups;
-    float mu[8], rs[8], aa[8], c1[8], c2[8];
+    // dx = a*(g - c1 - (x - mu)*rs*c2) = a*g + P*x + Q  with  P = -a*rs*c2,  Q = a*(rs*c2*mu - c1):
+    // three per-channel vectors in registers instead of five, two FMAs per element
+    float aa[8], P[8], Q[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const int c = cg * 8 + j;
-        mu[j] = mean[c];
-        rs[j] = rstd[c];
-        aa[j] = __bfloat162float(gamma[c]) * rs[j];
-        c1[j] = coef[c];
-        c2[j] = coef[C + c];
+        const float rs = rstd[c], mu = mean[c];
+        aa[j] = __bfloat162float(gamma[c]) * rs;
+        P[j] = -aa[j] * rs * coef[C + c];
+        Q[j] = aa[j] * (rs * coef[C + c] * mu - coef[c]);
     }
-    for (long long r = row0; r < M; r += row_stride) {
-        const size_t off = static_cast<size_t>(r) * C + cg * 8;
-        float gv[8], xv[8], o[8];
-        unpack8f(ld_global_nc_v4(dy + off), gv);
-        unpack8f(ld_global_nc_v4(x + off), xv);
-        const unsigned int mb = relu ? mask[off >> 3] : 0xffu;
+    for (long long r = row0; r < M; r += 2 * row_stride) {      // two rows (four 16-byte loads) in flight
+        const long long r2 = r + row_stride;
+        const bool two = r2 < M;
+        const size_t off0 = static_cast<size_t>(r) * C + cg * 8;
+        const size_t off1 = static_cast<size_t>(two ? r2 : r) * C + cg * 8;
+        const uint4 g0 = ld_global_nc_v4(dy + off0), x0 = ld_global_nc_v4(x + off0);
+        const uint4 g1 = ld_global_nc_v4(dy + off1), x1 = ld_global_nc_v4(x + off1);
+        const unsigned int m0 = relu ? mask[off0 >> 3] : 0xffu;
+        const unsigned int m1 = relu ? mask[off1 >> 3] : 0xffu;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float g = ((mb >> j) & 1u) ? gv[j] : 0.f;
-            gv[j] = g;
-            o[j] = aa[j] * (g - c1[j] - (xv[j] - mu[j]) * rs[j] * c2[j]);
+        for (int q = 0; q < 2; ++q) {
+            if (q == 1 && !two) break;
+            float gv[8], xv[8], o[8];
+            unpack8f(q ? g1 : g0, gv);
+            unpack8f(q ? x1 : x0, xv);
+            const unsigned int mb = q ? m1 : m0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float g = ((mb >> j) & 1u) ? gv[j] : 0.f;
+                gv[j] = g;
+                o[j] = fmaf(aa[j], g, fmaf(P[j], xv[j], Q[j]));
+            }
+            const size_t off = q ? off1 : off0;
+            st_global_v4(dx + off, pack8f(o));
+            if (dres) st_global_v4(dres + off, pack8f(gv));
         }
-        st_global_v4(dx + off, pack8f(o));
-        if (dres) st_global_v4(dres + off, pack8f(gv));
     }
 }
 
