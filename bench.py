@@ -11,7 +11,7 @@ Rank 0 prints ONE JSON line.  ``value`` is whole-job samples/s with device-resid
 timed with CUDA events bracketed by barrier+synchronize, max over ranks; ``e2e`` is the
 same metric through the public ``tony_b200.runtime.Trainer.step`` call, including every
 step's pinned-host -> device input copy and device -> host loss read (both arms read step i's
-loss after step i+1 has been enqueued: ``Trainer.step_async``).
+loss after step i+2 has been enqueued: ``Trainer.step_async``).
 
 ``--impl stock`` runs the identical model on stock PyTorch (cuBLAS/ATen/NCCL DDP/fused
 AdamW) — the data plane a TonY-launched job uses today.  ``--impl reference`` reports that
@@ -307,13 +307,15 @@ def main(argv=None) -> int:
         e0.record()
         if hasattr(trainer, "step_async"):
             # public pipelined API: step i's loss is read (D2H, pinned) after step i+1 is enqueued
-            pending = None
+            # (two steps of run-ahead: with several ranks a one-step window makes every host wake-up
+            # jitter visible, because the fused collectives wait for the slowest rank)
+            pending = []
             for i in range(args.steps):
-                fut = trainer.step_async(host[i % nb])
-                if pending is not None:
-                    val = pending.result()
-                pending = fut
-            val = pending.result()
+                pending.append(trainer.step_async(host[i % nb]))
+                if len(pending) > 2:
+                    val = pending.pop(0).result()
+            while pending:
+                val = pending.pop(0).result()
         else:
             for i in range(args.steps):
                 val = trainer.step(host[i % nb])
