@@ -19,7 +19,6 @@ import argparse
 import json
 import os
 import re
-import secrets
 import subprocess
 import sys
 import threading

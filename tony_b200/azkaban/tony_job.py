@@ -10,7 +10,6 @@ hand over a ``.job``/properties dict (Azkaban, Airflow, cron) can call :func:`ru
 from __future__ import annotations
 
 import os
-import shlex
 from typing import Dict, List, Optional, Tuple
 
 from ..cli.cluster_submitter import ClusterSubmitter

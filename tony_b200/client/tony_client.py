@@ -21,7 +21,7 @@ import shutil
 import subprocess
 import sys
 import time
-from typing import Callable, Dict, List, Optional, Set
+from typing import Dict, List, Optional, Set
 
 from ..am.session import TaskInfo, TaskStatus
 from ..conf import keys as K

@@ -20,7 +20,6 @@ import os
 import shutil
 import subprocess
 import threading
-import time
 from collections import deque
 from dataclasses import dataclass, field
 from typing import Callable, Deque, Dict, List, Optional, Tuple

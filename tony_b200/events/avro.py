@@ -15,7 +15,7 @@ import io
 import json
 import os
 import struct
-from typing import Any, BinaryIO, Dict, Iterator, List, Optional, Tuple
+from typing import Any, BinaryIO, Dict, List, Optional, Tuple
 
 MAGIC = b"Obj\x01"
 SYNC_SIZE = 16

@@ -18,8 +18,8 @@ import re
 import shutil
 import threading
 import time
-from dataclasses import dataclass, field
-from typing import Dict, List, Optional
+from dataclasses import dataclass
+from typing import List, Optional
 
 from ..conf import keys as K
 from ..conf.configuration import read_xml

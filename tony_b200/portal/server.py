@@ -22,7 +22,7 @@ import time
 from collections import OrderedDict
 from dataclasses import asdict
 from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
-from typing import Callable, Dict, List, Optional
+from typing import Callable, List, Optional
 
 from ..conf import keys as K
 from ..conf.configuration import TonyConfiguration

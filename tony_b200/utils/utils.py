@@ -18,7 +18,7 @@ import tarfile
 import time
 import zipfile
 from dataclasses import dataclass, field
-from typing import Callable, Dict, Iterable, List, Optional, Sequence
+from typing import Callable, Dict, Iterable, List, Optional
 
 from ..conf import keys as K
 from ..conf.configuration import TonyConfiguration, parse_memory_string
