@@ -154,3 +154,29 @@ def test_docker_env_file(tmp_path):
     path = D.write_env_file(conf, {"A": "1", "B": "x y", "BAD": "line1\nline2"}, str(tmp_path))
     lines = open(path).read().splitlines()
     assert "A=1" in lines and "B=x y" in lines and not any(l.startswith("BAD=") for l in lines)
+
+
+def test_batchnorm_act_cpu_fallback_matches_torch():
+    """BatchNormAct off the GPU (or in eval mode) must be plain BatchNorm2d (+ residual) (+ ReLU)."""
+    import torch
+
+    from tony_b200.models.nn import BatchNormAct
+
+    torch.manual_seed(0)
+    bn = BatchNormAct(6, relu=True)
+    ref = torch.nn.BatchNorm2d(6)
+    with torch.no_grad():
+        bn.weight.copy_(torch.rand(6) + 0.5)
+        bn.bias.copy_(torch.randn(6) * 0.1)
+        ref.weight.copy_(bn.weight.float())
+        ref.bias.copy_(bn.bias.float())
+    x = torch.randn(4, 6, 5, 5).to(torch.bfloat16)
+    res = torch.randn(4, 6, 5, 5).to(torch.bfloat16)
+    y = bn(x, residual=res)
+    want = torch.relu(ref(x.float()) + res.float())
+    assert (y.float() - want).abs().max().item() < 0.1
+    assert (bn.running_mean - ref.running_mean).abs().max().item() < 2e-2     # running statistics are updated
+    bn.eval()
+    ref.eval()
+    y2 = bn(x)
+    assert (y2.float() - torch.relu(ref(x.float()))).abs().max().item() < 0.1
