@@ -96,6 +96,11 @@ size_t tony_layernorm_bwd_scratch_bytes(int H);
 int tony_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
                        const float* rstd, void* dx, void* dgamma, void* dbeta, int rows, int H,
                        float* scratch, size_t scratch_bytes, int accumulate, void* stream);
+/* Same, with dx += add: the gradient of a residual branch that bypassed the LayerNorm (pre-LN
+ * transformer blocks), so autograd needs no separate elementwise add to merge the two. */
+int tony_layernorm_bwd_add(const void* dy, const void* x, const void* gamma, const float* mean,
+                           const float* rstd, const void* add, void* dx, void* dgamma, void* dbeta, int rows,
+                           int H, float* scratch, size_t scratch_bytes, int accumulate, void* stream);
 
 /* ---- softmax cross-entropy, forward + backward in one pass --------------------------- */
 /* logits [rows, V] bf16 (row stride ld) are overwritten with dlogits =

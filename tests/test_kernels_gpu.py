@@ -573,3 +573,20 @@ def test_wgrad_gemm_carries_the_bias_gradient(M, N, K, acc):
     ref_b = dy.float().sum(0) + (db0.float() if acc else 0)
     _close(dw, ref_w, rel=2e-2)
     _close(db, ref_b, rel=2e-2)
+
+
+def test_layer_norm_residual_fuses_the_branch_gradient():
+    torch.manual_seed(12)
+    x, g, b = _rand(6, 40, 1024), _rand(1024, scale=0.3) + 1.0, _rand(1024, scale=0.1)
+    w = _rand(1024, 1024, scale=0.03)
+    la = [t.clone().requires_grad_() for t in (x, g, b, w)]
+    h, r = F.layer_norm_residual(la[0], la[1], la[2])
+    ya = F.linear(h, la[3], None, residual=r)
+    lb = [t.clone().requires_grad_() for t in (x, g, b, w)]
+    yb = F.linear(F.layer_norm(lb[0], lb[1], lb[2]), lb[3], None) + lb[0]
+    _close(ya, yb, rel=1e-2)
+    go = _rand(6, 40, 1024)
+    ya.backward(go)
+    yb.backward(go)
+    for p_, q_ in zip(la, lb):
+        _close(p_.grad, q_.grad, rel=2e-2)

@@ -90,7 +90,8 @@ template <int NV>
 __global__ void __launch_bounds__(LN_WARPS * 32)
 layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                         const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean,
-                        const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx, int rows) {
+                        const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx, int rows,
+                        const __nv_bfloat16* __restrict__ add) {
     constexpr int H = NV * 256;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int row = blockIdx.x * LN_WARPS + warp; row < rows; row += gridDim.x * LN_WARPS) {
@@ -128,6 +129,12 @@ layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat1
             for (int j = 0; j < 8; ++j) {
                 const float xh = (xv[j] - mu) * rs;
                 o[j] = (dv[j] * gv[j] - fmaf(xh, c1, c2)) * rs;
+            }
+            if (add) {   // gradient of a residual branch that bypassed this LayerNorm (pre-LN blocks)
+                float av[8];
+                unpack8(ld_global_nc_v4(add + off + (i * 32 + lane) * 8), av);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] += av[j];
             }
             st_global_v4(dx + off + (i * 32 + lane) * 8, pack8(o));
         }
@@ -240,13 +247,14 @@ static int launch_fwd(const void* x, const void* gamma, const void* beta, void* 
 template <int NV>
 static int launch_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
                       const float* rstd, void* dx, void* dgamma, void* dbeta, int rows, float* scratch,
-                      int accumulate, cudaStream_t s) {
+                      int accumulate, cudaStream_t s, const void* add = nullptr) {
     constexpr int H = NV * 256;
     const int sms = device_sm_count();
     const int grid = std::min((rows + LN_WARPS - 1) / LN_WARPS, sms * 8);
     layernorm_bwd_dx_kernel<NV><<<grid, LN_WARPS * 32, 0, s>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
-        static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<__nv_bfloat16*>(dx), rows);
+        static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<__nv_bfloat16*>(dx), rows,
+        static_cast<const __nv_bfloat16*>(add));
     TONY_CUDA_CHECK(cudaGetLastError());
     // scratch: [4 KB counters][partials: slabs x 2 x H floats]
     const int col_tiles = H / 256;
@@ -292,10 +300,10 @@ extern "C" size_t tony_layernorm_bwd_scratch_bytes(int H) {
     return 4096 + static_cast<size_t>(LN_MAX_PARTIALS) * 2 * static_cast<size_t>(H) * sizeof(float);
 }
 
-extern "C" int tony_layernorm_bwd(const void* dy, const void* x, const void* gamma,
-                                  const float* mean, const float* rstd, void* dx, void* dgamma,
-                                  void* dbeta, int rows, int H, float* scratch,
-                                  size_t scratch_bytes, int accumulate, void* stream) {
+static int layernorm_bwd_impl(const void* dy, const void* x, const void* gamma, const float* mean,
+                              const float* rstd, void* dx, void* dgamma, void* dbeta, int rows, int H,
+                              float* scratch, size_t scratch_bytes, int accumulate, void* stream,
+                              const void* add) {
     if (!dy || !x || !gamma || !mean || !rstd || !dx || !dgamma || !dbeta || !scratch || rows <= 0)
         return TONY_ERR_INVALID;
     if (scratch_bytes < tony_layernorm_bwd_scratch_bytes(H)) {
@@ -304,16 +312,32 @@ extern "C" int tony_layernorm_bwd(const void* dy, const void* x, const void* gam
     }
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     switch (H) {
-        case 256: return launch_bwd<1>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
-        case 512: return launch_bwd<2>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
-        case 768: return launch_bwd<3>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
-        case 1024: return launch_bwd<4>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
-        case 1280: return launch_bwd<5>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
-        case 1536: return launch_bwd<6>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
-        case 2048: return launch_bwd<8>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
-        case 4096: return launch_bwd<16>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s);
+        case 256: return launch_bwd<1>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s, add);
+        case 512: return launch_bwd<2>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s, add);
+        case 768: return launch_bwd<3>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s, add);
+        case 1024: return launch_bwd<4>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s, add);
+        case 1280: return launch_bwd<5>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s, add);
+        case 1536: return launch_bwd<6>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s, add);
+        case 2048: return launch_bwd<8>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s, add);
+        case 4096: return launch_bwd<16>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, scratch, accumulate, s, add);
         default:
             set_last_error("tony_layernorm_bwd", "H must be one of 256,512,768,1024,1280,1536,2048,4096");
             return TONY_ERR_UNSUPPORTED;
     }
+}
+
+extern "C" int tony_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
+                                  const float* rstd, void* dx, void* dgamma, void* dbeta, int rows, int H,
+                                  float* scratch, size_t scratch_bytes, int accumulate, void* stream) {
+    return layernorm_bwd_impl(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, H, scratch, scratch_bytes,
+                              accumulate, stream, nullptr);
+}
+
+extern "C" int tony_layernorm_bwd_add(const void* dy, const void* x, const void* gamma, const float* mean,
+                                      const float* rstd, const void* add, void* dx, void* dgamma, void* dbeta,
+                                      int rows, int H, float* scratch, size_t scratch_bytes, int accumulate,
+                                      void* stream) {
+    if (!add) return TONY_ERR_INVALID;
+    return layernorm_bwd_impl(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, H, scratch, scratch_bytes,
+                              accumulate, stream, add);
 }

@@ -52,8 +52,12 @@ class GPT2Block(nn.Module):
         self.mlp = MLP(c.hidden, c.inner, "gelu_tanh", out_std=out_std, device=device)
 
     def forward(self, x):
-        x = self.attn(self.ln1(x), residual=x)
-        return self.mlp(self.ln2(x), residual=x)
+        # pre-LN: the residual branch leaves through the LayerNorm node, so its gradient is added inside
+        # the LayerNorm backward kernel instead of by a separate elementwise add
+        h, r = self.ln1.with_residual(x)
+        x = self.attn(h, residual=r)
+        h, r = self.ln2.with_residual(x)
+        return self.mlp(h, residual=r)
 
 
 class GPT2LMHead(nn.Module):

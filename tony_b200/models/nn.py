@@ -51,6 +51,11 @@ class LayerNorm(nn.Module):
     def forward(self, x):
         return F.layer_norm(x, self.weight, self.bias, self.eps)
 
+    def with_residual(self, x):
+        """``(layer_norm(x), x)`` as one autograd node for pre-LN blocks (see
+        ``functional.layer_norm_residual``): feed the second value to the block's residual input."""
+        return F.layer_norm_residual(x, self.weight, self.bias, self.eps)
+
 
 class Embedding(nn.Module):
     def __init__(self, num: int, dim: int, std: float = 0.02, device=None):

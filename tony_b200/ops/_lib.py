@@ -164,6 +164,7 @@ def _declare(lib) -> None:
     lib.tony_bn_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_longlong, c_int, c_int, vp, c_size_t, vp]
     lib.tony_maxpool3x3s2_fwd.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, vp]
     lib.tony_maxpool3x3s2_bwd.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, vp]
+    lib.tony_layernorm_bwd_add.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, c_int, c_int, vp, c_size_t, c_int, vp]
     lib.tony_attention_fwd_bf16.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_float, vp]
     lib.tony_attention_bwd_bf16.argtypes = [vp, vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int,
                                             c_float, vp]

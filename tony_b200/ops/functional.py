@@ -387,6 +387,70 @@ def layer_norm(x, gamma, beta, eps: float = 1e-5):
     return _LayerNormFn.apply(x, gamma, beta, eps)
 
 
+class _LayerNormResidualFn(torch.autograd.Function):
+    """Pre-LN block entry: returns ``(layer_norm(x), x)``.  The second output is the residual branch;
+    because both outputs belong to one autograd node, backward receives the normalised branch's
+    gradient AND the residual branch's gradient together and adds the latter inside the LayerNorm
+    backward kernel (``tony_layernorm_bwd_add``) instead of in a separate elementwise pass."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        H = x.shape[-1]
+        x2 = x.reshape(-1, H)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        _check_bf16(x2, gamma, beta)
+        rows = x2.shape[0]
+        y = torch.empty_like(x2)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        check(_lib.lib().tony_layernorm_fwd(ptr(x2), ptr(gamma), ptr(beta), ptr(y), ptr(mean),
+                                            ptr(rstd), rows, H, float(eps), cur_stream()),
+              "tony_layernorm_fwd")
+        ctx.save_for_backward(x2, gamma, mean, rstd)
+        ctx.beta = beta
+        ctx.x_shape = x.shape
+        return y.view(x.shape), x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, dy, dres):
+        x2, gamma, mean, rstd = ctx.saved_tensors
+        H = x2.shape[1]
+        dy2 = dy.reshape(-1, H)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        rows = x2.shape[0]
+        lib = _lib.lib()
+        dx = torch.empty_like(x2)
+        dg, db = _GradDest(gamma), _GradDest(ctx.beta)
+        if dg.tensor is None:
+            dg_t = torch.empty(H, dtype=torch.bfloat16, device=x2.device)
+            db_t = torch.empty(H, dtype=torch.bfloat16, device=x2.device)
+            acc = False
+        else:
+            dg_t, db_t = dg.tensor, db.tensor
+            acc = dg.accumulate
+        nbytes = int(lib.tony_layernorm_bwd_scratch_bytes(H))
+        scratch = workspace("ln_bwd", nbytes, x2.device)
+        if dres is None:
+            check(lib.tony_layernorm_bwd(ptr(dy2), ptr(x2), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx),
+                                         ptr(dg_t), ptr(db_t), rows, H, ptr(scratch), nbytes, int(acc),
+                                         cur_stream()), "tony_layernorm_bwd")
+        else:
+            dr2 = dres.reshape(-1, H)
+            if not dr2.is_contiguous():
+                dr2 = dr2.contiguous()
+            check(lib.tony_layernorm_bwd_add(ptr(dy2), ptr(x2), ptr(gamma), ptr(mean), ptr(rstd), ptr(dr2),
+                                             ptr(dx), ptr(dg_t), ptr(db_t), rows, H, ptr(scratch), nbytes,
+                                             int(acc), cur_stream()), "tony_layernorm_bwd_add")
+        return dx.view(ctx.x_shape), dg.finish(dg_t), db.finish(db_t), None
+
+
+def layer_norm_residual(x, gamma, beta, eps: float = 1e-5):
+    """``(layer_norm(x), x)`` for pre-LN blocks: use the second value as the residual input."""
+    return _LayerNormResidualFn.apply(x, gamma, beta, eps)
+
+
 # ---------------------------------------------------------------------------------------
 class _SoftmaxXentFn(torch.autograd.Function):
     """Fused softmax cross-entropy.  The logits buffer is consumed: forward overwrites it
