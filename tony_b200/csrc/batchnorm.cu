@@ -112,11 +112,13 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, const BnDims d, float* __re
     float a1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float a2[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (col < d.Cw) {
-        long long r = r0 + warp;
-        for (; r + 3 * 8 < r1; r += 4 * 8) {   // four rows in flight per warp
+        for (long long r = r0 + warp; r < r1; r += 4 * 8) {   // four rows in flight per warp, last batch predicated
             uint4 u[4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) u[q] = ld_global_nc_v4(x + (r + q * 8) * d.Cw + col);
+            for (int q = 0; q < 4; ++q) {
+                const long long rr = r + q * 8;
+                u[q] = rr < r1 ? ld_global_nc_v4(x + rr * d.Cw + col) : make_uint4(0, 0, 0, 0);
+            }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 float v[8];
@@ -126,15 +128,6 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, const BnDims d, float* __re
                     a1[j] += v[j];
                     a2[j] = fmaf(v[j], v[j], a2[j]);
                 }
-            }
-        }
-        for (; r < r1; r += 8) {
-            float v[8];
-            unpack8f(ld_global_nc_v4(x + r * d.Cw + col), v);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                a1[j] += v[j];
-                a2[j] = fmaf(v[j], v[j], a2[j]);
             }
         }
     }

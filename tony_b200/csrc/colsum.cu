@@ -75,12 +75,16 @@ colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, lon
     const int r1 = min(rows, r0 + rows_per_slab);
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (col < cols) {
-        int r = r0 + warp;
-        for (; r + 7 * (CS_THREADS / 32) < r1; r += 8 * (CS_THREADS / 32)) {  // 8 loads in flight
+        // eight rows in flight per warp; the last batch is predicated instead of falling back to a
+        // one-row-at-a-time loop (each of those iterations was a full memory round trip)
+        constexpr int W = CS_THREADS / 32;
+        for (int r = r0 + warp; r < r1; r += 8 * W) {
             uint4 u[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k)
-                u[k] = ld_global_nc_v4(x + static_cast<size_t>(r + k * (CS_THREADS / 32)) * ld + col);
+            for (int k = 0; k < 8; ++k) {
+                const int rr = r + k * W;
+                u[k] = rr < r1 ? ld_global_nc_v4(x + static_cast<size_t>(rr) * ld + col) : make_uint4(0, 0, 0, 0);
+            }
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const uint32_t w[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
@@ -90,16 +94,6 @@ colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, lon
                     acc[2 * j] += f.x;
                     acc[2 * j + 1] += f.y;
                 }
-            }
-        }
-        for (; r < r1; r += CS_THREADS / 32) {
-            const uint4 u = ld_global_nc_v4(x + static_cast<size_t>(r) * ld + col);
-            const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float2 f = unpack_bf16x2(w[j]);
-                acc[2 * j] += f.x;
-                acc[2 * j + 1] += f.y;
             }
         }
     }

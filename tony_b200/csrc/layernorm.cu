@@ -159,15 +159,23 @@ layernorm_bwd_dgdb_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloa
     float ab[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     constexpr int W = LN_RED_THREADS / 32;
     int r = r0 + warp;
-    for (; r + 3 * W < r1; r += 4 * W) {  // four rows (eight 16-byte loads) in flight per warp
+    for (; r < r1; r += 4 * W) {  // four rows (eight 16-byte loads) in flight per warp; last batch predicated
         uint4 xq[4], dq[4];
         float mu[4], rs[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            xq[k] = ld_global_nc_v4(x + static_cast<size_t>(r + k * W) * H + col);
-            dq[k] = ld_global_nc_v4(dy + static_cast<size_t>(r + k * W) * H + col);
-            mu[k] = mean[r + k * W];
-            rs[k] = rstd[r + k * W];
+            const int rr = r + k * W;
+            if (rr < r1) {
+                xq[k] = ld_global_nc_v4(x + static_cast<size_t>(rr) * H + col);
+                dq[k] = ld_global_nc_v4(dy + static_cast<size_t>(rr) * H + col);
+                mu[k] = mean[rr];
+                rs[k] = rstd[rr];
+            } else {
+                xq[k] = make_uint4(0, 0, 0, 0);
+                dq[k] = xq[k];
+                mu[k] = 0.f;
+                rs[k] = 0.f;
+            }
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -179,17 +187,6 @@ layernorm_bwd_dgdb_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloa
                 ag[j] = fmaf(dv[j], (xv[j] - mu[k]) * rs[k], ag[j]);
                 ab[j] += dv[j];
             }
-        }
-    }
-    for (; r < r1; r += W) {
-        float xv[8], dv[8];
-        unpack8(ld_global_nc_v4(x + static_cast<size_t>(r) * H + col), xv);
-        unpack8(ld_global_nc_v4(dy + static_cast<size_t>(r) * H + col), dv);
-        const float mu = mean[r], rs = rstd[r];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            ag[j] = fmaf(dv[j], (xv[j] - mu) * rs, ag[j]);
-            ab[j] += dv[j];
         }
     }
 #pragma unroll
