@@ -578,37 +578,41 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
             const bool diag = p.causal && (j * ATT_BK + ATT_BK - 1 > q0);
             mbar_wait(sc_full, j & 1);
             tcgen05_fence_after();
+            // pull the whole block (64 scores + 64 dP values) into registers and hand the TMEM columns
+            // back at once: the next block's score MMAs run while this one's exponentials do
+            uint32_t rs[64], rp[64];
+            tmem_ld_32x32(tS + lane_addr, rs);
+            tmem_ld_32x32(tS + lane_addr + 32, rs + 32);
+            tmem_ld_32x32(tdP + lane_addr, rp);
+            tmem_ld_32x32(tdP + lane_addr + 32, rp + 32);
+            tmem_ld_wait();
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sc_free);
             if (j > 0) mbar_wait(dq_done, (j - 1) & 1);   // previous dS tile consumed
-#pragma unroll 1
+#pragma unroll
             for (int c = 0; c < 2; ++c) {
-                uint32_t rs[32], rp[32];
-                tmem_ld_32x32(tS + lane_addr + c * 32, rs);
-                tmem_ld_32x32(tdP + lane_addr + c * 32, rp);
-                tmem_ld_wait();
                 uint32_t w[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
-                    float p0 = ex2_approx(fmaf(__uint_as_float(rs[2 * i]), p.scale_log2, neg_l));
-                    float p1 = ex2_approx(fmaf(__uint_as_float(rs[2 * i + 1]), p.scale_log2, neg_l));
+                    const int e = c * 32 + 2 * i;
+                    float p0 = ex2_approx(fmaf(__uint_as_float(rs[e]), p.scale_log2, neg_l));
+                    float p1 = ex2_approx(fmaf(__uint_as_float(rs[e + 1]), p.scale_log2, neg_l));
                     if (diag) {
-                        if (c * 32 + 2 * i > rel) p0 = 0.f;
-                        if (c * 32 + 2 * i + 1 > rel) p1 = 0.f;
+                        if (e > rel) p0 = 0.f;
+                        if (e + 1 > rel) p1 = 0.f;
                     }
-                    w[i] = pack_bf16x2(p0 * (__uint_as_float(rp[2 * i]) - drow),
-                                       p1 * (__uint_as_float(rp[2 * i + 1]) - drow));
+                    w[i] = pack_bf16x2(p0 * (__uint_as_float(rp[e]) - drow),
+                                       p1 * (__uint_as_float(rp[e + 1]) - drow));
                 }
 #pragma unroll
                 for (int v = 0; v < 4; ++v)
                     st_shared_v4(sdS_u32 + panel_unit_offset(row, c * 4 + v),
                                  make_uint4(w[4 * v], w[4 * v + 1], w[4 * v + 2], w[4 * v + 3]));
             }
-            tcgen05_fence_before();
-            fence_proxy_async();
+            fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(sc_free);
-                mbar_arrive(ds_full);
-            }
+            if (lane == 0) mbar_arrive(ds_full);
         }
         mbar_wait(dq_done, (nblk - 1) & 1);
         tcgen05_fence_after();
@@ -816,7 +820,7 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
                 }
             }
             tcgen05_fence_before();
-            fence_proxy_async();
+            fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) {
                 mbar_arrive(sc_free);
