@@ -13,9 +13,16 @@ same metric through the public ``tony_b200.runtime.Trainer.step`` call, includin
 step's pinned-host -> device input copy and device -> host loss read (both arms read step i's
 loss after step i+2 has been enqueued: ``Trainer.step_async``).
 
-``--impl stock`` runs the identical model on stock PyTorch (cuBLAS/ATen/NCCL DDP/fused
-AdamW) — the data plane a TonY-launched job uses today.  ``--impl reference`` reports that
-the reference itself (a Java/YARN launcher with no data plane) cannot be installed here.
+``--impl stock`` / ``--impl stock-bf16`` run the identical model on stock PyTorch (cuBLAS/ATen/
+NCCL DDP/fused AdamW; fp32 parameters under autocast, or bf16-resident parameters) — the data
+plane a TonY-launched job uses today.  ``--impl reference`` reports that the reference itself (a
+Java/YARN launcher with no data plane) cannot be installed here.
+
+By default (``--compare 1``) the own arm is followed, in the same process group on the same box,
+by both stock variants; the better one is the baseline: ``vs_baseline`` = own value / its value
+and ``baseline`` carries both variants' numbers and the end-to-end ratio.  ``--secondary 1`` adds
+the other two parts of BASELINE.json's metric: ResNet-50 img/s (own and stock) and, on one GPU,
+the launcher's submit-to-barrier / submit-to-first-step latency.
 """
 from __future__ import annotations
 
@@ -38,7 +45,7 @@ REFERENCE_UNAVAILABLE = (
 
 SMI_QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,utilization.gpu")
 
 
 class ClockSampler:
@@ -67,7 +74,7 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-        sm, smax, reasons = [], [], set()
+        sm, smax, watts, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         try:
             for line in open(self.path):
@@ -75,11 +82,15 @@ class ClockSampler:
                 if len(f) < 9 or not f[0].isdigit():
                     continue
                 try:
-                    power = float(f[3])
-                    if power < 250:  # idle GPU or idle sample: only GPUs under load count
+                    # only GPUs that are executing kernels count (an idle neighbour GPU parks its clock);
+                    # the filter is on utilisation, never on power: a throttled GPU draws little power
+                    # and must stay in the record
+                    util = float(f[9]) if len(f) > 9 else 100.0
+                    if util < 50.0:
                         continue
                     sm.append(float(f[1]))
                     smax.append(float(f[2]))
+                    watts.append(float(f[3]))
                 except ValueError:
                     continue
                 for name, val in zip(names, f[5:9]):
@@ -96,6 +107,7 @@ class ClockSampler:
             out["sm_mhz"] = statistics.median(sm)
             out["sm_max_mhz"] = max(smax)
             out["samples_under_load"] = len(sm)
+            out["power_w_median"] = statistics.median(watts)
         out["reasons"] = sorted(reasons)
         return out
 
@@ -105,7 +117,7 @@ def parse_args(argv=None):
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "stock", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "stock", "stock-bf16", "reference"])
     ap.add_argument("--model", default="bert-large", choices=["bert-large", "bert-tiny", "gpt2-medium", "resnet50", "widedeep"])
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default 32 BERT / 8 GPT-2)")
     ap.add_argument("--seq", type=int, default=0)
@@ -115,33 +127,40 @@ def parse_args(argv=None):
     ap.add_argument("--bucket-mb", type=float, default=64.0)
     ap.add_argument("--comm-ctas", type=int, default=32)
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--compare", type=int, default=1,
+                    help="1: after the own arm, run the stock-PyTorch arms (fp32 params + autocast, and "
+                         "bf16-resident params) in the same process group and report vs_baseline")
+    ap.add_argument("--secondary", type=int, default=1,
+                    help="1: with --model bert-large also measure ResNet-50 img/s (own and stock) and, on "
+                         "one GPU, the launcher's submit-to-first-step latency")
     return ap.parse_args(argv)
 
 
-def build(args, device):
+def build(args, impl, model_key, device):
     import torch
 
     from tony_b200.models import bert, gpt2, stock
 
-    if args.model.startswith("bert"):
-        cfg = bert.BertConfig.large() if args.model == "bert-large" else bert.BertConfig.tiny()
+    ours = impl == "ours"
+    if model_key.startswith("bert"):
+        cfg = bert.BertConfig.large() if model_key == "bert-large" else bert.BertConfig.tiny()
         seq = args.seq or min(512, cfg.max_positions)
-        batch = args.batch or (32 if args.model == "bert-large" else 8)
+        batch = args.batch or (32 if model_key == "bert-large" else 8)
         make = lambda seed, pin=False, dev="cpu": bert.synthetic_batch(cfg, batch, seq, dev, pin, seed)
         flops = bert.train_flops_per_sample(cfg, seq)
-        model = bert.BertForPreTraining(cfg, device=device) if args.impl == "ours" else stock.StockBertForPreTraining(cfg)
-        metric = "bert_large_pretrain_samples_per_sec" if args.model == "bert-large" else "bert_tiny_samples_per_sec"
-        name = "BERT-large (24L/1024H/16A, vocab 30522, MLM 80 preds + NSP)" if args.model == "bert-large" else "BERT-tiny"
-    elif args.model == "resnet50":
+        model = bert.BertForPreTraining(cfg, device=device) if ours else stock.StockBertForPreTraining(cfg)
+        metric = "bert_large_pretrain_samples_per_sec" if model_key == "bert-large" else "bert_tiny_samples_per_sec"
+        name = "BERT-large (24L/1024H/16A, vocab 30522, MLM 80 preds + NSP)" if model_key == "bert-large" else "BERT-tiny"
+    elif model_key == "resnet50":
         from tony_b200.models import resnet
 
-        batch = args.batch or 256
+        batch = args.batch if (args.batch and args.model == "resnet50") else 256
         make = lambda seed, pin=False, dev="cpu": resnet.synthetic_batch(batch, dev, pin, seed)
-        flops = 3 * 4.1e9 * 2 / 2  # ~4.1 GMACs forward per 224x224 image, x3 for fwd+bwd
-        model = resnet.ResNet50(device=device) if args.impl == "ours" else resnet.stock_resnet50(device=device)
+        flops = 3 * 4.1e9 * 2  # ~4.1 GMACs forward per 224x224 image, x3 for fwd+bwd
+        model = resnet.ResNet50(device=device) if ours else resnet.stock_resnet50(device=device)
         return model, make, batch, 224, flops, "resnet50_train_img_per_sec", \
-            "ResNet-50 v1.5, 224x224, bf16 channels-last (3x3/7x7 convs + BN on cuDNN in both arms)"
-    elif args.model == "widedeep":
+            "ResNet-50 v1.5, 224x224, bf16 channels-last"
+    elif model_key == "widedeep":
         from tony_b200.models import widedeep
 
         cfg = widedeep.WideDeepConfig()
@@ -149,7 +168,7 @@ def build(args, device):
         make = lambda seed, pin=False, dev="cpu": widedeep.synthetic_batch(cfg, batch, dev, pin, seed)
         dims = [26 * 128 + 16] + cfg.hidden
         flops = 6.0 * sum(a * b for a, b in zip(dims[:-1], dims[1:]))
-        model = widedeep.WideDeep(cfg, device=device) if args.impl == "ours" else widedeep.StockWideDeep(cfg)
+        model = widedeep.WideDeep(cfg, device=device) if ours else widedeep.StockWideDeep(cfg)
         return model, make, batch, 1, flops, "widedeep_ps_samples_per_sec", \
             "wide&deep recommender (26 x 100k-row tables, tower 3344-4096-4096-2048-1024)"
     else:
@@ -158,22 +177,26 @@ def build(args, device):
         batch = args.batch or 8
         make = lambda seed, pin=False, dev="cpu": gpt2.synthetic_batch(cfg, batch, seq, dev, pin, seed)
         flops = gpt2.train_flops_per_sample(cfg, seq)
-        model = gpt2.GPT2LMHead(cfg, device=device) if args.impl == "ours" else stock.StockGPT2LMHead(cfg)
+        model = gpt2.GPT2LMHead(cfg, device=device) if ours else stock.StockGPT2LMHead(cfg)
         metric = "gpt2_medium_samples_per_sec"
         name = "GPT-2 medium (24L/1024H/16A, vocab 50257)"
     return model, make, batch, seq, flops, metric, name
 
 
 class StockTrainer:
-    """Baseline arm: autocast-bf16 + DDP(NCCL) + fused AdamW, same step contract as Trainer."""
+    """Baseline arm: DDP(NCCL) + fused AdamW/SGD, same step contract as Trainer.  Two variants:
+    fp32 parameters under bf16 autocast (what a stock mixed-precision job runs) and bf16-resident
+    parameters with no autocast (no per-GEMM weight casts, no fp32 master: the cheapest stock step)."""
 
-    def __init__(self, model, device, world, sgd=False, autocast=True):
+    def __init__(self, model, device, world, sgd=False, autocast=True, bf16_params=False):
         import torch
 
         self.torch = torch
         self.device = device
-        self.autocast = autocast
+        self.autocast = autocast and not bf16_params
         self.model = model.to(device)
+        if bf16_params:
+            self.model = self.model.to(torch.bfloat16)
         if world > 1:
             from torch.nn.parallel import DistributedDataParallel as DDP
 
@@ -217,6 +240,153 @@ class StockTrainer:
         return _Fut()
 
 
+def run_arm(args, impl, model_key, rank, world, device, sample_clocks=True):
+    """Build one arm (own kernels or a stock-PyTorch variant), warm it up, and time it twice: with
+    device-resident inputs (CUDA events, barrier + synchronize on both sides, max over ranks) and end to
+    end through the public step call (pinned-host inputs copied every step, loss read back every step)."""
+    import gc
+
+    import torch
+    import torch.distributed as dist
+
+    from tony_b200 import runtime
+
+    torch.manual_seed(1234)
+    if model_key == "resnet50" and os.environ.get("TONY_B200_CUDNN_BENCHMARK", "1") == "1":
+        # fixed-shape CNN: let cuDNN time its algorithms once (standard practice; the stock arm
+        # needs it, the own arm only where a layer is still routed to the library)
+        torch.backends.cudnn.benchmark = True
+    model, make, batch, seq, flops_per_sample, metric, model_name = build(args, impl, model_key, device)
+
+    if impl == "ours":
+        from tony_b200.ops import _lib
+
+        kw = dict(overlap=not args.no_overlap, bucket_mb=args.bucket_mb, comm_ctas=args.comm_ctas, device=device,
+                  cuda_graph=None if args.cuda_graph < 0 else bool(args.cuda_graph))
+        if model_key == "resnet50":
+            model = model.to(device=device, dtype=torch.bfloat16)
+            trainer = runtime.Trainer(model, lr=0.1, optimizer="sgd", weight_decay=1e-4, generic_hooks=True, **kw)
+        elif model_key == "widedeep":
+            from tony_b200.parallel.ps import ps_parameters
+
+            trainer = runtime.Trainer(model, lr=1e-3, weight_decay=0.0, ps_sharded=ps_parameters(model), **kw)
+        else:
+            trainer = runtime.Trainer(model, lr=1e-4, weight_decay=0.01, **kw)
+        launches = _lib.launch_count
+    else:
+        bf16 = impl == "stock-bf16"
+        trainer = StockTrainer(model, device, world, sgd=(model_key == "resnet50"),
+                               autocast=(model_key != "resnet50"), bf16_params=bf16 or model_key == "resnet50")
+        launches = lambda: 0
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # distinct batches so no step can reuse cached results; device copies for the kernel-level loop
+    nb = 4
+    host = [make(100 + rank * 17 + i, pin=True) for i in range(nb)]
+    devb = [trainer.to_device(b) for b in host]
+    last = None
+    for i in range(args.warmup):
+        last = trainer.step_device(devb[i % nb])
+    sync_all()
+    warm_loss = float(last.item()) if args.warmup else float("nan")
+
+    # ---- kernel-level number: device-resident inputs, no host sync inside -------------
+    sampler = ClockSampler(rank == 0 and sample_clocks)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = launches()
+    sync_all()
+    e0.record()
+    for i in range(args.steps):
+        last = trainer.step_device(devb[i % nb])
+    e1.record()
+    sync_all()
+    l1 = launches()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    final_loss = float(last.item())
+
+    # ---- end-to-end: public API, per-step H2D of pinned inputs + D2H of the loss -----
+    e2e = None
+    if not args.skip_e2e:
+        h2d = sum(v.numel() * v.element_size() for v in host[0].values())
+        sync_all()
+        e0.record()
+        # public pipelined API: step i's loss is read (D2H, pinned) after step i+2 is enqueued
+        # (two steps of run-ahead: with several ranks a one-step window makes every host wake-up
+        # jitter visible, because the fused collectives wait for the slowest rank)
+        pending = []
+        val = float("nan")
+        for i in range(args.steps):
+            pending.append(trainer.step_async(host[i % nb]))
+            if len(pending) > 2:
+                val = pending.pop(0).result()
+        while pending:
+            val = pending.pop(0).result()
+        e1.record()
+        sync_all()
+        ms2 = torch.tensor([e0.elapsed_time(e1)], device=device)
+        if world > 1:
+            dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
+        e2e = {"value": round(batch * world * args.steps / (float(ms2.item()) / 1e3), 2),
+               "unit": "img/s" if model_key == "resnet50" else "samples/s",
+               "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
+               "ms_per_step": round(float(ms2.item()) / args.steps, 3), "last_loss": round(val, 4)}
+    clocks = sampler.stop()
+    if impl == "ours":
+        trainer.check()
+    res = {
+        "impl": impl, "metric": metric, "model_name": model_name, "batch": batch, "seq": seq,
+        "value": batch * world * args.steps / (ms_total / 1e3), "ms_per_step": ms_total / args.steps,
+        "e2e": e2e, "gpu_launches": int(l1 - l0), "clocks": clocks, "flops_per_sample": flops_per_sample,
+        "loss_after_warmup": round(warm_loss, 4), "loss_final": round(final_loss, 4),
+        "cuda_graph": bool(getattr(trainer, "cuda_graph", False)),
+    }
+    # release this arm's memory before the next one is built
+    del trainer, model, devb, host, last
+    gc.collect()
+    torch.cuda.empty_cache()
+    return res
+
+
+def launcher_latency():
+    """Submit -> gang barrier -> first step through this repo's launcher (2 CPU workers, gloo): the
+    third part of BASELINE.json's metric.  Rank 0 of a 1-GPU run only; best effort."""
+    import subprocess as sp
+
+    try:
+        out = sp.run([sys.executable, os.path.join(ROOT, "tools", "launch_latency.py"), "--repeat", "1",
+                      "--arms", "ours"], capture_output=True, text=True, timeout=180)
+        res = {}
+        for line in out.stdout.splitlines():
+            try:
+                rec = json.loads(line)
+            except ValueError:
+                continue
+            if "median_ms" in rec:
+                res["submit_to_first_step_ms"] = rec["median_ms"]
+                res["workers"] = rec["workers"]
+            tl = dict((k, v) for k, v in reversed(rec.get("launcher_timeline_ms_since_submit", [])))
+            if "gang_barrier_open" in tl:
+                res["submit_to_barrier_ms"] = round(tl["gang_barrier_open"], 1)
+        res["note"] = ("2 CPU workers over gloo; first step includes the user process's `import torch`; "
+                       "the reference (JVM + YARN) cannot run here, its structural floor is > 5 s before "
+                       "the user process starts (BASELINE.md)")
+        return res or {"error": (out.stderr or out.stdout)[-300:]}
+    except Exception as e:  # noqa: BLE001 - a secondary number must never fail the bench
+        return {"error": repr(e)[:300]}
+
+
+def _brief(r):
+    return {"value": round(r["value"], 2), "ms_per_step": round(r["ms_per_step"], 3),
+            "e2e": r["e2e"]["value"] if r["e2e"] else None, "loss_final": r["loss_final"]}
+
+
 def main(argv=None) -> int:
     args = parse_args(argv)
     if args.impl == "reference":
@@ -241,123 +411,90 @@ def main(argv=None) -> int:
     if world != args.gpus:
         if rank == 0:
             sys.stderr.write(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}; using {world}\n")
-    torch.manual_seed(1234)
-    if args.model == "resnet50" and os.environ.get("TONY_B200_CUDNN_BENCHMARK", "1") == "1":
-        # fixed-shape CNN: let cuDNN time its algorithms once (standard practice; BOTH arms)
-        torch.backends.cudnn.benchmark = True
-    model, make, batch, seq, flops_per_sample, metric, model_name = build(args, device)
 
-    if args.impl == "ours":
-        from tony_b200.ops import _lib
+    main_res = run_arm(args, args.impl, args.model, rank, world, device)
 
-        kw = dict(overlap=not args.no_overlap, bucket_mb=args.bucket_mb, comm_ctas=args.comm_ctas, device=device,
-                  cuda_graph=None if args.cuda_graph < 0 else bool(args.cuda_graph))
-        if args.model == "resnet50":
-            model = model.to(device=device, dtype=torch.bfloat16)
-            trainer = runtime.Trainer(model, lr=0.1, optimizer="sgd", weight_decay=1e-4, generic_hooks=True, **kw)
-        elif args.model == "widedeep":
-            from tony_b200.parallel.ps import ps_parameters
+    # ---- baseline arms in the same process group, same box, same steps / warm-up ----------------
+    baseline = None
+    if args.impl == "ours" and args.compare:
+        variants = {}
+        for impl in (("stock",) if args.model in ("resnet50", "widedeep") else ("stock", "stock-bf16")):
+            try:
+                variants[impl] = run_arm(args, impl, args.model, rank, world, device, sample_clocks=False)
+            except Exception as e:  # noqa: BLE001
+                variants[impl] = None
+                sys.stderr.write(f"baseline arm {impl} failed: {e!r}\n")
+        good = {k: v for k, v in variants.items() if v}
+        if good:
+            best = max(good, key=lambda k: good[k]["value"])
+            b = good[best]
+            baseline = {
+                "what": "stock PyTorch on the same box in the same run (cuBLASLt/ATen/cuDNN SDPA, fused "
+                        "AdamW, DDP/NCCL); the better of fp32-params+autocast and bf16-resident params; "
+                        "the reference itself has no data plane and no published number (BASELINE.md)",
+                "best": best, "value": round(b["value"], 2),
+                "e2e": b["e2e"]["value"] if b["e2e"] else None,
+                "variants": {k: _brief(v) for k, v in good.items()},
+                "ratio": round(main_res["value"] / b["value"], 4),
+                "e2e_ratio": (round(main_res["e2e"]["value"] / b["e2e"]["value"], 4)
+                              if main_res["e2e"] and b["e2e"] else None),
+            }
 
-            trainer = runtime.Trainer(model, lr=1e-3, weight_decay=0.0, ps_sharded=ps_parameters(model), **kw)
-        else:
-            trainer = runtime.Trainer(model, lr=1e-4, weight_decay=0.01, **kw)
-        launches = _lib.launch_count
-    else:
-        trainer = StockTrainer(model, device, world, sgd=(args.model == "resnet50"),
-                               autocast=(args.model != "resnet50"))
-        launches = lambda: 0
-
-    def sync_all():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # distinct batches so no step can reuse cached results; device copies for the kernel-level loop
-    nb = 4
-    host = [make(100 + rank * 17 + i, pin=True) for i in range(nb)]
-    devb = [trainer.to_device(b) for b in host]
-    for i in range(args.warmup):
-        last = trainer.step_device(devb[i % nb])
-    sync_all()
-    warm_loss = float(last.item()) if args.warmup else float("nan")
-
-    # ---- kernel-level number: device-resident inputs, no host sync inside -------------
-    sampler = ClockSampler(rank == 0)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    l0 = launches()
-    sync_all()
-    e0.record()
-    for i in range(args.steps):
-        last = trainer.step_device(devb[i % nb])
-    e1.record()
-    sync_all()
-    l1 = launches()
-    ms = torch.tensor([e0.elapsed_time(e1)], device=device)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = float(ms.item())
-    final_loss = float(last.item())
-
-    # ---- end-to-end: public API, per-step H2D of pinned inputs + D2H of the loss -----
-    e2e = None
-    if not args.skip_e2e:
-        h2d = sum(v.numel() * v.element_size() for v in host[0].values())
-        sync_all()
-        e0.record()
-        if hasattr(trainer, "step_async"):
-            # public pipelined API: step i's loss is read (D2H, pinned) after step i+1 is enqueued
-            # (two steps of run-ahead: with several ranks a one-step window makes every host wake-up
-            # jitter visible, because the fused collectives wait for the slowest rank)
-            pending = []
-            for i in range(args.steps):
-                pending.append(trainer.step_async(host[i % nb]))
-                if len(pending) > 2:
-                    val = pending.pop(0).result()
-            while pending:
-                val = pending.pop(0).result()
-        else:
-            for i in range(args.steps):
-                val = trainer.step(host[i % nb])
-        e1.record()
-        sync_all()
-        ms2 = torch.tensor([e0.elapsed_time(e1)], device=device)
-        if world > 1:
-            dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
-        e2e = {"value": round(batch * world * args.steps / (float(ms2.item()) / 1e3), 2),
-               "unit": "samples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
-               "ms_per_step": round(float(ms2.item()) / args.steps, 3), "last_loss": round(val, 4)}
-    clocks = sampler.stop()
-    if args.impl == "ours":
-        trainer.check()
+    # ---- the other two parts of BASELINE.json's metric -------------------------------------------
+    secondary = None
+    if args.impl == "ours" and args.secondary and args.model == "bert-large":
+        secondary = {}
+        try:
+            r_o = run_arm(args, "ours", "resnet50", rank, world, device, sample_clocks=False)
+            r_s = run_arm(args, "stock", "resnet50", rank, world, device, sample_clocks=False) if args.compare else None
+            secondary["resnet50_img_per_sec"] = dict(
+                _brief(r_o), unit="img/s", per_gpu_batch=r_o["batch"], gpu_launches=r_o["gpu_launches"],
+                stock=_brief(r_s) if r_s else None,
+                ratio=round(r_o["value"] / r_s["value"], 4) if r_s else None,
+                e2e_ratio=round(r_o["e2e"]["value"] / r_s["e2e"]["value"], 4) if (r_s and r_o["e2e"] and r_s["e2e"]) else None)
+        except Exception as e:  # noqa: BLE001
+            secondary["resnet50_img_per_sec"] = {"error": repr(e)[:300]}
+        if world == 1 and rank == 0:
+            secondary["launcher"] = launcher_latency()
 
     if rank == 0:
-        value = batch * world * args.steps / (ms_total / 1e3)
+        r = main_res
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except (OSError, ValueError):
             pass
-        tflops = value / world * flops_per_sample / 1e12
+        tflops = r["value"] / world * r["flops_per_sample"] / 1e12
         denom = peaks.get("bf16_tflops_sustained") or 1400.0
+        if args.impl == "ours":
+            optim = ("SGD momentum" if args.model == "resnet50" else "AdamW") + \
+                " (fp32 master + moments, sharded 1/N per rank)"
+        else:
+            optim = "torch.optim fused, " + ("bf16-resident params" if args.impl == "stock-bf16" or args.model == "resnet50"
+                                             else "fp32 params + autocast")
         out = {
-            "metric": metric, "value": round(value, 2), "unit": "img/s" if args.model == "resnet50" else "samples/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_total / args.steps, 3),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-            "data": "synthetic (random token ids, random-init weights)", "impl": args.impl,
-            "config": {"model": model_name, "global_batch": batch * world, "per_gpu_batch": batch,
-                       "seq_len": seq, "parallelism": f"dp{world}",
-                       "optimizer": "AdamW (fp32 master + moments, sharded 1/N per rank)" if args.impl == "ours"
-                       else "torch.optim.AdamW(fused=True), fp32 params + autocast",
-                       "dropout": 0.0,
-                       "cuda_graph": bool(getattr(trainer, "cuda_graph", False)),
+            "metric": r["metric"], "value": round(r["value"], 2),
+            "unit": "img/s" if args.model == "resnet50" else "samples/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(r["ms_per_step"], 3),
+            "higher_is_better": True, "scaling": "weak",
+            # BASELINE.md publishes no reference number; its operative baseline is the stock-PyTorch arm,
+            # measured here in the same run: vs_baseline = value / that arm's value
+            "vs_baseline": baseline["ratio"] if baseline else None,
+            "dtype": "bf16",
+            "data": "synthetic (random token ids / images, random-init weights)", "impl": args.impl,
+            "config": {"model": r["model_name"], "global_batch": r["batch"] * world, "per_gpu_batch": r["batch"],
+                       "seq_len": r["seq"], "parallelism": f"dp{world}", "optimizer": optim, "dropout": 0.0,
+                       "cuda_graph": r["cuda_graph"],
                        "l2": "no explicit flush: every step streams >0.67 GB of weights plus GBs of "
                              "activations, far larger than the 126 MB L2; 4 distinct input batches rotate"},
-            "clocks": clocks,
-            "e2e": e2e,
-            "gpu_launches": int(l1 - l0),
+            "clocks": r["clocks"],
+            "e2e": r["e2e"],
+            "gpu_launches": r["gpu_launches"],
             "model_tflops_per_gpu": round(tflops, 1),
             "mfu_of_measured_sustained_peak": round(tflops / denom, 3),
-            "loss_after_warmup": round(warm_loss, 4), "loss_final": round(final_loss, 4),
+            "loss_after_warmup": r["loss_after_warmup"], "loss_final": r["loss_final"],
+            "baseline": baseline,
+            "secondary": secondary,
         }
         sys.stdout.flush()
         os.write(result_fd, (json.dumps(out) + "\n").encode())

@@ -219,3 +219,46 @@ def test_checkpoint_roundtrip_includes_sharded_embedding_bag(tmp_path):
     m2, t2 = make()
     assert checkpoint.load_latest(str(tmp_path), t2) == 3
     assert abs(t2.step(batch) - nxt) < 2e-2 * max(1.0, abs(nxt))
+
+
+@pytest.mark.parametrize("with_attention", [False, True])
+def test_overlap_launch_does_not_race_with_dgrad(with_attention, monkeypatch):
+    """overlap=True launches a bucket's fused reduce+optimizer from inside backward.  That kernel
+    rewrites the bf16 weights, so every dgrad GEMM reading a weight must already be enqueued when
+    the weight's gradient slot is finished.  Tiny buckets make every bucket close on a single fc1 /
+    fc2 / qkv / out weight; the parameters must then be bit-identical to the overlap=False run."""
+    import copy
+
+    from torch import nn
+
+    from tony_b200 import runtime
+    from tony_b200.models import bert
+
+    if with_attention:
+        monkeypatch.setenv("TONY_B200_ATTENTION", "tcgen05")   # own kernels: no atomics, deterministic
+    dev = torch.device("cuda")
+    cfg = bert.BertConfig(vocab_size=1000, hidden=256, layers=3, heads=4, inner=1024, max_positions=128)
+
+    class Stack(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.layers = nn.ModuleList(bert.BertLayer(cfg, device=dev) for _ in range(cfg.layers))
+
+        def forward(self, x):
+            for layer in self.layers:
+                x = layer(x) if with_attention else layer.ln2(layer.mlp(x, residual=x))
+            return x.float().square().mean()
+
+    torch.manual_seed(5)
+    base = Stack()
+    twin = copy.deepcopy(base)
+    a = runtime.Trainer(base, lr=1e-2, device=dev, bucket_mb=0.01, overlap=True)
+    b = runtime.Trainer(twin, lr=1e-2, device=dev, bucket_mb=0.01, overlap=False)
+    assert len(a.store.buckets) >= 4 * cfg.layers
+    xs = [torch.randn(4, 128, cfg.hidden, device=dev).to(torch.bfloat16) for _ in range(2)]
+    for i in range(5):
+        a.step_device({"x": xs[i % 2]})
+        b.step_device({"x": xs[i % 2]})
+    torch.cuda.synchronize()
+    a.check()
+    assert torch.equal(a.store.param_buf, b.store.param_buf)

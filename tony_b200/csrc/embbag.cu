@@ -44,11 +44,16 @@ embbag_gather_kernel(const tony_embbag_comm comm, const EmbBagArgs a, __nv_bfloa
         const int u = static_cast<int>(i - pair * a.units);
         const int f = static_cast<int>(pair % a.fields);
         const long long id = a.ids[pair];
-        const int owner = static_cast<int>(id % a.world);
-        const long long lrow = id / a.world;
-        const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(comm.table[owner]) +
-                                   ((static_cast<long long>(f) * a.rows_per_shard + lrow) * a.units + u) * 8;
-        const uint4 v = ld_global_v4(src);
+        // an id outside [0, rows_per_shard * world) would index another field's rows or memory past the
+        // shard on some peer: such a pair reads as a zero row (and scatters nothing in backward)
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (id >= 0 && id < a.rows_per_shard * a.world) {
+            const int owner = static_cast<int>(id % a.world);
+            const long long lrow = id / a.world;
+            const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(comm.table[owner]) +
+                                       ((static_cast<long long>(f) * a.rows_per_shard + lrow) * a.units + u) * 8;
+            v = ld_global_v4(src);
+        }
         if (u < a.deep_units)
             st_global_v4(deep + (pair * a.deep_units + u) * 8, v);
         else
@@ -67,6 +72,7 @@ embbag_scatter_kernel(const tony_embbag_comm comm, const EmbBagArgs a, const __n
         const int u = static_cast<int>(i - pair * a.units);
         const int f = static_cast<int>(pair % a.fields);
         const long long id = a.ids[pair];
+        if (id < 0 || id >= a.rows_per_shard * a.world) continue;   // never reduce into memory we do not own
         const int owner = static_cast<int>(id % a.world);
         const long long lrow = id / a.world;
         const uint4 v = u < a.deep_units

@@ -269,9 +269,11 @@ class _MlpFn(torch.autograd.Function):
         dy2 = dy.reshape(-1, N)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        dw2, db2 = _weight_bias_grad(dy2, h, w2, ctx.b2)
+        # Order matters with overlap=True: finishing a parameter's slot may close its bucket and launch
+        # the fused reduce+optimizer on the comm stream, which REWRITES the bf16 weights.  Every GEMM
+        # that reads a weight is therefore enqueued before that weight's gradient slot is finished.
         dpre = gemm(dy2, w2, b_mn=True, flags=_ACT_BWD[ctx.act], aux=pre)  # (dY.W2) * act'(pre)
-        dw1, db1 = _weight_bias_grad(dpre, x2, w1, ctx.b1)
+        dw2, db2 = _weight_bias_grad(dy2, h, w2, ctx.b2)
         dx = None
         if ctx.needs_input_grad[0]:
             if ctx.self_residual:
@@ -280,6 +282,7 @@ class _MlpFn(torch.autograd.Function):
                 dx = gemm(dpre, w1, b_mn=True, flags=EPI_RESIDUAL, aux=dy2).view(ctx.x_shape)
             else:
                 dx = gemm(dpre, w1, b_mn=True).view(ctx.x_shape)
+        dw1, db1 = _weight_bias_grad(dpre, x2, w1, ctx.b1)
         return dx, dw1, db1, dw2, db2, (dy if ctx.has_res else None), None, None
 
 
@@ -809,14 +812,15 @@ class _AttentionBlockFn(torch.autograd.Function):
         dy2 = dy.reshape(B * S, H)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        dwo, dbo = _weight_bias_grad(dy2, o2, wo, ctx.bo)
+        # dgrad GEMMs before the matching wgrad: see the ordering note in _MlpFn.backward
         do = gemm(dy2, wo, b_mn=True)
+        dwo, dbo = _weight_bias_grad(dy2, o2, wo, ctx.bo)
         dqkv = _attention_core_backward(ctx.saved_core, do.view(B, S, H)).view(B * S, 3 * H)
         ctx.saved_core = None
-        dwqkv, dbqkv = _weight_bias_grad(dqkv, x2, wqkv, ctx.bqkv)
         dx = None
         if ctx.needs_input_grad[0]:
             dx = gemm(dqkv, wqkv, b_mn=True, flags=EPI_RESIDUAL, aux=dy2).view(B, S, H)
+        dwqkv, dbqkv = _weight_bias_grad(dqkv, x2, wqkv, ctx.bqkv)
         return dx, dwqkv, dbqkv, dwo, dbo, None, None
 
 

@@ -37,7 +37,10 @@ def save(directory: str, trainer, step: Optional[int] = None) -> str:
         opt_state = dict(opt_state, _step_modules=extra)
     _atomic_save(opt_state, f"{base}.opt.rank{st.rank:03d}of{st.world:03d}.pt")
     if st.rank == 0:
-        _atomic_save({"param_buf": st.param_buf, "numel": st.numel, "step": step}, f"{base}.params.pt")
+        # module buffers (BatchNorm running statistics) are model state outside the flat store
+        buffers = {k: v.detach().clone() for k, v in trainer.model.named_buffers()}
+        _atomic_save({"param_buf": st.param_buf, "numel": st.numel, "step": step, "buffers": buffers},
+                     f"{base}.params.pt")
         tmp = f"{base}.meta.json.tmp"
         with open(tmp, "w") as f:
             json.dump({"step": step, "world": st.world, "numel": st.numel}, f)
@@ -71,9 +74,22 @@ def load_latest(directory: str, trainer) -> Optional[int]:
     if params["numel"] != st.numel:
         raise ValueError("checkpoint was written for a different model layout")
     st.param_buf.copy_(params["param_buf"])
+    own = dict(trainer.model.named_buffers())
+    with torch.no_grad():
+        for k, v in params.get("buffers", {}).items():
+            if k in own and own[k].shape == v.shape:
+                own[k].copy_(v.to(own[k].dtype))
     opt_state = torch.load(f"{base}.opt.rank{st.rank:03d}of{st.world:03d}.pt", map_location=st.device)
     extra = opt_state.pop("_step_modules", [])
     trainer.opt.load_state_dict(opt_state)
+    # rank 0's bf16 copy is exact only where weights are broadcast; a parameter-server bucket keeps
+    # each rank's own shard current and nothing else, so re-derive this rank's shard of every bucket
+    # from its fp32 master (bit-identical to what the optimizer kernel last stored)
+    with torch.no_grad():
+        for b in st.buckets:
+            lo, chunk = st.shard_range(b)
+            m0 = b.begin // st.world
+            st.param_buf[lo: lo + chunk].copy_(trainer.opt.master[m0: m0 + chunk])
     mods = [m for m in getattr(trainer, "_step_modules", []) if hasattr(m, "tony_load_state_dict")]
     if len(extra) != len(mods):
         raise ValueError("checkpoint was written for a different set of sharded modules")

@@ -76,12 +76,16 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workers", type=int, default=2)
     ap.add_argument("--repeat", type=int, default=3)
+    ap.add_argument("--arms", default="ours,torchrun", help="comma list of: ours, torchrun")
     a = ap.parse_args()
+    arms = set(a.arms.split(","))
     work = tempfile.mkdtemp(prefix="tony_latency_")
     script = os.path.join(work, "job.py")
     with open(script, "w") as f:
         f.write(JOB)
     for name, fn in (("tony_b200 launcher (pytorch runtime)", ours), ("torch.distributed.run", torchrun)):
+        if fn.__name__ not in arms:
+            continue
         vals = [fn(a.workers, script, work) for _ in range(a.repeat)]
         print(json.dumps({"arm": name, "workers": a.workers, "submit_to_first_step_ms": [round(v) for v in vals],
                           "median_ms": round(statistics.median(vals))}), flush=True)
