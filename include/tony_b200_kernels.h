@@ -132,6 +132,51 @@ int tony_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out,
 int tony_colsum_bf16_static(const void* x, int rows, int cols, long long ld, void* out,
                             int accumulate, void* stream);
 
+/* ---- implicit-GEMM 2-D convolution on tcgen05 (TMA im2col mode), NHWC activations, KRSC filters ---- */
+/* x: [N, H, W, C] bf16 (a channels-last activation), w: [K, R, S, C] bf16, y: [N, P, Q, K] with
+ * P = (H + 2*pad - R) / stride + 1.  C % 8 == 0 and K % 8 == 0, R*S <= 16, stride 1 or 2 (same in both
+ * dimensions), symmetric padding.  No im2col matrix is materialised: the TMA unit gathers each filter
+ * tap's pixels (zero-filling the padding) into the tensor cores' shared-memory layout.
+ * Replaces cuDNN's convolution forward / backward-data / backward-filter in the CNN jobs the
+ * reference launches (tony-examples/horovod-on-tony/tensorflow2_mnist.py:48-49,
+ * tony-examples/mnist-tensorflow/mnist_distributed.py:87-97). */
+typedef struct {
+    int N, H, W, C;   /* input activation */
+    int K, R, S;      /* filter: K output channels, R x S taps */
+    int stride, pad;
+    /* padding after the last row / column; -1 = same as `pad`.  Even-sized filters need pad_hi = pad - 1
+     * to keep the output size. */
+    int pad_hi;
+    /* 0 = pad both dimensions; 1 = pad rows only (pad_w = 0).  With x_stride_w below this lets a layer
+     * fold its horizontal taps into the channel dimension (see models/resnet.py: the 7x7 stem). */
+    int pad_h_only;
+    /* element strides of x between neighbouring pixels / rows / images; 0 = dense NHWC.  x_stride_w may
+     * be SMALLER than C (overlapping pixel windows): the "channels" of pixel w are then the C elements
+     * starting at w * x_stride_w.  Multiples of 8 elements. */
+    long long x_stride_w, x_stride_h, x_stride_n;
+} tony_conv_desc;
+int tony_conv2d_out_size(int in, int filter, int stride, int pad);
+/* stat_sum / stat_sqsum (both or neither; fp32 [K], caller-zeroed): the epilogue adds the per-channel
+ * sum and sum of squares of the bf16 output (BatchNorm batch statistics) with one atomic per column
+ * per warp, so the BatchNorm that follows needs no statistics pass over y. */
+int tony_conv2d_fprop_bf16(const tony_conv_desc* d, const void* x, const void* w, void* y, float* stat_sum,
+                           float* stat_sqsum, void* stream);
+/* dx [N, H, W, C] from dy [N, P, Q, K]; flags: 0 or TONY_EPI_ACCUMULATE (dx += ...).  A stride-2 layer
+ * runs one launch per output parity class, each a stride-1 convolution over dy. */
+int tony_conv2d_dgrad_bf16(const tony_conv_desc* d, const void* dy, const void* w, void* dx, unsigned int flags,
+                           void* stream);
+/* dw [K, R, S, C] from dy and x (needs C % 64 == 0); split-K over the output pixels with fp32
+ * partials in `workspace` (tony_conv2d_wgrad_workspace_bytes); flags: 0 or TONY_EPI_ACCUMULATE. */
+size_t tony_conv2d_wgrad_workspace_bytes(const tony_conv_desc* d);
+int tony_conv2d_wgrad_bf16(const tony_conv_desc* d, const void* dy, const void* x, void* dw, unsigned int flags,
+                           void* workspace, size_t workspace_bytes, void* stream);
+
+/* 2x2 space-to-depth of an image batch for a 7x7 / stride-2 / 3-channel stem: x [N, 3, H, W] bf16 (NCHW,
+ * H and W even) -> xs [N, H/2, W/2 + 3, 16] with xs[n, i, 2 + j, (dy*2 + dx)*4 + c] = x[n, c, 2i+dy, 2j+dx],
+ * zero elsewhere.  The stem then is a 4 x 4 / stride-1 convolution that tony_conv2d_fprop_bf16 runs with
+ * R = 4, S = 1, C = 64 and x_stride_w = 16 (the 4 horizontal taps are 64 contiguous elements). */
+int tony_stem_space_to_depth(const void* x, void* xs, int N, int H, int W, void* stream);
+
 /* ---- fused attention on a packed QKV activation (tcgen05 + TMA, head_dim 64) ------------ */
 /* qkv: [batch*seq, 3, heads, 64] bf16 (the fused QKV projection's output, read in place);
  * out: [batch*seq, heads*64] bf16; lse: [batch*heads, seq] fp32 log2-sum-exp saved for backward.
@@ -197,6 +242,12 @@ size_t tony_bn_scratch_bytes(int C);
 int tony_bn_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y, void* mask,
                 float* mean, float* rstd, float* running_mean, float* running_var, long long M, int C,
                 float eps, float momentum, int relu, float* scratch, size_t scratch_bytes, void* stream);
+/* Same forward when the per-channel sum and sum of squares of x already exist (fp32 [C], produced by
+ * tony_conv2d_fprop_bf16's epilogue): ONE launch, no statistics pass over x and no scratch. */
+int tony_bn_fwd_from_sums(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+                          void* mask, float* mean, float* rstd, float* running_mean, float* running_var, long long M,
+                          int C, float eps, float momentum, int relu, const float* stat_sum, const float* stat_sqsum,
+                          void* stream);
 /* Backward of the same: dx, dgamma, dbeta (bf16) and, when dres != NULL, the residual branch's
  * gradient.  `mask` is the M*C/8-byte ReLU bit mask the forward wrote (one bit per element;
  * required when relu != 0, pass it to tony_bn_fwd as well).  Two launches. */

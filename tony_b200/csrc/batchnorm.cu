@@ -169,21 +169,61 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, const BnDims d, float* __re
     if (threadIdx.x == 0) counters[blockIdx.x] = 0;
 }
 
+// Statistics that arrived as per-channel sums (accumulated by the convolution's epilogue): every thread
+// derives the coefficients of its 8 channels itself, the threads of row 0 also publish mean / rstd and
+// the running statistics, so the forward BatchNorm is ONE launch and one read of x.
+struct BnSums {
+    const float* sum;       // nullptr: coefficients come from `ab` (bn_stats_kernel ran)
+    const float* sqsum;
+    const __nv_bfloat16* gamma;
+    const __nv_bfloat16* beta;
+    float eps, momentum;
+    float* mean;
+    float* rstd;
+    float* running_mean;
+    float* running_var;
+};
+
 // y = relu(x*a + b (+ residual)); every thread keeps the 8 channels it owns in registers.
 __global__ void __launch_bounds__(BN_THREADS, 4)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ residual,
                 const float* __restrict__ ab, __nv_bfloat16* __restrict__ y, unsigned char* __restrict__ mask,
-                long long M, int C, int relu) {
+                long long M, int C, int relu, const BnSums sums) {
     const int groups = C / 8;                                    // divides 256 for every supported C
     const long long tid = static_cast<long long>(blockIdx.x) * BN_THREADS + threadIdx.x;
     const int cg = static_cast<int>(tid % groups);
     const long long row0 = tid / groups;
     const long long row_stride = static_cast<long long>(gridDim.x) * BN_THREADS / groups;
     float a[8], b[8];
+    if (sums.sum == nullptr) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        a[j] = ab[cg * 8 + j];
-        b[j] = ab[C + cg * 8 + j];
+        for (int j = 0; j < 8; ++j) {
+            a[j] = ab[cg * 8 + j];
+            b[j] = ab[C + cg * 8 + j];
+        }
+    } else {
+        const float inv_m = 1.0f / static_cast<float>(M);
+        float g[8], be[8];
+        unpack8f(__ldg(reinterpret_cast<const uint4*>(sums.gamma + cg * 8)), g);
+        unpack8f(__ldg(reinterpret_cast<const uint4*>(sums.beta + cg * 8)), be);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c = cg * 8 + j;
+            const float mu = sums.sum[c] * inv_m;
+            const float var = fmaxf(sums.sqsum[c] * inv_m - mu * mu, 0.f);
+            const float rs = rsqrtf(var + sums.eps);
+            a[j] = g[j] * rs;
+            b[j] = be[j] - mu * a[j];
+            if (row0 == 0) {
+                sums.mean[c] = mu;
+                sums.rstd[c] = rs;
+                if (sums.running_mean) {
+                    const float unbiased = M > 1 ? var * static_cast<float>(M) / static_cast<float>(M - 1) : var;
+                    sums.running_mean[c] = (1.f - sums.momentum) * sums.running_mean[c] + sums.momentum * mu;
+                    sums.running_var[c] = (1.f - sums.momentum) * sums.running_var[c] + sums.momentum * unbiased;
+                }
+            }
+        }
     }
     for (long long r = row0; r < M; r += 2 * row_stride) {      // two rows in flight
         const long long r2 = r + row_stride;
@@ -423,9 +463,27 @@ extern "C" int tony_bn_fwd(const void* x, const void* residual, const void* gamm
     TONY_CUDA_CHECK(cudaGetLastError());
     bn_apply_kernel<<<elementwise_grid(M, C), BN_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(residual), ab,
-        static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(mask), M, C, relu);
+        static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(mask), M, C, relu, BnSums{});
     TONY_CUDA_CHECK(cudaGetLastError());
     count_launch(2);
+    return TONY_OK;
+}
+
+extern "C" int tony_bn_fwd_from_sums(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+                                     void* mask, float* mean, float* rstd, float* running_mean, float* running_var,
+                                     long long M, int C, float eps, float momentum, int relu, const float* stat_sum,
+                                     const float* stat_sqsum, void* stream) {
+    if (!x || !gamma || !beta || !y || !mean || !rstd || !stat_sum || !stat_sqsum) return TONY_ERR_INVALID;
+    BnDims d;
+    int rc = make_dims("tony_bn_fwd_from_sums", M, C, &d);
+    if (rc != TONY_OK) return rc;
+    BnSums sums{stat_sum, stat_sqsum, static_cast<const __nv_bfloat16*>(gamma), static_cast<const __nv_bfloat16*>(beta),
+                eps, momentum, mean, rstd, running_mean, running_var};
+    bn_apply_kernel<<<elementwise_grid(M, C), BN_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(residual), nullptr,
+        static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(mask), M, C, relu, sums);
+    TONY_CUDA_CHECK(cudaGetLastError());
+    count_launch(1);
     return TONY_OK;
 }
 

@@ -38,6 +38,7 @@ SOURCES = [
     "attention.cu",
     "embbag.cu",
     "batchnorm.cu",
+    "conv_tcgen05.cu",
 ]
 
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]

@@ -31,6 +31,9 @@ int device_sm_count();         // SM count of the current device (cached)
 // 2-D bf16 tensor map, 128-byte swizzle, `inner` contiguous (defined in gemm_tcgen05.cu)
 int make_tmap_2d_bf16(CUtensorMap* map, const void* ptr, long long inner_extent, long long outer_extent,
                       long long ld, int box_inner, int box_outer);
+// C (+)= alpha * sum over `splits` fp32 partial planes [M][N] (defined in gemm_tcgen05.cu)
+int launch_splitk_reduce(const float* ws, int splits, int M, int N, __nv_bfloat16* C, long long ldc, float alpha,
+                         unsigned int flags, cudaStream_t stream);
 
 // ----------------------------------------------------------------------------
 // Small device utilities

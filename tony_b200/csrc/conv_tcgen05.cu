@@ -1,0 +1,819 @@
+// tony_b200 — implicit-GEMM 2-D convolution on tcgen05 tensor cores (K8a of SURVEY.md §8), sm_100a only.
+//
+// Activations are NHWC bf16 (a channels-last tensor), filters KRSC bf16 ([Cout][R][S][Cin]).  No im2col
+// matrix is ever materialised: the TMA unit's im2col mode gathers, for one filter tap, the 128 (or 64)
+// input pixels that a tile of consecutive output pixels needs — padding, stride and image borders are
+// resolved by the tensor map (out-of-bounds pixels arrive as zeros) — straight into the 128-byte
+// swizzled shared-memory layout tcgen05.mma reads.  One persistent warp-specialised kernel serves
+//
+//   fprop  Y[pix, co]  = sum_{tap, ci}  X[pix (+) tap, ci] * W[co, tap, ci]
+//          A = im2col(X) K-major, B = W K-major, K = taps x Cin
+//   dgrad  dX[pix, ci] = sum_{tap, co} dY[pix (-) tap, co] * W[co, tap, ci]
+//          A = im2col(dY) K-major, B = W MN-major (ci contiguous, no transposed copy of the filter);
+//          a stride-2 layer runs one launch per output parity class (each class is a small
+//          stride-1 convolution over dY), writing its rows at stride 2
+//   wgrad  dW[co, tap, ci] = sum_{pix} dY[pix, co] * X[pix (+) tap, ci]
+//          A = dY MN-major (plain 2-D TMA), B = im2col(X) MN-major, K = output pixels, split-K
+//
+// Roles per CTA (576 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 2-17
+// epilogue (TMEM -> registers -> swizzled smem transpose -> 16-byte global stores).  The fp32
+// accumulator is double-buffered in TMEM so the epilogue of tile i overlaps the MMAs of tile i+1.
+// The forward epilogue can also accumulate the per-channel sum and sum of squares of the bf16 output
+// (BatchNorm batch statistics) so the following BatchNorm needs no statistics pass over Y.
+//
+// The reference (zuston/TonY) has no device code; this replaces the cuDNN convolutions of the
+// CNN jobs it launches (tony-examples/horovod-on-tony/tensorflow2_mnist.py:48-49,
+// tony-examples/mnist-tensorflow/mnist_distributed.py:87-97).
+#include "common.cuh"
+#include "tony_b200_kernels.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+
+namespace tony {
+
+constexpr int CV_BLOCK_M = 128;
+constexpr int CV_BLOCK_K = 64;
+constexpr int CV_UMMA_K = 16;
+constexpr int CV_THREADS = 576;
+constexpr int CV_EPI_WARPS = 16;
+constexpr int CV_STAGING_BYTES = CV_EPI_WARPS * 2048;
+constexpr int CV_CHUNK_BYTES = 64 * 128;   // [64 rows][128 B]
+constexpr int CV_MAX_TAPS = 16;
+
+struct ConvTap {
+    unsigned short off_w, off_h;   // im2col offsets from the tile's base pixel
+    int wsel;                      // tap slot (r * S + s) inside the filter
+};
+
+struct ConvParams {
+    int M, N;
+    int num_m_blocks, num_n_blocks, num_k_blocks, splits, kb_per_split;
+    int b_mn_major;                // MODE 0: filter operand K-major (fprop) or MN-major (dgrad)
+    int ntaps, cblocks;            // 64-channel blocks per tap of the im2col'd tensor
+    int w_tap_stride;              // elements between two taps along the filter's inner dimension
+    int P, Q;                      // positions the im2col traversal visits per image (rows, columns)
+    int lower_w, lower_h, stride_w, stride_h;
+    ConvTap taps[CV_MAX_TAPS];
+    int out_strided, OH, OW, osh, osw, oph, opw;   // MODE 0 output row of pixel (n, p, q)
+    __nv_bfloat16* C;
+    long long ldc;
+    uint32_t flags;
+    float* workspace;              // split-K partials [splits][M][N]
+    float* stat_sum;               // optional [N]: += column sums of the bf16 output
+    float* stat_sqsum;             // optional [N]: += column sums of squares
+};
+
+__device__ __forceinline__ void tma_load_im2col_4d(const CUtensorMap* map, uint64_t* bar, void* smem_dst,
+                                                   int32_t c, int32_t w, int32_t h, int32_t n,
+                                                   uint16_t off_w, uint16_t off_h) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+        :
+        : "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c), "r"(w),
+          "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+        : "memory");
+}
+
+__device__ __forceinline__ uint32_t cv_stg_addr(uint32_t base, int row, int unit) {
+    return base + row * 64 + ((unit ^ ((row >> 1) & 3)) << 4);
+}
+
+// pixel index -> row index of the output tensor (rows of `ldc` elements)
+__device__ __forceinline__ long long cv_out_row(const ConvParams& p, int m) {
+    if (!p.out_strided) return m;
+    const int pq = p.P * p.Q;
+    const int n = m / pq;
+    const int rem = m - n * pq;
+    const int pp = rem / p.Q;
+    const int qq = rem - pp * p.Q;
+    return (static_cast<long long>(n) * p.OH + pp * p.osh + p.oph) * p.OW + qq * p.osw + p.opw;
+}
+
+template <int BLOCK_N, int STAGES, int MODE>
+__global__ void __launch_bounds__(CV_THREADS, 1)
+conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                         const ConvParams p) {
+    constexpr uint32_t A_BYTES = CV_BLOCK_M * CV_BLOCK_K * 2;
+    constexpr uint32_t B_BYTES = BLOCK_N * CV_BLOCK_K * 2;
+    constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+    constexpr uint32_t TMEM_COLS = (2 * BLOCK_N < 32) ? 32 : 2 * BLOCK_N;
+    constexpr int N_CHUNKS = BLOCK_N / 64;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(
+        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    uint8_t* staging = smem + STAGES * STAGE_BYTES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + CV_STAGING_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+    const int warp_idx = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp_idx == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full_bar[s], 1);
+            mbar_init(&tmem_empty_bar[s], CV_EPI_WARPS);
+        }
+        fence_barrier_init();
+    }
+    if (warp_idx == 1) tmem_alloc<TMEM_COLS>(tmem_base_slot);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_base_slot;
+    pdl_launch_dependents();
+
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    const int num_units = num_tiles * p.splits;
+    const int worker = static_cast<int>(blockIdx.x);
+    const int num_workers = static_cast<int>(gridDim.x);
+    const int pq = p.P * p.Q;
+
+    if (warp_idx == 0) {
+        // ---------------------------------------------------------------- TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            pdl_wait();
+            for (int unit = worker; unit < num_units; unit += num_workers) {
+                const int tile = unit / p.splits;
+                const int split = unit - tile * p.splits;
+                const int m_blk = tile / p.num_n_blocks;
+                const int n_blk = tile - m_blk * p.num_n_blocks;
+                const int kb0 = split * p.kb_per_split;
+                const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
+                if (MODE == 0) {
+                    const int m0 = m_blk * CV_BLOCK_M;
+                    const int img = m0 / pq;
+                    const int rem = m0 - img * pq;
+                    const int p0 = rem / p.Q;
+                    const int q0 = rem - p0 * p.Q;
+                    const int cw = p.lower_w + q0 * p.stride_w;
+                    const int ch = p.lower_h + p0 * p.stride_h;
+                    int t = kb0 / p.cblocks;
+                    int cc = kb0 - t * p.cblocks;
+                    for (int kb = kb0; kb < kb1; ++kb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        uint8_t* sa = smem + stage * STAGE_BYTES;
+                        uint8_t* sb = sa + A_BYTES;
+                        mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+                        const ConvTap tap = p.taps[t];
+                        tma_load_im2col_4d(&tmap_a, &full_bar[stage], sa, cc * 64, cw, ch, img, tap.off_w, tap.off_h);
+                        const int winner = tap.wsel * p.w_tap_stride;
+                        if (!p.b_mn_major) {
+                            tma_load_2d(&tmap_b, &full_bar[stage], sb, winner + cc * 64, n_blk * BLOCK_N);
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < N_CHUNKS; ++c)
+                                tma_load_2d(&tmap_b, &full_bar[stage], sb + c * CV_CHUNK_BYTES,
+                                            winner + n_blk * BLOCK_N + c * 64, cc * 64);
+                        }
+                        if (++cc == p.cblocks) {
+                            cc = 0;
+                            ++t;
+                        }
+                        if (++stage == STAGES) {
+                            stage = 0;
+                            phase ^= 1;
+                        }
+                    }
+                } else {
+                    const int total_chunks = p.ntaps * p.cblocks;
+                    const int g0 = n_blk * N_CHUNKS;
+                    const int valid = min(N_CHUNKS, total_chunks - g0);
+                    for (int kb = kb0; kb < kb1; ++kb) {
+                        const int k0 = kb * CV_BLOCK_K;
+                        const int img = k0 / pq;
+                        const int rem = k0 - img * pq;
+                        const int p0 = rem / p.Q;
+                        const int q0 = rem - p0 * p.Q;
+                        const int cw = p.lower_w + q0 * p.stride_w;
+                        const int ch = p.lower_h + p0 * p.stride_h;
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        uint8_t* sa = smem + stage * STAGE_BYTES;
+                        uint8_t* sb = sa + A_BYTES;
+                        mbar_expect_tx(&full_bar[stage], A_BYTES + valid * CV_CHUNK_BYTES);
+#pragma unroll
+                        for (int c = 0; c < CV_BLOCK_M / 64; ++c)
+                            tma_load_2d(&tmap_a, &full_bar[stage], sa + c * CV_CHUNK_BYTES, m_blk * CV_BLOCK_M + c * 64, k0);
+#pragma unroll
+                        for (int c = 0; c < N_CHUNKS; ++c) {
+                            if (c < valid) {
+                                const int g = g0 + c;
+                                const int t = g / p.cblocks;
+                                const int cc = g - t * p.cblocks;
+                                const ConvTap tap = p.taps[t];
+                                tma_load_im2col_4d(&tmap_b, &full_bar[stage], sb + c * CV_CHUNK_BYTES, cc * 64, cw, ch,
+                                                   img, tap.off_w, tap.off_h);
+                            }
+                        }
+                        if (++stage == STAGES) {
+                            stage = 0;
+                            phase ^= 1;
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp_idx == 1) {
+        // ---------------------------------------------------------------- MMA issuer
+        if (lane == 0) {
+            const uint32_t a_mn = MODE == 1 ? 1u : 0u;
+            const uint32_t b_mn = MODE == 1 ? 1u : static_cast<uint32_t>(p.b_mn_major);
+            const uint32_t idesc = make_idesc_bf16(CV_BLOCK_M, BLOCK_N, a_mn, b_mn);
+            const uint32_t a_lbo = a_mn ? CV_CHUNK_BYTES : 16;
+            const uint32_t b_lbo = b_mn ? CV_CHUNK_BYTES : 16;
+            const uint32_t a_kstep = a_mn ? (CV_UMMA_K * 128) >> 4 : (CV_UMMA_K * 2) >> 4;
+            const uint32_t b_kstep = b_mn ? (CV_UMMA_K * 128) >> 4 : (CV_UMMA_K * 2) >> 4;
+            int stage = 0;
+            uint32_t phase = 0;
+            int iter = 0;
+            for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
+                const int tile = unit / p.splits;
+                const int split = unit - tile * p.splits;
+                const int as = iter & 1;
+                const uint32_t aphase = (iter >> 1) & 1;
+                mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
+                tcgen05_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+                const int kb0 = split * p.kb_per_split;
+                const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tcgen05_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+                    const uint32_t sb = sa + A_BYTES;
+                    const uint64_t da = make_umma_desc_sw128(sa, a_lbo, 1024);
+                    const uint64_t db = make_umma_desc_sw128(sb, b_lbo, 1024);
+#pragma unroll
+                    for (int k = 0; k < CV_BLOCK_K / CV_UMMA_K; ++k)
+                        umma_bf16(d_tmem, da + k * a_kstep, db + k * b_kstep, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                    umma_commit(&empty_bar[stage]);
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                umma_commit(&tmem_full_bar[as]);
+            }
+        }
+    } else {
+        // ---------------------------------------------------------------- epilogue warps (2..17)
+        const int quarter = warp_idx & 3;
+        const int group = (warp_idx - 2) >> 2;
+        const uint32_t stg = smem_u32(staging + (warp_idx - 2) * 2048);
+        const int unit16 = lane & 3;
+        int iter = 0;
+        for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
+            const int tile = unit / p.splits;
+            const int split = unit - tile * p.splits;
+            const int m_blk = tile / p.num_n_blocks;
+            const int n_blk = tile - m_blk * p.num_n_blocks;
+            const int as = iter & 1;
+            const uint32_t aphase = (iter >> 1) & 1;
+            const int row0 = m_blk * CV_BLOCK_M + quarter * 32;
+            // the four output rows this lane stores (and, for ACCUMULATE, loads) in every 32-column chunk
+            long long orow[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int m = row0 + i * 8 + (lane >> 2);
+                orow[i] = m < p.M ? cv_out_row(p, m) : -1;
+            }
+            mbar_wait(&tmem_full_bar[as], aphase);
+            tcgen05_fence_after();
+            const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BLOCK_N;
+#pragma unroll 1
+            for (int c = group; c < BLOCK_N / 32; c += CV_EPI_WARPS / 4) {
+                uint32_t r[32];
+                tmem_ld_32x32(taddr0 + c * 32, r);
+                tmem_ld_wait();
+                const int col0 = n_blk * BLOCK_N + c * 32;
+                if (col0 >= p.N || row0 >= p.M) continue;   // warp-uniform
+                if (p.splits > 1) {
+                    const int row = row0 + lane;
+                    if (row < p.M) {
+                        float* dst = p.workspace + (static_cast<size_t>(split) * p.M + row) * p.N + col0;
+#pragma unroll
+                        for (int g = 0; g < 8; ++g) {
+                            if (col0 + g * 4 < p.N)
+                                *reinterpret_cast<float4*>(dst + g * 4) =
+                                    make_float4(__uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]),
+                                                __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]));
+                        }
+                    }
+                    continue;
+                }
+                const int gc = col0 + unit16 * 8;
+                if (p.flags & TONY_EPI_ACCUMULATE) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        uint4 v = make_uint4(0, 0, 0, 0);
+                        if (orow[i] >= 0 && gc < p.N) v = ld_global_v4(p.C + orow[i] * p.ldc + gc);
+                        st_shared_v4(cv_stg_addr(stg, i * 8 + (lane >> 2), unit16), v);
+                    }
+                    __syncwarp();
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const uint4 v = ld_shared_v4(cv_stg_addr(stg, lane, u));
+                        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float2 f = unpack_bf16x2(w[j]);
+                            r[u * 8 + 2 * j] = __float_as_uint(__uint_as_float(r[u * 8 + 2 * j]) + f.x);
+                            r[u * 8 + 2 * j + 1] = __float_as_uint(__uint_as_float(r[u * 8 + 2 * j + 1]) + f.y);
+                        }
+                    }
+                    __syncwarp();
+                }
+                uint32_t o[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    o[j] = pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    st_shared_v4(cv_stg_addr(stg, lane, u), make_uint4(o[4 * u], o[4 * u + 1], o[4 * u + 2], o[4 * u + 3]));
+                __syncwarp();
+                float s1[8], s2[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint4 v = ld_shared_v4(cv_stg_addr(stg, i * 8 + (lane >> 2), unit16));
+                    if (orow[i] >= 0 && gc < p.N) {
+                        st_global_v4(p.C + orow[i] * p.ldc + gc, v);
+                        if (p.stat_sum != nullptr) {
+                            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const float2 f = unpack_bf16x2(w[j]);
+                                s1[2 * j] += f.x;
+                                s1[2 * j + 1] += f.y;
+                                s2[2 * j] = fmaf(f.x, f.x, s2[2 * j]);
+                                s2[2 * j + 1] = fmaf(f.y, f.y, s2[2 * j + 1]);
+                            }
+                        }
+                    }
+                }
+                __syncwarp();
+                if (p.stat_sum != nullptr) {
+                    // lanes with equal (lane & 3) hold the same 8 columns for different rows: fold the 8
+                    // row groups with shuffles, then one red.add per column per warp
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+#pragma unroll
+                        for (int o2 = 4; o2 < 32; o2 <<= 1) {
+                            s1[j] += __shfl_xor_sync(0xffffffffu, s1[j], o2);
+                            s2[j] += __shfl_xor_sync(0xffffffffu, s2[j], o2);
+                        }
+                    }
+                    if (lane < 4 && gc < p.N) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            atomicAdd(p.stat_sum + gc + j, s1[j]);
+                            atomicAdd(p.stat_sqsum + gc + j, s2[j]);
+                        }
+                    }
+                }
+            }
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
+        }
+    }
+
+    __syncwarp();
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp_idx == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc<TMEM_COLS>(tmem_base);
+    }
+}
+
+// 2x2 space-to-depth of a 3-channel NCHW image batch for the 7x7 / stride-2 stem convolution:
+//   xs[n, i, 2 + j, (dy*2 + dx)*4 + c] = x[n, c, 2i + dy, 2j + dx]   (c < 3; channel 3 of each group is 0)
+// with two zero pixels before and one after every row.  On this tensor the stem is a stride-1 convolution
+// with 4 x 4 taps over 16 channels, and because NHWC keeps a row's pixels adjacent, the 4 horizontal taps
+// of an output pixel are 64 CONTIGUOUS elements: the convolution kernel reads them as one 64-"channel"
+// pixel through a tensor map whose pixel stride (16 elements) is smaller than its channel extent (64).
+__global__ void __launch_bounds__(256)
+stem_space_to_depth_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ xs, int N, int H, int W) {
+    const int H2 = H / 2, W2 = W / 2, WP = W2 + 3;
+    const long long total = static_cast<long long>(N) * H2 * WP;
+    const size_t plane = static_cast<size_t>(H) * W;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int jp = static_cast<int>(i % WP);
+        const long long t = i / WP;
+        const int ii = static_cast<int>(t % H2);
+        const int n = static_cast<int>(t / H2);
+        uint32_t o[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        const int j = jp - 2;
+        if (j >= 0 && j < W2) {
+            const __nv_bfloat16* base = x + static_cast<size_t>(n) * 3 * plane + static_cast<size_t>(2 * ii) * W + 2 * j;
+            uint32_t v[3][2];   // [c][dy] = pair (dx = 0, 1)
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+#pragma unroll
+                for (int dy = 0; dy < 2; ++dy)
+                    v[c][dy] = __ldg(reinterpret_cast<const uint32_t*>(base + c * plane + dy * W));
+#pragma unroll
+            for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+                for (int dx = 0; dx < 2; ++dx) {
+                    const int sh = dx * 16;
+                    const uint32_t c0 = (v[0][dy] >> sh) & 0xffffu, c1 = (v[1][dy] >> sh) & 0xffffu,
+                                   c2 = (v[2][dy] >> sh) & 0xffffu;
+                    o[(dy * 2 + dx) * 2] = c0 | (c1 << 16);
+                    o[(dy * 2 + dx) * 2 + 1] = c2;
+                }
+        }
+        uint4* dst = reinterpret_cast<uint4*>(xs + static_cast<size_t>(i) * 16);
+        dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// Host side
+// ----------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeIm2col)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                     const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                     const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeIm2col get_im2col_fn() {
+    static PFN_encodeIm2col fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_encodeIm2col>(ptr);
+    });
+    return fn;
+}
+
+// im2col map over an NHWC bf16 tensor: 64 channels x `pixels` pixels per load
+static int make_im2col_tmap(CUtensorMap* map, const void* ptr, int N, int H, int W, int C, int lower_w, int lower_h,
+                            int upper_w, int upper_h, int stride_w, int stride_h, int pixels, long long es_w = 0,
+                            long long es_h = 0, long long es_n = 0) {
+    static thread_local bool tls_ctx_bound = false;
+    if (!tls_ctx_bound) {
+        cudaFree(nullptr);
+        tls_ctx_bound = true;
+    }
+    PFN_encodeIm2col enc = get_im2col_fn();
+    if (!enc) {
+        set_last_error("cuTensorMapEncodeIm2col", "driver entry point not found");
+        return TONY_ERR_UNSUPPORTED;
+    }
+    cuuint64_t gdim[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
+                          static_cast<cuuint64_t>(N)};
+    if (es_w == 0) es_w = C;
+    if (es_h == 0) es_h = es_w * W;
+    if (es_n == 0) es_n = es_h * H;
+    cuuint64_t gstride[3] = {static_cast<cuuint64_t>(es_w) * 2, static_cast<cuuint64_t>(es_h) * 2,
+                             static_cast<cuuint64_t>(es_n) * 2};
+    int lower[2] = {lower_w, lower_h};
+    int upper[2] = {upper_w, upper_h};
+    cuuint32_t estride[4] = {1, static_cast<cuuint32_t>(stride_w), static_cast<cuuint32_t>(stride_h), 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), gdim, gstride, lower, upper,
+                     64, static_cast<cuuint32_t>(pixels), estride, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[160];
+        snprintf(buf, sizeof(buf), "CUresult %d (N %d H %d W %d C %d corners %d %d %d %d stride %d %d)",
+                 static_cast<int>(r), N, H, W, C, lower_w, lower_h, upper_w, upper_h, stride_w, stride_h);
+        set_last_error("cuTensorMapEncodeIm2col", buf);
+        return TONY_ERR_CUDA;
+    }
+    return TONY_OK;
+}
+
+template <int BLOCK_N, int STAGES, int MODE>
+static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, int grid, cudaStream_t stream) {
+    constexpr size_t SMEM =
+        static_cast<size_t>(STAGES) * (CV_BLOCK_M + BLOCK_N) * CV_BLOCK_K * 2 + CV_STAGING_BYTES + 1024 + 256;
+    static bool configured[64] = {false};
+    int dev = 0;
+    TONY_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        TONY_CUDA_CHECK(cudaFuncSetAttribute(conv_bf16_tcgen05_kernel<BLOCK_N, STAGES, MODE>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SMEM)));
+        configured[dev] = true;
+    }
+    static int pdl = -1;
+    if (pdl < 0) {
+        const char* e = getenv("TONY_B200_PDL");
+        pdl = e ? atoi(e) : 1;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(CV_THREADS);
+    cfg.dynamicSmemBytes = SMEM;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    TONY_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_bf16_tcgen05_kernel<BLOCK_N, STAGES, MODE>, ta, tb, p));
+    count_launch();
+    return TONY_OK;
+}
+
+template <int MODE>
+static int dispatch_conv(int block_n, const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, int grid,
+                         cudaStream_t stream) {
+    if (block_n == 64) return launch_conv<64, 8, MODE>(ta, tb, p, grid, stream);
+    if (block_n == 128) return launch_conv<128, 6, MODE>(ta, tb, p, grid, stream);
+    return launch_conv<256, 4, MODE>(ta, tb, p, grid, stream);
+}
+
+static int pick_block_n(int n) { return n <= 64 ? 64 : (n <= 128 ? 128 : 256); }
+
+static int check_desc(const char* what, const tony_conv_desc* d) {
+    if (!d || d->N <= 0 || d->H <= 0 || d->W <= 0 || d->C <= 0 || d->K <= 0 || d->R <= 0 || d->S <= 0 ||
+        d->stride <= 0 || d->pad < 0) {
+        set_last_error(what, "bad convolution descriptor");
+        return TONY_ERR_INVALID;
+    }
+    if ((d->C % 8) || (d->K % 8) || d->R * d->S > CV_MAX_TAPS || d->stride > 2) {
+        set_last_error(what, "needs C % 8 == 0, K % 8 == 0, R*S <= 16, stride 1 or 2");
+        return TONY_ERR_UNSUPPORTED;
+    }
+    return TONY_OK;
+}
+
+}  // namespace tony
+
+using namespace tony;
+
+extern "C" int tony_conv2d_out_size(int in, int filter, int stride, int pad) {
+    return (in + 2 * pad - filter) / stride + 1;
+}
+
+// Y[N, P, Q, K] = conv(X[N, H, W, C], Wt[K, R, S, C])
+extern "C" int tony_conv2d_fprop_bf16(const tony_conv_desc* d, const void* x, const void* w, void* y,
+                                      float* stat_sum, float* stat_sqsum, void* stream_v) {
+    int rc = check_desc("tony_conv2d_fprop_bf16", d);
+    if (rc) return rc;
+    if (!x || !w || !y || ((stat_sum == nullptr) != (stat_sqsum == nullptr))) return TONY_ERR_INVALID;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    const int pad_w = d->pad_h_only ? 0 : d->pad;
+    const int pad_hi_h = d->pad_hi < 0 ? d->pad : d->pad_hi;
+    const int pad_hi_w = d->pad_h_only ? 0 : pad_hi_h;
+    const int P = (d->H + d->pad + pad_hi_h - d->R) / d->stride + 1;
+    const int Q = (d->W + pad_w + pad_hi_w - d->S) / d->stride + 1;
+    if (P <= 0 || Q <= 0) return TONY_ERR_INVALID;
+    ConvParams p = {};
+    p.M = d->N * P * Q;
+    p.N = d->K;
+    const int block_n = pick_block_n(p.N);
+    p.num_m_blocks = (p.M + CV_BLOCK_M - 1) / CV_BLOCK_M;
+    p.num_n_blocks = (p.N + block_n - 1) / block_n;
+    p.ntaps = d->R * d->S;
+    p.cblocks = (d->C + 63) / 64;
+    p.num_k_blocks = p.ntaps * p.cblocks;
+    p.splits = 1;
+    p.kb_per_split = p.num_k_blocks;
+    p.b_mn_major = 0;
+    p.w_tap_stride = d->C;
+    p.P = P;
+    p.Q = Q;
+    p.lower_w = -pad_w;
+    p.lower_h = -d->pad;
+    p.stride_w = p.stride_h = d->stride;
+    for (int r = 0; r < d->R; ++r)
+        for (int s = 0; s < d->S; ++s) {
+            ConvTap& t = p.taps[r * d->S + s];
+            t.off_w = static_cast<unsigned short>(s);
+            t.off_h = static_cast<unsigned short>(r);
+            t.wsel = r * d->S + s;
+        }
+    p.out_strided = 0;
+    p.C = static_cast<__nv_bfloat16*>(y);
+    p.ldc = d->K;
+    p.flags = 0;
+    p.stat_sum = stat_sum;
+    p.stat_sqsum = stat_sqsum;
+    CUtensorMap ta, tb;
+    rc = make_im2col_tmap(&ta, x, d->N, d->H, d->W, d->C, -pad_w, -d->pad, pad_hi_w - (d->S - 1),
+                          pad_hi_h - (d->R - 1), d->stride, d->stride, CV_BLOCK_M, d->x_stride_w, d->x_stride_h,
+                          d->x_stride_n);
+    if (rc) return rc;
+    rc = make_tmap_2d_bf16(&tb, w, static_cast<long long>(p.ntaps) * d->C, d->K, static_cast<long long>(p.ntaps) * d->C,
+                           64, block_n);
+    if (rc) return rc;
+    const long long units = static_cast<long long>(p.num_m_blocks) * p.num_n_blocks;
+    const int grid = static_cast<int>(std::min<long long>(units, device_sm_count()));
+    return dispatch_conv<0>(block_n, ta, tb, p, grid, stream);
+}
+
+// dX[N, H, W, C] (+)= conv_transpose(dY[N, P, Q, K], Wt[K, R, S, C]);  flags: TONY_EPI_ACCUMULATE
+extern "C" int tony_conv2d_dgrad_bf16(const tony_conv_desc* d, const void* dy, const void* w, void* dx,
+                                      unsigned int flags, void* stream_v) {
+    int rc = check_desc("tony_conv2d_dgrad_bf16", d);
+    if (rc) return rc;
+    if (!dy || !w || !dx || (flags & ~TONY_EPI_ACCUMULATE)) return TONY_ERR_INVALID;
+    if (d->pad_h_only || (d->pad_hi >= 0 && d->pad_hi != d->pad) || d->x_stride_w || d->x_stride_h || d->x_stride_n) {
+        set_last_error("tony_conv2d_dgrad_bf16", "dense NHWC input with symmetric padding only");
+        return TONY_ERR_UNSUPPORTED;
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    const int P = tony_conv2d_out_size(d->H, d->R, d->stride, d->pad);
+    const int Q = tony_conv2d_out_size(d->W, d->S, d->stride, d->pad);
+    if (P <= 0 || Q <= 0) return TONY_ERR_INVALID;
+    const int st = d->stride;
+    const int block_n = pick_block_n(d->C);
+    CUtensorMap tb;
+    // the filter seen as [K rows][R*S*C] : B(n = ci, k = co) of tap t sits at inner offset t*C + ci
+    rc = make_tmap_2d_bf16(&tb, w, static_cast<long long>(d->R) * d->S * d->C, d->K,
+                           static_cast<long long>(d->R) * d->S * d->C, 64, 64);
+    if (rc) return rc;
+    // a parity class with no filter tap (1x1 stride 2: every odd row / column) receives no gradient
+    bool need_zero = false;
+    for (int ph = 0; ph < st; ++ph) {
+        int nr = 0, ns = 0;
+        for (int r = 0; r < d->R; ++r) nr += ((ph + d->pad - r) % st == 0);
+        for (int s = 0; s < d->S; ++s) ns += ((ph + d->pad - s) % st == 0);
+        if (nr == 0 || ns == 0) need_zero = true;
+    }
+    if (need_zero && !(flags & TONY_EPI_ACCUMULATE))
+        TONY_CUDA_CHECK(cudaMemsetAsync(dx, 0, static_cast<size_t>(d->N) * d->H * d->W * d->C * 2, stream));
+    for (int ph = 0; ph < st; ++ph)
+        for (int pw = 0; pw < st; ++pw) {
+            // positions h = st*i + ph; contributing filter rows r with (h + pad - r) % st == 0 read
+            // dY row i + (ph + pad - r) / st
+            int dh[CV_MAX_TAPS], rr[CV_MAX_TAPS], nh = 0, dw[CV_MAX_TAPS], ss[CV_MAX_TAPS], nw = 0;
+            for (int r = 0; r < d->R; ++r) {
+                const int num = ph + d->pad - r;
+                if (((num % st) + st) % st == 0) {
+                    dh[nh] = (num >= 0 ? num / st : -((-num) / st));
+                    rr[nh++] = r;
+                }
+            }
+            for (int s = 0; s < d->S; ++s) {
+                const int num = pw + d->pad - s;
+                if (((num % st) + st) % st == 0) {
+                    dw[nw] = (num >= 0 ? num / st : -((-num) / st));
+                    ss[nw++] = s;
+                }
+            }
+            const int HP = (d->H - ph + st - 1) / st;   // rows of dX in this class
+            const int WP = (d->W - pw + st - 1) / st;
+            if (nh == 0 || nw == 0 || HP <= 0 || WP <= 0) continue;
+            if (nh * nw > CV_MAX_TAPS) return TONY_ERR_UNSUPPORTED;
+            int min_h = dh[0], min_w = dw[0];
+            for (int i = 1; i < nh; ++i) min_h = std::min(min_h, dh[i]);
+            for (int i = 1; i < nw; ++i) min_w = std::min(min_w, dw[i]);
+            ConvParams p = {};
+            p.M = d->N * HP * WP;
+            p.N = d->C;
+            p.num_m_blocks = (p.M + CV_BLOCK_M - 1) / CV_BLOCK_M;
+            p.num_n_blocks = (p.N + block_n - 1) / block_n;
+            p.ntaps = nh * nw;
+            p.cblocks = (d->K + 63) / 64;
+            p.num_k_blocks = p.ntaps * p.cblocks;
+            p.splits = 1;
+            p.kb_per_split = p.num_k_blocks;
+            p.b_mn_major = 1;
+            p.w_tap_stride = d->C;
+            p.P = HP;
+            p.Q = WP;
+            p.lower_w = min_w;
+            p.lower_h = min_h;
+            p.stride_w = p.stride_h = 1;
+            for (int i = 0; i < nh; ++i)
+                for (int j = 0; j < nw; ++j) {
+                    ConvTap& t = p.taps[i * nw + j];
+                    t.off_h = static_cast<unsigned short>(dh[i] - min_h);
+                    t.off_w = static_cast<unsigned short>(dw[j] - min_w);
+                    t.wsel = rr[i] * d->S + ss[j];
+                }
+            p.out_strided = (st > 1) ? 1 : 0;
+            p.OH = d->H;
+            p.OW = d->W;
+            p.osh = p.osw = st;
+            p.oph = ph;
+            p.opw = pw;
+            p.C = static_cast<__nv_bfloat16*>(dx);
+            p.ldc = d->C;
+            p.flags = flags;
+            CUtensorMap ta;
+            // traversal visits exactly HP x WP base pixels: count = dim + upper - lower  (stride 1)
+            rc = make_im2col_tmap(&ta, dy, d->N, P, Q, d->K, min_w, min_h, WP - Q + min_w, HP - P + min_h, 1, 1,
+                                  CV_BLOCK_M);
+            if (rc) return rc;
+            const long long units = static_cast<long long>(p.num_m_blocks) * p.num_n_blocks;
+            const int grid = static_cast<int>(std::min<long long>(units, device_sm_count()));
+            rc = dispatch_conv<0>(block_n, ta, tb, p, grid, stream);
+            if (rc) return rc;
+        }
+    return TONY_OK;
+}
+
+extern "C" size_t tony_conv2d_wgrad_workspace_bytes(const tony_conv_desc* d) {
+    if (!d) return 0;
+    // worst case: one split per SM over a single tile row
+    return static_cast<size_t>(160) * std::max(d->K, 128) * (static_cast<size_t>(d->R) * d->S * d->C + 256) * 4;
+}
+
+// dW[K, R, S, C] (+)= sum over output pixels of dY[pix, K]^T . im2col(X)[pix, (r, s, c)]
+extern "C" int tony_conv2d_wgrad_bf16(const tony_conv_desc* d, const void* dy, const void* x, void* dw,
+                                      unsigned int flags, void* workspace, size_t workspace_bytes, void* stream_v) {
+    int rc = check_desc("tony_conv2d_wgrad_bf16", d);
+    if (rc) return rc;
+    if (!dy || !x || !dw || (flags & ~TONY_EPI_ACCUMULATE)) return TONY_ERR_INVALID;
+    if (d->C % 64) {
+        set_last_error("tony_conv2d_wgrad_bf16", "needs C % 64 == 0");
+        return TONY_ERR_UNSUPPORTED;
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    const int pad_w = d->pad_h_only ? 0 : d->pad;
+    const int pad_hi_h = d->pad_hi < 0 ? d->pad : d->pad_hi;
+    const int pad_hi_w = d->pad_h_only ? 0 : pad_hi_h;
+    const int P = (d->H + d->pad + pad_hi_h - d->R) / d->stride + 1;
+    const int Q = (d->W + pad_w + pad_hi_w - d->S) / d->stride + 1;
+    if (P <= 0 || Q <= 0) return TONY_ERR_INVALID;
+    const long long pixels = static_cast<long long>(d->N) * P * Q;
+    ConvParams p = {};
+    p.M = d->K;
+    p.N = d->R * d->S * d->C;
+    const int block_n = pick_block_n(p.N);
+    p.num_m_blocks = (p.M + CV_BLOCK_M - 1) / CV_BLOCK_M;
+    p.num_n_blocks = (p.N + block_n - 1) / block_n;
+    p.ntaps = d->R * d->S;
+    p.cblocks = d->C / 64;
+    p.num_k_blocks = static_cast<int>((pixels + CV_BLOCK_K - 1) / CV_BLOCK_K);
+    const int sms = device_sm_count();
+    const long long tiles = static_cast<long long>(p.num_m_blocks) * p.num_n_blocks;
+    int splits = 1;
+    if (workspace != nullptr) {
+        splits = static_cast<int>(std::max<long long>(1, sms / tiles));
+        splits = std::min(splits, std::max(1, p.num_k_blocks / 8));
+        while (splits > 1 && static_cast<size_t>(splits) * p.M * static_cast<size_t>(p.N) * 4 > workspace_bytes) --splits;
+    }
+    p.kb_per_split = (p.num_k_blocks + splits - 1) / splits;
+    p.splits = (p.num_k_blocks + p.kb_per_split - 1) / p.kb_per_split;
+    p.P = P;
+    p.Q = Q;
+    p.lower_w = -pad_w;
+    p.lower_h = -d->pad;
+    p.stride_w = p.stride_h = d->stride;
+    for (int r = 0; r < d->R; ++r)
+        for (int s = 0; s < d->S; ++s) {
+            ConvTap& t = p.taps[r * d->S + s];
+            t.off_w = static_cast<unsigned short>(s);
+            t.off_h = static_cast<unsigned short>(r);
+            t.wsel = r * d->S + s;
+        }
+    p.out_strided = 0;
+    p.C = static_cast<__nv_bfloat16*>(dw);
+    p.ldc = p.N;
+    p.flags = flags;
+    p.workspace = static_cast<float*>(workspace);
+    CUtensorMap ta, tb;
+    // dY as [pixels][K]: A(m = co, k = pixel) is MN-major, 64 x 64 boxes
+    rc = make_tmap_2d_bf16(&ta, dy, d->K, pixels, d->K, 64, 64);
+    if (rc) return rc;
+    rc = make_im2col_tmap(&tb, x, d->N, d->H, d->W, d->C, -pad_w, -d->pad, pad_hi_w - (d->S - 1),
+                          pad_hi_h - (d->R - 1), d->stride, d->stride, CV_BLOCK_K, d->x_stride_w, d->x_stride_h,
+                          d->x_stride_n);
+    if (rc) return rc;
+    const long long units = tiles * p.splits;
+    const int grid = static_cast<int>(std::min<long long>(units, sms));
+    rc = dispatch_conv<1>(block_n, ta, tb, p, grid, stream);
+    if (rc) return rc;
+    if (p.splits > 1)
+        return launch_splitk_reduce(static_cast<const float*>(workspace), p.splits, p.M, p.N,
+                                    static_cast<__nv_bfloat16*>(dw), p.ldc, 1.0f, flags, stream);
+    return TONY_OK;
+}
+
+// x: [N, 3, H, W] bf16 NCHW (H, W even) -> xs: [N, H/2, W/2 + 3, 16] bf16 (see stem_space_to_depth_kernel)
+extern "C" int tony_stem_space_to_depth(const void* x, void* xs, int N, int H, int W, void* stream) {
+    if (!x || !xs || N <= 0 || H <= 0 || W <= 0 || (H & 1) || (W & 1)) return TONY_ERR_INVALID;
+    const long long total = static_cast<long long>(N) * (H / 2) * (W / 2 + 3);
+    const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, device_sm_count() * 32LL));
+    stem_space_to_depth_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(xs), N, H, W);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}

@@ -1119,6 +1119,20 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
     return TONY_OK;
 }
 
+// Fold split-K partials (shared with the convolution weight-gradient kernel).
+int tony::launch_splitk_reduce(const float* ws, int splits, int M, int N, __nv_bfloat16* C, long long ldc, float alpha,
+                               unsigned int flags, cudaStream_t stream) {
+    const size_t total4 = static_cast<size_t>(M) * N / 4;
+    const int threads = 256;
+    const int blocks = static_cast<int>(std::min<size_t>((total4 + threads - 1) / threads,
+                                                         static_cast<size_t>(device_sm_count()) * 8));
+    splitk_reduce_kernel<<<blocks, threads, 0, stream>>>(ws, splits, M, N, C, ldc, alpha, flags, nullptr, nullptr,
+                                                         nullptr, 0);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}
+
 extern "C" int tony_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K,
                                  int a_mn_major, int b_mn_major, long long lda, long long ldb,
                                  long long ldc, unsigned int flags, float alpha, const void* bias,

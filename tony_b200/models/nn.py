@@ -94,13 +94,15 @@ class BatchNormAct(nn.Module):
         self.register_buffer("running_var", torch.ones(channels, dtype=torch.float32, device=device))
         self.relu, self.eps, self.momentum = relu, eps, momentum
 
-    def forward(self, x, residual=None):
+    def forward(self, x, residual=None, stats=None):
+        """``stats``: fp32 ``[2, C]`` per-channel sum / sum of squares of ``x`` when the convolution that
+        produced ``x`` accumulated them in its epilogue (then no statistics pass over ``x`` runs)."""
         if self.running_mean.dtype != torch.float32:     # model.to(bfloat16) also casts buffers: undo
             self.running_mean = self.running_mean.float()
             self.running_var = self.running_var.float()
         if self.training and F.batch_norm_act_supported(x):
             return F.batch_norm_act(x, self.weight, self.bias, self.running_mean, self.running_var, residual,
-                                    self.eps, self.momentum, self.relu)
+                                    self.eps, self.momentum, self.relu, stats)
         rm, rv = self.running_mean.to(x.dtype), self.running_var.to(x.dtype)
         y = torch.nn.functional.batch_norm(x, rm, rv, self.weight, self.bias, self.training, self.momentum, self.eps)
         if self.training:

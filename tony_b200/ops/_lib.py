@@ -56,6 +56,14 @@ class EmbBagComm(Structure):
     _fields_ = [("table", c_void_p * MAX_RANKS), ("grad", c_void_p * MAX_RANKS), ("rank", c_int), ("world", c_int)]
 
 
+class ConvDesc(Structure):
+    """Mirror of ``tony_conv_desc``."""
+
+    _fields_ = [("N", c_int), ("H", c_int), ("W", c_int), ("C", c_int), ("K", c_int), ("R", c_int), ("S", c_int),
+                ("stride", c_int), ("pad", c_int), ("pad_hi", c_int), ("pad_h_only", c_int), ("x_stride_w", c_longlong),
+                ("x_stride_h", c_longlong), ("x_stride_n", c_longlong)]
+
+
 class NvlsComm(Structure):
     """Mirror of ``tony_nvls_comm``."""
 
@@ -161,10 +169,19 @@ def _declare(lib) -> None:
     lib.tony_bn_scratch_bytes.restype = c_size_t
     lib.tony_bn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_longlong, c_int, c_float, c_float, c_int,
                                 vp, c_size_t, vp]
+    lib.tony_bn_fwd_from_sums.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_longlong, c_int, c_float, c_float,
+                                          c_int, vp, vp, vp]
     lib.tony_bn_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_longlong, c_int, c_int, vp, c_size_t, vp]
     lib.tony_maxpool3x3s2_fwd.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, vp]
     lib.tony_maxpool3x3s2_bwd.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, vp]
     lib.tony_layernorm_bwd_add.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, c_int, c_int, vp, c_size_t, c_int, vp]
+    lib.tony_stem_space_to_depth.argtypes = [vp, vp, c_int, c_int, c_int, vp]
+    lib.tony_conv2d_out_size.argtypes = [c_int, c_int, c_int, c_int]
+    lib.tony_conv2d_fprop_bf16.argtypes = [POINTER(ConvDesc), vp, vp, vp, vp, vp, vp]
+    lib.tony_conv2d_dgrad_bf16.argtypes = [POINTER(ConvDesc), vp, vp, vp, c_uint, vp]
+    lib.tony_conv2d_wgrad_workspace_bytes.argtypes = [POINTER(ConvDesc)]
+    lib.tony_conv2d_wgrad_workspace_bytes.restype = c_size_t
+    lib.tony_conv2d_wgrad_bf16.argtypes = [POINTER(ConvDesc), vp, vp, vp, c_uint, vp, c_size_t, vp]
     lib.tony_attention_fwd_bf16.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_float, vp]
     lib.tony_attention_bwd_bf16.argtypes = [vp, vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int,
                                             c_float, vp]

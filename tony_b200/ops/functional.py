@@ -597,7 +597,7 @@ class _BatchNormActFn(torch.autograd.Function):
     two launches forward, two backward (csrc/batchnorm.cu)."""
 
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu):
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, stats=None):
         N, C, H, W = x.shape
         x = x.contiguous(memory_format=torch.channels_last)
         res = residual.contiguous(memory_format=torch.channels_last) if residual is not None else None
@@ -607,11 +607,18 @@ class _BatchNormActFn(torch.autograd.Function):
         rstd = torch.empty(C, dtype=torch.float32, device=x.device)
         # one bit per element: backward applies the ReLU mask without re-reading y or the residual
         mask = torch.empty(M * C // 8, dtype=torch.uint8, device=x.device) if relu else None
-        nbytes = _lib.lib().tony_bn_scratch_bytes(C)
-        scratch = workspace("batchnorm", nbytes, x.device)
-        check(_lib.lib().tony_bn_fwd(ptr(x), ptr(res), ptr(gamma), ptr(beta), ptr(y), ptr(mask), ptr(mean),
-                                     ptr(rstd), ptr(running_mean), ptr(running_var), M, C, eps, momentum,
-                                     int(relu), ptr(scratch), nbytes, cur_stream()), "tony_bn_fwd")
+        if stats is not None:
+            # the producing convolution's epilogue already summed x and x^2 per channel: one launch
+            check(_lib.lib().tony_bn_fwd_from_sums(ptr(x), ptr(res), ptr(gamma), ptr(beta), ptr(y), ptr(mask),
+                                                   ptr(mean), ptr(rstd), ptr(running_mean), ptr(running_var), M, C,
+                                                   eps, momentum, int(relu), ptr(stats[0]), ptr(stats[1]),
+                                                   cur_stream()), "tony_bn_fwd_from_sums")
+        else:
+            nbytes = _lib.lib().tony_bn_scratch_bytes(C)
+            scratch = workspace("batchnorm", nbytes, x.device)
+            check(_lib.lib().tony_bn_fwd(ptr(x), ptr(res), ptr(gamma), ptr(beta), ptr(y), ptr(mask), ptr(mean),
+                                         ptr(rstd), ptr(running_mean), ptr(running_var), M, C, eps, momentum,
+                                         int(relu), ptr(scratch), nbytes, cur_stream()), "tony_bn_fwd")
         ctx.save_for_backward(x, gamma, mean, rstd, mask)
         ctx.meta = (M, C, int(relu), residual is not None)
         return y
@@ -629,14 +636,15 @@ class _BatchNormActFn(torch.autograd.Function):
         check(_lib.lib().tony_bn_bwd(ptr(dy), ptr(x), ptr(mask), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx),
                                      ptr(dres), ptr(dgamma), ptr(dbeta), M, C, relu, ptr(scratch), nbytes,
                                      cur_stream()), "tony_bn_bwd")
-        return dx, dgamma, dbeta, dres, None, None, None, None, None
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None
 
 
 def batch_norm_act(x, gamma, beta, running_mean=None, running_var=None, residual=None, eps: float = 1e-5,
-                   momentum: float = 0.1, relu: bool = True):
+                   momentum: float = 0.1, relu: bool = True, stats: Optional[torch.Tensor] = None):
     """``relu(batch_norm(x) + residual)`` with batch statistics, for ``x`` ``[N, C, H, W]`` bf16 in
-    channels-last memory format and ``C`` a power of two in [8, 2048]."""
-    return _BatchNormActFn.apply(x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu)
+    channels-last memory format and ``C`` a power of two in [8, 2048].  ``stats`` (fp32 ``[2, C]``): the
+    per-channel sum / sum of squares of ``x`` when the producing convolution already accumulated them."""
+    return _BatchNormActFn.apply(x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, stats)
 
 
 def batch_norm_act_supported(x) -> bool:
@@ -674,6 +682,202 @@ def max_pool_3x3_s2(x):
     if x.is_cuda and x.dtype == torch.bfloat16 and x.shape[1] % 8 == 0:
         return _MaxPool3x3s2Fn.apply(x)
     return torch.nn.functional.max_pool2d(x, 3, 2, 1)
+
+
+# ---------------------------------------------------------------------------------------
+# convolution: implicit GEMM on tcgen05, TMA im2col mode (csrc/conv_tcgen05.cu)
+# ---------------------------------------------------------------------------------------
+def _conv_desc(N, H, W, C, K, R, S, stride, pad, pad_h_only=False, strides=(0, 0, 0), pad_hi=-1):
+    return _lib.ConvDesc(N, H, W, C, K, R, S, stride, pad, pad_hi, int(pad_h_only), *strides)
+
+
+def _conv_out(n, f, stride, pad, pad_hi=-1):
+    return (n + pad + (pad if pad_hi < 0 else pad_hi) - f) // stride + 1
+
+
+def conv2d_nhwc(x_nhwc: torch.Tensor, w_krsc: torch.Tensor, stride: int = 1, pad: int = 0, *,
+                stats: Optional[torch.Tensor] = None, logical=None, pad_h_only: bool = False,
+                pad_hi: int = -1) -> torch.Tensor:
+    """Raw forward: ``x`` ``[N, H, W, C]``, ``w`` ``[K, R, S, C]`` -> ``[N, P, Q, K]`` (all bf16, contiguous).
+    ``stats`` (fp32 ``[2, K]``, zeroed by the caller) receives the output's per-channel sum / sum of squares.
+    ``logical=(N, H, W, C, stride_w, stride_h, stride_n)`` overrides the activation's geometry (windowed
+    views whose pixel stride is smaller than C, see ``StemConv``)."""
+    _check_bf16(x_nhwc, w_krsc)
+    K, R, S, C = w_krsc.shape
+    if logical is None:
+        N, H, W, Cx = x_nhwc.shape
+        strides = (0, 0, 0)
+    else:
+        N, H, W, Cx = logical[:4]
+        strides = tuple(logical[4:])
+    if Cx != C:
+        raise ValueError(f"channel mismatch: activation {Cx}, filter {C}")
+    d = _conv_desc(N, H, W, C, K, R, S, stride, pad, pad_h_only, strides, pad_hi)
+    lib = _lib.lib()
+    P = _conv_out(H, R, stride, pad, pad_hi)
+    Q = _conv_out(W, S, stride, 0, 0) if pad_h_only else _conv_out(W, S, stride, pad, pad_hi)
+    y = torch.empty((N, P, Q, K), dtype=torch.bfloat16, device=x_nhwc.device)
+    s1 = ptr(stats[0]) if stats is not None else None
+    s2 = ptr(stats[1]) if stats is not None else None
+    import ctypes as _ct
+    check(lib.tony_conv2d_fprop_bf16(_ct.byref(d), ptr(x_nhwc), ptr(w_krsc), ptr(y), s1, s2, cur_stream()),
+          "tony_conv2d_fprop_bf16")
+    return y
+
+
+def conv2d_dgrad_nhwc(dy_nhwc, w_krsc, x_shape, stride, pad, out=None, accumulate=False):
+    """``dx`` ``[N, H, W, C]`` from ``dy`` ``[N, P, Q, K]``; ``accumulate`` adds into ``out``."""
+    import ctypes as _ct
+
+    K, R, S, C = w_krsc.shape
+    N, H, W, _ = x_shape
+    d = _conv_desc(N, H, W, C, K, R, S, stride, pad)
+    if out is None:
+        out = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=dy_nhwc.device)
+        accumulate = False
+    check(_lib.lib().tony_conv2d_dgrad_bf16(_ct.byref(d), ptr(dy_nhwc), ptr(w_krsc), ptr(out),
+                                            EPI_ACCUMULATE if accumulate else 0, cur_stream()),
+          "tony_conv2d_dgrad_bf16")
+    return out
+
+
+def conv2d_wgrad_nhwc(dy_nhwc, x_nhwc, w_shape, stride, pad, out=None, accumulate=False, logical=None,
+                      pad_h_only=False, pad_hi=-1):
+    """``dw`` ``[K, R, S, C]`` from ``dy`` ``[N, P, Q, K]`` and ``x`` ``[N, H, W, C]`` (split-K over the pixels)."""
+    import ctypes as _ct
+
+    K, R, S, C = w_shape
+    if logical is None:
+        N, H, W, _ = x_nhwc.shape
+        strides = (0, 0, 0)
+    else:
+        N, H, W, _ = logical[:4]
+        strides = tuple(logical[4:])
+    d = _conv_desc(N, H, W, C, K, R, S, stride, pad, pad_h_only, strides, pad_hi)
+    lib = _lib.lib()
+    if out is None:
+        out = torch.empty(tuple(w_shape), dtype=torch.bfloat16, device=dy_nhwc.device)
+        accumulate = False
+    nbytes = int(lib.tony_conv2d_wgrad_workspace_bytes(_ct.byref(d)))
+    ws = workspace("conv_wgrad", nbytes, dy_nhwc.device)
+    check(lib.tony_conv2d_wgrad_bf16(_ct.byref(d), ptr(dy_nhwc), ptr(x_nhwc), ptr(out),
+                                     EPI_ACCUMULATE if accumulate else 0, ptr(ws), nbytes, cur_stream()),
+          "tony_conv2d_wgrad_bf16")
+    return out
+
+
+class _Conv2dFn(torch.autograd.Function):
+    """Convolution of a channels-last ``[N, C, H, W]`` activation with a ``[K, R, S, C]`` filter.
+
+    forward / dgrad / wgrad all run on the implicit-GEMM tcgen05 kernel; stride-1 pointwise layers
+    are a plain GEMM over the activation viewed as ``[N*H*W, C]`` (CTA-pair kernel, split-K wgrad).
+    The weight gradient goes straight into the parameter's slot of the flat gradient bucket."""
+
+    @staticmethod
+    def forward(ctx, x, weight, stride, pad, stats):
+        x = x.contiguous(memory_format=torch.channels_last)
+        xn = x.permute(0, 2, 3, 1)                      # [N, H, W, C] view, contiguous
+        K, R, S, C = weight.shape
+        if R == 1 and S == 1 and stride == 1 and pad == 0 and stats is None:
+            N, H, W, _ = xn.shape
+            yn = gemm(xn.reshape(N * H * W, C), weight.view(K, C)).view(N, H, W, K)
+        else:
+            yn = conv2d_nhwc(xn, weight, stride, pad, stats=stats)
+        ctx.save_for_backward(xn, weight)
+        ctx.geom = (stride, pad)
+        return yn.permute(0, 3, 1, 2)                   # [N, K, P, Q], channels-last memory
+
+    @staticmethod
+    def backward(ctx, dy):
+        xn, weight = ctx.saved_tensors
+        stride, pad = ctx.geom
+        K, R, S, C = weight.shape
+        dyn = dy.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1)
+        N, H, W, _ = xn.shape
+        pointwise = R == 1 and S == 1 and stride == 1 and pad == 0
+        dx = None
+        if ctx.needs_input_grad[0]:                      # before the weight's slot is finished (see _MlpFn)
+            if pointwise:
+                dxn = gemm(dyn.reshape(N * H * W, K), weight.view(K, C), b_mn=True).view(N, H, W, C)
+            else:
+                dxn = conv2d_dgrad_nhwc(dyn, weight, xn.shape, stride, pad)
+            dx = dxn.permute(0, 3, 1, 2)
+        dest = _GradDest(weight)
+        if pointwise:
+            out = gemm(dyn.reshape(N * H * W, K), xn.reshape(N * H * W, C), a_mn=True, b_mn=True,
+                       out=dest.tensor.view(K, C) if dest.tensor is not None else None,
+                       flags=EPI_ACCUMULATE if dest.accumulate else 0).view(K, R, S, C)
+        else:
+            out = conv2d_wgrad_nhwc(dyn, xn, weight.shape, stride, pad, out=dest.tensor, accumulate=dest.accumulate)
+        return dx, dest.finish(out), None, None, None
+
+
+def conv2d(x, weight, stride: int = 1, pad: int = 0, stats: Optional[torch.Tensor] = None):
+    """``conv2d`` for a bf16 channels-last ``x`` ``[N, C, H, W]`` and a ``[K, R, S, C]`` (KRSC) filter."""
+    return _Conv2dFn.apply(x, weight, stride, pad, stats)
+
+
+def conv2d_supported(x, weight, stride) -> bool:
+    K, R, S, C = weight.shape
+    return (x.is_cuda and x.dtype == torch.bfloat16 and C % 64 == 0 and K % 8 == 0 and R * S <= 16
+            and stride in (1, 2))
+
+
+class _StemConvFn(torch.autograd.Function):
+    """7x7 / stride 2 / pad 3 convolution of a 3-channel NCHW image batch, as a 4x4 stride-1 convolution
+    on the 2x2 space-to-depth image whose 4 horizontal taps are read as one 64-element pixel (see
+    ``tony_stem_space_to_depth``).  ``w2`` is the filter in that layout: ``[K, 4, 1, 64]``."""
+
+    @staticmethod
+    def forward(ctx, images, w2, stats):
+        _check_bf16(images, w2)
+        N, C3, H, W = images.shape
+        if C3 != 3 or H % 2 or W % 2:
+            raise ValueError("stem expects [N, 3, H, W] with even H, W")
+        images = images.contiguous()
+        H2, W2 = H // 2, W // 2
+        xs = torch.empty((N, H2, W2 + 3, 16), dtype=torch.bfloat16, device=images.device)
+        check(_lib.lib().tony_stem_space_to_depth(ptr(images), ptr(xs), N, H, W, cur_stream()),
+              "tony_stem_space_to_depth")
+        logical = (N, H2, W2, 64, 16, (W2 + 3) * 16, H2 * (W2 + 3) * 16)
+        yn = conv2d_nhwc(xs, w2, 1, 2, stats=stats, logical=logical, pad_h_only=True, pad_hi=1)
+        ctx.save_for_backward(xs)
+        ctx.logical, ctx.wshape = logical, tuple(w2.shape)
+        return yn.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (xs,) = ctx.saved_tensors
+        dyn = dy.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1)
+        dw2 = conv2d_wgrad_nhwc(dyn, xs, ctx.wshape, 1, 2, logical=ctx.logical, pad_h_only=True, pad_hi=1)
+        return None, dw2, None
+
+
+def stem_weight_index(device=None) -> torch.Tensor:
+    """Gather index that lays a ``[K, 7, 7, 3]`` (KRSC) stem filter, flattened to ``[K, 147]`` with one
+    zero column appended (index 147), out as the ``[K, 4*64]`` filter of the space-to-depth form:
+    position ``a*64 + b*16 + (dy*2+dx)*4 + c`` holds tap ``(r, s) = (2a+dy-1, 2b+dx-1)``."""
+    idx = torch.full((4, 4, 2, 2, 4), 147, dtype=torch.long)
+    for a in range(4):
+        for b in range(4):
+            for dy in range(2):
+                for dx in range(2):
+                    r, s_ = 2 * a + dy - 1, 2 * b + dx - 1
+                    if 0 <= r < 7 and 0 <= s_ < 7:
+                        for c in range(3):
+                            idx[a, b, dy, dx, c] = (r * 7 + s_) * 3 + c
+    return idx.reshape(-1).to(device) if device is not None else idx.reshape(-1)
+
+
+def stem_conv7x7s2(images, weight_krsc, stats: Optional[torch.Tensor] = None, index: Optional[torch.Tensor] = None):
+    """``conv2d(images, W, stride=2, padding=3)`` for ``images`` ``[N, 3, H, W]`` bf16 (NCHW) and
+    ``weight_krsc`` ``[K, 7, 7, 3]``; returns channels-last ``[N, K, H/2, W/2]``."""
+    K = weight_krsc.shape[0]
+    if index is None:
+        index = stem_weight_index(weight_krsc.device)
+    flat = torch.cat([weight_krsc.reshape(K, 147), weight_krsc.new_zeros(K, 1)], dim=1)
+    w2 = flat.index_select(1, index).view(K, 4, 1, 64)
+    return _StemConvFn.apply(images, w2, stats)
 
 
 class _BroadcastAddParamFn(torch.autograd.Function):
