@@ -176,6 +176,9 @@ int tony_conv2d_wgrad_bf16(const tony_conv_desc* d, const void* dy, const void* 
  * zero elsewhere.  The stem then is a 4 x 4 / stride-1 convolution that tony_conv2d_fprop_bf16 runs with
  * R = 4, S = 1, C = 64 and x_stride_w = 16 (the 4 horizontal taps are 64 contiguous elements). */
 int tony_stem_space_to_depth(const void* x, void* xs, int N, int H, int W, void* stream);
+/* Same transform with the 4-pixel horizontal window written out: xw [N, H/2, W/2, 64] (dense NHWC input
+ * for tony_conv2d_fprop_bf16 with R = 4, S = 1, C = 64; 4x the bytes of xs). */
+int tony_stem_space_to_depth_window(const void* x, void* xw, int N, int H, int W, void* stream);
 
 /* ---- fused attention on a packed QKV activation (tcgen05 + TMA, head_dim 64) ------------ */
 /* qkv: [batch*seq, 3, heads, 64] bf16 (the fused QKV projection's output, read in place);

@@ -31,6 +31,9 @@ int device_sm_count();         // SM count of the current device (cached)
 // 2-D bf16 tensor map, 128-byte swizzle, `inner` contiguous (defined in gemm_tcgen05.cu)
 int make_tmap_2d_bf16(CUtensorMap* map, const void* ptr, long long inner_extent, long long outer_extent,
                       long long ld, int box_inner, int box_outer);
+// same with a 64-byte swizzle (32 bf16 per row): the layout of the epilogue's per-warp staging tiles
+int make_tmap_2d_bf16_sw64(CUtensorMap* map, const void* ptr, long long inner_extent, long long outer_extent,
+                           long long ld, int box_inner, int box_outer);
 // C (+)= alpha * sum over `splits` fp32 partial planes [M][N] (defined in gemm_tcgen05.cu)
 int launch_splitk_reduce(const float* ws, int splits, int M, int N, __nv_bfloat16* C, long long ldc, float alpha,
                          unsigned int flags, cudaStream_t stream);
@@ -147,6 +150,20 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* ba
           "r"(c0), "r"(c1)
         : "memory");
 }
+
+// TMA store: shared (this CTA) -> global tile, tracked by the thread's bulk async-group.  The map clips
+// rows / columns beyond the tensor, so ragged tiles need no predicates.
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t smem_src, int32_t c0, int32_t c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 :
+                 : "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_src), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all of this thread's committed stores have finished READING shared memory (the buffer may be rewritten)
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// ... and have completed (writes performed)
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");

@@ -103,19 +103,27 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     constexpr uint32_t TMEM_COLS = (2 * BLOCK_N < 32) ? 32 : 2 * BLOCK_N;
     constexpr int N_CHUNKS = BLOCK_N / 64;
 
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>(
-        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    // 128-byte swizzled operand tiles need a 1024-byte aligned base.  The dynamic shared-memory window of a
+    // kernel without static shared memory starts 1024-aligned; there is no room left to round up by hand
+    // (the 256-column variant uses 226.25 of the 227 KB), so a misaligned base traps instead.
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    if ((smem_u32(smem_raw) & 1023u) != 0) __trap();
+    uint8_t* smem = smem_raw;
     uint8_t* staging = smem + STAGES * STAGE_BYTES;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + CV_STAGING_BYTES);
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full_bar = empty_bar + STAGES;
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;
     uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+    // per-CTA partial BatchNorm statistics [2][BLOCK_N]: folded over every tile this CTA produces for
+    // one column block and added to global memory once (one atomic per column per CTA, not per warp)
+    float* stat_acc = reinterpret_cast<float*>(tmem_base_slot + 4);
 
     const int warp_idx = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
+    if (p.stat_sum != nullptr)
+        for (int i = threadIdx.x; i < 2 * BLOCK_N; i += CV_THREADS) stat_acc[i] = 0.f;
     if (warp_idx == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
         tma_prefetch_desc(&tmap_b);
@@ -276,12 +284,27 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         const int group = (warp_idx - 2) >> 2;
         const uint32_t stg = smem_u32(staging + (warp_idx - 2) * 2048);
         const int unit16 = lane & 3;
+        const int etid = threadIdx.x - 64;     // 0..511 among the epilogue warps
+        int stat_nblk = -1;
         int iter = 0;
         for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
             const int tile = unit / p.splits;
             const int split = unit - tile * p.splits;
             const int m_blk = tile / p.num_n_blocks;
             const int n_blk = tile - m_blk * p.num_n_blocks;
+            if (p.stat_sum != nullptr && n_blk != stat_nblk) {
+                if (stat_nblk >= 0) {
+                    // this CTA moves on to another column block: hand the finished partials over
+                    asm volatile("bar.sync 1, 512;" ::: "memory");
+                    for (int i = etid; i < 2 * BLOCK_N; i += 512) {
+                        const int col = stat_nblk * BLOCK_N + (i % BLOCK_N);
+                        if (col < p.N) atomicAdd((i < BLOCK_N ? p.stat_sum : p.stat_sqsum) + col, stat_acc[i]);
+                        stat_acc[i] = 0.f;
+                    }
+                    asm volatile("bar.sync 1, 512;" ::: "memory");
+                }
+                stat_nblk = n_blk;
+            }
             const int as = iter & 1;
             const uint32_t aphase = (iter >> 1) & 1;
             const int row0 = m_blk * CV_BLOCK_M + quarter * 32;
@@ -379,11 +402,12 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                             s2[j] += __shfl_xor_sync(0xffffffffu, s2[j], o2);
                         }
                     }
-                    if (lane < 4 && gc < p.N) {
+                    if (lane < 4) {
+                        const int lc = c * 32 + unit16 * 8;
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
-                            atomicAdd(p.stat_sum + gc + j, s1[j]);
-                            atomicAdd(p.stat_sqsum + gc + j, s2[j]);
+                            atomicAdd(stat_acc + lc + j, s1[j]);
+                            atomicAdd(stat_acc + BLOCK_N + lc + j, s2[j]);
                         }
                     }
                 }
@@ -391,6 +415,13 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
+        }
+        if (p.stat_sum != nullptr && stat_nblk >= 0) {
+            asm volatile("bar.sync 1, 512;" ::: "memory");
+            for (int i = etid; i < 2 * BLOCK_N; i += 512) {
+                const int col = stat_nblk * BLOCK_N + (i % BLOCK_N);
+                if (col < p.N) atomicAdd((i < BLOCK_N ? p.stat_sum : p.stat_sqsum) + col, stat_acc[i]);
+            }
         }
     }
 
@@ -442,6 +473,50 @@ stem_space_to_depth_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* _
                 }
         }
         uint4* dst = reinterpret_cast<uint4*>(xs + static_cast<size_t>(i) * 16);
+        dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+    }
+}
+
+// Same transform with the horizontal window written out: xw[n, i, q, b*16 + ch] = xs[n, i, q + b, ch]
+// (b = 0..3), a dense [N, H/2, W/2, 64] tensor (4x the bytes of xs).  Every thread produces one
+// 32-byte group (n, i, q, b).
+__global__ void __launch_bounds__(256)
+stem_space_to_depth_window_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ xw, int N, int H,
+                                  int W) {
+    const int H2 = H / 2, W2 = W / 2;
+    const long long total = static_cast<long long>(N) * H2 * W2 * 4;
+    const size_t plane = static_cast<size_t>(H) * W;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int b = static_cast<int>(i & 3);
+        long long t = i >> 2;
+        const int q = static_cast<int>(t % W2);
+        t /= W2;
+        const int ii = static_cast<int>(t % H2);
+        const int n = static_cast<int>(t / H2);
+        uint32_t o[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        const int j = q + b - 2;
+        if (j >= 0 && j < W2) {
+            const __nv_bfloat16* base = x + static_cast<size_t>(n) * 3 * plane + static_cast<size_t>(2 * ii) * W + 2 * j;
+            uint32_t v[3][2];
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+#pragma unroll
+                for (int dy = 0; dy < 2; ++dy)
+                    v[c][dy] = __ldg(reinterpret_cast<const uint32_t*>(base + c * plane + dy * W));
+#pragma unroll
+            for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+                for (int dx = 0; dx < 2; ++dx) {
+                    const int sh = dx * 16;
+                    const uint32_t c0 = (v[0][dy] >> sh) & 0xffffu, c1 = (v[1][dy] >> sh) & 0xffffu,
+                                   c2 = (v[2][dy] >> sh) & 0xffffu;
+                    o[(dy * 2 + dx) * 2] = c0 | (c1 << 16);
+                    o[(dy * 2 + dx) * 2 + 1] = c2;
+                }
+        }
+        uint4* dst = reinterpret_cast<uint4*>(xw + static_cast<size_t>(i) * 16);
         dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
         dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
     }
@@ -508,7 +583,8 @@ static int make_im2col_tmap(CUtensorMap* map, const void* ptr, int N, int H, int
 template <int BLOCK_N, int STAGES, int MODE>
 static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, int grid, cudaStream_t stream) {
     constexpr size_t SMEM =
-        static_cast<size_t>(STAGES) * (CV_BLOCK_M + BLOCK_N) * CV_BLOCK_K * 2 + CV_STAGING_BYTES + 1024 + 256;
+        static_cast<size_t>(STAGES) * (CV_BLOCK_M + BLOCK_N) * CV_BLOCK_K * 2 + CV_STAGING_BYTES + 256 +
+        2 * BLOCK_N * 4;
     static bool configured[64] = {false};
     int dev = 0;
     TONY_CUDA_CHECK(cudaGetDevice(&dev));
@@ -813,6 +889,19 @@ extern "C" int tony_stem_space_to_depth(const void* x, void* xs, int N, int H, i
     const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, device_sm_count() * 32LL));
     stem_space_to_depth_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(xs), N, H, W);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}
+
+// x: [N, 3, H, W] bf16 NCHW -> xw: [N, H/2, W/2, 64] bf16, the 4-pixel horizontal window of the space-to-depth
+// image written out per output column (dense input for tony_conv2d_fprop_bf16 with R = 4, S = 1, C = 64)
+extern "C" int tony_stem_space_to_depth_window(const void* x, void* xw, int N, int H, int W, void* stream) {
+    if (!x || !xw || N <= 0 || H <= 0 || W <= 0 || (H & 1) || (W & 1)) return TONY_ERR_INVALID;
+    const long long total = static_cast<long long>(N) * (H / 2) * (W / 2) * 4;
+    const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, device_sm_count() * 32LL));
+    stem_space_to_depth_window_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(xw), N, H, W);
     count_launch();
     TONY_CUDA_CHECK(cudaGetLastError());
     return TONY_OK;

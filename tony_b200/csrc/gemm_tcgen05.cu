@@ -66,6 +66,7 @@ struct GemmParams {
     __nv_bfloat16* rowsum_out;     // nullptr = off
     int rowsum_accumulate;
     float* rowsum_ws;              // split-K: partial row sums [splits][M]
+    int tma_store;                 // epilogue writes C / aux_out with TMA tensor stores (UTMASTG)
 };
 
 __device__ __forceinline__ void tile_coords(const GemmParams& p, int tile, int& m_blk, int& n_blk) {
@@ -184,9 +185,32 @@ __device__ __forceinline__ void store_tile_rows(__nv_bfloat16* g, long long ld, 
     __syncwarp();
 }
 
-__device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, const uint32_t (&r)[32], int row0,
+// this lane's row (16 packed words) -> the warp's staging tile -> ONE TMA tensor store of the 32 x 32 tile
+// (64-byte swizzle = the staging tile's XOR pattern; rows / columns past M / N are clipped by the map)
+__device__ __forceinline__ void store_tile_tma(const CUtensorMap* map, int row0, int col0, uint32_t stg, int lane,
+                                               const uint32_t (&in)[16]) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+        st_shared_v4(stg_addr(stg, lane, u), make_uint4(in[4 * u], in[4 * u + 1], in[4 * u + 2], in[4 * u + 3]));
+    fence_proxy_async_smem();      // generic-proxy writes -> async-proxy (TMA) read
+    __syncwarp();
+    if (lane == 0) {
+        tma_store_2d(map, stg, col0, row0);
+        tma_store_commit();
+    }
+}
+
+// before the staging tile is written again: the previous TMA store must have finished reading it
+__device__ __forceinline__ void staging_acquire(int lane) {
+    if (lane == 0) tma_store_wait_read();
+    __syncwarp();
+}
+
+__device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, const CUtensorMap* tmap_c,
+                                                 const CUtensorMap* tmap_aux, const uint32_t (&r)[32], int row0,
                                                  int col0, uint32_t stg, int lane) {
     const uint32_t flags = p.flags;
+    if (p.tma_store) staging_acquire(lane);
     float v[32];
     if (flags & TONY_EPI_BIAS) {
 #pragma unroll
@@ -230,7 +254,12 @@ __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, const uint
     if (flags & TONY_EPI_SAVE_PREACT) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) o[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-        store_tile_rows(p.aux_out, p.ldc, row0, col0, p.M, p.N, stg, lane, o);
+        if (p.tma_store) {
+            store_tile_tma(tmap_aux, row0, col0, stg, lane, o);
+            staging_acquire(lane);
+        } else {
+            store_tile_rows(p.aux_out, p.ldc, row0, col0, p.M, p.N, stg, lane, o);
+        }
     }
     if (flags & TONY_EPI_GELU_ERF) {
 #pragma unroll
@@ -254,13 +283,17 @@ __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, const uint
     }
 #pragma unroll
     for (int j = 0; j < 16; ++j) o[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-    store_tile_rows(p.C, p.ldc, row0, col0, p.M, p.N, stg, lane, o);
+    if (p.tma_store)
+        store_tile_tma(tmap_c, row0, col0, stg, lane, o);
+    else
+        store_tile_rows(p.C, p.ldc, row0, col0, p.M, p.N, stg, lane, o);
 }
 
 template <int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
-                         const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
+                         const __grid_constant__ CUtensorMap tmap_b, const __grid_constant__ CUtensorMap tmap_c,
+                         const __grid_constant__ CUtensorMap tmap_aux, const GemmParams p) {
     constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;
     constexpr uint32_t B_BYTES = BLOCK_N * BLOCK_K * 2;
     constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
@@ -439,12 +472,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                         }
                         continue;
                     }
-                    epilogue_chunk32(p, r, row0, col0, stg, lane);
+                    epilogue_chunk32(p, &tmap_c, &tmap_aux, r, row0, col0, stg, lane);
                 }
                 tcgen05_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
             }
+            if (p.tma_store && lane == 0) tma_store_wait_all();   // shared memory stays valid until read
         }
     }
     else {
@@ -476,7 +510,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
 template <int STAGES, bool ROWSUM>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
-                              const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
+                              const __grid_constant__ CUtensorMap tmap_b, const __grid_constant__ CUtensorMap tmap_c,
+                              const __grid_constant__ CUtensorMap tmap_aux, const GemmParams p) {
     constexpr int HALF_N = 128;                       // B rows held by each CTA
     constexpr int TILE_N = 256;
     constexpr int TILE_M = 256;
@@ -671,7 +706,7 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     }
                     continue;
                 }
-                epilogue_chunk32(p, r, row0, col0, stg, lane);
+                epilogue_chunk32(p, &tmap_c, &tmap_aux, r, row0, col0, stg, lane);
             }
             if (rowsum && n_blk == 0 && group == 0) {
                 // one warp per TMEM lane quarter: column 0 of the row-sum accumulator is this lane's row
@@ -694,6 +729,7 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tmem_empty_bar[as]), 0));
         }
+        if (p.tma_store && lane == 0) tma_store_wait_all();
     }
 
     __syncwarp();
@@ -827,9 +863,24 @@ int make_operand_tmap(CUtensorMap* map, const void* ptr, int mn_extent, int k_ex
     return TONY_OK;
 }
 
+static int make_tmap_2d_bf16_mode(CUtensorMap* map, const void* ptr, long long inner_extent, long long outer_extent,
+                                  long long ld, int box_inner, int box_outer, CUtensorMapSwizzle swz);
+
 // Generic 2-D bf16 map with 128-byte swizzle: `inner` is the contiguous dimension.
 int make_tmap_2d_bf16(CUtensorMap* map, const void* ptr, long long inner_extent, long long outer_extent,
                       long long ld, int box_inner, int box_outer) {
+    return make_tmap_2d_bf16_mode(map, ptr, inner_extent, outer_extent, ld, box_inner, box_outer,
+                                  CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+int make_tmap_2d_bf16_sw64(CUtensorMap* map, const void* ptr, long long inner_extent, long long outer_extent,
+                           long long ld, int box_inner, int box_outer) {
+    return make_tmap_2d_bf16_mode(map, ptr, inner_extent, outer_extent, ld, box_inner, box_outer,
+                                  CU_TENSOR_MAP_SWIZZLE_64B);
+}
+
+static int make_tmap_2d_bf16_mode(CUtensorMap* map, const void* ptr, long long inner_extent, long long outer_extent,
+                                  long long ld, int box_inner, int box_outer, CUtensorMapSwizzle swz) {
     static thread_local bool tls_ctx_bound = false;
     if (!tls_ctx_bound) {
         cudaFree(nullptr);
@@ -845,7 +896,7 @@ int make_tmap_2d_bf16(CUtensorMap* map, const void* ptr, long long inner_extent,
     cuuint64_t gstride[1] = {static_cast<cuuint64_t>(ld) * 2};
     cuuint32_t estride[2] = {1, 1};
     CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride,
-                     box, estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     box, estride, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         char buf[64];
@@ -873,7 +924,8 @@ int device_sm_count() {
 // pdl_wait) before the previous kernel in the stream has fully drained.  TONY_B200_PDL=0 disables.
 template <typename Kern>
 static cudaError_t launch_pdl(Kern kern, int grid, size_t smem, cudaStream_t stream, const CUtensorMap& ta,
-                              const CUtensorMap& tb, const GemmParams& p) {
+                              const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
+                              const GemmParams& p) {
     static int pdl = -1;
     if (pdl < 0) {
         const char* e = getenv("TONY_B200_PDL");
@@ -889,12 +941,12 @@ static cudaError_t launch_pdl(Kern kern, int grid, size_t smem, cudaStream_t str
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, kern, ta, tb, p);
+    return cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tx, p);
 }
 
 template <int BLOCK_N, int STAGES>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
-                       cudaStream_t stream) {
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
+                       const GemmParams& p, int grid, cudaStream_t stream) {
     constexpr size_t SMEM =
         static_cast<size_t>(STAGES) * (BLOCK_M + BLOCK_N) * BLOCK_K * 2 + EPI_STAGING_BYTES + 1024 + 256;
     static bool configured[64] = {false};
@@ -906,14 +958,14 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
                                              static_cast<int>(SMEM)));
         configured[dev] = true;
     }
-    TONY_CUDA_CHECK(launch_pdl(gemm_bf16_tcgen05_kernel<BLOCK_N, STAGES>, grid, SMEM, stream, ta, tb, p));
+    TONY_CUDA_CHECK(launch_pdl(gemm_bf16_tcgen05_kernel<BLOCK_N, STAGES>, grid, SMEM, stream, ta, tb, tc, tx, p));
     count_launch();
     return TONY_OK;
 }
 
 template <int STAGES, bool ROWSUM>
-static int launch_gemm_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
-                            cudaStream_t stream) {
+static int launch_gemm_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
+                            const CUtensorMap& tx, const GemmParams& p, int grid, cudaStream_t stream) {
     constexpr size_t SMEM = static_cast<size_t>(STAGES) * (BLOCK_M + 128) * BLOCK_K * 2 + EPI_STAGING_BYTES +
                             (ROWSUM ? 1024 : 0) + 1024 + 256;
     static bool configured[64] = {false};
@@ -925,7 +977,7 @@ static int launch_gemm_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const 
                                              static_cast<int>(SMEM)));
         configured[dev] = true;
     }
-    TONY_CUDA_CHECK(launch_pdl(gemm_bf16_tcgen05_2cta_kernel<STAGES, ROWSUM>, grid, SMEM, stream, ta, tb, p));
+    TONY_CUDA_CHECK(launch_pdl(gemm_bf16_tcgen05_2cta_kernel<STAGES, ROWSUM>, grid, SMEM, stream, ta, tb, tc, tx, p));
     count_launch();
     return TONY_OK;
 }
@@ -1051,7 +1103,25 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
     rc = make_operand_tmap(&tb, B, N, K, ldb, b_mn_major, use_2cta ? 128 : block_n);
     if (rc) return rc;
 
+    // epilogue output maps: 32 x 32 boxes, 64-byte swizzle (the staging tile's own XOR pattern)
+    static int tma_store_mode = -1;
+    if (tma_store_mode < 0) {
+        const char* e = getenv("TONY_B200_GEMM_TMA_STORE");
+        tma_store_mode = e ? atoi(e) : 1;
+    }
+    CUtensorMap tc = ta, tx = ta;   // placeholders when unused
+    const int use_tma_store = tma_store_mode && splits == 1;
+    if (use_tma_store) {
+        rc = make_tmap_2d_bf16_sw64(&tc, C, N, M, ldc, 32, 32);
+        if (rc) return rc;
+        if (flags & TONY_EPI_SAVE_PREACT) {
+            rc = make_tmap_2d_bf16_sw64(&tx, aux_out, N, M, ldc, 32, 32);
+            if (rc) return rc;
+        }
+    }
+
     GemmParams p;
+    p.tma_store = use_tma_store;
     p.M = M;
     p.N = N;
     p.K = K;
@@ -1096,12 +1166,12 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
     const long long units = tiles * splits;
     const int grid = static_cast<int>(std::min<long long>(units, workers)) + copy_ctas;
     if (use_2cta)
-        rc = rowsum_out ? launch_gemm_2cta<6, true>(ta, tb, p, grid * 2, stream)
-                        : launch_gemm_2cta<6, false>(ta, tb, p, grid * 2, stream);
+        rc = rowsum_out ? launch_gemm_2cta<6, true>(ta, tb, tc, tx, p, grid * 2, stream)
+                        : launch_gemm_2cta<6, false>(ta, tb, tc, tx, p, grid * 2, stream);
     else if (block_n == 256)
-        rc = launch_gemm<256, 4>(ta, tb, p, grid, stream);
+        rc = launch_gemm<256, 4>(ta, tb, tc, tx, p, grid, stream);
     else
-        rc = launch_gemm<128, 6>(ta, tb, p, grid, stream);
+        rc = launch_gemm<128, 6>(ta, tb, tc, tx, p, grid, stream);
     if (rc) return rc;
 
     if (splits > 1) {

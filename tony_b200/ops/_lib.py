@@ -176,6 +176,7 @@ def _declare(lib) -> None:
     lib.tony_maxpool3x3s2_bwd.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_int, vp]
     lib.tony_layernorm_bwd_add.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, c_int, c_int, vp, c_size_t, c_int, vp]
     lib.tony_stem_space_to_depth.argtypes = [vp, vp, c_int, c_int, c_int, vp]
+    lib.tony_stem_space_to_depth_window.argtypes = [vp, vp, c_int, c_int, c_int, vp]
     lib.tony_conv2d_out_size.argtypes = [c_int, c_int, c_int, c_int]
     lib.tony_conv2d_fprop_bf16.argtypes = [POINTER(ConvDesc), vp, vp, vp, vp, vp, vp]
     lib.tony_conv2d_dgrad_bf16.argtypes = [POINTER(ConvDesc), vp, vp, vp, c_uint, vp]

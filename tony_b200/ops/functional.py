@@ -836,10 +836,17 @@ class _StemConvFn(torch.autograd.Function):
             raise ValueError("stem expects [N, 3, H, W] with even H, W")
         images = images.contiguous()
         H2, W2 = H // 2, W // 2
-        xs = torch.empty((N, H2, W2 + 3, 16), dtype=torch.bfloat16, device=images.device)
-        check(_lib.lib().tony_stem_space_to_depth(ptr(images), ptr(xs), N, H, W, cur_stream()),
-              "tony_stem_space_to_depth")
-        logical = (N, H2, W2, 64, 16, (W2 + 3) * 16, H2 * (W2 + 3) * 16)
+        if os.environ.get("TONY_B200_STEM_WINDOW", "dense") == "overlap":
+            # 4x fewer bytes, but 128-pixel im2col loads through the overlapping map measured 16x slower
+            xs = torch.empty((N, H2, W2 + 3, 16), dtype=torch.bfloat16, device=images.device)
+            check(_lib.lib().tony_stem_space_to_depth(ptr(images), ptr(xs), N, H, W, cur_stream()),
+                  "tony_stem_space_to_depth")
+            logical = (N, H2, W2, 64, 16, (W2 + 3) * 16, H2 * (W2 + 3) * 16)
+        else:
+            xs = torch.empty((N, H2, W2, 64), dtype=torch.bfloat16, device=images.device)
+            check(_lib.lib().tony_stem_space_to_depth_window(ptr(images), ptr(xs), N, H, W, cur_stream()),
+                  "tony_stem_space_to_depth_window")
+            logical = (N, H2, W2, 64, 0, 0, 0)
         yn = conv2d_nhwc(xs, w2, 1, 2, stats=stats, logical=logical, pad_h_only=True, pad_hi=1)
         ctx.save_for_backward(xs)
         ctx.logical, ctx.wshape = logical, tuple(w2.shape)
