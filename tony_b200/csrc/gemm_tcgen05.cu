@@ -1080,7 +1080,11 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
             splits = force_splits;
         } else if (force_splits == 0 && (tiles * 2 <= workers || wave_efficiency(tiles, workers) < 0.75)) {
             double best = wave_efficiency(tiles, workers);
-            for (int s = 2; s <= 16; ++s) {
+            // up to 16 splits normally; very long reductions over one or two output tiles (pointwise-convolution
+            // weight gradients: K = every pixel of the batch) may use one split per SM
+            int max_s = 16;
+            if (tiles * 32 <= workers) max_s = static_cast<int>(workers / tiles);
+            for (int s = 2; s <= max_s; ++s) {
                 if (num_k / s < 8) break;  // keep >= 512 reduction elements per split
                 const double e = wave_efficiency(tiles * s, workers);
                 if (e > best + 0.05) {
