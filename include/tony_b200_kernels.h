@@ -322,6 +322,20 @@ int tony_fused_reduce_optim(const tony_fused_comm* comm, size_t begin, size_t co
  * of every rank's `grad[]` buffer, result written to every rank's `param[]` buffer. */
 int tony_symm_allreduce_bf16(const tony_fused_comm* comm, size_t begin, size_t count, float scale,
                              unsigned int epoch, int num_ctas, void* stream);
+/* Stand-alone collectives over peer memory (K0c): input = every rank's `grad[]` buffer, output = its
+ * `param[]` buffer, over the same byte range [begin_bytes, begin_bytes + bytes) on every rank
+ * (bytes % (world*16) == 0).  fp32 != 0 sums 32-bit floats, else bf16 (fp32 accumulation either way);
+ * all-gather and broadcast move raw bytes (any dtype).  Each rank pulls over NVLink with 16-byte loads
+ * and writes only its own output (all-reduce also stores its reduced shard to every peer).  Replaces
+ * ncclReduceScatter / ncclAllGather / ncclBroadcast in Horovod-style jobs
+ * (tony-examples/horovod-on-tony/tensorflow2_mnist.py:85-86 broadcast_variables,
+ * tensorflow2_keras_mnist.py:75 metric averaging). */
+#define TONY_COLL_ALLREDUCE 0
+#define TONY_COLL_REDUCE_SCATTER 1
+#define TONY_COLL_ALLGATHER 2
+#define TONY_COLL_BROADCAST 3
+int tony_symm_collective(const tony_fused_comm* comm, int op, int fp32, size_t begin_bytes, size_t bytes,
+                         float scale, int root, unsigned int epoch, int num_ctas, void* stream);
 /* All-rank barrier on the GPU (arrive + wait on flag words). */
 int tony_symm_barrier(const tony_fused_comm* comm, unsigned int epoch, void* stream);
 
@@ -365,6 +379,12 @@ int tony_fused_reduce_optim_nvls(const tony_nvls_comm* comm, size_t begin, size_
                                  float weight_decay, float bc1, float bc2, float grad_scale,
                                  const unsigned char* wd_mask, int broadcast, unsigned int call_index,
                                  int num_ctas, void* stream);
+
+/* Broadcast through the switch: the root publishes `count` bf16-sized elements at element offset `begin`
+ * of its own parameter buffer to every rank's parameter buffer with multimem.st (16 bytes per store leave
+ * the root once; the NVSwitch replicates them).  All ranks call it with the same call_index. */
+int tony_nvls_broadcast(const tony_nvls_comm* comm, size_t begin, size_t count, int root,
+                        unsigned int call_index, int num_ctas, void* stream);
 
 /* ---- all-gather fused into a GEMM (K3) ---------------------------------------------- */
 /* Y = epi(X . W^T) where W [N,K] is row-sharded over `world` ranks (rows

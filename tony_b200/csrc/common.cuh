@@ -165,6 +165,29 @@ __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.b
 // ... and have completed (writes performed)
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
+// Tiled 2-D load delivered to the same shared-memory offset of every CTA in `cta_mask` of this cluster;
+// each destination's mbarrier (same offset) is credited with the bytes.  Loads of this kind read only
+// this GPU's memory (weights / activations of the local rank).
+__device__ __forceinline__ void tma_load_2d_multicast(const CUtensorMap* map, uint64_t* bar, void* smem_dst,
+                                                      int32_t c0, int32_t c1, uint16_t cta_mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        " [%0], [%1, {%3, %4}], [%2], %5;"
+        :
+        : "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1),
+          "h"(cta_mask)
+        : "memory");
+}
+
+// tcgen05.commit whose arrival goes to the barrier at this offset in every CTA of `mask` (1-CTA MMAs)
+__device__ __forceinline__ void umma_commit_multicast(uint64_t* bar, uint16_t mask) {
+    asm volatile(
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+            smem_u32(bar)),
+        "h"(mask)
+        : "memory");
+}
+
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }

@@ -64,6 +64,7 @@ struct ConvParams {
     float* workspace;              // split-K partials [splits][M][N]
     float* stat_sum;               // optional [N]: += column sums of the bf16 output
     float* stat_sqsum;             // optional [N]: += column sums of squares
+    int dbg;                       // timing experiments only (TONY_B200_CONV_DBG): 1 = skip A loads, 2 = skip B loads
 };
 
 __device__ __forceinline__ void tma_load_im2col_4d(const CUtensorMap* map, uint64_t* bar, void* smem_dst,
@@ -93,10 +94,17 @@ __device__ __forceinline__ long long cv_out_row(const ConvParams& p, int m) {
     return (static_cast<long long>(n) * p.OH + pp * p.osh + p.oph) * p.OW + qq * p.osw + p.opw;
 }
 
-template <int BLOCK_N, int STAGES, int MODE>
+// CS > 1 (MODE 0 only): CS CTAs of a cluster work on CS consecutive pixel tiles of the same column block in
+// lockstep and share the filter operand: every CTA fetches 1/CS of each B tile and the TMA unit multicasts
+// it into all CS shared memories, so the filter crosses L2 -> SM once per cluster instead of once per CTA
+// (at 256 output channels the filter is 2/3 of a CTA's operand traffic, and that traffic - not the MMAs -
+// bounds the kernel).  A slot is refilled only after every CTA of the cluster has consumed it: each MMA
+// thread's tcgen05.commit arrives on the `empty` barrier of all CS CTAs.
+template <int BLOCK_N, int STAGES, int MODE, int CS>
 __global__ void __launch_bounds__(CV_THREADS, 1)
 conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                          const ConvParams p) {
+    static_assert(CS == 1 || MODE == 0, "operand multicast is implemented for the fprop / dgrad form");
     constexpr uint32_t A_BYTES = CV_BLOCK_M * CV_BLOCK_K * 2;
     constexpr uint32_t B_BYTES = BLOCK_N * CV_BLOCK_K * 2;
     constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
@@ -129,7 +137,7 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         tma_prefetch_desc(&tmap_b);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], 1);
+            mbar_init(&empty_bar[s], CS);      // one tcgen05.commit arrival per CTA of the cluster
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tmem_full_bar[s], 1);
@@ -139,28 +147,34 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     }
     if (warp_idx == 1) tmem_alloc<TMEM_COLS>(tmem_base_slot);
     tcgen05_fence_before();
-    __syncthreads();
+    if (CS > 1) cluster_sync_all(); else __syncthreads();   // peers' barriers exist before any multicast
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_base_slot;
     pdl_launch_dependents();
 
-    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    // Work units.  CS == 1: unit = (tile, split), tile = m_blk * num_n + n_blk, CTA-strided.  CS > 1: a unit
+    // is a GROUP of CS consecutive m-blocks of one column block; the cluster's CTAs take one m-block each
+    // (a CTA whose m-block lies past the end still loads its share of B and runs the barriers).
+    const uint32_t crank = CS > 1 ? cluster_ctarank() : 0u;
+    const int num_tiles = CS > 1 ? ((p.num_m_blocks + CS - 1) / CS) * p.num_n_blocks : p.num_m_blocks * p.num_n_blocks;
     const int num_units = num_tiles * p.splits;
-    const int worker = static_cast<int>(blockIdx.x);
-    const int num_workers = static_cast<int>(gridDim.x);
+    const int worker = static_cast<int>(blockIdx.x) / CS;
+    const int num_workers = static_cast<int>(gridDim.x) / CS;
     const int pq = p.P * p.Q;
+    constexpr uint16_t MC_MASK = static_cast<uint16_t>((1u << CS) - 1u);
 
     if (warp_idx == 0) {
         // ---------------------------------------------------------------- TMA producer
-        if (lane == 0) {
+        // (whole warp in the loop, one elected lane issues: see the note at the MMA issuer)
+        {
             int stage = 0;
             uint32_t phase = 0;
             pdl_wait();
             for (int unit = worker; unit < num_units; unit += num_workers) {
                 const int tile = unit / p.splits;
                 const int split = unit - tile * p.splits;
-                const int m_blk = tile / p.num_n_blocks;
-                const int n_blk = tile - m_blk * p.num_n_blocks;
+                const int m_blk = (tile / p.num_n_blocks) * CS + static_cast<int>(crank);
+                const int n_blk = tile % p.num_n_blocks;
                 const int kb0 = split * p.kb_per_split;
                 const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
                 if (MODE == 0) {
@@ -177,18 +191,52 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         uint8_t* sa = smem + stage * STAGE_BYTES;
                         uint8_t* sb = sa + A_BYTES;
-                        mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
                         const ConvTap tap = p.taps[t];
-                        tma_load_im2col_4d(&tmap_a, &full_bar[stage], sa, cc * 64, cw, ch, img, tap.off_w, tap.off_h);
                         const int winner = tap.wsel * p.w_tap_stride;
-                        if (!p.b_mn_major) {
-                            tma_load_2d(&tmap_b, &full_bar[stage], sb, winner + cc * 64, n_blk * BLOCK_N);
+                        if (elect_one()) {
+                        if (p.dbg) {   // wrong results on purpose: which operand's loads bound the kernel?
+                            const bool la = !(p.dbg & 1), lb = !(p.dbg & 2);
+                            mbar_expect_tx(&full_bar[stage], (la ? A_BYTES : 0) + (lb ? B_BYTES : 0));
+                            if (la) tma_load_im2col_4d(&tmap_a, &full_bar[stage], sa, cc * 64, cw, ch, img, tap.off_w, tap.off_h);
+                            if (lb) tma_load_2d(&tmap_b, &full_bar[stage], sb, winner + cc * 64, n_blk * BLOCK_N);
                         } else {
+                        mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+                        tma_load_im2col_4d(&tmap_a, &full_bar[stage], sa, cc * 64, cw, ch, img, tap.off_w, tap.off_h);
+                        if (CS == 1) {
+                            if (!p.b_mn_major) {
+                                tma_load_2d(&tmap_b, &full_bar[stage], sb, winner + cc * 64, n_blk * BLOCK_N);
+                            } else {
 #pragma unroll
-                            for (int c = 0; c < N_CHUNKS; ++c)
-                                tma_load_2d(&tmap_b, &full_bar[stage], sb + c * CV_CHUNK_BYTES,
-                                            winner + n_blk * BLOCK_N + c * 64, cc * 64);
+                                for (int c = 0; c < N_CHUNKS; ++c)
+                                    tma_load_2d(&tmap_b, &full_bar[stage], sb + c * CV_CHUNK_BYTES,
+                                                winner + n_blk * BLOCK_N + c * 64, cc * 64);
+                            }
+                        } else if (!p.b_mn_major) {
+                            // K-major filter tile [BLOCK_N rows][64 k]: this CTA's BLOCK_N / CS rows, to everyone
+                            constexpr int ROWS = BLOCK_N / CS;
+                            tma_load_2d_multicast(&tmap_b, &full_bar[stage], sb + crank * ROWS * 128, winner + cc * 64,
+                                                  n_blk * BLOCK_N + static_cast<int>(crank) * ROWS, MC_MASK);
+                        } else if (N_CHUNKS >= CS) {
+                            // MN-major filter tile: whole [64 k][64 n] chunks dealt round-robin to the CTAs
+#pragma unroll
+                            for (int c = 0; c < N_CHUNKS / CS; ++c) {
+                                const int ch = c * CS + static_cast<int>(crank);
+                                tma_load_2d_multicast(&tmap_b, &full_bar[stage], sb + ch * CV_CHUNK_BYTES,
+                                                      winner + n_blk * BLOCK_N + ch * 64, cc * 64, MC_MASK);
+                            }
+                        } else {
+                            // fewer chunks than CTAs: each chunk's 64 k-rows are cut into CS / N_CHUNKS parts
+                            constexpr int PPC = CS / (N_CHUNKS > 0 ? N_CHUNKS : 1);
+                            constexpr int ROWS = 64 / (PPC > 0 ? PPC : 1);
+                            const int ch = static_cast<int>(crank) / PPC;
+                            const int part = static_cast<int>(crank) % PPC;
+                            tma_load_2d_multicast(&tmap_b, &full_bar[stage],
+                                                  sb + ch * CV_CHUNK_BYTES + part * ROWS * 128,
+                                                  winner + n_blk * BLOCK_N + ch * 64, cc * 64 + part * ROWS, MC_MASK);
                         }
+                        }
+                        }
+                        __syncwarp();
                         if (++cc == p.cblocks) {
                             cc = 0;
                             ++t;
@@ -213,6 +261,7 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         uint8_t* sa = smem + stage * STAGE_BYTES;
                         uint8_t* sb = sa + A_BYTES;
+                        if (elect_one()) {
                         mbar_expect_tx(&full_bar[stage], A_BYTES + valid * CV_CHUNK_BYTES);
 #pragma unroll
                         for (int c = 0; c < CV_BLOCK_M / 64; ++c)
@@ -228,6 +277,8 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                                                    img, tap.off_w, tap.off_h);
                             }
                         }
+                        }
+                        __syncwarp();
                         if (++stage == STAGES) {
                             stage = 0;
                             phase ^= 1;
@@ -238,7 +289,12 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         }
     } else if (warp_idx == 1) {
         // ---------------------------------------------------------------- MMA issuer
-        if (lane == 0) {
+        // The WHOLE warp runs this loop and one elected lane issues: every operand of tcgen05.mma / commit is
+        // then provably warp-uniform and lives in uniform registers.  Inside an `if (lane == 0)` region the
+        // compiler wraps each UTCHMMA in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop (about 25 instructions per
+        // MMA), which made this one thread - not the tensor core - the limit: ~700 clk per k-block measured
+        // with every load disabled, against 128-512 clk of MMA work.
+        {
             const uint32_t a_mn = MODE == 1 ? 1u : 0u;
             const uint32_t b_mn = MODE == 1 ? 1u : static_cast<uint32_t>(p.b_mn_major);
             const uint32_t idesc = make_idesc_bf16(CV_BLOCK_M, BLOCK_N, a_mn, b_mn);
@@ -266,16 +322,21 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                     const uint32_t sb = sa + A_BYTES;
                     const uint64_t da = make_umma_desc_sw128(sa, a_lbo, 1024);
                     const uint64_t db = make_umma_desc_sw128(sb, b_lbo, 1024);
+                    if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < CV_BLOCK_K / CV_UMMA_K; ++k)
-                        umma_bf16(d_tmem, da + k * a_kstep, db + k * b_kstep, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-                    umma_commit(&empty_bar[stage]);
+                        for (int k = 0; k < CV_BLOCK_K / CV_UMMA_K; ++k)
+                            umma_bf16(d_tmem, da + k * a_kstep, db + k * b_kstep, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        if (CS > 1) umma_commit_multicast(&empty_bar[stage], MC_MASK);   // frees the slot cluster-wide
+                        else umma_commit(&empty_bar[stage]);
+                    }
+                    __syncwarp();
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
-                umma_commit(&tmem_full_bar[as]);
+                if (elect_one()) umma_commit(&tmem_full_bar[as]);
+                __syncwarp();
             }
         }
     } else {
@@ -290,8 +351,8 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
             const int tile = unit / p.splits;
             const int split = unit - tile * p.splits;
-            const int m_blk = tile / p.num_n_blocks;
-            const int n_blk = tile - m_blk * p.num_n_blocks;
+            const int m_blk = (tile / p.num_n_blocks) * CS + static_cast<int>(crank);
+            const int n_blk = tile % p.num_n_blocks;
             if (p.stat_sum != nullptr && n_blk != stat_nblk) {
                 if (stat_nblk >= 0) {
                     // this CTA moves on to another column block: hand the finished partials over
@@ -427,7 +488,7 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
 
     __syncwarp();
     tcgen05_fence_before();
-    __syncthreads();
+    if (CS > 1) cluster_sync_all(); else __syncthreads();   // no CTA leaves while peers may still write to it
     if (warp_idx == 1) {
         tcgen05_fence_after();
         tmem_dealloc<TMEM_COLS>(tmem_base);
@@ -580,7 +641,7 @@ static int make_im2col_tmap(CUtensorMap* map, const void* ptr, int N, int H, int
     return TONY_OK;
 }
 
-template <int BLOCK_N, int STAGES, int MODE>
+template <int BLOCK_N, int STAGES, int MODE, int CS>
 static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, int grid, cudaStream_t stream) {
     constexpr size_t SMEM =
         static_cast<size_t>(STAGES) * (CV_BLOCK_M + BLOCK_N) * CV_BLOCK_K * 2 + CV_STAGING_BYTES + 256 +
@@ -589,9 +650,34 @@ static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvP
     int dev = 0;
     TONY_CUDA_CHECK(cudaGetDevice(&dev));
     if (dev >= 0 && dev < 64 && !configured[dev]) {
-        TONY_CUDA_CHECK(cudaFuncSetAttribute(conv_bf16_tcgen05_kernel<BLOCK_N, STAGES, MODE>,
+        TONY_CUDA_CHECK(cudaFuncSetAttribute(conv_bf16_tcgen05_kernel<BLOCK_N, STAGES, MODE, CS>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SMEM)));
         configured[dev] = true;
+    }
+    if (CS > 1) {
+        // persistent clusters: no more of them than can be resident at once (cluster placement may leave
+        // a few SMs unused), each takes whole groups of CS tiles
+        static int max_clusters[64] = {0};
+        if (dev >= 0 && dev < 64 && max_clusters[dev] == 0) {
+            cudaLaunchConfig_t q = {};
+            q.gridDim = dim3(device_sm_count() / CS * CS);
+            q.blockDim = dim3(CV_THREADS);
+            q.dynamicSmemBytes = SMEM;
+            cudaLaunchAttribute qa[1];
+            qa[0].id = cudaLaunchAttributeClusterDimension;
+            qa[0].val.clusterDim.x = CS;
+            qa[0].val.clusterDim.y = 1;
+            qa[0].val.clusterDim.z = 1;
+            q.attrs = qa;
+            q.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, conv_bf16_tcgen05_kernel<BLOCK_N, STAGES, MODE, CS>, &q) !=
+                    cudaSuccess || n <= 0)
+                n = device_sm_count() / CS;
+            max_clusters[dev] = n;
+        }
+        const int groups = ((p.num_m_blocks + CS - 1) / CS) * p.num_n_blocks;
+        grid = std::min(groups, max_clusters[dev >= 0 && dev < 64 ? dev : 0]) * CS;
     }
     static int pdl = -1;
     if (pdl < 0) {
@@ -603,22 +689,59 @@ static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvP
     cfg.blockDim = dim3(CV_THREADS);
     cfg.dynamicSmemBytes = SMEM;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (CS > 1) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = CS;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        ++na;
+    }
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
-    TONY_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_bf16_tcgen05_kernel<BLOCK_N, STAGES, MODE>, ta, tb, p));
+    cfg.numAttrs = na;
+    TONY_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_bf16_tcgen05_kernel<BLOCK_N, STAGES, MODE, CS>, ta, tb, p));
     count_launch();
     return TONY_OK;
 }
 
+// cluster size of the fprop / dgrad kernels (filter multicast); TONY_B200_CONV_CLUSTER = 1 | 2 | 4
+static int conv_cluster_size() {
+    static int cs = -1;
+    if (cs < 0) {
+        const char* e = getenv("TONY_B200_CONV_CLUSTER");
+        cs = e ? atoi(e) : 2;
+        if (cs != 1 && cs != 2 && cs != 4) cs = 2;
+    }
+    return cs;
+}
+
+template <int MODE, int CS>
+static int dispatch_conv_cs(int block_n, const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, int grid,
+                            cudaStream_t stream) {
+    if (block_n == 64) return launch_conv<64, 8, MODE, CS>(ta, tb, p, grid, stream);
+    if (block_n == 128) return launch_conv<128, 6, MODE, CS>(ta, tb, p, grid, stream);
+    return launch_conv<256, 4, MODE, CS>(ta, tb, p, grid, stream);
+}
+
 template <int MODE>
 static int dispatch_conv(int block_n, const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, int grid,
-                         cudaStream_t stream) {
-    if (block_n == 64) return launch_conv<64, 8, MODE>(ta, tb, p, grid, stream);
-    if (block_n == 128) return launch_conv<128, 6, MODE>(ta, tb, p, grid, stream);
-    return launch_conv<256, 4, MODE>(ta, tb, p, grid, stream);
+                         cudaStream_t stream, int cs = 1) {
+    if (MODE == 0 && cs == 2) return dispatch_conv_cs<0, 2>(block_n, ta, tb, p, grid, stream);
+    if (MODE == 0 && cs == 4) return dispatch_conv_cs<0, 4>(block_n, ta, tb, p, grid, stream);
+    return dispatch_conv_cs<MODE, 1>(block_n, ta, tb, p, grid, stream);
+}
+
+// rows of one filter-operand TMA box when `cs` CTAs share the tile (see the kernel's B loads)
+static int filter_box_rows(int block_n, int b_mn_major, int cs) {
+    if (!b_mn_major) return block_n / cs;
+    const int chunks = block_n / 64;
+    return chunks >= cs ? 64 : 64 / (cs / chunks);
 }
 
 static int pick_block_n(int n) { return n <= 64 ? 64 : (n <= 128 ? 128 : 256); }
@@ -688,17 +811,22 @@ extern "C" int tony_conv2d_fprop_bf16(const tony_conv_desc* d, const void* x, co
     p.flags = 0;
     p.stat_sum = stat_sum;
     p.stat_sqsum = stat_sqsum;
+    {
+        const char* e = getenv("TONY_B200_CONV_DBG");
+        p.dbg = e ? atoi(e) : 0;
+    }
     CUtensorMap ta, tb;
     rc = make_im2col_tmap(&ta, x, d->N, d->H, d->W, d->C, -pad_w, -d->pad, pad_hi_w - (d->S - 1),
                           pad_hi_h - (d->R - 1), d->stride, d->stride, CV_BLOCK_M, d->x_stride_w, d->x_stride_h,
                           d->x_stride_n);
     if (rc) return rc;
+    const int cs = (p.num_m_blocks >= 8 && !p.dbg) ? conv_cluster_size() : 1;
     rc = make_tmap_2d_bf16(&tb, w, static_cast<long long>(p.ntaps) * d->C, d->K, static_cast<long long>(p.ntaps) * d->C,
-                           64, block_n);
+                           64, filter_box_rows(block_n, 0, cs));
     if (rc) return rc;
     const long long units = static_cast<long long>(p.num_m_blocks) * p.num_n_blocks;
     const int grid = static_cast<int>(std::min<long long>(units, device_sm_count()));
-    return dispatch_conv<0>(block_n, ta, tb, p, grid, stream);
+    return dispatch_conv<0>(block_n, ta, tb, p, grid, stream, cs);
 }
 
 // dX[N, H, W, C] (+)= conv_transpose(dY[N, P, Q, K], Wt[K, R, S, C]);  flags: TONY_EPI_ACCUMULATE
@@ -719,8 +847,10 @@ extern "C" int tony_conv2d_dgrad_bf16(const tony_conv_desc* d, const void* dy, c
     const int block_n = pick_block_n(d->C);
     CUtensorMap tb;
     // the filter seen as [K rows][R*S*C] : B(n = ci, k = co) of tap t sits at inner offset t*C + ci
+    const long long min_tiles = static_cast<long long>(d->N) * (d->H / st) * (d->W / st) / CV_BLOCK_M;
+    const int cs = min_tiles >= 8 ? conv_cluster_size() : 1;
     rc = make_tmap_2d_bf16(&tb, w, static_cast<long long>(d->R) * d->S * d->C, d->K,
-                           static_cast<long long>(d->R) * d->S * d->C, 64, 64);
+                           static_cast<long long>(d->R) * d->S * d->C, 64, filter_box_rows(block_n, 1, cs));
     if (rc) return rc;
     // a parity class with no filter tap (1x1 stride 2: every odd row / column) receives no gradient
     bool need_zero = false;
@@ -798,7 +928,7 @@ extern "C" int tony_conv2d_dgrad_bf16(const tony_conv_desc* d, const void* dy, c
             if (rc) return rc;
             const long long units = static_cast<long long>(p.num_m_blocks) * p.num_n_blocks;
             const int grid = static_cast<int>(std::min<long long>(units, device_sm_count()));
-            rc = dispatch_conv<0>(block_n, ta, tb, p, grid, stream);
+            rc = dispatch_conv<0>(block_n, ta, tb, p, grid, stream, cs);
             if (rc) return rc;
         }
     return TONY_OK;

@@ -340,7 +340,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (worker >= 0) {
         if (warp_idx == 0) {
             // ------------------------------------------------ TMA producer
-            if (lane == 0) {
+            // The whole warp runs the loop and ONE elected lane issues (here and in the MMA warp): the
+            // operands of UTMALDG / UTCHMMA / UTCBAR are then warp-uniform values in uniform registers.
+            // Inside an `if (lane == 0)` region the compiler cannot prove that and wraps every such
+            // instruction in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop - about 25 instructions per MMA,
+            // which made the issuing thread, not the tensor core, the limit of the main loop.
+            {
                 int stage = 0;
                 uint32_t phase = 0;
                 pdl_wait();  // everything above overlapped the previous kernel's tail
@@ -350,11 +355,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     int m_blk, n_blk;
                     tile_coords(p, tile, m_blk, n_blk);
                     if (p.b_ready != nullptr) {
-                        while (static_cast<int32_t>(ld_acquire_gpu(p.b_ready + n_blk) -
-                                                    p.b_ready_epoch) < 0) {
-                            __nanosleep(64);
+                        if (elect_one()) {
+                            while (static_cast<int32_t>(ld_acquire_gpu(p.b_ready + n_blk) -
+                                                        p.b_ready_epoch) < 0) {
+                                __nanosleep(64);
+                            }
+                            fence_proxy_async();  // generic-proxy copies -> async-proxy TMA reads
                         }
-                        fence_proxy_async();  // generic-proxy copies -> async-proxy TMA reads
+                        __syncwarp();
                     }
                     const int kb0 = split * p.kb_per_split;
                     const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
@@ -362,6 +370,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         uint8_t* sa = smem + stage * STAGE_BYTES;
                         uint8_t* sb = sa + A_BYTES;
+                        if (elect_one()) {
                         mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
                         if (!p.a_mn_major) {
                             tma_load_2d(&tmap_a, &full_bar[stage], sa, kb * BLOCK_K, m_blk * BLOCK_M);
@@ -379,6 +388,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                                 tma_load_2d(&tmap_b, &full_bar[stage], sb + c * CHUNK_BYTES,
                                             n_blk * BLOCK_N + c * 64, kb * BLOCK_K);
                         }
+                        }
+                        __syncwarp();
                         if (++stage == STAGES) {
                             stage = 0;
                             phase ^= 1;
@@ -387,8 +398,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 }
             }
         } else if (warp_idx == 1) {
-            // ------------------------------------------------ MMA issuer
-            if (lane == 0) {
+            // ------------------------------------------------ MMA issuer (whole warp, elected lane issues)
+            {
                 const uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N, p.a_mn_major, p.b_mn_major);
                 // K-major: 8-row groups 1024 B apart, k-step = 32 B inside the swizzle row.
                 // MN-major: 64-wide chunks CHUNK_BYTES apart (LBO), 8 k-rows = 1024 B (SBO),
@@ -417,18 +428,22 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                         const uint32_t sb = sa + A_BYTES;
                         const uint64_t da = make_umma_desc_sw128(sa, a_lbo, 1024);
                         const uint64_t db = make_umma_desc_sw128(sb, b_lbo, 1024);
+                        if (elect_one()) {
 #pragma unroll
-                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                            umma_bf16(d_tmem, da + k * a_kstep, db + k * b_kstep, idesc,
-                                      (kb > kb0 || k > 0) ? 1u : 0u);
+                            for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                                umma_bf16(d_tmem, da + k * a_kstep, db + k * b_kstep, idesc,
+                                          (kb > kb0 || k > 0) ? 1u : 0u);
+                            }
+                            umma_commit(&empty_bar[stage]);  // frees the smem slot when MMAs retire
                         }
-                        umma_commit(&empty_bar[stage]);  // frees the smem slot when MMAs retire
+                        __syncwarp();
                         if (++stage == STAGES) {
                             stage = 0;
                             phase ^= 1;
                         }
                     }
-                    umma_commit(&tmem_full_bar[as]);  // accumulator complete -> epilogue
+                    if (elect_one()) umma_commit(&tmem_full_bar[as]);  // accumulator complete -> epilogue
+                    __syncwarp();
                 }
             }
         } else {
@@ -573,8 +588,8 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int num_clusters = static_cast<int>(gridDim.x >> 1);
 
     if (warp_idx == 0) {
-        // ---------------------------------------------------- TMA producer (both CTAs)
-        if (lane == 0) {
+        // ---------------------------------------------------- TMA producer (both CTAs; whole warp, one lane issues)
+        {
             int stage = 0;
             uint32_t phase = 0;
             pdl_wait();
@@ -592,6 +607,7 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     uint8_t* sa = smem + stage * STAGE_BYTES;
                     uint8_t* sb = sa + A_BYTES;
                     const uint32_t bar = mapa_u32(smem_u32(&full_bar[stage]), 0);  // leader's barrier
+                    if (elect_one()) {
                     if (leader) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
                     if (!p.a_mn_major) {
                         tma_load_2d_2cta(&tmap_a, bar, sa, kb * BLOCK_K, m0);
@@ -607,6 +623,8 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
                         for (int c = 0; c < HALF_N / 64; ++c)
                             tma_load_2d_2cta(&tmap_b, bar, sb + c * CHUNK_BYTES, n0 + c * 64, kb * BLOCK_K);
                     }
+                    }
+                    __syncwarp();
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
@@ -615,8 +633,8 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
             }
         }
     } else if (warp_idx == 1) {
-        // ---------------------------------------------------- MMA issuer (leader CTA only)
-        if (leader && lane == 0) {
+        // ---------------------------------------------------- MMA issuer (leader CTA only; whole warp, one lane issues)
+        if (leader) {
             const uint32_t idesc = make_idesc_bf16(TILE_M, TILE_N, p.a_mn_major, p.b_mn_major);
             const uint32_t a_lbo = p.a_mn_major ? CHUNK_BYTES : 16;
             const uint32_t b_lbo = p.b_mn_major ? CHUNK_BYTES : 16;
@@ -647,25 +665,29 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     const uint32_t sb = sa + A_BYTES;
                     const uint64_t da = make_umma_desc_sw128(sa, a_lbo, 1024);
                     const uint64_t db = make_umma_desc_sw128(sb, b_lbo, 1024);
+                    if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                        umma_bf16_2cta(d_tmem, da + k * a_kstep, db + k * b_kstep, idesc,
-                                       (kb > kb0 || k > 0) ? 1u : 0u);
-                    }
-                    if (do_rowsum) {
-                        // D2[256 x 16] += A_tile[256 x 64] . ones[64 x 16]: every column is the row sum
-#pragma unroll
-                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-                            umma_bf16_2cta(tmem_base + TILE_N, da + k * a_kstep, d_ones, idesc_ones,
+                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                            umma_bf16_2cta(d_tmem, da + k * a_kstep, db + k * b_kstep, idesc,
                                            (kb > kb0 || k > 0) ? 1u : 0u);
+                        }
+                        if (do_rowsum) {
+                            // D2[256 x 16] += A_tile[256 x 64] . ones[64 x 16]: every column is the row sum
+#pragma unroll
+                            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                                umma_bf16_2cta(tmem_base + TILE_N, da + k * a_kstep, d_ones, idesc_ones,
+                                               (kb > kb0 || k > 0) ? 1u : 0u);
+                        }
+                        umma_commit_2cta(&empty_bar[stage], 3);   // frees the slot in both CTAs
                     }
-                    umma_commit_2cta(&empty_bar[stage], 3);   // frees the slot in both CTAs
+                    __syncwarp();
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
-                umma_commit_2cta(&tmem_full_bar[as], 3);      // accumulators complete in both CTAs
+                if (elect_one()) umma_commit_2cta(&tmem_full_bar[as], 3);      // accumulators complete in both CTAs
+                __syncwarp();
             }
         }
     } else {

@@ -316,6 +316,187 @@ fused_reduce_optim_nvls_kernel(OptHyper h, NvlsArgs a) {
     }
 }
 
+// ---- stand-alone collectives over peer memory (K0c): all-reduce / reduce-scatter in bf16 or fp32,
+// all-gather and broadcast of raw bytes.  Input is every rank's `grad` buffer, output its `param` buffer;
+// `begin` / `bytes` delimit the same byte range on every rank (bytes % (world * 16) == 0).
+//   all-reduce     out[range]            = scale * sum_r in_r[range]           (every rank)
+//   reduce-scatter out[my 1/world shard] = scale * sum_r in_r[my shard]
+//   all-gather     out[shard r]          = in_r[shard r]                       for every r
+//   broadcast      out[range]            = in_root[range]
+// Pull design: a rank only ever writes its own output; flag barrier before (inputs ready) and after (nobody
+// still reads my input), as in the fused kernel above.
+struct CollArgs {
+    tony_fused_comm comm;
+    size_t begin, bytes;
+    int op, fp32, root;
+    float scale;
+    uint32_t epoch;
+    unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ bool coll_arrive_and_wait(const CollArgs& a, int slot, int tid) {
+    const int world = a.comm.world, rank = a.comm.rank;
+    bool ok = true;
+    if (tid < world && tid != rank) {
+        st_release_sys(a.comm.flags[tid] + slot * TONY_MAX_RANKS + rank, a.epoch);
+        ok = wait_flag_sys(a.comm.flags[rank] + slot * TONY_MAX_RANKS + tid, a.epoch, a.timeout_ns);
+        if (!ok) *a.comm.status = TONY_ERR_TIMEOUT;
+    }
+    return ok;
+}
+
+__global__ void __launch_bounds__(512)
+symm_collective_kernel(CollArgs a) {
+    __shared__ int sh_flag;
+    const int world = a.comm.world, rank = a.comm.rank;
+    const int tid = threadIdx.x;
+    if (world > 1) {
+        if (tid == 0) sh_flag = 1;
+        __syncthreads();
+        if (blockIdx.x == 0) {
+            __threadfence_system();
+            if (!coll_arrive_and_wait(a, 0, tid)) sh_flag = 0;
+        } else if (tid < world && tid != rank) {
+            if (!wait_flag_sys(a.comm.flags[rank] + tid, a.epoch, a.timeout_ns)) {
+                *a.comm.status = TONY_ERR_TIMEOUT;
+                sh_flag = 0;
+            }
+        }
+        __syncthreads();
+        if (!sh_flag) return;
+    }
+    const size_t chunk = a.bytes / world;
+    const size_t gtid = blockIdx.x * static_cast<size_t>(blockDim.x) + tid;
+    const size_t gstride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    if (a.op == TONY_COLL_ALLREDUCE || a.op == TONY_COLL_REDUCE_SCATTER) {
+        const size_t my = a.begin + static_cast<size_t>(rank) * chunk;
+        for (size_t v = gtid; v < chunk / 16; v += gstride) {
+            const size_t off = my + v * 16;
+            uint4 gv[TONY_MAX_RANKS];
+#pragma unroll
+            for (int j = 0; j < TONY_MAX_RANKS; ++j) {
+                if (j < world) {
+                    int r = rank + j;
+                    if (r >= world) r -= world;
+                    gv[j] = ld_global_v4(static_cast<const char*>(a.comm.grad[r]) + off);
+                }
+            }
+            uint4 w;
+            if (a.fp32) {
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int j = 0; j < TONY_MAX_RANKS; ++j) {
+                    if (j < world) {
+                        acc.x += __uint_as_float(gv[j].x);
+                        acc.y += __uint_as_float(gv[j].y);
+                        acc.z += __uint_as_float(gv[j].z);
+                        acc.w += __uint_as_float(gv[j].w);
+                    }
+                }
+                w = make_uint4(__float_as_uint(acc.x * a.scale), __float_as_uint(acc.y * a.scale),
+                               __float_as_uint(acc.z * a.scale), __float_as_uint(acc.w * a.scale));
+            } else {
+                float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int j = 0; j < TONY_MAX_RANKS; ++j) {
+                    if (j < world) {
+                        float t[8];
+                        unpack8f(gv[j], t);
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) g[k] += t[k];
+                    }
+                }
+                w.x = pack_bf16x2(g[0] * a.scale, g[1] * a.scale);
+                w.y = pack_bf16x2(g[2] * a.scale, g[3] * a.scale);
+                w.z = pack_bf16x2(g[4] * a.scale, g[5] * a.scale);
+                w.w = pack_bf16x2(g[6] * a.scale, g[7] * a.scale);
+            }
+            if (a.op == TONY_COLL_ALLREDUCE) {
+#pragma unroll
+                for (int j = 0; j < TONY_MAX_RANKS; ++j) {
+                    if (j < world) {
+                        int r = rank + j;
+                        if (r >= world) r -= world;
+                        st_global_v4(static_cast<char*>(a.comm.param[r]) + off, w);
+                    }
+                }
+            } else {
+                st_global_v4(static_cast<char*>(a.comm.param[rank]) + off, w);
+            }
+        }
+    } else {
+        // all-gather: segment j comes from rank j's input; broadcast: every segment from the root's
+        char* out = static_cast<char*>(a.comm.param[rank]);
+        for (size_t v = gtid; v < a.bytes / 16; v += gstride) {
+            const size_t off = a.begin + v * 16;
+            int src = a.root;
+            if (a.op == TONY_COLL_ALLGATHER) {
+                src = static_cast<int>((v * 16) / chunk);
+                src = (src + rank) % world;      // start with the local shard, spread the peers
+                const size_t o2 = a.begin + static_cast<size_t>(src) * chunk + (v * 16) % chunk;
+                st_global_v4(out + o2, ld_global_v4(static_cast<const char*>(a.comm.grad[src]) + o2));
+                continue;
+            }
+            st_global_v4(out + off, ld_global_v4(static_cast<const char*>(a.comm.grad[src]) + off));
+        }
+    }
+    if (world > 1) {
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0) {
+            const unsigned int prev = atomicAdd(a.comm.counter, 1u);
+            sh_flag = (prev == gridDim.x - 1) ? 2 : 1;
+        }
+        __syncthreads();
+        if (sh_flag == 2) {
+            __threadfence_system();
+            if (tid == 0) *a.comm.counter = 0;
+            coll_arrive_and_wait(a, 1, tid);
+        }
+    }
+}
+
+// NVLS broadcast: the root reads its own parameter buffer and publishes it to every rank with multimem.st
+// (one store per 16 bytes leaves the root, the switch replicates it); everyone joins the two flag phases.
+__global__ void __launch_bounds__(512)
+nvls_broadcast_kernel(NvlsArgs a, int root) {
+    __shared__ int sh_flag;
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        sh_flag = 1;
+        if (blockIdx.x == 0) {
+            __threadfence_system();
+            multimem_red_add_release(a.comm.flags_mc + NVLS_FLAG_A, 1u);
+        }
+        if (!wait_flag_sys(a.comm.flags_local + NVLS_FLAG_A, a.target, a.timeout_ns)) {
+            *a.comm.status = TONY_ERR_TIMEOUT;
+            sh_flag = 0;
+        }
+    }
+    __syncthreads();
+    if (!sh_flag) return;
+    if (a.comm.rank == root) {
+        const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(a.comm.param_local);
+        for (size_t v = blockIdx.x * static_cast<size_t>(blockDim.x) + tid; v < a.count / 8;
+             v += static_cast<size_t>(gridDim.x) * blockDim.x) {
+            const size_t idx = a.begin + v * 8;
+            multimem_st_bf16x8(static_cast<__nv_bfloat16*>(a.comm.param_mc) + idx, ld_global_v4(src + idx));
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned int prev = atomicAdd(a.comm.counter, 1u);
+        if (prev == gridDim.x - 1) {
+            __threadfence_system();
+            *a.comm.counter = 0;
+            multimem_red_add_release(a.comm.flags_mc + NVLS_FLAG_B, 1u);
+            if (!wait_flag_sys(a.comm.flags_local + NVLS_FLAG_B, a.target, a.timeout_ns))
+                *a.comm.status = TONY_ERR_TIMEOUT;
+        }
+    }
+}
+
 __global__ void symm_barrier_kernel(FusedArgs a) {
     __threadfence_system();
     arrive_and_wait_all(a, 0, threadIdx.x);
@@ -541,6 +722,64 @@ extern "C" int tony_fused_reduce_optim_nvls(const tony_nvls_comm* comm, size_t b
     grid = std::min(grid, device_sm_count());
     fused_reduce_optim_nvls_kernel<<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(
         make_hyper(optimizer, lr, beta1_or_momentum, beta2, eps, weight_decay, bc1, bc2, grad_scale, 0), a);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}
+
+extern "C" int tony_symm_collective(const tony_fused_comm* comm, int op, int fp32, size_t begin_bytes, size_t bytes,
+                                    float scale, int root, unsigned int epoch, int num_ctas, void* stream) {
+    int rc = check_comm(comm, "tony_symm_collective");
+    if (rc) return rc;
+    if (op < TONY_COLL_ALLREDUCE || op > TONY_COLL_BROADCAST || bytes == 0 ||
+        (bytes % (static_cast<size_t>(comm->world) * 16)) != 0 || (begin_bytes % 16) != 0 || root < 0 ||
+        root >= comm->world) {
+        set_last_error("tony_symm_collective", "bytes must be a multiple of world*16, begin of 16, root < world");
+        return TONY_ERR_INVALID;
+    }
+    CollArgs a;
+    a.comm = *comm;
+    a.begin = begin_bytes;
+    a.bytes = bytes;
+    a.op = op;
+    a.fp32 = fp32;
+    a.root = root;
+    a.scale = scale;
+    a.epoch = epoch;
+    a.timeout_ns = comm_timeout_ns();
+    const int threads = 512;
+    const size_t nvec = bytes / 16;
+    int grid = comm->world == 1 ? device_sm_count() * 2 : (num_ctas > 0 ? num_ctas : 32);
+    grid = static_cast<int>(std::min<size_t>(grid, std::max<size_t>(1, (nvec + threads - 1) / threads)));
+    symm_collective_kernel<<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(a);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}
+
+extern "C" int tony_nvls_broadcast(const tony_nvls_comm* comm, size_t begin, size_t count, int root,
+                                   unsigned int call_index, int num_ctas, void* stream) {
+    if (!comm || comm->world < 2 || comm->world > TONY_MAX_RANKS || comm->rank < 0 || comm->rank >= comm->world ||
+        !comm->param_mc || !comm->param_local || !comm->flags_mc || !comm->flags_local || !comm->counter ||
+        !comm->status || call_index == 0 || root < 0 || root >= comm->world || count == 0 || (count % 8) ||
+        (begin % 8)) {
+        set_last_error("tony_nvls_broadcast", "bad comm descriptor or range (count, begin multiples of 8)");
+        return TONY_ERR_INVALID;
+    }
+    NvlsArgs a;
+    a.comm = *comm;
+    a.begin = begin;
+    a.count = count;
+    a.state_offset = 0;
+    a.master = a.s1 = a.s2 = nullptr;
+    a.wd_mask = nullptr;
+    a.broadcast = 1;
+    a.target = static_cast<uint32_t>(comm->world) * call_index;
+    a.timeout_ns = comm_timeout_ns();
+    const int threads = 512;
+    int grid = num_ctas > 0 ? num_ctas : 32;
+    grid = static_cast<int>(std::min<size_t>(grid, std::max<size_t>(1, (count / 8 + threads - 1) / threads)));
+    nvls_broadcast_kernel<<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(a, root);
     count_launch();
     TONY_CUDA_CHECK(cudaGetLastError());
     return TONY_OK;

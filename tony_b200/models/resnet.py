@@ -70,6 +70,14 @@ class ConvBN(nn.Module):
         y = F.conv2d(x, self.weight, self.stride, self.pad, stats)
         return self.bn(y, residual=residual, stats=stats)
 
+    def forward_fork(self, x):
+        """-> (bn(conv(x)), x): the block input also feeds the residual branch; its gradient is merged in the
+        epilogue of this (pointwise) convolution's data-gradient GEMM."""
+        arena = self._arena[0]
+        stats = arena.take(self.weight.shape[0]) if (self.use_stats and arena is not None and self.training) else None
+        y, idt = F.conv1x1_fork(x, self.weight, stats)
+        return self.bn(y, stats=stats), idt
+
 
 class StemConvBN(nn.Module):
     """7x7/2 convolution of the 3-channel image (space-to-depth form) -> BatchNorm -> ReLU."""
@@ -140,6 +148,9 @@ class Bottleneck(nn.Module):
             self.down = nn.Sequential(_conv(cin, cout, 1, stride, device), _bn(cout, device, relu=False))
 
     def forward(self, x):
+        if self.fused and self.down is None and isinstance(self.cb1, ConvBN) and x.requires_grad:
+            y, idt = self.cb1.forward_fork(x)          # identity block: x feeds conv1 AND the residual add
+            return self.cb3(self.cb2(y), residual=idt)
         idt = x if self.down is None else self.down(x)
         if self.fused:      # ReLU and the residual add ride in the BatchNorm kernels
             return self.cb3(self.cb2(self.cb1(x)), residual=idt)

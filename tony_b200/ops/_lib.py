@@ -140,6 +140,9 @@ def _declare(lib) -> None:
                                             c_int, vp]
     lib.tony_symm_allreduce_bf16.argtypes = [POINTER(FusedComm), c_size_t, c_size_t, c_float, c_uint,
                                              c_int, vp]
+    lib.tony_symm_collective.argtypes = [POINTER(FusedComm), c_int, c_int, c_size_t, c_size_t, c_float, c_int,
+                                         c_uint, c_int, vp]
+    lib.tony_nvls_broadcast.argtypes = [POINTER(NvlsComm), c_size_t, c_size_t, c_int, c_uint, c_int, vp]
     lib.tony_symm_barrier.argtypes = [POINTER(FusedComm), c_uint, vp]
     lib.tony_allgather_gemm_bf16.argtypes = [vp, POINTER(c_void_p), vp, vp, c_int, c_int, c_int,
                                              c_int, c_int, c_uint, vp, vp, vp, c_uint, c_int, vp]

@@ -812,6 +812,53 @@ class _Conv2dFn(torch.autograd.Function):
         return dx, dest.finish(out), None, None, None
 
 
+class _PointwiseConvForkFn(torch.autograd.Function):
+    """``(conv1x1(x, w), x)`` as ONE autograd node: the second output is the residual branch of a
+    bottleneck block.  Backward then receives the main path's gradient and the residual branch's gradient
+    together and adds the latter in the epilogue of the data-gradient GEMM (``dx = dy . W + d_residual``)
+    instead of in a separate elementwise kernel over the activation."""
+
+    @staticmethod
+    def forward(ctx, x, weight, stats):
+        x = x.contiguous(memory_format=torch.channels_last)
+        xn = x.permute(0, 2, 3, 1)
+        K, R, S, C = weight.shape
+        N, H, W, _ = xn.shape
+        if stats is None:
+            yn = gemm(xn.reshape(N * H * W, C), weight.view(K, C)).view(N, H, W, K)
+        else:
+            yn = conv2d_nhwc(xn, weight, 1, 0, stats=stats)
+        ctx.save_for_backward(xn, weight)
+        return yn.permute(0, 3, 1, 2), x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, dy, dres):
+        xn, weight = ctx.saved_tensors
+        K, R, S, C = weight.shape
+        N, H, W, _ = xn.shape
+        M = N * H * W
+        dyn = dy.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1).reshape(M, K)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if dres is not None:
+                dr = dres.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1).reshape(M, C)
+                dxn = gemm(dyn, weight.view(K, C), b_mn=True, flags=EPI_RESIDUAL, aux=dr)
+            else:
+                dxn = gemm(dyn, weight.view(K, C), b_mn=True)
+            dx = dxn.view(N, H, W, C).permute(0, 3, 1, 2)
+        dest = _GradDest(weight)
+        out = gemm(dyn, xn.reshape(M, C), a_mn=True, b_mn=True,
+                   out=dest.tensor.view(K, C) if dest.tensor is not None else None,
+                   flags=EPI_ACCUMULATE if dest.accumulate else 0).view(K, R, S, C)
+        return dx, dest.finish(out), None
+
+
+def conv1x1_fork(x, weight, stats: Optional[torch.Tensor] = None):
+    """``(conv2d(x, weight), x)`` for a stride-1 pointwise ``[K, 1, 1, C]`` filter; use the second value
+    as the block's residual input (see ``_PointwiseConvForkFn``)."""
+    return _PointwiseConvForkFn.apply(x, weight, stats)
+
+
 def conv2d(x, weight, stride: int = 1, pad: int = 0, stats: Optional[torch.Tensor] = None):
     """``conv2d`` for a bf16 channels-last ``x`` ``[N, C, H, W]`` and a ``[K, R, S, C]`` (KRSC) filter."""
     return _Conv2dFn.apply(x, weight, stride, pad, stats)

@@ -71,7 +71,10 @@ def main():
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--stem", type=int, default=1)
     ap.add_argument("--md", default="")
+    ap.add_argument("--passes", default="fprop,fprop+stats,dgrad,wgrad")
+    ap.add_argument("--no-lib", action="store_true", help="skip the cuDNN arm")
     a = ap.parse_args()
+    want = set(a.passes.split(","))
     torch.backends.cudnn.benchmark = True
     N = a.batch
     rows = []
@@ -118,8 +121,10 @@ def main():
                                lambda: torch.ops.aten.convolution_backward(dyt, x, wt, None, [s, s], [pad, pad], [1, 1],
                                                                            False, [0, 0], 1, [False, True, False]))
         for pname, (ours, lib) in passes.items():
+            if pname not in want:
+                continue
             t_o = timeit(ours, a.iters)
-            t_l = timeit(lib, a.iters) if lib is not None else None
+            t_l = timeit(lib, a.iters) if (lib is not None and not a.no_lib) else None
             rec = {"layer": name, "count": count, "cin": ci, "cout": co, "k": k, "stride": s, "hw": h, "pass": pname,
                    "ours_us": round(t_o, 1), "cudnn_us": round(t_l, 1) if t_l else None,
                    "ours_tflops": round(flops / t_o / 1e6, 1), "ratio_cudnn_over_ours": round(t_l / t_o, 3) if t_l else None,
@@ -128,7 +133,7 @@ def main():
             rows.append(rec)
             if pname != "fprop+stats":
                 tot["ours"] += count * t_o
-                tot["cudnn"] += count * t_l
+                tot["cudnn"] += count * (t_l or 0.0)
         del x, w, y, yt, dy
     if a.stem:
         x = torch.randn(N, 3, 224, 224, device=dev).to(torch.bfloat16)
@@ -157,7 +162,7 @@ def main():
             print(json.dumps(rec), flush=True)
             rows.append(rec)
     print(json.dumps({"total_weighted_us": {k: round(v) for k, v in tot.items()},
-                      "cudnn_over_ours": round(tot["cudnn"] / tot["ours"], 3), "batch": N}), flush=True)
+                      "cudnn_over_ours": round(tot["cudnn"] / max(tot["ours"], 1e-9), 3), "batch": N}), flush=True)
     if a.md:
         with open(a.md, "w") as f:
             f.write("| layer | x | Cin | Cout | k | s | HW | pass | ours us | cuDNN us | ours TFLOP/s | cuDNN/ours |\n")
