@@ -145,8 +145,11 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
     const uint32_t tP = tmem_base + 2 * ATT_BK + ATT_D;
     const int stride = static_cast<int>(gridDim.x);
 
+    // Producer and MMA warps: the WHOLE warp runs the loop and one elected lane issues, so the operands of
+    // UTMALDG / UTCHMMA / UTCBAR are warp-uniform values in uniform registers (inside `if (lane == 0)` the
+    // compiler wraps each of them in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop, ~25 instructions per MMA).
     if (warp_idx == 0) {
-        if (lane == 0) {
+        {
             uint32_t g = 0;   // running block index across work items
             uint32_t n = 0;
             for (int w = blockIdx.x; w < p.num_items; w += stride, ++n) {
@@ -154,24 +157,33 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
                 const int b = a.bh / p.heads, h = a.bh - b * p.heads;
                 const int row_base = b * p.seq;
                 mbar_wait_relaxed(q_empty, (n & 1) ^ 1);   // every S of the previous item has retired
-                mbar_expect_tx(q_full, ATT_TILE_BYTES);
-                tma_load_2d(&tmap_qkv128, q_full, sQ, h * ATT_D, row_base + a.qt * ATT_BM);
+                if (elect_one()) {
+                    mbar_expect_tx(q_full, ATT_TILE_BYTES);
+                    tma_load_2d(&tmap_qkv128, q_full, sQ, h * ATT_D, row_base + a.qt * ATT_BM);
+                }
+                __syncwarp();
                 for (int j = 0; j < a.nblk; ++j, ++g) {
                     const uint32_t slot = g % ATT_FWD_SLOTS;
                     const uint32_t par = ((g / ATT_FWD_SLOTS) & 1) ^ 1;
                     mbar_wait_relaxed(&k_empty[slot], par);
-                    mbar_expect_tx(&k_full[slot], ATT_HALF_BYTES);
-                    tma_load_2d(&tmap_qkv64, &k_full[slot], sK + slot * ATT_HALF_BYTES,
-                                p.hidden + h * ATT_D, row_base + j * ATT_BK);
+                    if (elect_one()) {
+                        mbar_expect_tx(&k_full[slot], ATT_HALF_BYTES);
+                        tma_load_2d(&tmap_qkv64, &k_full[slot], sK + slot * ATT_HALF_BYTES,
+                                    p.hidden + h * ATT_D, row_base + j * ATT_BK);
+                    }
+                    __syncwarp();
                     mbar_wait_relaxed(&v_empty[slot], par);
-                    mbar_expect_tx(&v_full[slot], ATT_HALF_BYTES);
-                    tma_load_2d(&tmap_qkv64, &v_full[slot], sV + slot * ATT_HALF_BYTES,
-                                2 * p.hidden + h * ATT_D, row_base + j * ATT_BK);
+                    if (elect_one()) {
+                        mbar_expect_tx(&v_full[slot], ATT_HALF_BYTES);
+                        tma_load_2d(&tmap_qkv64, &v_full[slot], sV + slot * ATT_HALF_BYTES,
+                                    2 * p.hidden + h * ATT_D, row_base + j * ATT_BK);
+                    }
+                    __syncwarp();
                 }
             }
         }
     } else if (warp_idx == 1) {
-        if (lane == 0) {
+        {
             // Event loop over two cursors on the flattened (item, block) sequence: the score
             // MMAs run up to two blocks ahead of the P V MMAs; whichever has all its inputs
             // ready is issued, so neither waits behind the other's barrier.
@@ -191,18 +203,23 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
                     bool ok = gs < 2 || mbar_test_wait(&s_free[gs & 1], ((gs - 2) >> 1) & 1);
                     if (ok && js == 0) ok = mbar_test_wait(q_full, ns & 1);
                     if (ok) ok = mbar_test_wait(&k_full[slot], (gs / ATT_FWD_SLOTS) & 1);
+                    ok = __all_sync(0xffffffffu, ok);     // one warp-uniform decision
                     if (ok) {
                         tcgen05_fence_after();
                         const uint64_t dk = make_umma_desc_sw128(smem_u32(sK + slot * ATT_HALF_BYTES), 16, 1024);
                         const uint32_t tS = tmem_base + (gs & 1) * ATT_BK;
+                        const bool last = js + 1 == nblk_s;
+                        if (elect_one()) {
 #pragma unroll
-                        for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tS, dq + k * 2, dk + k * 2, idesc_s, k > 0);
-                        umma_commit(&k_empty[slot]);
-                        umma_commit(&s_full[gs & 1]);
+                            for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tS, dq + k * 2, dk + k * 2, idesc_s, k > 0);
+                            umma_commit(&k_empty[slot]);
+                            umma_commit(&s_full[gs & 1]);
+                            if (last) umma_commit(q_empty);   // Q may be replaced once these MMAs retire
+                        }
+                        __syncwarp();
                         progressed = true;
                         ++gs;
                         if (++js == nblk_s) {
-                            umma_commit(q_empty);   // Q may be replaced once these MMAs retire
                             js = 0;
                             ++ns;
                             ws += stride;
@@ -216,15 +233,19 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
                     bool ok = mbar_test_wait(&p_full[bsel], (gp >> 1) & 1);
                     if (ok) ok = mbar_test_wait(&v_full[slot], (gp / ATT_FWD_SLOTS) & 1);
                     if (ok && jp == 0 && np > 0) ok = mbar_test_wait(o_free, (np - 1) & 1);   // previous O read out
+                    ok = __all_sync(0xffffffffu, ok);
                     if (ok) {
                         tcgen05_fence_after();
                         const uint64_t dv = make_umma_desc_sw128(smem_u32(sV + slot * ATT_HALF_BYTES), 8192, 1024);
+                        if (elect_one()) {
 #pragma unroll
-                        for (int k = 0; k < ATT_BK / 16; ++k)   // A: P from TMEM, 8 columns per k-step; B: 16 key rows = 2048 B
-                            umma_bf16_ts(tO, tP + bsel * (ATT_BK / 2) + k * 8, dv + k * 128, idesc_o,
-                                         (jp > 0 || k > 0) ? 1u : 0u);
-                        umma_commit(&v_empty[slot]);
-                        umma_commit(&pv_done[bsel]);
+                            for (int k = 0; k < ATT_BK / 16; ++k)   // A: P from TMEM, 8 columns per k-step; B: 16 key rows = 2048 B
+                                umma_bf16_ts(tO, tP + bsel * (ATT_BK / 2) + k * 8, dv + k * 128, idesc_o,
+                                             (jp > 0 || k > 0) ? 1u : 0u);
+                            umma_commit(&v_empty[slot]);
+                            umma_commit(&pv_done[bsel]);
+                        }
+                        __syncwarp();
                         progressed = true;
                         ++gp;
                         if (++jp == nblk_p) {
@@ -508,23 +529,29 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
     const uint32_t tdP = tmem_base + ATT_BK;
     const uint32_t tdQ = tmem_base + 2 * ATT_BK;
 
-    if (warp_idx == 0) {
-        if (lane == 0) {
-            mbar_expect_tx(qdo_full, 2 * ATT_TILE_BYTES);
-            tma_load_2d(&tmap_qkv128, qdo_full, sQ, h * ATT_D, row_base + q0);
-            tma_load_2d(&tmap_do128, qdo_full, sdO, h * ATT_D, row_base + q0);
+    if (warp_idx == 0) {   // whole warp in the loop, one elected lane issues (see attention_fwd_kernel)
+        {
+            if (elect_one()) {
+                mbar_expect_tx(qdo_full, 2 * ATT_TILE_BYTES);
+                tma_load_2d(&tmap_qkv128, qdo_full, sQ, h * ATT_D, row_base + q0);
+                tma_load_2d(&tmap_do128, qdo_full, sdO, h * ATT_D, row_base + q0);
+            }
+            __syncwarp();
             for (int i = 0; i < 2 * nblk; ++i) {
                 const int slot = i % ATT_BWD_SLOTS;
                 const uint32_t use = static_cast<uint32_t>(i / ATT_BWD_SLOTS);
                 mbar_wait(&ring_empty[slot], (use & 1) ^ 1);
-                mbar_expect_tx(&ring_full[slot], ATT_HALF_BYTES);
                 const int col = ((i & 1) ? 2 * p.hidden : p.hidden) + h * ATT_D;   // K_j then V_j
-                tma_load_2d(&tmap_qkv64, &ring_full[slot], sRing + slot * ATT_HALF_BYTES, col,
-                            row_base + (i >> 1) * ATT_BK);
+                if (elect_one()) {
+                    mbar_expect_tx(&ring_full[slot], ATT_HALF_BYTES);
+                    tma_load_2d(&tmap_qkv64, &ring_full[slot], sRing + slot * ATT_HALF_BYTES, col,
+                                row_base + (i >> 1) * ATT_BK);
+                }
+                __syncwarp();
             }
         }
     } else if (warp_idx == 1) {
-        if (lane == 0) {
+        {
             const uint32_t idesc_sc = make_idesc_bf16(ATT_BM, ATT_BK, 0, 0);
             const uint32_t idesc_dq = make_idesc_bf16(ATT_BM, ATT_D, 0, 1);
             const uint64_t dq = make_umma_desc_sw128(smem_u32(sQ), 16, 1024);
@@ -538,12 +565,15 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
                 tcgen05_fence_after();
                 const uint64_t dk = make_umma_desc_sw128(smem_u32(sRing + sk * ATT_HALF_BYTES), 16, 1024);
                 const uint64_t dv = make_umma_desc_sw128(smem_u32(sRing + sv * ATT_HALF_BYTES), 16, 1024);
+                if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tS, dq + k * 2, dk + k * 2, idesc_sc, k > 0);
+                    for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tS, dq + k * 2, dk + k * 2, idesc_sc, k > 0);
 #pragma unroll
-                for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tdP, ddo + k * 2, dv + k * 2, idesc_sc, k > 0);
-                umma_commit(&ring_empty[sv]);
-                umma_commit(sc_full);
+                    for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tdP, ddo + k * 2, dv + k * 2, idesc_sc, k > 0);
+                    umma_commit(&ring_empty[sv]);
+                    umma_commit(sc_full);
+                }
+                __syncwarp();
             };
             mbar_wait(qdo_full, 0);
             issue_sc(0);
@@ -558,11 +588,14 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
                 const int sk = (2 * j) % ATT_BWD_SLOTS;
                 const uint64_t dkmn =
                     make_umma_desc_sw128(smem_u32(sRing + sk * ATT_HALF_BYTES), 8192, 1024);
+                if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < ATT_BK / 16; ++k)
-                    umma_bf16(tdQ, dds + k * 2, dkmn + k * 128, idesc_dq, (j > 0 || k > 0) ? 1u : 0u);
-                umma_commit(&ring_empty[sk]);
-                umma_commit(dq_done);
+                    for (int k = 0; k < ATT_BK / 16; ++k)
+                        umma_bf16(tdQ, dds + k * 2, dkmn + k * 128, idesc_dq, (j > 0 || k > 0) ? 1u : 0u);
+                    umma_commit(&ring_empty[sk]);
+                    umma_commit(dq_done);
+                }
+                __syncwarp();
             }
         }
     } else {
@@ -703,25 +736,31 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
     const uint32_t tdV = tmem_base + 2 * ATT_BK;
     const uint32_t tdK = tmem_base + 3 * ATT_BK;
 
-    if (warp_idx == 0) {
-        if (lane == 0) {
-            mbar_expect_tx(kv_full, 2 * ATT_TILE_BYTES);
-            tma_load_2d(&tmap_qkv128, kv_full, sK, p.hidden + h * ATT_D, row_base + k0);
-            tma_load_2d(&tmap_qkv128, kv_full, sV, 2 * p.hidden + h * ATT_D, row_base + k0);
+    if (warp_idx == 0) {   // whole warp in the loop, one elected lane issues (see attention_fwd_kernel)
+        {
+            if (elect_one()) {
+                mbar_expect_tx(kv_full, 2 * ATT_TILE_BYTES);
+                tma_load_2d(&tmap_qkv128, kv_full, sK, p.hidden + h * ATT_D, row_base + k0);
+                tma_load_2d(&tmap_qkv128, kv_full, sV, 2 * p.hidden + h * ATT_D, row_base + k0);
+            }
+            __syncwarp();
             for (int n = 0; n < 2 * nblk; ++n) {
                 const int slot = n % ATT_KV_SLOTS;
                 const uint32_t use = static_cast<uint32_t>(n / ATT_KV_SLOTS);
                 mbar_wait(&ring_empty[slot], (use & 1) ^ 1);
-                mbar_expect_tx(&ring_full[slot], ATT_HALF_BYTES);
                 const int qrow = row_base + (i0 + (n >> 1)) * ATT_BK;
-                if (n & 1)
-                    tma_load_2d(&tmap_do64, &ring_full[slot], sRing + slot * ATT_HALF_BYTES, h * ATT_D, qrow);
-                else
-                    tma_load_2d(&tmap_qkv64, &ring_full[slot], sRing + slot * ATT_HALF_BYTES, h * ATT_D, qrow);
+                if (elect_one()) {
+                    mbar_expect_tx(&ring_full[slot], ATT_HALF_BYTES);
+                    if (n & 1)
+                        tma_load_2d(&tmap_do64, &ring_full[slot], sRing + slot * ATT_HALF_BYTES, h * ATT_D, qrow);
+                    else
+                        tma_load_2d(&tmap_qkv64, &ring_full[slot], sRing + slot * ATT_HALF_BYTES, h * ATT_D, qrow);
+                }
+                __syncwarp();
             }
         }
     } else if (warp_idx == 1) {
-        if (lane == 0) {
+        {
             const uint32_t idesc_sc = make_idesc_bf16(ATT_BM, ATT_BK, 0, 0);
             const uint32_t idesc_acc = make_idesc_bf16(ATT_BM, ATT_D, 0, 1);
             const uint64_t dk = make_umma_desc_sw128(smem_u32(sK), 16, 1024);
@@ -736,11 +775,14 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
                 tcgen05_fence_after();
                 const uint64_t dq = make_umma_desc_sw128(smem_u32(sRing + sq * ATT_HALF_BYTES), 16, 1024);
                 const uint64_t ddo = make_umma_desc_sw128(smem_u32(sRing + sdo * ATT_HALF_BYTES), 16, 1024);
+                if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tSt, dk + k * 2, dq + k * 2, idesc_sc, k > 0);
+                    for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tSt, dk + k * 2, dq + k * 2, idesc_sc, k > 0);
 #pragma unroll
-                for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tdPt, dv + k * 2, ddo + k * 2, idesc_sc, k > 0);
-                umma_commit(sc_full);
+                    for (int k = 0; k < ATT_D / 16; ++k) umma_bf16(tdPt, dv + k * 2, ddo + k * 2, idesc_sc, k > 0);
+                    umma_commit(sc_full);
+                }
+                __syncwarp();
             };
             mbar_wait(kv_full, 0);
             issue_sc(0);
@@ -755,15 +797,18 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
                 const int sq = (2 * n) % ATT_KV_SLOTS, sdo = (2 * n + 1) % ATT_KV_SLOTS;
                 const uint64_t dqmn = make_umma_desc_sw128(smem_u32(sRing + sq * ATT_HALF_BYTES), 8192, 1024);
                 const uint64_t ddomn = make_umma_desc_sw128(smem_u32(sRing + sdo * ATT_HALF_BYTES), 8192, 1024);
+                if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < ATT_BK / 16; ++k)
-                    umma_bf16(tdV, dpt + k * 2, ddomn + k * 128, idesc_acc, (n > 0 || k > 0) ? 1u : 0u);
+                    for (int k = 0; k < ATT_BK / 16; ++k)
+                        umma_bf16(tdV, dpt + k * 2, ddomn + k * 128, idesc_acc, (n > 0 || k > 0) ? 1u : 0u);
 #pragma unroll
-                for (int k = 0; k < ATT_BK / 16; ++k)
-                    umma_bf16(tdK, ddst + k * 2, dqmn + k * 128, idesc_acc, (n > 0 || k > 0) ? 1u : 0u);
-                umma_commit(&ring_empty[sq]);
-                umma_commit(&ring_empty[sdo]);
-                umma_commit(acc_done);
+                    for (int k = 0; k < ATT_BK / 16; ++k)
+                        umma_bf16(tdK, ddst + k * 2, dqmn + k * 128, idesc_acc, (n > 0 || k > 0) ? 1u : 0u);
+                    umma_commit(&ring_empty[sq]);
+                    umma_commit(&ring_empty[sdo]);
+                    umma_commit(acc_done);
+                }
+                __syncwarp();
             }
         }
     } else {

@@ -194,7 +194,7 @@ __device__ __forceinline__ void store_tile_tma(const CUtensorMap* map, int row0,
         st_shared_v4(stg_addr(stg, lane, u), make_uint4(in[4 * u], in[4 * u + 1], in[4 * u + 2], in[4 * u + 3]));
     fence_proxy_async_smem();      // generic-proxy writes -> async-proxy (TMA) read
     __syncwarp();
-    if (lane == 0) {
+    if (elect_one()) {     // converged warp, uniform operands: no per-lane broadcast loop around UTMASTG
         tma_store_2d(map, stg, col0, row0);
         tma_store_commit();
     }
@@ -202,7 +202,7 @@ __device__ __forceinline__ void store_tile_tma(const CUtensorMap* map, int row0,
 
 // before the staging tile is written again: the previous TMA store must have finished reading it
 __device__ __forceinline__ void staging_acquire(int lane) {
-    if (lane == 0) tma_store_wait_read();
+    if (elect_one()) tma_store_wait_read();
     __syncwarp();
 }
 
@@ -493,7 +493,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
             }
-            if (p.tma_store && lane == 0) tma_store_wait_all();   // shared memory stays valid until read
+            if (p.tma_store && elect_one()) tma_store_wait_all();   // shared memory stays valid until read
         }
     }
     else {
@@ -751,7 +751,7 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tmem_empty_bar[as]), 0));
         }
-        if (p.tma_store && lane == 0) tma_store_wait_all();
+        if (p.tma_store && elect_one()) tma_store_wait_all();
     }
 
     __syncwarp();
