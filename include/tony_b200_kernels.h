@@ -317,6 +317,20 @@ int tony_fused_reduce_optim(const tony_fused_comm* comm, size_t begin, size_t co
                             const unsigned char* wd_mask, int broadcast, unsigned int epoch,
                             int num_ctas, void* stream);
 
+/* Dedicated parameter servers (the reference's literal ps/worker split, tony.ps.instances = P,
+ * tony.worker.instances = W on P + W GPUs: tony-core/src/main/resources/tony-default.xml:160-170,204-223):
+ * the bucket is cut into num_owners = P shards; the rank with owner_index in [0, P) reduces every rank's
+ * gradients for its shard (workers contribute, servers keep zero gradients), applies the optimizer to its
+ * shard of the fp32 state and stores the new bf16 weights into its OWN parameter buffer; ranks with
+ * owner_index = -1 (workers) only take part in the two flag phases.  Workers pull the weights in their
+ * next forward with tony_allgather_gemm_bf16 over the P shards. */
+int tony_fused_reduce_optim_owners(const tony_fused_comm* comm, size_t begin, size_t count, float* master,
+                                   float* state1, float* state2, size_t state_offset, int optimizer, float lr,
+                                   float beta1_or_momentum, float beta2, float eps, float weight_decay,
+                                   float bc1, float bc2, float grad_scale, const unsigned char* wd_mask,
+                                   int num_owners, int owner_index, unsigned int epoch, int num_ctas,
+                                   void* stream);
+
 /* Plain collectives on symmetric buffers (validation + hvd.allreduce/broadcast shims).
  * out-of-place all-reduce(sum) * scale of `count` bf16 elements at element offset `begin`
  * of every rank's `grad[]` buffer, result written to every rank's `param[]` buffer. */

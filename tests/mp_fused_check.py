@@ -190,6 +190,40 @@ def main():
     assert torch.isfinite(deep2.float()).all()
     dist.barrier()
 
+    # ---- 5b. dedicated parameter servers: only the LAST rank owns the bucket --------------------
+    torch.manual_seed(11)
+    n2 = 8 * 256 * 12
+    pinit = torch.randn(n2, device=dev) * 0.1
+    comm.param[:n2].copy_(pinit.to(torch.bfloat16))
+    owner = world - 1
+    is_owner = rank == owner
+    m2 = comm.param[:n2].float().clone() if is_owner else torch.zeros(8, device=dev)
+    s1, s2 = torch.zeros_like(m2), torch.zeros_like(m2)
+    refp = comm.param[:n2].float().clone().requires_grad_(True)
+    ropt = torch.optim.AdamW([refp], lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.0)
+    for step in range(1, 3):
+        torch.manual_seed(300 * step + rank)
+        g2 = (torch.randn(n2, device=dev) * 0.3).to(torch.bfloat16)
+        if is_owner:
+            g2.zero_()                       # a server computes no gradient
+        comm.grad[:n2].copy_(g2)
+        gs = g2.float().clone()
+        dist.all_reduce(gs)
+        refp.grad = gs / (world - 1)         # averaged over the workers
+        ropt.step()
+        torch.cuda.synchronize()
+        dist.barrier()
+        _lib.check(lib.tony_fused_reduce_optim_owners(
+            ctypes.byref(comm.c), 0, n2, _lib.ptr(m2), _lib.ptr(s1), _lib.ptr(s2), 0, _lib.OPT_ADAMW, 1e-2, 0.9,
+            0.95, 1e-8, 0.0, 1 - 0.9 ** step, 1 - 0.95 ** step, 1.0 / (world - 1), None, 1, 0 if is_owner else -1,
+            comm.next_epoch(), 16, _lib.cur_stream()), "fused owners")
+        torch.cuda.synchronize()
+        comm.check_status()
+    if is_owner:
+        err = (comm.param[:n2].float() - refp.detach()).abs().max().item()
+        assert err <= 1e-2 * refp.detach().abs().max().item() + 2e-3, f"owner-sharded update err {err}"
+    dist.barrier()
+
     # ---- 6. hvd shim ---------------------------------------------------------------------------
     import tony_b200.parallel.hvd as hvd
 
@@ -199,6 +233,79 @@ def main():
     assert abs(out[0].item() - world * (world + 1) / 2) < 1e-2
     bt = hvd.broadcast(torch.full((17,), float(rank + 5), device=dev), root_rank=0)
     assert abs(bt[3].item() - 5.0) < 1e-2
+
+    # fp32 wire: values a bf16 wire would round (1 + 2^-12) must survive exactly
+    fine = torch.full((4099,), 1.0 + 2.0 ** -12, device=dev)
+    assert torch.equal(hvd.allreduce(fine, average=True), fine), "fp32 all-reduce lost precision"
+    v = torch.randn(3, 1001, device=dev)
+    ref32 = v.clone()
+    dist.all_reduce(ref32)
+    got32 = hvd.allreduce(v, average=False)
+    assert (got32 - ref32).abs().max().item() <= 1e-5 * ref32.abs().max().item() + 1e-6
+    # bf16 wire against NCCL
+    vb = (torch.randn(5000, device=dev) * 0.5).to(torch.bfloat16)
+    refb = vb.float().clone()
+    dist.all_reduce(refb)
+    gotb = hvd.allreduce(vb, average=False).float()
+    assert (gotb - refb).abs().max().item() <= 2e-2 * refb.abs().max().item() + 1e-3
+    assert (gotb - refb).abs().mean().item() <= 4e-3 * refb.abs().max().item() + 1e-4
+    try:
+        hvd.allreduce(torch.ones(4, dtype=torch.int64, device=dev))
+        raise AssertionError("integer all-reduce must be refused")
+    except TypeError:
+        pass
+    # broadcast moves raw bytes: integers, odd sizes, a non-zero root
+    root = world - 1
+    ib = torch.arange(1003, device=dev, dtype=torch.int64) * (rank + 1)
+    gb = hvd.broadcast(ib, root_rank=root)
+    assert torch.equal(gb, torch.arange(1003, device=dev, dtype=torch.int64) * (root + 1))
+    # all-gather / reduce-scatter against NCCL
+    part = torch.randn(7, 33, device=dev) + rank
+    gathered = hvd.allgather(part)
+    ref_parts = [torch.empty_like(part) for _ in range(world)]
+    dist.all_gather(ref_parts, part)
+    assert torch.equal(gathered, torch.cat(ref_parts))
+    full = torch.randn(world * 16, 8, device=dev)
+    rs = hvd.reducescatter(full)
+    ref_full = full.clone()
+    dist.all_reduce(ref_full)
+    assert (rs - ref_full[rank * 16:(rank + 1) * 16]).abs().max().item() <= 1e-5 * ref_full.abs().max().item() + 1e-6
+
+    # broadcast_parameters + DistributedOptimizer: ranks start from different weights, the root's win,
+    # then identical fused steps keep every rank's parameters bit-identical and match an fp32 AdamW
+    # fed the NCCL-averaged gradients
+    torch.manual_seed(50 + rank)
+    net = torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.ReLU(), torch.nn.Linear(128, 32)).to(dev).to(torch.bfloat16)
+    hvd.broadcast_parameters(net.state_dict(), root_rank=0)
+    w0 = net[0].weight.detach().float().clone()
+    chk = w0.clone()
+    dist.broadcast(chk, src=0)
+    assert torch.equal(w0, chk), "broadcast_parameters did not deliver rank 0's weights"
+    ref_net = torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.ReLU(), torch.nn.Linear(128, 32)).to(dev).float()
+    ref_net.load_state_dict({k: v.float() for k, v in net.state_dict().items()})
+    ref_opt = torch.optim.AdamW(ref_net.parameters(), lr=1e-2, weight_decay=0.0)
+    hopt = hvd.DistributedOptimizer(net, optimizer="adamw", lr=1e-2, weight_decay=0.0, bucket_mb=0.01,
+                                    generic_hooks=True)
+    for step in range(3):
+        torch.manual_seed(900 + 10 * step + rank)
+        xb = torch.randn(32, 64, device=dev)
+        net(xb.to(torch.bfloat16)).float().square().mean().backward()
+        hopt.step()
+        hopt.synchronize()
+        ref_net(xb).square().mean().backward()
+        for q in ref_net.parameters():
+            dist.all_reduce(q.grad)
+            q.grad /= world
+        ref_opt.step()
+        ref_opt.zero_grad()
+    torch.cuda.synchronize()
+    hopt.check()
+    mine = net[2].weight.detach().float()
+    same = mine.clone()
+    dist.broadcast(same, src=0)
+    assert torch.equal(mine, same), "ranks diverged under DistributedOptimizer"
+    err = (mine - ref_net[2].weight.detach()).abs().max().item()
+    assert err <= 3e-2 * ref_net[2].weight.detach().abs().max().item() + 2e-3, f"DistributedOptimizer err {err}"
 
     dist.barrier()
     if rank == 0:

@@ -69,3 +69,42 @@ def test_gpt2_chief_failure_restart_resumes_from_checkpoint(tmp_path):
         assert rc == 0, _logs(client)
         text = _logs(client)
         assert "simulating a crash" in text and "resumed from step 4" in text, text[-3000:]
+
+
+def test_horovod_shaped_mnist_job_through_launcher():
+    """examples/horovod-on-tony: a job written against the hvd-shaped API (init / broadcast_parameters /
+    DistributedOptimizer / fp32 metric all-reduce), launched with framework=horovod."""
+    os.environ["TONY_B200_QUIET"] = "1"
+    os.environ.pop("TONY_B200_FAKE_GPUS", None)
+    n = min(2, torch.cuda.device_count())
+    with MiniCluster() as cluster:
+        rc, client = _submit(cluster, "horovod-on-tony/torch_mnist_hvd.py", "--steps 30 --batch 128",
+                             ["tony.application.framework=horovod", f"tony.worker.instances={n}",
+                              "tony.worker.gpus=1"])
+        assert rc == 0, _logs(client)
+        text = _logs(client)
+        assert "done: loss" in text, text[-2000:]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs (1 ps + 1 worker at least)")
+def test_widedeep_dedicated_parameter_servers_through_launcher():
+    """BASELINE config 4's role split: ps tasks on their own GPUs own the shards and run only the fused
+    reduce + update; workers train; the untracked ps tasks are torn down by the AM when the workers end.
+    2 ps + 6 workers on an 8-GPU box, 1 + 1 on a 2-GPU box."""
+    os.environ["TONY_B200_QUIET"] = "1"
+    os.environ.pop("TONY_B200_FAKE_GPUS", None)
+    gpus = torch.cuda.device_count()
+    n_ps, n_w = (2, 6) if gpus >= 8 else (1, gpus - 1 if gpus < 4 else 3)
+    with MiniCluster() as cluster:
+        rc, client = _submit(cluster, "widedeep-ps/widedeep_train.py", "--tiny --steps 12 --batch 512",
+                             ["tony.application.framework=pytorch", f"tony.ps.instances={n_ps}", "tony.ps.gpus=1",
+                              f"tony.worker.instances={n_w}", "tony.worker.gpus=1"])
+        assert rc == 0, _logs(client)
+        st = {f"{t.name}:{t.index}": t.status for t in client.task_infos}
+        assert all(st[f"worker:{i}"] == TaskStatus.SUCCEEDED for i in range(n_w)), st
+        text = _logs(client)
+        assert f"done ({n_ps} ps + {n_w} workers)" in text, text[-3000:]
+        assert "serving done, waiting for teardown" in text
+        import re
+        m = re.search(r"loss ([0-9.]+) -> ([0-9.]+)", text)
+        assert m and float(m.group(2)) < float(m.group(1)), text[-1500:]

@@ -117,6 +117,11 @@ struct FusedArgs {
     uint32_t epoch;
     unsigned long long timeout_ns;
     float ar_scale;  // plain all-reduce: out = sum * ar_scale
+    // Dedicated parameter servers: the bucket is cut into num_owners shards (not world) and only rank
+    // owner_index >= 0 reduces / updates its shard; every rank still joins both flag phases and every
+    // rank's gradient buffer is summed (servers that compute no gradient keep theirs zero).
+    // num_owners == 0: the symmetric default (every rank owns 1/world).
+    int num_owners, owner_index;
 };
 
 // Phase A/C helper: tell every peer we reached `epoch` in flag slot `slot`, then wait for all.
@@ -155,9 +160,11 @@ fused_reduce_optim_kernel(OptHyper h, FusedArgs a) {
     }
 
     // ---- B: reduce my shard from all peers, update, broadcast ---------------------------
-    const size_t chunk = a.count / world;
-    const size_t my_begin = a.begin + static_cast<size_t>(rank) * chunk;
-    const size_t nvec = chunk / 8;
+    const int nsh = a.num_owners > 0 ? a.num_owners : world;
+    const int my = a.num_owners > 0 ? a.owner_index : rank;
+    const size_t chunk = a.count / nsh;
+    const size_t my_begin = a.begin + static_cast<size_t>(my < 0 ? 0 : my) * chunk;
+    const size_t nvec = my < 0 ? 0 : chunk / 8;      // a pure worker owns nothing
     for (size_t v = blockIdx.x * static_cast<size_t>(blockDim.x) + tid; v < nvec;
          v += static_cast<size_t>(gridDim.x) * blockDim.x) {
         const size_t idx = my_begin + v * 8;
@@ -250,6 +257,7 @@ struct NvlsArgs {
     int broadcast;
     uint32_t target;  // world * call_index: every rank added 1 per call to the multicast flag
     unsigned long long timeout_ns;
+    int num_owners, owner_index;   // see FusedArgs
 };
 
 constexpr int NVLS_FLAG_A = 40, NVLS_FLAG_B = 41;  // words of the flag block used by this path
@@ -275,9 +283,11 @@ fused_reduce_optim_nvls_kernel(OptHyper h, NvlsArgs a) {
     if (!sh_flag) return;
 
     // ---- B: in-switch reduction of my shard, optimizer, multicast store of the new weights ---
-    const size_t chunk = a.count / world;
-    const size_t my_begin = a.begin + static_cast<size_t>(rank) * chunk;
-    const size_t nvec = chunk / 8;
+    const int nsh = a.num_owners > 0 ? a.num_owners : world;
+    const int my = a.num_owners > 0 ? a.owner_index : rank;
+    const size_t chunk = a.count / nsh;
+    const size_t my_begin = a.begin + static_cast<size_t>(my < 0 ? 0 : my) * chunk;
+    const size_t nvec = my < 0 ? 0 : chunk / 8;
     const __nv_bfloat16* gmc = static_cast<const __nv_bfloat16*>(a.comm.grad_mc);
     for (size_t v = blockIdx.x * static_cast<size_t>(blockDim.x) + tid; v < nvec;
          v += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -594,7 +604,7 @@ extern "C" int tony_sgd_flat(float* master, float* momentum_buf, const void* gra
 static int launch_fused(const OptHyper& h, FusedArgs& a, int num_ctas, void* stream) {
     a.timeout_ns = comm_timeout_ns();
     const int threads = 512;
-    const size_t nvec = a.count / a.comm.world / 8;
+    const size_t nvec = a.count / (a.num_owners > 0 ? a.num_owners : a.comm.world) / 8;
     // world == 1 is pure HBM streaming: fill the machine.  With peers the kernel is NVLink
     // bound and shares the GPU with backward, so it stays on the caller's CTA budget.
     int grid = a.comm.world == 1 ? device_sm_count() * 4 : (num_ctas > 0 ? num_ctas : 32);
@@ -606,24 +616,29 @@ static int launch_fused(const OptHyper& h, FusedArgs& a, int num_ctas, void* str
     return TONY_OK;
 }
 
-extern "C" int tony_fused_reduce_optim(const tony_fused_comm* comm, size_t begin, size_t count,
-                                       float* master, float* state1, float* state2,
-                                       size_t state_offset, int optimizer, float lr,
-                                       float beta1_or_momentum, float beta2, float eps,
-                                       float weight_decay, float bc1, float bc2, float grad_scale,
-                                       const unsigned char* wd_mask, int broadcast,
-                                       unsigned int epoch, int num_ctas, void* stream) {
+static int fused_reduce_optim_impl(const tony_fused_comm* comm, size_t begin, size_t count, float* master,
+                                   float* state1, float* state2, size_t state_offset, int optimizer, float lr,
+                                   float beta1_or_momentum, float beta2, float eps, float weight_decay, float bc1,
+                                   float bc2, float grad_scale, const unsigned char* wd_mask, int broadcast,
+                                   unsigned int epoch, int num_ctas, void* stream, int num_owners,
+                                   int owner_index) {
     int rc = check_comm(comm, "tony_fused_reduce_optim");
     if (rc) return rc;
-    if (count == 0 || (count % (static_cast<size_t>(comm->world) * 8)) != 0 || (begin % 8) != 0 ||
-        (state_offset % 8) != 0) {
-        set_last_error("tony_fused_reduce_optim", "count must be a multiple of world*8; begin/state_offset of 8");
+    const int nsh = num_owners > 0 ? num_owners : comm->world;
+    if (count == 0 || (count % (static_cast<size_t>(nsh) * 8)) != 0 || (begin % 8) != 0 ||
+        (state_offset % 8) != 0 || num_owners < 0 || num_owners > comm->world ||
+        (num_owners > 0 && (owner_index < -1 || owner_index >= num_owners || broadcast))) {
+        set_last_error("tony_fused_reduce_optim",
+                       "count must be a multiple of shards*8; begin/state_offset of 8; owner shards imply broadcast = 0");
         return TONY_ERR_INVALID;
     }
-    if (!master || !state1 || (optimizer == TONY_OPT_ADAMW && !state2) ||
+    const bool owns = num_owners == 0 || owner_index >= 0;
+    if ((owns && (!master || !state1 || (optimizer == TONY_OPT_ADAMW && !state2))) ||
         (optimizer != TONY_OPT_ADAMW && optimizer != TONY_OPT_SGD))
         return TONY_ERR_INVALID;
     FusedArgs a;
+    a.num_owners = num_owners;
+    a.owner_index = owner_index;
     a.comm = *comm;
     a.begin = begin;
     a.count = count;
@@ -640,6 +655,30 @@ extern "C" int tony_fused_reduce_optim(const tony_fused_comm* comm, size_t begin
                         a, num_ctas, stream);
 }
 
+extern "C" int tony_fused_reduce_optim(const tony_fused_comm* comm, size_t begin, size_t count,
+                                       float* master, float* state1, float* state2,
+                                       size_t state_offset, int optimizer, float lr,
+                                       float beta1_or_momentum, float beta2, float eps,
+                                       float weight_decay, float bc1, float bc2, float grad_scale,
+                                       const unsigned char* wd_mask, int broadcast,
+                                       unsigned int epoch, int num_ctas, void* stream) {
+    return fused_reduce_optim_impl(comm, begin, count, master, state1, state2, state_offset, optimizer, lr,
+                                   beta1_or_momentum, beta2, eps, weight_decay, bc1, bc2, grad_scale, wd_mask,
+                                   broadcast, epoch, num_ctas, stream, 0, 0);
+}
+
+extern "C" int tony_fused_reduce_optim_owners(const tony_fused_comm* comm, size_t begin, size_t count,
+                                              float* master, float* state1, float* state2, size_t state_offset,
+                                              int optimizer, float lr, float beta1_or_momentum, float beta2,
+                                              float eps, float weight_decay, float bc1, float bc2,
+                                              float grad_scale, const unsigned char* wd_mask, int num_owners,
+                                              int owner_index, unsigned int epoch, int num_ctas, void* stream) {
+    if (num_owners <= 0) return TONY_ERR_INVALID;
+    return fused_reduce_optim_impl(comm, begin, count, master, state1, state2, state_offset, optimizer, lr,
+                                   beta1_or_momentum, beta2, eps, weight_decay, bc1, bc2, grad_scale, wd_mask, 0,
+                                   epoch, num_ctas, stream, num_owners, owner_index);
+}
+
 extern "C" int tony_symm_allreduce_bf16(const tony_fused_comm* comm, size_t begin, size_t count,
                                         float scale, unsigned int epoch, int num_ctas,
                                         void* stream) {
@@ -650,6 +689,8 @@ extern "C" int tony_symm_allreduce_bf16(const tony_fused_comm* comm, size_t begi
         return TONY_ERR_INVALID;
     }
     FusedArgs a;
+    a.num_owners = 0;
+    a.owner_index = 0;
     a.comm = *comm;
     a.begin = begin;
     a.count = count;
@@ -669,6 +710,8 @@ extern "C" int tony_symm_barrier(const tony_fused_comm* comm, unsigned int epoch
         if (!comm->flags[r]) return TONY_ERR_INVALID;
     if (!comm->status) return TONY_ERR_INVALID;
     FusedArgs a;
+    a.num_owners = 0;
+    a.owner_index = 0;
     a.comm = *comm;
     a.begin = a.count = a.state_offset = 0;
     a.master = a.s1 = a.s2 = nullptr;
@@ -704,6 +747,8 @@ extern "C" int tony_fused_reduce_optim_nvls(const tony_nvls_comm* comm, size_t b
     }
     if (optimizer >= 0 && (!master || !state1 || (optimizer == TONY_OPT_ADAMW && !state2))) return TONY_ERR_INVALID;
     NvlsArgs a;
+    a.num_owners = 0;
+    a.owner_index = 0;
     a.comm = *comm;
     a.begin = begin;
     a.count = count;
@@ -767,6 +812,8 @@ extern "C" int tony_nvls_broadcast(const tony_nvls_comm* comm, size_t begin, siz
         return TONY_ERR_INVALID;
     }
     NvlsArgs a;
+    a.num_owners = 0;
+    a.owner_index = 0;
     a.comm = *comm;
     a.begin = begin;
     a.count = count;

@@ -40,7 +40,7 @@ class WideDeep(nn.Module):
     NVLink, gradients are reduced into the owners' shards, each owner updates only its rows);
     ``sparse="dense"`` is the replicated nn.Embedding-style layout with dense gradients."""
 
-    def __init__(self, c: WideDeepConfig, device=None, sharded: bool = True, sparse: str = "auto"):
+    def __init__(self, c: WideDeepConfig, device=None, sharded: bool = True, sparse: str = "auto", roles=None):
         super().__init__()
         self.config = c
         if sparse == "auto":
@@ -49,7 +49,8 @@ class WideDeep(nn.Module):
         if sparse == "bag":
             from ..parallel.ps import ShardedEmbeddingBag
 
-            self.bag = ShardedEmbeddingBag(c.num_fields, c.vocab_per_field, c.embed_dim, 8, std=0.01, device=device)
+            self.bag = ShardedEmbeddingBag(c.num_fields, c.vocab_per_field, c.embed_dim, 8, std=0.01, device=device,
+                                           roles=roles)
         else:
             self.deep_tables = nn.ModuleList(Embedding(c.vocab_per_field, c.embed_dim, std=0.01, device=device)
                                              for _ in range(c.num_fields))

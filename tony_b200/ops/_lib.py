@@ -138,6 +138,9 @@ def _declare(lib) -> None:
                                             c_size_t, c_int, c_float, c_float, c_float, c_float,
                                             c_float, c_float, c_float, c_float, vp, c_int, c_uint,
                                             c_int, vp]
+    lib.tony_fused_reduce_optim_owners.argtypes = [POINTER(FusedComm), c_size_t, c_size_t, vp, vp, vp, c_size_t,
+                                                   c_int, c_float, c_float, c_float, c_float, c_float, c_float,
+                                                   c_float, c_float, vp, c_int, c_int, c_uint, c_int, vp]
     lib.tony_symm_allreduce_bf16.argtypes = [POINTER(FusedComm), c_size_t, c_size_t, c_float, c_uint,
                                              c_int, vp]
     lib.tony_symm_collective.argtypes = [POINTER(FusedComm), c_int, c_int, c_size_t, c_size_t, c_float, c_int,

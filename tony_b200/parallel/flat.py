@@ -34,6 +34,22 @@ def _round_up(x: int, m: int) -> int:
 
 
 @dataclass
+class PsRoles:
+    """Dedicated parameter servers: ``owners`` are the global ranks of the ``ps`` tasks (they hold the
+    shards of every ps-sharded weight and run its optimizer), ``workers`` the ranks that compute
+    gradients.  ``None`` everywhere means the symmetric layout (every rank is both)."""
+
+    owners: List[int]
+    workers: List[int]
+
+    def owner_index(self, rank: int) -> int:
+        return self.owners.index(rank) if rank in self.owners else -1
+
+    def is_worker(self, rank: int) -> bool:
+        return rank in self.workers
+
+
+@dataclass
 class Bucket:
     index: int
     begin: int
@@ -42,6 +58,8 @@ class Bucket:
     pending: int = 0
     launched: bool = False
     ps_sharded: bool = False  # parameter-server bucket: weights stay sharded (no broadcast)
+    state_off: int = 0        # this rank's slice of the fp32 optimizer state (set by FusedOptimizer)
+    state_cnt: int = 0
 
 
 class ParamSlot:
@@ -74,7 +92,7 @@ class ParamSlot:
 class FlatParamStore:
     def __init__(self, params: Iterable[Tuple[str, torch.nn.Parameter]], device, group=None,
                  bucket_mb: float = 64.0, no_decay: Optional[Sequence[str]] = None,
-                 ps_sharded: Optional[Iterable[torch.nn.Parameter]] = None):
+                 ps_sharded: Optional[Iterable[torch.nn.Parameter]] = None, roles: Optional[PsRoles] = None):
         named = []
         seen = set()
         for name, p in params:
@@ -88,6 +106,8 @@ class FlatParamStore:
 
         self.device = torch.device(device)
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.roles = roles
+        n_owners = len(roles.owners) if roles else self.world
         bucket_elems = max(ALIGN * self.world, int(bucket_mb * (1 << 20) / 2))
         bucket_align = ALIGN * self.world
 
@@ -113,8 +133,8 @@ class FlatParamStore:
             if id(p) in ps_ids:
                 # a parameter-server weight is a bucket of its own: rank r's 1/world shard of
                 # the bucket is exactly rows [r*N/world, (r+1)*N/world) of the [N, K] matrix
-                if p.dim() != 2 or n % bucket_align or p.shape[0] % self.world:
-                    raise ValueError(f"{name}: a ps-sharded weight must be 2-D with rows % world == 0 "
+                if p.dim() != 2 or n % bucket_align or p.shape[0] % n_owners or n % (ALIGN * n_owners):
+                    raise ValueError(f"{name}: a ps-sharded weight must be 2-D with rows % shards == 0 "
                                      f"and numel % {bucket_align} == 0")
                 close_bucket()
                 cur.ps_sharded = True
@@ -217,6 +237,11 @@ class FlatParamStore:
         self._pending_hook_grads = pending
 
     def shard_range(self, b: Bucket) -> Tuple[int, int]:
+        """(first element, length) of the part of bucket ``b`` whose optimizer state this rank holds."""
+        if b.ps_sharded and self.roles is not None:
+            oi = self.roles.owner_index(self.rank)
+            chunk = b.count // len(self.roles.owners)
+            return (b.begin + oi * chunk, chunk) if oi >= 0 else (b.begin, 0)
         chunk = b.count // self.world
         return b.begin + self.rank * chunk, chunk
 
@@ -244,14 +269,23 @@ class FusedOptimizer:
         self.t = 0
         self._step_open = False
         world = store.world
-        n_shard = store.numel // world
         dev = store.device
-        self.master = torch.empty(n_shard, dtype=torch.float32, device=dev)
+        # this rank's slices of the fp32 state, bucket after bucket (1/world of an all-reduce bucket;
+        # 1/num_owners of a parameter-server bucket on its owners, nothing on pure workers)
+        n_shard = 0
+        for b in store.buckets:
+            _, chunk = store.shard_range(b)
+            b.state_off, b.state_cnt = n_shard, chunk
+            n_shard += chunk
+        n_alloc = max(n_shard, 8)
+        self.master = torch.empty(n_alloc, dtype=torch.float32, device=dev)
         for b in store.buckets:
             lo, chunk = store.shard_range(b)
-            self.master[b.begin // world: b.begin // world + chunk].copy_(store.param_buf[lo: lo + chunk])
-        self.state1 = torch.zeros(n_shard, dtype=torch.float32, device=dev)
-        self.state2 = torch.zeros(n_shard, dtype=torch.float32, device=dev) if self.kind == OPT_ADAMW else None
+            self.master[b.state_off: b.state_off + chunk].copy_(store.param_buf[lo: lo + chunk])
+        self.state1 = torch.zeros(n_alloc, dtype=torch.float32, device=dev)
+        self.state2 = torch.zeros(n_alloc, dtype=torch.float32, device=dev) if self.kind == OPT_ADAMW else None
+        # gradients are averaged over the ranks that produce them (dedicated servers contribute zeros)
+        self.contributors = len(store.roles.workers) if store.roles else world
         self.comm_stream = torch.cuda.Stream(device=dev)
         self._join = torch.cuda.Event()
         store._ready_cb = self._bucket_ready if overlap else None
@@ -271,20 +305,30 @@ class FusedOptimizer:
         else:
             b1, b2, bc1, bc2 = self.momentum, 0.0, 1.0, 1.0
         comm = st.comm
+        gscale = self.grad_scale / self.contributors
+        if b.ps_sharded and st.roles is not None:
+            # dedicated parameter servers: the bucket is cut over the owners only
+            check(_lib.lib().tony_fused_reduce_optim_owners(
+                ctypes.byref(comm.c), b.begin, b.count, _lib.ptr(self.master), _lib.ptr(self.state1),
+                _lib.ptr(self.state2), b.state_off, self.kind, self.lr, b1, b2, self.eps, self.weight_decay,
+                bc1, bc2, gscale, _lib.ptr(st.wd_mask), len(st.roles.owners), st.roles.owner_index(st.rank),
+                comm.next_epoch(), num_ctas, ctypes.c_void_p(stream.cuda_stream)), "tony_fused_reduce_optim_owners")
+            b.launched = True
+            return
         if comm.nvls is not None:
             # in-switch reduction (multimem.ld_reduce) + multicast weight store
             check(_lib.lib().tony_fused_reduce_optim_nvls(
                 ctypes.byref(comm.nvls), b.begin, b.count, _lib.ptr(self.master), _lib.ptr(self.state1),
-                _lib.ptr(self.state2), b.begin // st.world, self.kind, self.lr, b1, b2, self.eps,
-                self.weight_decay, bc1, bc2, self.grad_scale / st.world, _lib.ptr(st.wd_mask),
+                _lib.ptr(self.state2), b.state_off, self.kind, self.lr, b1, b2, self.eps,
+                self.weight_decay, bc1, bc2, gscale, _lib.ptr(st.wd_mask),
                 int(self.broadcast and not b.ps_sharded), comm.next_nvls_call(), num_ctas,
                 ctypes.c_void_p(stream.cuda_stream)), "tony_fused_reduce_optim_nvls")
             b.launched = True
             return
         check(_lib.lib().tony_fused_reduce_optim(
             ctypes.byref(comm.c), b.begin, b.count, _lib.ptr(self.master), _lib.ptr(self.state1),
-            _lib.ptr(self.state2), b.begin // st.world, self.kind, self.lr, b1, b2, self.eps,
-            self.weight_decay, bc1, bc2, self.grad_scale / st.world, _lib.ptr(st.wd_mask),
+            _lib.ptr(self.state2), b.state_off, self.kind, self.lr, b1, b2, self.eps,
+            self.weight_decay, bc1, bc2, gscale, _lib.ptr(st.wd_mask),
             int(self.broadcast and not b.ps_sharded), comm.next_epoch(), num_ctas,
             ctypes.c_void_p(stream.cuda_stream)), "tony_fused_reduce_optim")
         b.launched = True

@@ -58,39 +58,127 @@ def _aligned(n: int, world: int) -> int:
     return (n + q - 1) // q * q
 
 
+def _as_bytes(t: torch.Tensor) -> torch.Tensor:
+    return t.contiguous().view(-1).view(torch.uint8)
+
+
 def allreduce(tensor: torch.Tensor, average: bool = True, name: Optional[str] = None) -> torch.Tensor:
-    """All-reduce any CUDA tensor through the fused kernel (bf16 on the wire, fp32 accumulation)."""
+    """Sum (or mean) of ``tensor`` over all ranks through the peer-memory kernels.
+
+    The wire format follows the tensor: bf16 tensors travel as bf16 (in-switch reduction when NVLS is
+    up), fp32 / fp16 / fp64 tensors travel and accumulate as fp32 - metric averaging
+    (tony-examples/horovod-on-tony/tensorflow2_keras_mnist.py:75) keeps full precision.  Integer and
+    bool tensors are refused: a floating-point sum would silently corrupt them."""
+    if not tensor.is_floating_point():
+        raise TypeError(f"hvd.allreduce: dtype {tensor.dtype} is not supported (floating-point tensors only; "
+                        "cast counters to float or use hvd.allgather / hvd.broadcast)")
     world = size()
     if world == 1:
         return tensor.clone()
     comm = _staging()
-    flat = tensor.reshape(-1)
-    out = torch.empty_like(flat)
     scale = 1.0 / world if average else 1.0
-    for lo in range(0, flat.numel(), STAGING_ELEMS):
-        n = min(STAGING_ELEMS, flat.numel() - lo)
-        npad = _aligned(n, world)
-        comm.grad[:n].copy_(flat[lo:lo + n])
+    if tensor.dtype == torch.bfloat16:
+        flat = tensor.reshape(-1)
+        out = torch.empty_like(flat)
+        for lo in range(0, flat.numel(), STAGING_ELEMS):
+            n = min(STAGING_ELEMS, flat.numel() - lo)
+            npad = _aligned(n, world)
+            comm.grad[:n].copy_(flat[lo:lo + n])
+            if npad > n:
+                comm.grad[n:npad].zero_()
+            comm.allreduce_(0, npad, scale=scale, num_ctas=64)
+            out[lo:lo + n].copy_(comm.param[:n])
+        return out.view_as(tensor)
+    flat = tensor.reshape(-1).float()
+    out = torch.empty_like(flat)
+    grad32, param32 = comm.grad.view(torch.float32), comm.param.view(torch.float32)
+    cap = STAGING_ELEMS // 2
+    for lo in range(0, flat.numel(), cap):
+        n = min(cap, flat.numel() - lo)
+        npad = (n + world * 4 - 1) // (world * 4) * (world * 4)      # bytes % (world * 16) == 0
+        grad32[:n].copy_(flat[lo:lo + n])
         if npad > n:
-            comm.grad[n:npad].zero_()
-        comm.allreduce_(0, npad, scale=scale, num_ctas=64)
-        out[lo:lo + n].copy_(comm.param[:n])
-    return out.view_as(tensor)
+            grad32[n:npad].zero_()
+        comm.collective_("allreduce", 0, npad * 4, fp32=True, scale=scale, num_ctas=64)
+        out[lo:lo + n].copy_(param32[:n])
+    return out.view_as(tensor).to(tensor.dtype)
 
 
 def broadcast(tensor: torch.Tensor, root_rank: int = 0) -> torch.Tensor:
-    """Broadcast = all-reduce in which only the root contributes."""
-    if size() == 1:
+    """The root's ``tensor`` on every rank (any dtype: the payload moves as raw bytes; with NVLS the root
+    publishes it through the switch with one multimem.st per 16 bytes)."""
+    world = size()
+    if world == 1:
         return tensor
-    src = tensor if rank() == root_rank else torch.zeros_like(tensor)
-    return allreduce(src, average=False)
+    comm = _staging()
+    src = _as_bytes(tensor)
+    out = torch.empty_like(src)
+    staging_bytes = comm.param.view(torch.uint8)
+    cap = STAGING_ELEMS * 2
+    for lo in range(0, src.numel(), cap):
+        n = min(cap, src.numel() - lo)
+        npad = (n + world * 16 - 1) // (world * 16) * (world * 16)
+        if rank() == root_rank:
+            staging_bytes[:n].copy_(src[lo:lo + n])
+        comm.broadcast_(0, npad // 2, root=root_rank, num_ctas=32)
+        out[lo:lo + n].copy_(staging_bytes[:n])
+    return out.view(tensor.dtype).view(tensor.shape)
+
+
+def allgather(tensor: torch.Tensor) -> torch.Tensor:
+    """Concatenation of every rank's ``tensor`` along dim 0 (equal shapes on all ranks, any dtype)."""
+    world = size()
+    if world == 1:
+        return tensor.clone()
+    comm = _staging()
+    src = _as_bytes(tensor)
+    n = src.numel()
+    seg = (n + 15) // 16 * 16
+    if seg * world > STAGING_ELEMS * 2:
+        raise ValueError("hvd.allgather: tensor larger than the staging buffer")
+    gbytes, pbytes = comm.grad.view(torch.uint8), comm.param.view(torch.uint8)
+    gbytes[rank() * seg: rank() * seg + n].copy_(src)
+    comm.collective_("allgather", 0, seg * world, num_ctas=32)
+    parts = [pbytes[r * seg: r * seg + n] for r in range(world)]
+    out = torch.cat(parts).view(tensor.dtype)
+    return out.view((world * tensor.shape[0],) + tuple(tensor.shape[1:])) if tensor.dim() else out
+
+
+def reducescatter(tensor: torch.Tensor, average: bool = False) -> torch.Tensor:
+    """This rank's 1/world slice (dim 0) of the sum of ``tensor`` over all ranks (bf16 or fp32 wire)."""
+    if not tensor.is_floating_point():
+        raise TypeError("hvd.reducescatter: floating-point tensors only")
+    world = size()
+    if world == 1:
+        return tensor.clone()
+    if tensor.shape[0] % world:
+        raise ValueError("hvd.reducescatter: dim 0 must be divisible by the number of ranks")
+    comm = _staging()
+    fp32 = tensor.dtype != torch.bfloat16
+    flat = tensor.reshape(-1).float() if fp32 else tensor.reshape(-1)
+    esize = 4 if fp32 else 2
+    n = flat.numel()
+    if (n // world * esize) % 16 or n * esize > STAGING_ELEMS * 2:
+        raise ValueError("hvd.reducescatter: each rank's slice must be a multiple of 16 bytes and fit the staging buffer")
+    g = comm.grad.view(torch.float32) if fp32 else comm.grad
+    pr = comm.param.view(torch.float32) if fp32 else comm.param
+    g[:n].copy_(flat)
+    comm.collective_("reduce_scatter", 0, n * esize, fp32=fp32, scale=(1.0 / world if average else 1.0), num_ctas=64)
+    chunk = n // world
+    out = pr[rank() * chunk:(rank() + 1) * chunk].clone()
+    return out.to(tensor.dtype).view((tensor.shape[0] // world,) + tuple(tensor.shape[1:]))
 
 
 def broadcast_parameters(params, root_rank: int = 0) -> None:
+    """``hvd.broadcast_parameters(model.state_dict(), root_rank=0)``: every tensor takes the root's value
+    (tony-examples/horovod-on-tony/tensorflow2_mnist.py:85-86 broadcast_variables)."""
     items = params.items() if hasattr(params, "items") else params
     for _, p in items:
+        if not torch.is_tensor(p):
+            continue
         with torch.no_grad():
-            p.copy_(broadcast(p.data, root_rank))
+            data = p.data if hasattr(p, "data") else p
+            data.copy_(broadcast(data, root_rank))
 
 
 class DistributedOptimizer:
@@ -114,3 +202,7 @@ class DistributedOptimizer:
 
     def synchronize(self):
         torch.cuda.current_stream().wait_stream(self.opt.comm_stream)
+
+    def check(self):
+        """Raise if a fused collective gave up waiting for a peer (GPU-side hang detection)."""
+        self.store.comm.check_status()

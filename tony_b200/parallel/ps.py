@@ -14,8 +14,11 @@ data-plane mode:
 * pull = ``tony_allgather_gemm_bf16``: the first GEMM that uses the weight in the next forward
   pulls the remote shards over NVLink slab by slab inside the same kernel that multiplies.
 
-Every rank is both a worker and a shard server, so 2 ps + 6 workers of the reference's
-examples map onto 8 symmetric ranks with no idle "ps" GPUs.
+Two layouts.  Symmetric (default): every rank is both a worker and a shard server, so no GPU idles.
+Dedicated (``PsRoles``, the reference's literal ``tony.ps.instances`` / ``tony.worker.instances``
+split): the ps ranks own every shard (weights, optimizer state, embedding rows) and run only the
+fused reduce + update kernels; the worker ranks run forward / backward, push gradients through the
+same kernels and pull weights / rows from the servers over NVLink.
 """
 from __future__ import annotations
 
@@ -50,14 +53,23 @@ class _AgLinearFn(torch.autograd.Function):
         if act not in (None, "none"):
             pre = torch.empty_like(y)
             flags |= EPI_SAVE_PREACT
-        world, rank = comm.world, comm.rank
-        rows = N // world
-        shard_ptrs = (ctypes.c_void_p * world)()
-        for r in range(world):
-            shard_ptrs[r] = int(comm.c.param[r]) + 2 * (slot.offset + r * rows * K)
+        roles = store.roles
+        if roles is None:
+            owners, my_shard = list(range(comm.world)), comm.rank
+        else:
+            # dedicated servers: the shards live on the ps ranks only; a worker owns none of them and
+            # starts its sweep at a shard chosen by its rank so the servers are read evenly
+            owners = roles.owners
+            oi = roles.owner_index(comm.rank)
+            my_shard = oi if oi >= 0 else comm.rank % len(owners)
+        nsh = len(owners)
+        rows = N // nsh
+        shard_ptrs = (ctypes.c_void_p * nsh)()
+        for i, r in enumerate(owners):
+            shard_ptrs[i] = int(comm.c.param[r]) + 2 * (slot.offset + i * rows * K)
         state.epoch += 1
         check(_lib.lib().tony_allgather_gemm_bf16(
-            ptr(x2), shard_ptrs, ptr(weight), ptr(y), M, N, K, rank, world, flags, ptr(bias), ptr(pre),
+            ptr(x2), shard_ptrs, ptr(weight), ptr(y), M, N, K, my_shard, nsh, flags, ptr(bias), ptr(pre),
             ptr(state.flags), state.epoch, state.copy_ctas, cur_stream()), "tony_allgather_gemm_bf16")
         ctx.save_for_backward(x2, weight, pre if pre is not None else y)
         ctx.bias, ctx.act, ctx.x_shape = bias, act, x.shape
@@ -183,14 +195,14 @@ class _EmbBagFn(torch.autograd.Function):
 
 class ShardedEmbeddingBag(nn.Module):
     """``fields`` categorical tables of ``vocab`` rows, each row ``[deep_dim | rest_dim]`` bf16,
-    row ``r`` owned by rank ``r % world`` (csrc/embbag.cu).  ``forward(ids[B, fields])`` returns the
+    row ``r`` owned by the ``r % shards``-th owner (every rank, or the ps ranks of ``roles``; csrc/embbag.cu).  ``forward(ids[B, fields])`` returns the
     concatenated deep activation ``[B, fields*deep_dim]`` and the per-field ``rest`` rows
     ``[B, fields, rest_dim]`` (the "wide" logit contributions).  The tables are NOT ``nn.Parameter``s:
     gradients arrive at the owners as NVLink reductions and ``tony_step`` (called by the Trainer after
     backward) runs AdamW on the local shard only."""
 
     def __init__(self, fields: int, vocab: int, deep_dim: int, rest_dim: int = 8, std: float = 0.01,
-                 device=None, group=None, seed: int = 1234):
+                 device=None, group=None, seed: int = 1234, roles=None):
         super().__init__()
         import torch.distributed as dist
 
@@ -204,7 +216,14 @@ class ShardedEmbeddingBag(nn.Module):
         self.row_elems = deep_dim + rest_dim
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
         self.rank = dist.get_rank(group) if self.world > 1 else 0
-        self.rows_per_shard = (vocab + self.world - 1) // self.world
+        # row r of every field lives on owners[r % len(owners)]: every rank by default, the ps ranks when
+        # the job runs dedicated parameter servers (`roles`)
+        self.roles = roles
+        self.owners = list(roles.owners) if roles is not None else list(range(self.world))
+        self.shard = self.owners.index(self.rank) if self.rank in self.owners else -1
+        self.contributors = len(roles.workers) if roles is not None else self.world
+        nsh = len(self.owners)
+        self.rows_per_shard = (vocab + nsh - 1) // nsh
         n = fields * self.rows_per_shard * self.row_elems
         n_pad = (n + 255) // 256 * 256
         if self.world > 1:
@@ -219,10 +238,10 @@ class ShardedEmbeddingBag(nn.Module):
             tptrs, gptrs = [self.table.data_ptr()], [self.grad.data_ptr()]
         self.grad.zero_()
         comm = _lib.EmbBagComm()
-        comm.rank, comm.world = self.rank, self.world
-        for r in range(self.world):
-            comm.table[r] = tptrs[r]
-            comm.grad[r] = gptrs[r]
+        comm.rank, comm.world = max(self.shard, 0), nsh          # the kernels index shards, not ranks
+        for i, r in enumerate(self.owners):
+            comm.table[i] = tptrs[r]
+            comm.grad[i] = gptrs[r]
         self.comm = comm
         # the same full table on every rank (seeded), of which this rank keeps rows rank::world
         master = torch.zeros(n_pad, dtype=torch.float32, device=device)
@@ -231,8 +250,9 @@ class ShardedEmbeddingBag(nn.Module):
         for f in range(fields):
             gen.manual_seed(seed + f)
             full = torch.randn(vocab, self.row_elems, generator=gen, device=device) * std
-            mine = full[self.rank::self.world]
-            view[f, : mine.shape[0]].copy_(mine)
+            if self.shard >= 0:
+                mine = full[self.shard::nsh]
+                view[f, : mine.shape[0]].copy_(mine)
         self.table.copy_(master.to(torch.bfloat16))
         self.opt = FlatAdamW(master, lr=1e-3, weight_decay=0.0)
         self.barrier = SymmBarrier(device, group)
@@ -250,8 +270,9 @@ class ShardedEmbeddingBag(nn.Module):
         """Owner-side update: wait for every rank's gradient reductions, AdamW on the local shard,
         clear the shard, and release the next step's gathers."""
         self.barrier()
-        self.opt.step(self.grad, self.table, grad_scale=1.0 / self.world)
-        self.grad.zero_()
+        if self.shard >= 0:
+            self.opt.step(self.grad, self.table, grad_scale=1.0 / self.contributors)
+            self.grad.zero_()
         self.barrier()
         self._dirty = False
 

@@ -319,6 +319,32 @@ class SymmComm:
                                                   self.next_epoch(), num_ctas, s),
               "tony_symm_allreduce_bf16")
 
+    COLL = {"allreduce": 0, "reduce_scatter": 1, "allgather": 2, "broadcast": 3}
+
+    def collective_(self, op: str, begin_bytes: int, nbytes: int, *, fp32: bool = False, scale: float = 1.0,
+                    root: int = 0, num_ctas: int = 0, stream=None):
+        """Stand-alone collective over the byte range ``[begin_bytes, begin_bytes + nbytes)`` of every rank's
+        ``grad`` (input) and ``param`` (output) buffers; ``nbytes % (world * 16) == 0``.  See
+        ``tony_symm_collective`` in the C header for the four operations."""
+        s = ctypes.c_void_p(stream.cuda_stream) if stream is not None else _lib.cur_stream()
+        check(_lib.lib().tony_symm_collective(ctypes.byref(self.c), self.COLL[op], int(fp32), begin_bytes, nbytes,
+                                              scale, root, self.next_epoch(), num_ctas, s), f"tony_symm_collective({op})")
+
+    def broadcast_(self, begin: int, count: int, root: int = 0, num_ctas: int = 0, stream=None):
+        """``param[begin:begin+count]`` on every rank = the root's ``param[begin:begin+count]`` (bf16-sized
+        elements; any payload).  With NVLS the root publishes through the switch with multimem.st; otherwise
+        it stages through its ``grad`` buffer and every rank pulls over NVLink."""
+        s = ctypes.c_void_p(stream.cuda_stream) if stream is not None else _lib.cur_stream()
+        if self.world == 1:
+            return
+        if self.nvls is not None:
+            check(_lib.lib().tony_nvls_broadcast(ctypes.byref(self.nvls), begin, count, root, self.next_nvls_call(),
+                                                 num_ctas, s), "tony_nvls_broadcast")
+            return
+        if self.rank == root:
+            self.grad[begin:begin + count].copy_(self.param[begin:begin + count])
+        self.collective_("broadcast", begin * 2, count * 2, root=root, num_ctas=num_ctas, stream=stream)
+
     def close(self):
         if self.world > 1:
             for b in (self.grad_buf, self.param_buf, self.flag_buf):

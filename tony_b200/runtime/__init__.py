@@ -28,11 +28,31 @@ def env_rank_world():
     return rank, world, local
 
 
-def init(backend: Optional[str] = None, device: Optional[str] = None):
-    """Initialise torch.distributed from the TonY env contract; returns (rank, world, device)."""
+def ps_roles():
+    """``PsRoles`` of a job launched with dedicated parameter servers (``tony.ps.instances > 0`` and
+    ``runtime.init(include_ps=True)``), else ``None``.  The launcher exports the all-task numbering as
+    ``TONY_B200_ALL_RANK`` / ``TONY_B200_ALL_WORLD`` / ``TONY_B200_PS_RANKS``."""
+    ps = os.environ.get("TONY_B200_PS_RANKS", "")
+    if not ps or not _state.get("include_ps"):
+        return None
+    from ..parallel.flat import PsRoles
+
+    world = int(os.environ["TONY_B200_ALL_WORLD"])
+    owners = sorted(int(x) for x in ps.split(",") if x != "")
+    return PsRoles(owners=owners, workers=[r for r in range(world) if r not in owners])
+
+
+def init(backend: Optional[str] = None, device: Optional[str] = None, include_ps: bool = False):
+    """Initialise torch.distributed from the TonY env contract; returns (rank, world, device).
+    ``include_ps``: number the ``ps`` tasks into the same process group (dedicated parameter servers on
+    their own GPUs; see ``ps_roles``) instead of the tracked-tasks-only ranks of the reference."""
     import torch
     import torch.distributed as dist
 
+    if include_ps and "TONY_B200_ALL_RANK" in os.environ:
+        os.environ["RANK"] = os.environ["TONY_B200_ALL_RANK"]
+        os.environ["WORLD_SIZE"] = os.environ["TONY_B200_ALL_WORLD"]
+        _state["include_ps"] = True
     rank, world, local = env_rank_world()
     use_cuda = torch.cuda.is_available() and device != "cpu"
     if use_cuda:
@@ -106,7 +126,7 @@ class Trainer:
                  betas=(0.9, 0.999), eps: float = 1e-8, momentum: float = 0.9, bucket_mb: float = 64.0,
                  overlap: bool = True, comm_ctas: int = 32, device=None, group=None,
                  broadcast: bool = True, generic_hooks: bool = False, ps_sharded=None,
-                 cuda_graph: Optional[bool] = None):
+                 cuda_graph: Optional[bool] = None, roles=None):
         import torch
 
         from ..parallel.flat import FlatParamStore, FusedOptimizer
@@ -114,9 +134,15 @@ class Trainer:
         self.torch = torch
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.model = model.to(self.device)
+        # dedicated parameter servers (PsRoles): ps ranks own the shards and run no forward / backward;
+        # every rank launches the bucket kernels in bucket order at step() so the flag epochs line up
+        self.roles = roles
+        self.is_worker = roles is None or roles.is_worker(self._rank())
+        if roles is not None:
+            overlap = False
         self.store = FlatParamStore(model.named_parameters(), self.device, group=group,
                                     bucket_mb=bucket_mb, no_decay=("bias", "ln", "LayerNorm", "norm", "bn"),
-                                    ps_sharded=ps_sharded)
+                                    ps_sharded=ps_sharded, roles=roles)
         for p, uses in getattr(model, "shared_params", {}).items():
             self.store.mark_shared(p, uses)
         if generic_hooks:
@@ -142,6 +168,23 @@ class Trainer:
         self._static_in: Optional[Dict[str, "object"]] = None
         self._static_loss = None
         self._eager_before_capture = 2
+
+    @staticmethod
+    def _rank() -> int:
+        import torch.distributed as dist
+
+        return dist.get_rank() if (dist.is_available() and dist.is_initialized()) else 0
+
+    def serve_step(self):
+        """One step of a dedicated parameter server: no forward / backward, only its side of every
+        bucket's fused reduce + update (its own gradients are zero) and of the sharded tables."""
+        for s in self.store.slots:
+            s.written = 0
+        self.opt.step()
+        for m in self._step_modules:
+            m.tony_step()
+        self.steps += 1
+        return self.torch.zeros((), device=self.device)
 
     def to_device(self, batch_cpu: Dict[str, "object"]):
         """Async H2D of a (pinned) host batch into FRESH device tensors (copy stream; the compute stream
@@ -235,6 +278,8 @@ class Trainer:
     def step_device(self, batch_dev) -> "object":
         """One optimisation step on device-resident inputs; returns the loss tensor (no sync).
         In CUDA-graph mode the returned tensor is overwritten by the next step."""
+        if not self.is_worker:
+            return self.serve_step()
         if self.cuda_graph and self.steps >= self._eager_before_capture:
             return self._graph_step(batch_dev)
         nvtx = self.torch.cuda.nvtx

@@ -88,8 +88,7 @@ def load_latest(directory: str, trainer) -> Optional[int]:
     with torch.no_grad():
         for b in st.buckets:
             lo, chunk = st.shard_range(b)
-            m0 = b.begin // st.world
-            st.param_buf[lo: lo + chunk].copy_(trainer.opt.master[m0: m0 + chunk])
+            st.param_buf[lo: lo + chunk].copy_(trainer.opt.master[b.state_off: b.state_off + chunk])
     mods = [m for m in getattr(trainer, "_step_modules", []) if hasattr(m, "tony_load_state_dict")]
     if len(extra) != len(mods):
         raise ValueError("checkpoint was written for a different set of sharded modules")

@@ -220,6 +220,19 @@ class PyTorchTaskAdapter(TaskAdapter):
         if ex.job_name not in tracked:
             rank = ex.task_index
         env[K.RANK] = str(rank)
+        # numbering over EVERY job type (tracked first, then untracked such as ps): a job whose ps tasks
+        # hold GPUs joins them into the same process group with runtime.init(include_ps=True)
+        everyone = tracked + sorted(j for j in spec if j not in tracked)
+        all_rank, all_world, ps_ranks = 0, 0, []
+        for j in everyone:
+            if j == ex.job_name:
+                all_rank = all_world + ex.task_index
+            if j == K.PS_JOB_NAME:
+                ps_ranks = list(range(all_world, all_world + len(spec[j])))
+            all_world += len(spec[j])
+        env["TONY_B200_ALL_RANK"] = str(all_rank)
+        env["TONY_B200_ALL_WORLD"] = str(all_world)
+        env["TONY_B200_PS_RANKS"] = ",".join(str(r) for r in ps_ranks)
         host, port = init[len(K.COMMUNICATION_BACKEND):].rsplit(":", 1)
         env["MASTER_ADDR"] = host
         env["MASTER_PORT"] = port
