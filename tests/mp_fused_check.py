@@ -283,8 +283,11 @@ def main():
     assert torch.equal(w0, chk), "broadcast_parameters did not deliver rank 0's weights"
     ref_net = torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.ReLU(), torch.nn.Linear(128, 32)).to(dev).float()
     ref_net.load_state_dict({k: v.float() for k, v in net.state_dict().items()})
-    ref_opt = torch.optim.AdamW(ref_net.parameters(), lr=1e-2, weight_decay=0.0)
-    hopt = hvd.DistributedOptimizer(net, optimizer="adamw", lr=1e-2, weight_decay=0.0, bucket_mb=0.01,
+    w2_start = ref_net[2].weight.detach().clone()
+    # SGD: the update is linear in the gradient, so bf16-vs-fp32 gradient noise stays proportionally small
+    # (Adam's sign-like first steps turn a rounding difference of a tiny gradient into a full +-lr move)
+    ref_opt = torch.optim.SGD(ref_net.parameters(), lr=0.05, momentum=0.9, weight_decay=0.0)
+    hopt = hvd.DistributedOptimizer(net, optimizer="sgd", lr=0.05, momentum=0.9, weight_decay=0.0, bucket_mb=0.01,
                                     generic_hooks=True)
     for step in range(3):
         torch.manual_seed(900 + 10 * step + rank)
@@ -304,8 +307,12 @@ def main():
     same = mine.clone()
     dist.broadcast(same, src=0)
     assert torch.equal(mine, same), "ranks diverged under DistributedOptimizer"
-    err = (mine - ref_net[2].weight.detach()).abs().max().item()
-    assert err <= 3e-2 * ref_net[2].weight.detach().abs().max().item() + 2e-3, f"DistributedOptimizer err {err}"
+    refw = ref_net[2].weight.detach()
+    moved = (refw - w2_start).abs().max().item()
+    assert moved > 1e-4, "reference did not move: the comparison would be vacuous"
+    err = (mine - refw).abs()
+    assert err.max().item() <= 0.1 * moved + 1.5e-2 * refw.abs().max().item(), f"DistributedOptimizer max err {err.max().item()}"
+    assert err.mean().item() <= 0.03 * moved + 4e-3 * refw.abs().max().item(), f"DistributedOptimizer mean err {err.mean().item()}"
 
     dist.barrier()
     if rank == 0:
