@@ -1,10 +1,17 @@
 #!/usr/bin/env bash
-# CI entry point (counterpart of the reference's `./gradlew clean check`): build the sm_100a
-# kernel library (nvcc cross-compiles without a GPU), byte-compile every module, run the CPU tiers.
+# CI entry point (counterpart of the reference's `./gradlew clean check`, build.gradle:112-113,290-304):
+# static gate with zero findings, byte-compile every module, build the sm_100a kernel library where a
+# CUDA toolkit exists (nvcc cross-compiles without a GPU), run the CPU tiers, and the GPU tier on a GPU box.
 set -euo pipefail
 cd "$(dirname "$0")"
-python -m tony_b200.csrc.build --selftest
-python -m compileall -q tony_b200 examples tests bench.py __graft_entry__.py
+python tools/lint.py
+python -m compileall -q tony_b200 examples tests tools bench.py __graft_entry__.py
+if command -v nvcc >/dev/null 2>&1 || [ -x /usr/local/cuda/bin/nvcc ]; then
+    python -m tony_b200.csrc.build --selftest
+else
+    echo "ci: no nvcc on this runner - skipping the kernel build (CPU tiers never load the library)"
+    export TONY_B200_NO_BUILD=1
+fi
 python -m pytest tests -x -q -m "not gpu"
 if python -c "import torch,sys; sys.exit(0 if torch.cuda.is_available() else 1)"; then
     python -m pytest tests -x -q -m gpu

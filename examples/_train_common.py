@@ -39,6 +39,13 @@ def train(build_model, make_batch, *, steps, lr, optimizer="adamw", ckpt_dir=Non
             os._exit(17)
     trainer.check()
     dt = time.time() - t0
+    n_steps = max(1, steps - start)
+    grad_bytes = 2 * trainer.store.numel
+    runtime.report_metrics({"STEP_TIME_MS": 1000.0 * dt / n_steps,
+                            "SAMPLES_PER_SEC": n_steps * samples_per_step / dt,
+                            # bytes this rank moves over NVLink per step: it pulls (world-1)/world of its
+                            # gradient shard set and publishes its weight shard to the other ranks
+                            "NVLINK_BYTES_PER_STEP": 2.0 * grad_bytes * (world - 1) / max(world, 1)})
     if rank == 0:
         print(f"done: {(steps - start) * samples_per_step * world / dt:.1f} samples/s over {world} GPUs", flush=True)
     if world > 1:

@@ -280,6 +280,12 @@ def test_callbacks_listener_history_and_first_step(cluster):
     types = [e.type for e in events]
     assert types[0] == "APPLICATION_INITED" and types[-1] == "APPLICATION_FINISHED"
     assert types.count("TASK_STARTED") == 3 and types.count("TASK_FINISHED") == 3
+    # training metrics reported by the user process + the launcher's own latency reach TaskFinished.metrics
+    fin = [e for e in events if e.type == "TASK_FINISHED" and e.event["taskType"] == "worker"]
+    for e in fin:
+        got_m = {m["name"]: m["value"] for m in e.event["metrics"]}
+        assert got_m.get("STEP_TIME_MS") == 12.5 and got_m.get("SAMPLES_PER_SEC") == 2560.0, got_m
+        assert 0 < got_m.get("SUBMIT_TO_FIRST_STEP_MS", -1) < 30000, got_m
     assert any(c.name == "tony.worker.instances" and c.value == "2" for c in history.parse_config(job_dir))
     assert os.path.exists(os.path.join(client.app_dir, K.TONY_FINAL_XML))
 

@@ -251,8 +251,6 @@ def test_packed_attention_matches_sdpa():
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True)])
 def test_gemm_every_kernel_variant(force, a_mn, b_mn):
     """1-CTA 128x128 / 128x256 kernels and the CTA-pair 256x256 kernel, forced through the _ex ABI."""
-    import ctypes
-
     from tony_b200.ops import _lib
     from tony_b200.ops._lib import EPI_BIAS, EPI_RESIDUAL
 
@@ -513,7 +511,6 @@ def test_batchnorm_kernels_stay_inside_their_buffers(M, C):
     """compute-sanitizer is not available on the GPU pool, so the fused BatchNorm entry points are
     called directly on guard-banded buffers with awkward row counts (odd, not foldable, smaller than
     a slab): every output must match the reference and no byte of any guard band may change."""
-    import ctypes
 
     from tony_b200.ops import _lib
     from tony_b200.ops._lib import check, cur_stream, ptr

@@ -109,7 +109,6 @@ def test_widedeep_ps_mode_single_gpu_trains():
 
 
 def test_allgather_gemm_matches_plain_gemm_single_gpu():
-    from tony_b200.ops import functional as F
     from tony_b200.parallel.ps import ShardedLinear
     from tony_b200 import runtime
 

@@ -7,7 +7,6 @@ import urllib.request
 
 from tony_b200.azkaban import tony_job
 from tony_b200.cluster.mini import MiniCluster
-from tony_b200.conf.configuration import read_xml
 from tony_b200.portal.server import Portal
 from tony_b200.proxy.proxy_server import ProxyServer
 

@@ -6,8 +6,6 @@ TestPortAllocation / TestHorovodDriver / TestGpuDeviceInformationParser of the r
 import json
 import os
 import socket
-import subprocess
-import sys
 import time
 import zipfile
 
@@ -58,7 +56,7 @@ def test_default_xml_matches_keys():
     xml = {n: v for n, v, _ in read_xml(DEFAULT_XML_PATH)}
     assert xml == K.DEFAULTS_MAP
     declared = {v for k, v in vars(K).items() if isinstance(v, str) and v.startswith("tony.") and k.isupper()}
-    missing = {k for k in declared if k not in xml and k not in K.KEYS_WITHOUT_DEFAULT and not k.endswith(".") and not k.endswith(".xml")}
+    missing = {k for k in declared if k not in xml and k not in K.KEYS_WITHOUT_DEFAULT and not k.endswith(".") and not k.endswith(".xml")}  # noqa
     assert not missing, missing
     # same defaults as the reference's tony-default.xml for every key it defines
     ref = os.path.join(REF, "tony-core/src/main/resources/tony-default.xml")

@@ -2,7 +2,6 @@
 TestUtils (poll, shell, job-type helpers), TestTaskExecutor, TestTaskStatus, TestEventHandler
 (queue drain / missing job dir), TestTonyClient (task merge / sort), framework plug-ins,
 the reusable-port helper and the docker env file."""
-import json
 import os
 import subprocess
 import sys

@@ -226,7 +226,9 @@ class ApplicationMaster:
 
     def updateMetrics(self, taskType: str, taskIndex: int, metrics: List[dict]):
         with self.lock:
-            self.metrics[U.task_id(taskType, int(taskIndex))] = {m["name"]: float(m["value"]) for m in metrics}
+            tid = U.task_id(taskType, int(taskIndex))
+            cur = self.metrics.setdefault(tid, {})
+            cur.update({m["name"]: float(m["value"]) for m in metrics})
         return None
 
     def markFirstStep(self, taskId: str, timestamp: float):
@@ -236,6 +238,9 @@ class ApplicationMaster:
                 self.timeline.append({"event": "first_step", "task": taskId,
                                       "t_ms": round(1000.0 * (timestamp - self.submit_time), 1)})
                 log(f"first step of {taskId}: {1000.0 * (timestamp - self.submit_time):.0f} ms after submit")
+                # lands in the task's TaskFinished.metrics next to the resource gauges
+                self.metrics.setdefault(taskId, {})["SUBMIT_TO_FIRST_STEP_MS"] = \
+                    round(1000.0 * (float(timestamp) - self.submit_time), 1)
         return None
 
     def getApplicationStatus(self):

@@ -23,7 +23,7 @@ import sys
 import time
 from typing import Dict, List, Optional, Set
 
-from ..am.session import TaskInfo, TaskStatus
+from ..am.session import TaskInfo
 from ..conf import keys as K
 from ..conf.configuration import TonyConfiguration, build_configuration, parse_memory_string
 from ..rpc.server import RpcClient

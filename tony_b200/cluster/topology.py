@@ -78,12 +78,75 @@ def parse_smi_xml(xml_text: str) -> GpuDeviceInformation:
     return info
 
 
+class NvmlSampler:
+    """GPU gauges straight from ``libnvidia-ml.so.1`` through ctypes: a few microseconds per sample
+    instead of forking ``nvidia-smi -x -q`` (about 100 ms, per task, per interval).  Only the calls the
+    monitor needs; any failure makes ``GpuDiscoverer`` fall back to the XML path."""
+
+    class _Util(__import__("ctypes").Structure):
+        _fields_ = [("gpu", __import__("ctypes").c_uint), ("memory", __import__("ctypes").c_uint)]
+
+    class _Mem(__import__("ctypes").Structure):
+        _fields_ = [("total", __import__("ctypes").c_ulonglong), ("free", __import__("ctypes").c_ulonglong),
+                    ("used", __import__("ctypes").c_ulonglong)]
+
+    class _Bar1(__import__("ctypes").Structure):
+        _fields_ = [("bar1Total", __import__("ctypes").c_ulonglong), ("bar1Free", __import__("ctypes").c_ulonglong),
+                    ("bar1Used", __import__("ctypes").c_ulonglong)]
+
+    def __init__(self):
+        import ctypes
+
+        self.ct = ctypes
+        self.lib = ctypes.CDLL("libnvidia-ml.so.1")
+        if self.lib.nvmlInit_v2() != 0:
+            raise OSError("nvmlInit_v2 failed")
+        n = ctypes.c_uint()
+        if self.lib.nvmlDeviceGetCount_v2(ctypes.byref(n)) != 0:
+            raise OSError("nvmlDeviceGetCount_v2 failed")
+        self.handles = []
+        for i in range(n.value):
+            h = ctypes.c_void_p()
+            if self.lib.nvmlDeviceGetHandleByIndex_v2(ctypes.c_uint(i), ctypes.byref(h)) != 0:
+                raise OSError("nvmlDeviceGetHandleByIndex_v2 failed")
+            self.handles.append(h)
+
+    def sample(self) -> GpuDeviceInformation:
+        ct = self.ct
+        info = GpuDeviceInformation()
+        for i, h in enumerate(self.handles):
+            p = PerGpuInfo(minor_number=i)
+            u, m, b, t = self._Util(), self._Mem(), self._Bar1(), ct.c_uint()
+            if self.lib.nvmlDeviceGetUtilizationRates(h, ct.byref(u)) == 0:
+                p.gpu_util_pct = float(u.gpu)
+            if self.lib.nvmlDeviceGetMemoryInfo(h, ct.byref(m)) == 0:
+                p.fb_total_mib, p.fb_used_mib = m.total / 2 ** 20, m.used / 2 ** 20
+            if self.lib.nvmlDeviceGetBAR1MemoryInfo(h, ct.byref(b)) == 0:
+                p.bar1_total_mib, p.bar1_used_mib = b.bar1Total / 2 ** 20, b.bar1Used / 2 ** 20
+            if self.lib.nvmlDeviceGetTemperature(h, ct.c_int(0), ct.byref(t)) == 0:
+                p.temperature_c = float(t.value)
+            mn = ct.c_uint()
+            if self.lib.nvmlDeviceGetMinorNumber(h, ct.byref(mn)) == 0:
+                p.minor_number = int(mn.value)
+            info.gpus.append(p)
+        return info
+
+
 class GpuDiscoverer:
-    """Find the nvidia-smi binary once, then sample it; gives up after repeated errors."""
+    """GPU gauges for the TaskMonitor: NVML in-process when the library loads (TONY_B200_NVML=0 disables),
+    else the reference's way - find the nvidia-smi binary once, fork ``-x -q`` and parse the XML; gives
+    up after repeated errors."""
 
     def __init__(self, exec_path: Optional[str] = None):
         self.binary = self._locate(exec_path)
         self.errors = 0
+        self.nvml: Optional[NvmlSampler] = None
+        if exec_path is None and os.environ.get("TONY_B200_NVML", "1") != "0" \
+                and os.environ.get("TONY_B200_FAKE_GPUS") is None:
+            try:
+                self.nvml = NvmlSampler()
+            except (OSError, AttributeError):
+                self.nvml = None
 
     @staticmethod
     def _locate(exec_path: Optional[str]) -> Optional[str]:
@@ -101,10 +164,17 @@ class GpuDiscoverer:
 
     @property
     def usable(self) -> bool:
-        return self.binary is not None and self.errors < MAX_REPEATED_ERRORS
+        return (self.nvml is not None or self.binary is not None) and self.errors < MAX_REPEATED_ERRORS
 
     def sample(self) -> Optional[GpuDeviceInformation]:
         if not self.usable:
+            return None
+        if self.nvml is not None:
+            try:
+                return self.nvml.sample()
+            except Exception:  # noqa: BLE001 - fall back to the XML path for good
+                self.nvml = None
+        if self.binary is None:
             return None
         try:
             out = subprocess.run([self.binary, "-x", "-q"], capture_output=True, text=True,

@@ -142,7 +142,9 @@ class TaskExecutor:
 
         self.monitor = TaskMonitor(push, self.conf.get_int(K.METRICS_INTERVAL_MS, 5000),
                                    gpu_enabled=self.conf.get_bool(K.GPU_METRICS_ENABLED, True) and bool(gpus),
-                                   gpu_exec_path=self.conf.get(K.GPU_EXEC_PATH), visible_gpus=gpus or None)
+                                   gpu_exec_path=self.conf.get(K.GPU_EXEC_PATH), visible_gpus=gpus or None,
+                                   user_metrics_path=os.path.join(self.mark_dir,
+                                                                  f"metrics.{self.job_name}.{self.task_index}"))
         self.monitor.start()
 
     def setup_ports(self, adapter) -> None:
@@ -196,6 +198,8 @@ class TaskExecutor:
                 if p is not None:
                     p.close()
         self.skew_if_requested()
+        if self.monitor:
+            self.monitor.flush()      # before the result: the AM emits TaskFinished on container exit
         try:
             self.client.call("registerExecutionResult", exitCode=exit_code, jobName=self.job_name,
                              jobIndex=str(self.task_index), sessionId=str(self.session_id))

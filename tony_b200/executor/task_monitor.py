@@ -4,7 +4,11 @@ Same eight gauges as the reference (tony-core/src/main/java/com/linkedin/tony/Ta
 :34-46,101-170): MAX/AVG of MEMORY_BYTES, GPU_UTILIZATION, GPU_FB_MEMORY_USAGE,
 GPU_MAIN_MEMORY_USAGE, running average ``avg += (x - avg) / n`` (:173-177), GPU sampling
 disabled after 10 consecutive nvidia-smi errors (:160-169).  Extended with the first-step
-marker so the launcher can report submit-to-first-step latency.
+marker so the launcher can report submit-to-first-step latency, and with the training metrics the
+user process reports through ``tony_b200.runtime.report_metrics`` (STEP_TIME_MS, SAMPLES_PER_SEC,
+NVLINK_BYTES_PER_STEP, ...): they travel the same updateMetrics RPC and end up in
+``TaskFinished.metrics`` (tony-core/src/main/avro/TaskFinished.avsc; emission at
+tony-core/src/main/java/com/linkedin/tony/ApplicationMaster.java:1246-1258).
 """
 from __future__ import annotations
 
@@ -59,8 +63,10 @@ def process_tree_rss_bytes(root_pid: int) -> int:
 class TaskMonitor:
     def __init__(self, push: Callable[[Dict[str, float]], None], interval_ms: int = 5000,
                  gpu_enabled: bool = True, gpu_exec_path: Optional[str] = None,
-                 visible_gpus: Optional[List[int]] = None, pid: Optional[int] = None):
+                 visible_gpus: Optional[List[int]] = None, pid: Optional[int] = None,
+                 user_metrics_path: Optional[str] = None):
         self.push = push
+        self.user_metrics_path = user_metrics_path
         self.interval_s = max(0.05, interval_ms / 1000.0)
         self.pid = pid or os.getpid()
         self.visible_gpus = visible_gpus
@@ -84,6 +90,27 @@ class TaskMonitor:
             except Exception:  # noqa: BLE001 - monitoring must never kill the task
                 pass
 
+    def read_user_metrics(self) -> None:
+        """Merge ``name=value`` lines the user process wrote (atomically) into the pushed gauges."""
+        if not self.user_metrics_path:
+            return
+        try:
+            with open(self.user_metrics_path) as f:
+                for line in f:
+                    k, _, v = line.strip().partition("=")
+                    if k and v:
+                        self.metrics[k] = float(v)
+        except (OSError, ValueError):
+            pass
+
+    def flush(self) -> None:
+        """Final push at task end, so a job shorter than one interval still reports its metrics."""
+        try:
+            self.read_user_metrics()
+            self.push(dict(self.metrics))
+        except Exception:  # noqa: BLE001
+            pass
+
     def set_max(self, name: str, value: float) -> None:
         if value > self.metrics[name]:
             self.metrics[name] = value
@@ -93,6 +120,7 @@ class TaskMonitor:
 
     def refresh(self, gpu_info: Optional[GpuDeviceInformation] = None, rss: Optional[int] = None) -> None:
         self.num_refreshes += 1
+        self.read_user_metrics()
         mem = process_tree_rss_bytes(self.pid) if rss is None else rss
         self.set_max(MAX_MEMORY_BYTES, mem)
         self.set_avg(AVG_MEMORY_BYTES, mem)

@@ -10,7 +10,6 @@ broadcast kernel, overlapped with backward.
 """
 from __future__ import annotations
 
-from typing import Optional
 
 import torch
 from torch import nn

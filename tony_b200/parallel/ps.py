@@ -195,7 +195,8 @@ class _EmbBagFn(torch.autograd.Function):
 
 class ShardedEmbeddingBag(nn.Module):
     """``fields`` categorical tables of ``vocab`` rows, each row ``[deep_dim | rest_dim]`` bf16,
-    row ``r`` owned by the ``r % shards``-th owner (every rank, or the ps ranks of ``roles``; csrc/embbag.cu).  ``forward(ids[B, fields])`` returns the
+    row ``r`` owned by the ``r % shards``-th owner (every rank, or the ps ranks of ``roles``;
+    csrc/embbag.cu).  ``forward(ids[B, fields])`` returns the
     concatenated deep activation ``[B, fields*deep_dim]`` and the per-field ``rest`` rows
     ``[B, fields, rest_dim]`` (the "wide" logit contributions).  The tables are NOT ``nn.Parameter``s:
     gradients arrive at the owners as NVLink reductions and ``tony_step`` (called by the Trainer after

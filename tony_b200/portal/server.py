@@ -198,14 +198,14 @@ class Portal:
             return 200, json.dumps([asdict(x) for x in data]), "application/json"
         if kind == "config":
             rows = [[e(c.name), e(c.value), str(c.final).lower(), e(c.source)] for c in data]
-            return 200, self._page(f"Configuration of {job_id}", ["Name", "Value", "Final", "Source"], rows), "text/html; charset=utf-8"
+            return 200, self._page(f"Configuration of {job_id}", ["Name", "Value", "Final", "Source"], rows), "text/html; charset=utf-8"  # noqa
         if kind == "jobs":
             rows = [[e(ev.type), e(json.dumps({k: v for k, v in ev.event.items() if k != '__type__'})),
                      self._ts(ev.timestamp)] for ev in data]
             return 200, self._page(f"Events of {job_id}", ["Type", "Event", "Timestamp"], rows), "text/html; charset=utf-8"
         rows = [[e(l.task_type), str(l.task_index), e(l.host), e(l.container_id),
                  f"<a href='{e(l.url)}'>{e(l.url)}</a>"] for l in data]
-        return 200, self._page(f"Logs of {job_id}", ["Task", "Index", "Host", "Container", "Log"], rows), "text/html; charset=utf-8"
+        return 200, self._page(f"Logs of {job_id}", ["Task", "Index", "Host", "Container", "Log"], rows), "text/html; charset=utf-8"  # noqa
 
 
 def main(argv=None) -> int:

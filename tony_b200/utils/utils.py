@@ -21,7 +21,7 @@ from dataclasses import dataclass, field
 from typing import Callable, Dict, Iterable, List, Optional
 
 from ..conf import keys as K
-from ..conf.configuration import TonyConfiguration, parse_memory_string
+from ..conf.configuration import TonyConfiguration
 
 
 @dataclass

@@ -8,7 +8,6 @@ import argparse
 import collections
 import csv
 import re
-import sys
 
 
 def main():

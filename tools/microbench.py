@@ -53,12 +53,12 @@ b = torch.zeros(H, device=dev, dtype=torch.bfloat16, requires_grad=True)
 dy = torch.randn(rows, H, device=dev).to(torch.bfloat16)
 report("layernorm_fwd 16384x1024", rows * H * 2 * 2, timeit(lambda: F.layer_norm(x.detach(), g.detach(), b.detach(), 1e-5)))
 y = F.layer_norm(x, g, b, 1e-5)
-report("layernorm_bwd 16384x1024 (+finalize)", rows * H * 2 * 3, timeit(lambda: torch.autograd.grad(y, (x, g, b), dy, retain_graph=True)))
+report("layernorm_bwd 16384x1024 (+finalize)", rows * H * 2 * 3, timeit(lambda: torch.autograd.grad(y, (x, g, b), dy, retain_graph=True)))  # noqa
 ref_ln = torch.nn.functional.layer_norm
 xr = x.detach().clone().requires_grad_(True)
 gr, br = g.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)
 yr = ref_ln(xr, (H,), gr, br, 1e-5)
-report("ATen layer_norm bwd 16384x1024 (stock)", rows * H * 2 * 3, timeit(lambda: torch.autograd.grad(yr, (xr, gr, br), dy, retain_graph=True)))
+report("ATen layer_norm bwd 16384x1024 (stock)", rows * H * 2 * 3, timeit(lambda: torch.autograd.grad(yr, (xr, gr, br), dy, retain_graph=True)))  # noqa
 
 for cols in (1024, 4096):
     m = torch.randn(rows, cols, device=dev).to(torch.bfloat16)

@@ -1,4 +1,3 @@
-import os, sys
 from cuda import cuda
 def ck(r):
     err = r[0]
@@ -12,7 +11,7 @@ for d in range(n):
     dev = ck(cuda.cuDeviceGet(d))
     mc = ck(cuda.cuDeviceGetAttribute(cuda.CUdevice_attribute.CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev))
     fab = ck(cuda.cuDeviceGetAttribute(cuda.CUdevice_attribute.CU_DEVICE_ATTRIBUTE_HANDLE_TYPE_FABRIC_SUPPORTED, dev))
-    fd = ck(cuda.cuDeviceGetAttribute(cuda.CUdevice_attribute.CU_DEVICE_ATTRIBUTE_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR_SUPPORTED, dev))
+    fd = ck(cuda.cuDeviceGetAttribute(cuda.CUdevice_attribute.CU_DEVICE_ATTRIBUTE_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR_SUPPORTED, dev))  # noqa
     print(f"dev {d}: multicast_supported={mc} fabric={fab} posix_fd={fd}")
 dev0 = ck(cuda.cuDeviceGet(0))
 ctx = ck(cuda.cuDevicePrimaryCtxRetain(dev0))

@@ -15,7 +15,7 @@ for M, N, K in shapes:
     c = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
     for name, L in libs.items():
         def run():
-            L.tony_gemm_bf16(ptr(a), ptr(b), ptr(c), M, N, K, 0, 0, K, K, N, 0, 1.0, None, None, 0, None, ptr(ws), ws.numel(), cur_stream())
+            L.tony_gemm_bf16(ptr(a), ptr(b), ptr(c), M, N, K, 0, 0, K, K, N, 0, 1.0, None, None, 0, None, ptr(ws), ws.numel(), cur_stream())  # noqa
         for _ in range(5): run()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
