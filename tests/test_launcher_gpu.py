@@ -108,3 +108,16 @@ def test_widedeep_dedicated_parameter_servers_through_launcher():
         import re
         m = re.search(r"loss ([0-9.]+) -> ([0-9.]+)", text)
         assert m and float(m.group(2)) < float(m.group(1)), text[-1500:]
+
+
+def test_nvml_sampler_reports_every_gpu():
+    """The in-process NVML path the TaskMonitor uses instead of forking nvidia-smi."""
+    from tony_b200.cluster.topology import GpuDiscoverer
+
+    os.environ.pop("TONY_B200_FAKE_GPUS", None)
+    d = GpuDiscoverer()
+    assert d.nvml is not None, "libnvidia-ml.so.1 did not load on a GPU box"
+    info = d.sample()
+    assert info is not None and len(info.gpus) == torch.cuda.device_count()
+    g = info.gpus[0]
+    assert g.fb_total_mib > 100_000 and 0 <= g.gpu_util_pct <= 100 and g.bar1_total_mib > 0

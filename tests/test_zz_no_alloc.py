@@ -85,3 +85,34 @@ def test_static_scratch_colsum_rejects_oversized_input():
     assert rc == 0, lib.tony_last_error()
     torch.cuda.synchronize()
     assert out.float().min().item() == 64 and out.float().max().item() == 64
+
+
+def test_static_scratch_colsum_allocates_nothing_and_handles_strided_rows():
+    """The reason this entry point exists: after its first call on a device (which resolves the built-in
+    array's address) further calls must not change the device's free memory at all.  Also a row stride
+    wider than the row (a column slice of a bigger matrix), and the argument checks a caller without any
+    error channel but the return code relies on."""
+    lib = _abi()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    torch.manual_seed(1)
+    big = (torch.randn(1000, 2048, device=dev) * 0.5).to(torch.bfloat16)
+    x = big[:, 256:256 + 1024]                      # ld = 2048 > cols = 1024, 16-byte aligned start
+    out = torch.empty(1024, dtype=torch.bfloat16, device=dev)
+    assert lib.tony_colsum_bf16_static(x.data_ptr(), 1000, 1024, x.stride(0), out.data_ptr(), 0, stream) == 0
+    torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info(dev)[0]
+    for _ in range(3):
+        rc = lib.tony_colsum_bf16_static(x.data_ptr(), 1000, 1024, x.stride(0), out.data_ptr(), 0, stream)
+        assert rc == 0, lib.tony_last_error()
+    torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info(dev)[0] == free_before, "the allocation-free entry point changed free memory"
+    _close(out, x.float().sum(0))
+    # refused, with TONY_ERR_INVALID (1): a column count / stride that is not a multiple of 8, a
+    # misaligned base pointer, null pointers
+    ERR_INVALID = 1
+    assert lib.tony_colsum_bf16_static(x.data_ptr(), 1000, 1020, x.stride(0), out.data_ptr(), 0, stream) == ERR_INVALID
+    assert lib.tony_colsum_bf16_static(x.data_ptr(), 1000, 1024, 2044, out.data_ptr(), 0, stream) == ERR_INVALID
+    assert lib.tony_colsum_bf16_static(x.data_ptr() + 2, 1000, 1024, x.stride(0), out.data_ptr(), 0, stream) == ERR_INVALID
+    assert lib.tony_colsum_bf16_static(None, 1000, 1024, x.stride(0), out.data_ptr(), 0, stream) == ERR_INVALID
+    assert lib.tony_colsum_bf16_static(x.data_ptr(), 1000, 1024, x.stride(0), None, 0, stream) == ERR_INVALID
