@@ -67,11 +67,15 @@ struct GemmParams {
     int rowsum_accumulate;
     float* rowsum_ws;              // split-K: partial row sums [splits][M]
     int tma_store;                 // epilogue writes C / aux_out with TMA tensor stores (UTMASTG)
+    int group_m;                   // m-blocks per n-sweep of the tile order
 };
 
 __device__ __forceinline__ void tile_coords(const GemmParams& p, int tile, int& m_blk, int& n_blk) {
-    // grouped ordering: 16 m-blocks share each sweep over n so A stays L2 resident
-    constexpr int GROUP_M = 16;
+    // grouped ordering: group_m m-blocks share each sweep over n so A stays L2 resident (16 by default;
+    // the all-gather GEMM uses 64 so that several waves of tiles run on the local weight shard before
+    // the first remote slab is needed - with 16 the sweep reached the remote n-blocks within the first
+    // two waves and the gather was exposed, not hidden)
+    const int GROUP_M = p.group_m;
     const int per_group = GROUP_M * p.num_n_blocks;
     const int group = tile / per_group;
     const int within = tile - group * per_group;
@@ -1148,6 +1152,7 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
 
     GemmParams p;
     p.tma_store = use_tma_store;
+    p.group_m = ag ? 64 : 16;
     p.M = M;
     p.N = N;
     p.K = K;

@@ -136,6 +136,11 @@ __device__ __forceinline__ bool arrive_and_wait_all(const FusedArgs& a, int slot
     return ok;
 }
 
+// U = 16-byte vectors per thread per loop trip.  The peer loads of one vector take microseconds over
+// NVLink; with one vector in flight per thread the 32 CTAs this kernel is allowed next to the backward
+// GEMMs moved ~80 GB/s per direction (measured, 2 ranks).  U vectors x `world` peers of loads are issued
+// before the first is consumed (U = 4 / 2 / 1 for world <= 2 / 4 / 8 keeps it within the register file).
+template <int U>
 __global__ void __launch_bounds__(512)
 fused_reduce_optim_kernel(OptHyper h, FusedArgs a) {
     __shared__ int sh_flag;
@@ -165,50 +170,63 @@ fused_reduce_optim_kernel(OptHyper h, FusedArgs a) {
     const size_t chunk = a.count / nsh;
     const size_t my_begin = a.begin + static_cast<size_t>(my < 0 ? 0 : my) * chunk;
     const size_t nvec = my < 0 ? 0 : chunk / 8;      // a pure worker owns nothing
-    for (size_t v = blockIdx.x * static_cast<size_t>(blockDim.x) + tid; v < nvec;
-         v += static_cast<size_t>(gridDim.x) * blockDim.x) {
-        const size_t idx = my_begin + v * 8;
-        uint4 gv[TONY_MAX_RANKS];
+    constexpr int MAXW = U == 4 ? 2 : (U == 2 ? 4 : TONY_MAX_RANKS);   // peers this instantiation can hold
+    const size_t tstride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (size_t v0 = blockIdx.x * static_cast<size_t>(blockDim.x) + tid; v0 < nvec; v0 += tstride * U) {
+        uint4 gv[U][MAXW];
 #pragma unroll
-        for (int j = 0; j < TONY_MAX_RANKS; ++j) {
-            if (j < world) {
-                int r = rank + j;
-                if (r >= world) r -= world;
-                gv[j] = ld_global_v4(static_cast<const __nv_bfloat16*>(a.comm.grad[r]) + idx);
-            }
-        }
-        float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int u = 0; u < U; ++u) {
+            const size_t v = v0 + u * tstride;
+            if (v < nvec) {
+                const size_t idx = my_begin + v * 8;
 #pragma unroll
-        for (int j = 0; j < TONY_MAX_RANKS; ++j) {
-            if (j < world) {
-                float t[8];
-                unpack8f(gv[j], t);
-#pragma unroll
-                for (int k = 0; k < 8; ++k) g[k] += t[k];
-            }
-        }
-        uint4 w;
-        if (h.optimizer >= 0) {
-            const size_t si = a.state_offset + v * 8;
-            const float wd = (a.wd_mask == nullptr || a.wd_mask[idx >> 8]) ? h.weight_decay : 0.f;
-            w = optim_update8(h, a.master, a.s1, a.s2, si, g, wd);
-        } else {
-            w.x = pack_bf16x2(g[0] * a.ar_scale, g[1] * a.ar_scale);
-            w.y = pack_bf16x2(g[2] * a.ar_scale, g[3] * a.ar_scale);
-            w.z = pack_bf16x2(g[4] * a.ar_scale, g[5] * a.ar_scale);
-            w.w = pack_bf16x2(g[6] * a.ar_scale, g[7] * a.ar_scale);
-        }
-        if (a.broadcast) {
-#pragma unroll
-            for (int j = 0; j < TONY_MAX_RANKS; ++j) {
-                if (j < world) {
-                    int r = rank + j;
-                    if (r >= world) r -= world;
-                    st_global_v4(static_cast<__nv_bfloat16*>(a.comm.param[r]) + idx, w);
+                for (int j = 0; j < MAXW; ++j) {
+                    if (j < world) {
+                        int r = rank + j;
+                        if (r >= world) r -= world;
+                        gv[u][j] = ld_global_v4(static_cast<const __nv_bfloat16*>(a.comm.grad[r]) + idx);
+                    }
                 }
             }
-        } else {
-            st_global_v4(static_cast<__nv_bfloat16*>(a.comm.param[rank]) + idx, w);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t v = v0 + u * tstride;
+            if (v >= nvec) break;
+            const size_t idx = my_begin + v * 8;
+            float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int j = 0; j < MAXW; ++j) {
+                if (j < world) {
+                    float t[8];
+                    unpack8f(gv[u][j], t);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) g[k] += t[k];
+                }
+            }
+            uint4 w;
+            if (h.optimizer >= 0) {
+                const size_t si = a.state_offset + v * 8;
+                const float wd = (a.wd_mask == nullptr || a.wd_mask[idx >> 8]) ? h.weight_decay : 0.f;
+                w = optim_update8(h, a.master, a.s1, a.s2, si, g, wd);
+            } else {
+                w.x = pack_bf16x2(g[0] * a.ar_scale, g[1] * a.ar_scale);
+                w.y = pack_bf16x2(g[2] * a.ar_scale, g[3] * a.ar_scale);
+                w.z = pack_bf16x2(g[4] * a.ar_scale, g[5] * a.ar_scale);
+                w.w = pack_bf16x2(g[6] * a.ar_scale, g[7] * a.ar_scale);
+            }
+            if (a.broadcast) {
+#pragma unroll
+                for (int j = 0; j < MAXW; ++j) {
+                    if (j < world) {
+                        int r = rank + j;
+                        if (r >= world) r -= world;
+                        st_global_v4(static_cast<__nv_bfloat16*>(a.comm.param[r]) + idx, w);
+                    }
+                }
+            } else {
+                st_global_v4(static_cast<__nv_bfloat16*>(a.comm.param[rank]) + idx, w);
+            }
         }
     }
 
@@ -289,26 +307,38 @@ fused_reduce_optim_nvls_kernel(OptHyper h, NvlsArgs a) {
     const size_t my_begin = a.begin + static_cast<size_t>(my < 0 ? 0 : my) * chunk;
     const size_t nvec = my < 0 ? 0 : chunk / 8;
     const __nv_bfloat16* gmc = static_cast<const __nv_bfloat16*>(a.comm.grad_mc);
-    for (size_t v = blockIdx.x * static_cast<size_t>(blockDim.x) + tid; v < nvec;
-         v += static_cast<size_t>(gridDim.x) * blockDim.x) {
-        const size_t idx = my_begin + v * 8;
-        const uint4 sum = multimem_ld_reduce_bf16x8(gmc + idx);
-        float g[8];
-        unpack8f(sum, g);
-        uint4 w;
-        if (h.optimizer >= 0) {
-            const float wd = (a.wd_mask == nullptr || a.wd_mask[idx >> 8]) ? h.weight_decay : 0.f;
-            w = optim_update8(h, a.master, a.s1, a.s2, a.state_offset + v * 8, g, wd);
-        } else {
-            w.x = pack_bf16x2(g[0] * h.grad_scale, g[1] * h.grad_scale);
-            w.y = pack_bf16x2(g[2] * h.grad_scale, g[3] * h.grad_scale);
-            w.z = pack_bf16x2(g[4] * h.grad_scale, g[5] * h.grad_scale);
-            w.w = pack_bf16x2(g[6] * h.grad_scale, g[7] * h.grad_scale);
+    // four in-switch reductions in flight per thread (each is a round trip through the NVSwitch)
+    constexpr int U = 4;
+    const size_t tstride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (size_t v0 = blockIdx.x * static_cast<size_t>(blockDim.x) + tid; v0 < nvec; v0 += tstride * U) {
+        uint4 sum[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t v = v0 + u * tstride;
+            if (v < nvec) sum[u] = multimem_ld_reduce_bf16x8(gmc + my_begin + v * 8);
         }
-        if (a.broadcast)
-            multimem_st_bf16x8(static_cast<__nv_bfloat16*>(a.comm.param_mc) + idx, w);
-        else
-            st_global_v4(static_cast<__nv_bfloat16*>(a.comm.param_local) + idx, w);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t v = v0 + u * tstride;
+            if (v >= nvec) break;
+            const size_t idx = my_begin + v * 8;
+            float g[8];
+            unpack8f(sum[u], g);
+            uint4 w;
+            if (h.optimizer >= 0) {
+                const float wd = (a.wd_mask == nullptr || a.wd_mask[idx >> 8]) ? h.weight_decay : 0.f;
+                w = optim_update8(h, a.master, a.s1, a.s2, a.state_offset + v * 8, g, wd);
+            } else {
+                w.x = pack_bf16x2(g[0] * h.grad_scale, g[1] * h.grad_scale);
+                w.y = pack_bf16x2(g[2] * h.grad_scale, g[3] * h.grad_scale);
+                w.z = pack_bf16x2(g[4] * h.grad_scale, g[5] * h.grad_scale);
+                w.w = pack_bf16x2(g[6] * h.grad_scale, g[7] * h.grad_scale);
+            }
+            if (a.broadcast)
+                multimem_st_bf16x8(static_cast<__nv_bfloat16*>(a.comm.param_mc) + idx, w);
+            else
+                st_global_v4(static_cast<__nv_bfloat16*>(a.comm.param_local) + idx, w);
+        }
     }
 
     // ---- C: last CTA out publishes "done" and waits for every rank's "done" ------------------
@@ -610,7 +640,13 @@ static int launch_fused(const OptHyper& h, FusedArgs& a, int num_ctas, void* str
     int grid = a.comm.world == 1 ? device_sm_count() * 4 : (num_ctas > 0 ? num_ctas : 32);
     grid = static_cast<int>(std::min<size_t>(grid, std::max<size_t>(1, (nvec + threads - 1) / threads)));
     if (a.comm.world > 1) grid = std::min(grid, device_sm_count());
-    fused_reduce_optim_kernel<<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(h, a);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (a.comm.world <= 2)
+        fused_reduce_optim_kernel<4><<<grid, threads, 0, st>>>(h, a);
+    else if (a.comm.world <= 4)
+        fused_reduce_optim_kernel<2><<<grid, threads, 0, st>>>(h, a);
+    else
+        fused_reduce_optim_kernel<1><<<grid, threads, 0, st>>>(h, a);
     count_launch();
     TONY_CUDA_CHECK(cudaGetLastError());
     return TONY_OK;
