@@ -26,7 +26,15 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--steps", type=int, default=50)
 ap.add_argument("--batch", type=int, default=8192)
 ap.add_argument("--tiny", action="store_true")
+ap.add_argument("--ps_ranks", default="", help="outside the launcher (torchrun): comma list of ranks that act "
+                                               "as dedicated parameter servers, e.g. 6,7")
 a = ap.parse_args()
+if a.ps_ranks and "TONY_B200_ALL_RANK" not in os.environ:
+    os.environ["TONY_B200_ALL_RANK"] = os.environ.get("RANK", "0")
+    os.environ["TONY_B200_ALL_WORLD"] = os.environ.get("WORLD_SIZE", "1")
+    os.environ["TONY_B200_PS_RANKS"] = a.ps_ranks
+    if int(os.environ["TONY_B200_ALL_RANK"]) in [int(x) for x in a.ps_ranks.split(",")]:
+        os.environ["JOB_NAME"] = "ps-torchrun"       # not "ps": no server.join() wait without an AM to end it
 
 rank, world, dev = runtime.init(include_ps=True)
 roles = runtime.ps_roles()                      # None in the symmetric layout

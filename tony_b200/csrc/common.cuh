@@ -188,6 +188,25 @@ __device__ __forceinline__ void umma_commit_multicast(uint64_t* bar, uint16_t ma
         : "memory");
 }
 
+// 1-D bulk copies (UBLKCP): global -> shared with mbarrier completion, shared -> global in a bulk group.
+// `src` may be peer-mapped memory (a plain, non-multicast load); sizes / addresses multiples of 16 bytes.
+__device__ __forceinline__ void bulk_load_1d(uint32_t smem_dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :
+                 : "r"(smem_dst), "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_store_1d(void* dst, uint32_t smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                 :
+                 : "l"(dst), "r"(smem_src), "r"(bytes)
+                 : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }

@@ -226,8 +226,8 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                             }
                         } else {
                             // fewer chunks than CTAs: each chunk's 64 k-rows are cut into CS / N_CHUNKS parts
-                            constexpr int PPC = CS / (N_CHUNKS > 0 ? N_CHUNKS : 1);
-                            constexpr int ROWS = 64 / (PPC > 0 ? PPC : 1);
+                            constexpr int PPC = (CS / (N_CHUNKS > 0 ? N_CHUNKS : 1)) > 0 ? CS / (N_CHUNKS > 0 ? N_CHUNKS : 1) : 1;
+                            constexpr int ROWS = 64 / PPC;
                             const int ch = static_cast<int>(crank) / PPC;
                             const int part = static_cast<int>(crank) % PPC;
                             tma_load_2d_multicast(&tmap_b, &full_bar[stage],

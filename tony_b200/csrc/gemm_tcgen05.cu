@@ -72,9 +72,9 @@ struct GemmParams {
 
 __device__ __forceinline__ void tile_coords(const GemmParams& p, int tile, int& m_blk, int& n_blk) {
     // grouped ordering: group_m m-blocks share each sweep over n so A stays L2 resident (16 by default;
-    // the all-gather GEMM uses 64 so that several waves of tiles run on the local weight shard before
-    // the first remote slab is needed - with 16 the sweep reached the remote n-blocks within the first
-    // two waves and the gather was exposed, not hidden)
+    // the all-gather GEMM uses 32 so that a few waves of tiles run on the local weight shard before the
+    // first remote slab is needed - with 16 the sweep reached the remote n-blocks within the first two
+    // waves and the gather was exposed, not hidden)
     const int GROUP_M = p.group_m;
     const int per_group = GROUP_M * p.num_n_blocks;
     const int group = tile / per_group;
@@ -86,50 +86,123 @@ __device__ __forceinline__ void tile_coords(const GemmParams& p, int tile, int& 
     if (n_blk >= p.num_n_blocks) n_blk -= p.num_n_blocks;
 }
 
-// Copy-CTA role of the all-gather-fused GEMM: walk the n-blocks in the same rotated order
-// the GEMM workers consume them, pull every row that lives on a peer over NVLink with
-// 16-byte loads (8 in flight per thread), then publish the slab with a release increment.
-template <int BLOCK_N>
-__device__ __forceinline__ void allgather_copy_role(const GemmParams& p) {
-    const int vec_per_row = p.K / 8;
-    const int nthreads = p.copy_ctas * GEMM_THREADS;
-    const int gtid = blockIdx.x * GEMM_THREADS + threadIdx.x;
-    for (int j = 0; j < p.num_n_blocks; ++j) {
-        int nb = p.n_rot + j;
-        if (nb >= p.num_n_blocks) nb -= p.num_n_blocks;
-        const int r0 = nb * BLOCK_N;
-        const int r1 = min(p.N, r0 + BLOCK_N);
-        const int total = (r1 - r0) * vec_per_row;
-        constexpr int U = 8;
-        for (int v0 = gtid; v0 < total; v0 += nthreads * U) {
-            uint4 buf[U];
-            __nv_bfloat16* dst[U];
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int v = v0 + u * nthreads;
-                dst[u] = nullptr;
-                if (v < total) {
-                    const int row = r0 + v / vec_per_row;
-                    const int cv = v - (row - r0) * vec_per_row;
-                    const int owner = row / p.ag_rows_per_rank;
-                    const __nv_bfloat16* src =
-                        p.ag_src[owner] +
-                        static_cast<size_t>(row - owner * p.ag_rows_per_rank) * p.K + cv * 8;
-                    __nv_bfloat16* d = p.ag_dst + static_cast<size_t>(row) * p.K + cv * 8;
-                    if (src != d) {
-                        dst[u] = d;
-                        buf[u] = ld_global_v4(src);
-                    }
-                }
+// Copy-CTA role of the all-gather-fused GEMM: walk the n-blocks (slabs of BLOCK_N weight rows) in the same
+// rotated order the GEMM workers consume them and bring every row that lives on a peer into the local
+// full matrix, then publish the slab with a release increment.  Rows are contiguous on both sides, so a
+// slab is one (or two) contiguous byte ranges per owner: they move as 16 KB bulk copies - peer memory ->
+// shared memory (cp.async.bulk + mbarrier), shared -> local global (cp.async.bulk store) - through a ring
+// in the CTA's otherwise unused operand buffers, RING / 2 loads in flight per CTA.  (The first version
+// copied with register loads, 8 x 16 B per thread per trip: one NVLink round trip per 74 KB per CTA.)
+template <int RING>
+__device__ __forceinline__ void allgather_copy_role(const GemmParams& p, int block_n, uint8_t* ring, uint64_t* bars) {
+    constexpr uint32_t CHUNK = 16384;
+    constexpr int AHEAD = RING / 2;
+    constexpr int QN = 32;                      // event queue (loads in flight + slab markers between them)
+    if (threadIdx.x != 0) return;
+    const size_t row_bytes = static_cast<size_t>(p.K) * 2;
+    const int me = static_cast<int>(blockIdx.x), ncopy = p.copy_ctas;
+    uint8_t* dst_base = reinterpret_cast<uint8_t*>(p.ag_dst);
+
+    // ---- walker: this CTA's chunks in sweep order, one division per slab / owner range, none per chunk ----
+    int wj = -1;                 // slab position in the rotated order (-1: not started)
+    int w_nb = 0;                // its n-block index
+    int w_row = 0, w_row_end = 0;   // rows of the slab not yet turned into a range
+    size_t r_off = 0, r_len = 0; // current owner range: byte offset in the full matrix, length
+    const uint8_t* r_src = nullptr;
+    size_t r_k = 0, r_chunks = 0;   // next chunk of the range that is mine, number of chunks in the range
+    int rr = 0;                  // round-robin phase so ranges shorter than ncopy chunks still spread evenly
+    bool w_done = false;
+
+    // events
+    size_t q_off[QN];
+    uint32_t q_bytes[QN];        // 0 = slab marker (q_off holds the n-block)
+    int qh = 0, qt = 0;
+    long long n_loaded = 0, n_stored = 0;
+    int in_flight = 0;
+
+    auto next_event = [&](size_t& off, uint32_t& bytes, const uint8_t*& src) -> bool {
+        // true: produced an event (bytes == 0: slab marker with off = n-block); false: sweep finished
+        for (;;) {
+            if (r_k < r_chunks) {
+                const size_t o = r_k * CHUNK;
+                off = r_off + o;
+                bytes = static_cast<uint32_t>(r_len - o < CHUNK ? r_len - o : CHUNK);
+                src = r_src + o;
+                r_k += ncopy;
+                return true;
             }
-#pragma unroll
-            for (int u = 0; u < U; ++u)
-                if (dst[u]) st_global_v4(dst[u], buf[u]);
+            if (w_row < w_row_end) {
+                // next owner range of the slab
+                const int owner = w_row / p.ag_rows_per_rank;
+                const int stop = min(w_row_end, (owner + 1) * p.ag_rows_per_rank);
+                r_off = static_cast<size_t>(w_row) * row_bytes;
+                r_len = static_cast<size_t>(stop - w_row) * row_bytes;
+                r_src = reinterpret_cast<const uint8_t*>(p.ag_src[owner]) +
+                        static_cast<size_t>(w_row - owner * p.ag_rows_per_rank) * row_bytes;
+                w_row = stop;
+                if (r_src == dst_base + r_off) {          // rows this rank owns are already in place
+                    r_k = r_chunks = 0;
+                    continue;
+                }
+                r_chunks = (r_len + CHUNK - 1) / CHUNK;
+                r_k = static_cast<size_t>((me - rr + ncopy) % ncopy);
+                rr = static_cast<int>((rr + r_chunks) % ncopy);
+                continue;
+            }
+            if (wj >= 0 && w_row_end > 0) {               // slab finished: marker, once
+                off = static_cast<size_t>(w_nb);
+                bytes = 0;
+                src = nullptr;
+                w_row_end = 0;
+                return true;
+            }
+            if (++wj >= p.num_n_blocks) {
+                w_done = true;
+                return false;
+            }
+            w_nb = p.n_rot + wj;
+            if (w_nb >= p.num_n_blocks) w_nb -= p.num_n_blocks;
+            w_row = w_nb * block_n;
+            w_row_end = min(p.N, w_row + block_n);
+            r_k = r_chunks = 0;
         }
-        __threadfence();
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.ag_flags + nb) : "memory");
+    };
+
+    for (;;) {
+        // fill: keep AHEAD loads in flight (markers ride along in the queue)
+        while (!w_done && in_flight < AHEAD && ((qt + 1) % QN) != qh) {
+            size_t off;
+            uint32_t bytes;
+            const uint8_t* src;
+            if (!next_event(off, bytes, src)) break;
+            q_off[qt] = off;
+            q_bytes[qt] = bytes;
+            qt = (qt + 1) % QN;
+            if (bytes) {
+                const int slot = static_cast<int>(n_loaded % RING);
+                mbar_expect_tx(&bars[slot], bytes);
+                bulk_load_1d(smem_u32(ring + slot * CHUNK), src, bytes, &bars[slot]);
+                ++n_loaded;
+                ++in_flight;
+            }
+        }
+        if (qh == qt) break;
+        const size_t off = q_off[qh];
+        const uint32_t bytes = q_bytes[qh];
+        qh = (qh + 1) % QN;
+        if (bytes) {
+            const int slot = static_cast<int>(n_stored % RING);
+            mbar_wait(&bars[slot], static_cast<uint32_t>((n_stored / RING) & 1));
+            bulk_store_1d(dst_base + off, smem_u32(ring + slot * CHUNK), bytes);
+            tma_store_commit();
+            ++n_stored;
+            --in_flight;
+            bulk_wait_read<AHEAD - 1>();      // the slot the next load reuses has been read out
+        } else {
+            tma_store_wait_all();             // this CTA's part of the slab is in local memory
+            fence_proxy_async();
+            __threadfence();
+            asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.ag_flags + off) : "memory");
         }
     }
 }
@@ -501,8 +574,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
     }
     else {
+        // ring slots: the 2 * STAGES single-arrival barriers (full + empty) and the operand buffers, unused here
         pdl_wait();
-        allgather_copy_role<BLOCK_N>(p);
+        allgather_copy_role<2 * STAGES>(p, BLOCK_N, smem, full_bar);
     }
 
     __syncwarp();
@@ -588,10 +662,15 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
 
     const int num_tiles = p.num_m_blocks * p.num_n_blocks;   // blocks of 256 x 256 here
     const int num_units = num_tiles * p.splits;
-    const int cluster_id = static_cast<int>(blockIdx.x >> 1);
-    const int num_clusters = static_cast<int>(gridDim.x >> 1);
+    // fused all-gather: the first copy_ctas CTAs (whole clusters) pull the remote weight shards, the rest work
+    const int copy_clusters = p.copy_ctas >> 1;
+    const int cluster_id = static_cast<int>(blockIdx.x >> 1) - copy_clusters;
+    const int num_clusters = static_cast<int>(gridDim.x >> 1) - copy_clusters;
 
-    if (warp_idx == 0) {
+    if (cluster_id < 0) {
+        pdl_wait();
+        allgather_copy_role<2 * STAGES>(p, TILE_N, smem, full_bar);
+    } else if (warp_idx == 0) {
         // ---------------------------------------------------- TMA producer (both CTAs; whole warp, one lane issues)
         {
             int stage = 0;
@@ -602,6 +681,14 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const int split = unit - tile * p.splits;
                 int m_blk, n_blk;
                 tile_coords(p, tile, m_blk, n_blk);
+                if (p.b_ready != nullptr) {
+                    if (elect_one()) {
+                        while (static_cast<int32_t>(ld_acquire_gpu(p.b_ready + n_blk) - p.b_ready_epoch) < 0)
+                            __nanosleep(64);
+                        fence_proxy_async();  // generic / bulk-copy writes -> this thread's TMA reads
+                    }
+                    __syncwarp();
+                }
                 const int m0 = m_blk * TILE_M + static_cast<int>(cta_rank) * BLOCK_M;
                 const int n0 = n_blk * TILE_N + static_cast<int>(cta_rank) * HALF_N;
                 const int kb0 = split * p.kb_per_split;
@@ -1069,10 +1156,11 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
     // CTA-pair kernel (256 x 256 tiles over 2 SMs): force_block_n == 512 forces it, 0 lets the
     // heuristic decide, 128 / 256 force the 1-CTA kernels.
     bool use_2cta = false;
-    if (!ag && copy_ctas == 0 && b_ready == nullptr && two_cta_mode() > 0 && (workers % 2) == 0) {
+    if (two_cta_mode() > 0 && (workers % 2) == 0 && (copy_ctas % 2) == 0 &&
+        (ag != nullptr || (copy_ctas == 0 && b_ready == nullptr))) {
         if (force_block_n == 512) {
             use_2cta = true;
-        } else if (force_block_n == 0 && N >= 256 && M >= 256) {
+        } else if ((force_block_n == 0 || (ag != nullptr && force_block_n == 256)) && N >= 256 && M >= 256) {
             // measured on BERT-large (profiles/): the pair kernel wins on every such shape,
             // even where its wave quantisation is worse, because each SM moves a third less
             // operand traffic and the smem ring is 6 deep
@@ -1152,7 +1240,9 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
 
     GemmParams p;
     p.tma_store = use_tma_store;
-    p.group_m = ag ? 64 : 16;
+    // all-gather GEMM: 32 m-blocks per sweep keep A's group + B inside the L2 (64 did not: +270 us of HBM
+    // re-reads at 16384 x 3344) while still giving the copy CTAs a few waves of local-shard tiles as head start
+    p.group_m = ag ? 32 : 16;
     p.M = M;
     p.N = N;
     p.K = K;
@@ -1196,9 +1286,10 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
 
     const long long units = tiles * splits;
     const int grid = static_cast<int>(std::min<long long>(units, workers)) + copy_ctas;
+    const int grid_pairs = static_cast<int>(std::min<long long>(units, workers)) * 2 + copy_ctas;   // CTAs
     if (use_2cta)
-        rc = rowsum_out ? launch_gemm_2cta<6, true>(ta, tb, tc, tx, p, grid * 2, stream)
-                        : launch_gemm_2cta<6, false>(ta, tb, tc, tx, p, grid * 2, stream);
+        rc = rowsum_out ? launch_gemm_2cta<6, true>(ta, tb, tc, tx, p, grid_pairs, stream)
+                        : launch_gemm_2cta<6, false>(ta, tb, tc, tx, p, grid_pairs, stream);
     else if (block_n == 256)
         rc = launch_gemm<256, 4>(ta, tb, tc, tx, p, grid, stream);
     else
@@ -1265,8 +1356,10 @@ extern "C" int tony_allgather_gemm_bf16(const void* X, const void* const* w_shar
         set_last_error("tony_allgather_gemm_bf16", "unsupported epilogue flag");
         return TONY_ERR_INVALID;
     }
-    if (copy_ctas <= 0) copy_ctas = 24;
-    copy_ctas = std::min(copy_ctas, device_sm_count() / 2);
+    // bulk copies keep 96 KB in flight per copy CTA: a handful saturate what the GEMM can consume
+    if (copy_ctas <= 0) copy_ctas = 4;
+    copy_ctas = std::min(copy_ctas, device_sm_count() / 2) & ~1;
+    if (copy_ctas < 2) copy_ctas = 2;
     AgHost ag;
     ag.src = w_shard;
     ag.dst = w_full;
