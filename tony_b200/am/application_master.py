@@ -330,6 +330,8 @@ class ApplicationMaster:
             if self.scheduler:
                 self.scheduler.register_dependency_completed(task.job_name)
             log(f"{task.id} completed with exit status {exit_status} -> {task.status.name}")
+            if exit_status != 0:
+                self.mark("task_failed", task=task.id, exit=exit_status)
             self.events.emit(ev.task_finished(task.job_name, task.index, task.status.name,
                                               self.metrics.get(task.id), diagnostics or None))
             if task.job_name in session.untracked and task.failed:
@@ -496,8 +498,10 @@ class ApplicationMaster:
     def reset(self) -> None:
         """Whole-session restart: kill every container, fresh session, bump the session id."""
         log("resetting for a new session attempt")
+        self.mark("session_reset", session=self.session_id + 1)
         self.rm.stop_all(new_attempt=True)
         with self.lock:
+            self.first_step.clear()      # the resumed session reports its own first step (time to recover)
             self.hb.reset()
             self.session_id += 1
             self.num_am_retries += 1

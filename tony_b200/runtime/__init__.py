@@ -145,8 +145,7 @@ class LossFuture:
         t = self._trainer
         if t.store.world > 1:
             t.store.comm.check_status()
-        if self._step == 1:
-            mark_first_step()
+        mark_first_step()
         return value
 
 
@@ -339,8 +338,7 @@ class Trainer:
             # GPU-side hang detection: a fused collective that gave up waiting for a dead peer
             # set the status word; fail the task so the launcher's failure policy takes over
             self.store.comm.check_status()
-        if self.steps == 1:
-            mark_first_step()
+        mark_first_step()       # no-op after this process's first completed step (also after a resume)
         return value
 
     def step_async(self, batch_cpu) -> "LossFuture":
