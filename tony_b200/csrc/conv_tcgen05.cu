@@ -65,6 +65,11 @@ struct ConvParams {
     float* stat_sum;               // optional [N]: += column sums of the bf16 output
     float* stat_sqsum;             // optional [N]: += column sums of squares
     int dbg;                       // timing experiments only (TONY_B200_CONV_DBG): 1 = skip A loads, 2 = skip B loads
+    // MODE 1, tiled form: a k-block is a bw x bh patch of output pixels of one image (bw * bh = 64) instead of
+    // 64 consecutive pixels, and both operands come through plain 4-D tiled maps - the filter tap is a
+    // coordinate shift and the padding is the map's out-of-range zero fill.  An experiment kept as an option:
+    // it is correct but not faster than the im2col form (see tony_conv2d_wgrad_bf16).
+    int tiled, bw, bh, nbw, nbh, pad_w, pad_h;
 };
 
 __device__ __forceinline__ void tma_load_im2col_4d(const CUtensorMap* map, uint64_t* bar, void* smem_dst,
@@ -251,6 +256,42 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                     const int g0 = n_blk * N_CHUNKS;
                     const int valid = min(N_CHUNKS, total_chunks - g0);
                     for (int kb = kb0; kb < kb1; ++kb) {
+                        if (p.tiled) {
+                            const int per_img = p.nbw * p.nbh;
+                            const int img = kb / per_img;
+                            const int rem = kb - img * per_img;
+                            const int by = rem / p.nbw;
+                            const int bx = rem - by * p.nbw;
+                            const int ow = bx * p.bw, oh = by * p.bh;        // first output pixel of the patch
+                            mbar_wait(&empty_bar[stage], phase ^ 1);
+                            uint8_t* sa = smem + stage * STAGE_BYTES;
+                            uint8_t* sb = sa + A_BYTES;
+                            if (elect_one()) {
+                                mbar_expect_tx(&full_bar[stage], A_BYTES + valid * CV_CHUNK_BYTES);
+#pragma unroll
+                                for (int c = 0; c < CV_BLOCK_M / 64; ++c)
+                                    tma_load_4d(&tmap_a, &full_bar[stage], sa + c * CV_CHUNK_BYTES,
+                                                m_blk * CV_BLOCK_M + c * 64, ow, oh, img);
+#pragma unroll
+                                for (int c = 0; c < N_CHUNKS; ++c) {
+                                    if (c < valid) {
+                                        const int g = g0 + c;
+                                        const int t = g / p.cblocks;
+                                        const int cc = g - t * p.cblocks;
+                                        const ConvTap tap = p.taps[t];
+                                        tma_load_4d(&tmap_b, &full_bar[stage], sb + c * CV_CHUNK_BYTES, cc * 64,
+                                                    ow * p.stride_w + tap.off_w - p.pad_w,
+                                                    oh * p.stride_h + tap.off_h - p.pad_h, img);
+                                    }
+                                }
+                            }
+                            __syncwarp();
+                            if (++stage == STAGES) {
+                                stage = 0;
+                                phase ^= 1;
+                            }
+                            continue;
+                        }
                         const int k0 = kb * CV_BLOCK_K;
                         const int img = k0 / pq;
                         const int rem = k0 - img * pq;
@@ -262,13 +303,14 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                         uint8_t* sa = smem + stage * STAGE_BYTES;
                         uint8_t* sb = sa + A_BYTES;
                         if (elect_one()) {
-                        mbar_expect_tx(&full_bar[stage], A_BYTES + valid * CV_CHUNK_BYTES);
+                        const bool la = !(p.dbg & 1), lb = !(p.dbg & 2);    // timing experiments only
+                        mbar_expect_tx(&full_bar[stage], (la ? A_BYTES : 0) + (lb ? valid * CV_CHUNK_BYTES : 0));
 #pragma unroll
                         for (int c = 0; c < CV_BLOCK_M / 64; ++c)
-                            tma_load_2d(&tmap_a, &full_bar[stage], sa + c * CV_CHUNK_BYTES, m_blk * CV_BLOCK_M + c * 64, k0);
+                            if (la) tma_load_2d(&tmap_a, &full_bar[stage], sa + c * CV_CHUNK_BYTES, m_blk * CV_BLOCK_M + c * 64, k0);
 #pragma unroll
                         for (int c = 0; c < N_CHUNKS; ++c) {
-                            if (c < valid) {
+                            if (c < valid && lb) {
                                 const int g = g0 + c;
                                 const int t = g / p.cblocks;
                                 const int cc = g - t * p.cblocks;
@@ -641,6 +683,50 @@ static int make_im2col_tmap(CUtensorMap* map, const void* ptr, int N, int H, int
     return TONY_OK;
 }
 
+typedef CUresult (*PFN_encodeTiled4)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// 4-D tiled map over a dense NHWC bf16 tensor: box = 64 channels x (bw x bh) pixels of one image, visited with
+// element strides (sw, sh) - a patch of the output grid seen through the convolution's stride
+static int make_patch_tmap(CUtensorMap* map, const void* ptr, int N, int H, int W, int C, int bw, int bh, int sw,
+                           int sh) {
+    static thread_local bool tls_ctx_bound = false;
+    if (!tls_ctx_bound) {
+        cudaFree(nullptr);
+        tls_ctx_bound = true;
+    }
+    static PFN_encodeTiled4 enc = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            enc = reinterpret_cast<PFN_encodeTiled4>(fn);
+    });
+    if (!enc) {
+        set_last_error("cuTensorMapEncodeTiled", "driver entry point not found");
+        return TONY_ERR_UNSUPPORTED;
+    }
+    cuuint64_t gdim[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
+                          static_cast<cuuint64_t>(N)};
+    cuuint64_t gstride[3] = {static_cast<cuuint64_t>(C) * 2, static_cast<cuuint64_t>(W) * C * 2,
+                             static_cast<cuuint64_t>(H) * W * C * 2};
+    cuuint32_t box[4] = {64, static_cast<cuuint32_t>(bw * sw), static_cast<cuuint32_t>(bh * sh), 1};
+    cuuint32_t estride[4] = {1, static_cast<cuuint32_t>(sw), static_cast<cuuint32_t>(sh), 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), gdim, gstride, box, estride,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[128];
+        snprintf(buf, sizeof(buf), "CUresult %d (4-D patch map, box %d x %d, stride %d)", static_cast<int>(r), bw, bh, sw);
+        set_last_error("cuTensorMapEncodeTiled", buf);
+        return TONY_ERR_CUDA;
+    }
+    return TONY_OK;
+}
+
 template <int BLOCK_N, int STAGES, int MODE, int CS>
 static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, int grid, cudaStream_t stream) {
     constexpr size_t SMEM =
@@ -967,6 +1053,38 @@ extern "C" int tony_conv2d_wgrad_bf16(const tony_conv_desc* d, const void* dy, c
     p.ntaps = d->R * d->S;
     p.cblocks = d->C / 64;
     p.num_k_blocks = static_cast<int>((pixels + CV_BLOCK_K - 1) / CV_BLOCK_K);
+    // tiled form (dense input; TONY_B200_CONV_WGRAD=tiled enables): pick the 64-pixel patch shape that wastes
+    // the fewest out-of-range pixels on this output grid.  Validated, but measured SLOWER than the im2col form
+    // (128 vs 99 us at 256 -> 256 channels, 14 x 14): the limit is not the im2col mode but the 48 KB of
+    // operands per 512 clk of MMAs - either way 384 rows of 128 bytes per k-block through the L2 -> SM path.
+    static int wgrad_tiled = -1;
+    if (wgrad_tiled < 0) {
+        const char* e = getenv("TONY_B200_CONV_WGRAD");
+        wgrad_tiled = (e && e[0] == 't') ? 1 : 0;
+    }
+    p.tiled = 0;
+    if (wgrad_tiled && !d->x_stride_w && !d->x_stride_h && !d->x_stride_n) {
+        double best = 0.0;
+        for (int bw = 1; bw <= 64; bw *= 2) {
+            const int bh = 64 / bw;
+            if (bw * d->stride > 256 || bh * d->stride > 256) continue;
+            const int nbw = (Q + bw - 1) / bw, nbh = (P + bh - 1) / bh;
+            const double eff = (static_cast<double>(Q) / (nbw * bw)) * (static_cast<double>(P) / (nbh * bh));
+            if (eff > best + 1e-9) {
+                best = eff;
+                p.bw = bw;
+                p.bh = bh;
+                p.nbw = nbw;
+                p.nbh = nbh;
+            }
+        }
+        if (best > 0.0) {
+            p.tiled = 1;
+            p.pad_w = pad_w;
+            p.pad_h = d->pad;
+            p.num_k_blocks = d->N * p.nbw * p.nbh;
+        }
+    }
     const int sms = device_sm_count();
     const long long tiles = static_cast<long long>(p.num_m_blocks) * p.num_n_blocks;
     int splits = 1;
@@ -994,14 +1112,26 @@ extern "C" int tony_conv2d_wgrad_bf16(const tony_conv_desc* d, const void* dy, c
     p.ldc = p.N;
     p.flags = flags;
     p.workspace = static_cast<float*>(workspace);
+    {
+        const char* e = getenv("TONY_B200_CONV_DBG");
+        p.dbg = e ? atoi(e) : 0;
+    }
     CUtensorMap ta, tb;
-    // dY as [pixels][K]: A(m = co, k = pixel) is MN-major, 64 x 64 boxes
-    rc = make_tmap_2d_bf16(&ta, dy, d->K, pixels, d->K, 64, 64);
-    if (rc) return rc;
-    rc = make_im2col_tmap(&tb, x, d->N, d->H, d->W, d->C, -pad_w, -d->pad, pad_hi_w - (d->S - 1),
-                          pad_hi_h - (d->R - 1), d->stride, d->stride, CV_BLOCK_K, d->x_stride_w, d->x_stride_h,
-                          d->x_stride_n);
-    if (rc) return rc;
+    if (p.tiled) {
+        // both operands as 64-pixel patches of one image; the tap is a coordinate shift, padding the zero fill
+        rc = make_patch_tmap(&ta, dy, d->N, P, Q, d->K, p.bw, p.bh, 1, 1);
+        if (rc) return rc;
+        rc = make_patch_tmap(&tb, x, d->N, d->H, d->W, d->C, p.bw, p.bh, d->stride, d->stride);
+        if (rc) return rc;
+    } else {
+        // dY as [pixels][K]: A(m = co, k = pixel) is MN-major, 64 x 64 boxes
+        rc = make_tmap_2d_bf16(&ta, dy, d->K, pixels, d->K, 64, 64);
+        if (rc) return rc;
+        rc = make_im2col_tmap(&tb, x, d->N, d->H, d->W, d->C, -pad_w, -d->pad, pad_hi_w - (d->S - 1),
+                              pad_hi_h - (d->R - 1), d->stride, d->stride, CV_BLOCK_K, d->x_stride_w, d->x_stride_h,
+                              d->x_stride_n);
+        if (rc) return rc;
+    }
     const long long units = tiles * p.splits;
     const int grid = static_cast<int>(std::min<long long>(units, sms));
     rc = dispatch_conv<1>(block_n, ta, tb, p, grid, stream);

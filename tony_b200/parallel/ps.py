@@ -108,7 +108,7 @@ class ShardedLinear(nn.Module):
     FlatParamStore, e.g. via ``Trainer(..., ps_sharded=model.ps_parameters())``)."""
 
     def __init__(self, in_features: int, out_features: int, bias: bool = True, act: Optional[str] = None,
-                 std: float = 0.02, copy_ctas: int = 4, device=None):
+                 std: float = 0.02, copy_ctas: int = 0, device=None):
         super().__init__()
         self.weight = _param(out_features, in_features, std=std, device=device)
         self.bias = _param(out_features, fill=0.0, device=device) if bias else None
