@@ -389,6 +389,24 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         const int unit16 = lane & 3;
         const int etid = threadIdx.x - 64;     // 0..511 among the epilogue warps
         int stat_nblk = -1;
+        // one column of BatchNorm partials per lane and 32-column chunk this warp owns (see the epilogue loop)
+        constexpr int STAT_SLOTS = (BLOCK_N / 32 + CV_EPI_WARPS / 4 - 1) / (CV_EPI_WARPS / 4);
+        static_assert(STAT_SLOTS <= 2, "the slot select below assumes at most two chunks per warp");
+        float acc1[STAT_SLOTS], acc2[STAT_SLOTS];
+#pragma unroll
+        for (int i = 0; i < STAT_SLOTS; ++i) acc1[i] = acc2[i] = 0.f;
+        // the four quarter warps of a group own the same columns: meet in shared memory, once per column block
+        auto stat_fold = [&]() {
+#pragma unroll
+            for (int i = 0; i < STAT_SLOTS; ++i) {
+                const int lc = (group + i * (CV_EPI_WARPS / 4)) * 32 + unit16 * 8 + (lane >> 2);
+                if (lc < BLOCK_N) {
+                    atomicAdd(stat_acc + lc, acc1[i]);
+                    atomicAdd(stat_acc + BLOCK_N + lc, acc2[i]);
+                }
+                acc1[i] = acc2[i] = 0.f;
+            }
+        };
         int iter = 0;
         for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
             const int tile = unit / p.splits;
@@ -398,6 +416,7 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
             if (p.stat_sum != nullptr && n_blk != stat_nblk) {
                 if (stat_nblk >= 0) {
                     // this CTA moves on to another column block: hand the finished partials over
+                    stat_fold();
                     asm volatile("bar.sync 1, 512;" ::: "memory");
                     for (int i = etid; i < 2 * BLOCK_N; i += 512) {
                         const int col = stat_nblk * BLOCK_N + (i % BLOCK_N);
@@ -495,23 +514,32 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                 }
                 __syncwarp();
                 if (p.stat_sum != nullptr) {
-                    // lanes with equal (lane & 3) hold the same 8 columns for different rows: fold the 8
-                    // row groups with shuffles, then one red.add per column per warp
+                    // lanes with equal (lane & 3) hold the same 8 columns for different rows.  Fold the 8 row groups
+                    // with a halving exchange (7 shuffles per array, not 24): lane (rg, unit16) ends with the warp's
+                    // sum for column unit16 * 8 + rg and keeps it in a register until this CTA leaves the column block
+                    const int rg = lane >> 2;
+                    float k1[4], k2[4];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-#pragma unroll
-                        for (int o2 = 4; o2 < 32; o2 <<= 1) {
-                            s1[j] += __shfl_xor_sync(0xffffffffu, s1[j], o2);
-                            s2[j] += __shfl_xor_sync(0xffffffffu, s2[j], o2);
-                        }
+                    for (int j = 0; j < 4; ++j) {
+                        const float snd1 = (rg & 4) ? s1[j] : s1[j + 4], snd2 = (rg & 4) ? s2[j] : s2[j + 4];
+                        k1[j] = ((rg & 4) ? s1[j + 4] : s1[j]) + __shfl_xor_sync(0xffffffffu, snd1, 16);
+                        k2[j] = ((rg & 4) ? s2[j + 4] : s2[j]) + __shfl_xor_sync(0xffffffffu, snd2, 16);
                     }
-                    if (lane < 4) {
-                        const int lc = c * 32 + unit16 * 8;
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            atomicAdd(stat_acc + lc + j, s1[j]);
-                            atomicAdd(stat_acc + BLOCK_N + lc + j, s2[j]);
-                        }
+                    for (int j = 0; j < 2; ++j) {
+                        const float snd1 = (rg & 2) ? k1[j] : k1[j + 2], snd2 = (rg & 2) ? k2[j] : k2[j + 2];
+                        k1[j] = ((rg & 2) ? k1[j + 2] : k1[j]) + __shfl_xor_sync(0xffffffffu, snd1, 8);
+                        k2[j] = ((rg & 2) ? k2[j + 2] : k2[j]) + __shfl_xor_sync(0xffffffffu, snd2, 8);
+                    }
+                    const float snd1 = (rg & 1) ? k1[0] : k1[1], snd2 = (rg & 1) ? k2[0] : k2[1];
+                    const float f1 = ((rg & 1) ? k1[1] : k1[0]) + __shfl_xor_sync(0xffffffffu, snd1, 4);
+                    const float f2 = ((rg & 1) ? k2[1] : k2[0]) + __shfl_xor_sync(0xffffffffu, snd2, 4);
+                    if (STAT_SLOTS == 1 || c == group) {
+                        acc1[0] += f1;
+                        acc2[0] += f2;
+                    } else {
+                        acc1[STAT_SLOTS - 1] += f1;
+                        acc2[STAT_SLOTS - 1] += f2;
                     }
                 }
             }
@@ -520,6 +548,7 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
             if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
         }
         if (p.stat_sum != nullptr && stat_nblk >= 0) {
+            stat_fold();
             asm volatile("bar.sync 1, 512;" ::: "memory");
             for (int i = etid; i < 2 * BLOCK_N; i += 512) {
                 const int col = stat_nblk * BLOCK_N + (i % BLOCK_N);
@@ -801,8 +830,10 @@ static int conv_cluster_size() {
     static int cs = -1;
     if (cs < 0) {
         const char* e = getenv("TONY_B200_CONV_CLUSTER");
-        cs = e ? atoi(e) : 2;
-        if (cs != 1 && cs != 2 && cs != 4) cs = 2;
+        // default 1: with the issue loops fixed the multicast forms measure equal (2) or slower (4) - the kernel
+        // sits at its MMA + issue floor, not on L2 -> SM bytes; kept as validated options
+        cs = e ? atoi(e) : 1;
+        if (cs != 1 && cs != 2 && cs != 4) cs = 1;
     }
     return cs;
 }

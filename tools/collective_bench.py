@@ -110,19 +110,23 @@ def main():
     form = "nvls" if comm.nvls is not None else "p2p"
     for n in sizes:
         S = 2.0 * n
+        # NVLink bytes per direction per GPU.  Reduce phase: every GPU's copy of the other (world-1)/world of the bucket
+        # leaves it (the switch pulls it for multimem.ld_reduce, or the owners read it with P2P loads) and its own
+        # reduced shard comes in; weight push: the updated shard goes out once through the switch (multimem.st) or
+        # world-1 times with P2P stores, and the other (world-1)/world of the bucket comes in.
         if world > 1:
-            link = (S / world) if form == "nvls" else (S * (world - 1) / world)
+            red_out, red_in = S * (world - 1) / world, (S / world if form == "nvls" else S * (world - 1) / world)
+            bc_out, bc_in = (S / world if form == "nvls" else S * (world - 1) / world), S * (world - 1) / world
+            link, link_nobc = max(red_out + bc_out, red_in + bc_in), max(red_out, red_in)
         else:
-            link = 0.0
+            link = link_nobc = 0.0
         hbm = 14.0 * S / world
         for name, opt, bc in (("K1 all-reduce + AdamW + broadcast", _lib.OPT_ADAMW, 1),
                               ("K2 reduce-scatter + sharded AdamW", _lib.OPT_ADAMW, 0),
                               ("K0b all-reduce", -1, 1)):
             for ctas in sorted({a.ctas, 148 if world > 1 else a.ctas}):
                 us = timed(lambda: fused(n, opt, bc, ctas))
-                link_b = link if (bc or opt >= 0) else link
-                if name.startswith("K2"):
-                    link_b = link / 2 if form == "p2p" else link / 2     # no weight push
+                link_b = link_nobc if name.startswith("K2") else link      # K2 has no weight push
                 hbm_b = hbm if opt >= 0 else (S / world) * 2
                 t_link = link_b / (LINK_GBS * 1e3)                        # us
                 t_hbm = hbm_b / (PEAKS["hbm_gbs"] * 1e3)

@@ -43,6 +43,7 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--max", type=int, default=12)
     ap.add_argument("--note", default="")
+    ap.add_argument("--pick", default="", help="comma-separated launch indices to show instead of de-duplicating by name + grid")
     a = ap.parse_args()
     raw = subprocess.run(["ncu", "-i", a.rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
@@ -55,9 +56,12 @@ def main():
     iname = hdr.index("Kernel Name")
     igrid = hdr.index("launch__grid_size") if "launch__grid_size" in hdr else None
     seen, picked = set(), []
-    for r in data:
+    for n, r in enumerate(data):
         key = (r[iname], r[igrid] if igrid is not None else "")
-        if key in seen:
+        if a.pick:
+            if str(n) not in a.pick.split(","):
+                continue
+        elif key in seen:
             continue
         seen.add(key)
         picked.append(r)
