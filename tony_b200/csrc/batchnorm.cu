@@ -28,11 +28,21 @@ constexpr int BN_THREADS = 256;
 // Partial rows: slabs * column tiles <= 4 CTAs per SM, so every SM gets the same number of CTAs (a
 // cap of 160 slabs left 12 SMs with twice the work for every layer narrower than 1024 channels).
 constexpr int BN_CTAS_PER_SM = 4;
+// the backward reduction keeps 8 row vectors in flight per thread and needs 80 registers: three CTAs per SM, and
+// a grid of exactly that many (four per SM ran as a full wave plus a one-third wave)
+constexpr int BN_BWD_CTAS_PER_SM = 3;
 constexpr int BN_MAX_SMS = 256;
 
-static size_t bn_partials_floats() {   // slabs * 2 * Cw  <=  4 * SMs * 2 * 256
+static size_t bn_slab_partials_floats() {   // slabs * 2 * Cw  <=  4 * SMs * 2 * 256
     return static_cast<size_t>(BN_CTAS_PER_SM) * BN_MAX_SMS * 2 * 256;
 }
+// second fold level: at most 64 groups of slabs x 2 x Cw, and groups ~ sqrt(slabs) with slabs * Cw <= 4 * SMs * 256
+constexpr size_t BN_GROUP_PARTIALS_FLOATS = 65536;
+constexpr int BN_GROUP_COUNTER0 = 64;
+__device__ __forceinline__ size_t bn_slab_partials_floats_dev() {
+    return static_cast<size_t>(BN_CTAS_PER_SM) * BN_MAX_SMS * 2 * 256;
+}        // counters[0..63]: one per column tile; then 64 group counters per tile
+static size_t bn_partials_floats() { return bn_slab_partials_floats() + BN_GROUP_PARTIALS_FLOATS; }
 
 __device__ __forceinline__ void unpack8f(const uint4& u, float (&v)[8]) {
     const uint32_t w[4] = {u.x, u.y, u.z, u.w};
@@ -97,7 +107,97 @@ __device__ __forceinline__ bool combine_groups(const BnDims& d, float& s1, float
     return true;
 }
 
-__global__ void __launch_bounds__(BN_THREADS)
+// Sum nparts rows of [2][cols] partials for columns col0 .. col0+255: warp w takes rows w, w+8, ..., two rows (8
+// float4 loads) in flight per thread, then the 8 warp sums meet in shared memory.  Thread t gets column col0 + t.
+__device__ __forceinline__ void fold_partials2_256(const float* __restrict__ partials, int nparts, int col0, int cols,
+                                                   float (*red)[256], float& s1, float& s2) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c = col0 + lane * 8;
+    const size_t stride = static_cast<size_t>(2) * cols;
+    float t1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float t2[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (c < cols) {
+        for (int k = warp; k < nparts; k += 16) {
+            float4 a[2][4];
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int kk = k + q * 8;
+                if (kk < nparts) {
+                    const float4* p = reinterpret_cast<const float4*>(partials + static_cast<size_t>(kk) * stride + c);
+                    const float4* p2 = reinterpret_cast<const float4*>(partials + static_cast<size_t>(kk) * stride + cols + c);
+                    a[q][0] = __ldcg(p);
+                    a[q][1] = __ldcg(p + 1);
+                    a[q][2] = __ldcg(p2);
+                    a[q][3] = __ldcg(p2 + 1);
+                } else {
+                    a[q][0] = a[q][1] = a[q][2] = a[q][3] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                t1[0] += a[q][0].x; t1[1] += a[q][0].y; t1[2] += a[q][0].z; t1[3] += a[q][0].w;
+                t1[4] += a[q][1].x; t1[5] += a[q][1].y; t1[6] += a[q][1].z; t1[7] += a[q][1].w;
+                t2[0] += a[q][2].x; t2[1] += a[q][2].y; t2[2] += a[q][2].z; t2[3] += a[q][2].w;
+                t2[4] += a[q][3].x; t2[5] += a[q][3].y; t2[6] += a[q][3].z; t2[7] += a[q][3].w;
+            }
+        }
+    }
+    s1 = cta_colsum(t1, red);
+    s2 = cta_colsum(t2, red);
+}
+
+// Every CTA of the (column tile, slab) grid hands in its two column partials; exactly one CTA per column tile
+// returns true with the totals (thread t: column tile * 256 + t).  Two levels, each closed by the CTA that
+// arrives last: groups of ~sqrt(slabs) slabs, then the group sums - a fixed summation order, and neither level
+// reads more than ~25 rows (one CTA walking all 592 slab rows was 25 us behind an 8 us streaming pass).
+__device__ __noinline__ bool fold_slab_partials(float p1, float p2, float* __restrict__ partials,
+                                                   unsigned int* __restrict__ counters, const BnDims& d,
+                                                   float (*red)[256], unsigned int* flag, float& s1, float& s2) {
+    const int nparts = static_cast<int>(gridDim.y);
+    int gs = 8;
+    while (gs * gs < nparts) ++gs;
+    const int ngroups = (nparts + gs - 1) / gs;
+    const int grp = static_cast<int>(blockIdx.y) / gs;
+    const int gsize = min(gs, nparts - grp * gs);
+    const int gc = blockIdx.x * 256 + threadIdx.x;
+    float* gparts = partials + bn_slab_partials_floats_dev();
+    unsigned int* gcount = counters + BN_GROUP_COUNTER0 + blockIdx.x * 64 + grp;
+    float* my = partials + static_cast<size_t>(blockIdx.y) * 2 * d.Cw;
+    if (gc < d.Cw) {
+        my[gc] = p1;
+        my[d.Cw + gc] = p2;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) *flag = (atomicAdd(gcount, 1u) == static_cast<unsigned int>(gsize - 1)) ? 1u : 0u;
+    __syncthreads();
+    if (!*flag) return false;
+    __threadfence();
+    fold_partials2_256(partials + static_cast<size_t>(grp) * gs * 2 * d.Cw, gsize, blockIdx.x * 256, d.Cw, red, s1, s2);
+    if (ngroups == 1) {
+        if (threadIdx.x == 0) *gcount = 0;
+        return true;
+    }
+    float* gp = gparts + static_cast<size_t>(grp) * 2 * d.Cw;
+    if (gc < d.Cw) {
+        gp[gc] = s1;
+        gp[d.Cw + gc] = s2;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        *gcount = 0;
+        *flag = (atomicAdd(&counters[blockIdx.x], 1u) == static_cast<unsigned int>(ngroups - 1)) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (!*flag) return false;
+    __threadfence();
+    fold_partials2_256(gparts, ngroups, blockIdx.x * 256, d.Cw, red, s1, s2);
+    if (threadIdx.x == 0) counters[blockIdx.x] = 0;
+    return true;
+}
+
+__global__ void __launch_bounds__(BN_THREADS, BN_CTAS_PER_SM)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, const BnDims d, float* __restrict__ partials,
                 unsigned int* __restrict__ counters, const __nv_bfloat16* __restrict__ gamma,
                 const __nv_bfloat16* __restrict__ beta, float eps, float momentum, float* __restrict__ mean,
@@ -133,22 +233,8 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, const BnDims d, float* __re
     }
     const float p1 = cta_colsum(a1, red);
     const float p2 = cta_colsum(a2, red);
-    const int gc = blockIdx.x * 256 + threadIdx.x;
-    float* my = partials + static_cast<size_t>(blockIdx.y) * 2 * d.Cw;
-    if (gc < d.Cw) {
-        my[gc] = p1;
-        my[d.Cw + gc] = p2;
-    }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) is_last = (atomicAdd(&counters[blockIdx.x], 1u) == gridDim.y - 1) ? 1u : 0u;
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    float s1 = fold_partials_256(partials, static_cast<size_t>(2) * d.Cw, static_cast<int>(gridDim.y),
-                                 blockIdx.x * 256, d.Cw, red);
-    float s2 = fold_partials_256(partials + d.Cw, static_cast<size_t>(2) * d.Cw, static_cast<int>(gridDim.y),
-                                 blockIdx.x * 256, d.Cw, red);
+    float s1, s2;
+    if (!fold_slab_partials(p1, p2, partials, counters, d, red, &is_last, s1, s2)) return;
     int c;
     if (combine_groups(d, s1, s2, red, c)) {
         const float inv_m = 1.0f / static_cast<float>(d.M);
@@ -166,7 +252,6 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, const BnDims d, float* __re
             running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
         }
     }
-    if (threadIdx.x == 0) counters[blockIdx.x] = 0;
 }
 
 // Statistics that arrived as per-channel sums (accumulated by the convolution's epilogue): every thread
@@ -265,7 +350,7 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
 }
 
 // Folded-view column sums of dy_m and dy_m * xhat.
-__global__ void __launch_bounds__(BN_THREADS, 3)
+__global__ void __launch_bounds__(BN_THREADS, BN_BWD_CTAS_PER_SM)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const unsigned char* __restrict__ mask, const BnDims d, const float* __restrict__ mean,
                      const float* __restrict__ rstd, int relu, float* __restrict__ partials, unsigned int* __restrict__ counters,
@@ -314,22 +399,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     }
     const float p1 = cta_colsum(a1, red);
     const float p2 = cta_colsum(a2, red);
-    const int gc = blockIdx.x * 256 + threadIdx.x;
-    float* my = partials + static_cast<size_t>(blockIdx.y) * 2 * d.Cw;
-    if (gc < d.Cw) {
-        my[gc] = p1;
-        my[d.Cw + gc] = p2;
-    }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) is_last = (atomicAdd(&counters[blockIdx.x], 1u) == gridDim.y - 1) ? 1u : 0u;
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    float s1 = fold_partials_256(partials, static_cast<size_t>(2) * d.Cw, static_cast<int>(gridDim.y),
-                                 blockIdx.x * 256, d.Cw, red);
-    float s2 = fold_partials_256(partials + d.Cw, static_cast<size_t>(2) * d.Cw, static_cast<int>(gridDim.y),
-                                 blockIdx.x * 256, d.Cw, red);
+    float s1, s2;
+    if (!fold_slab_partials(p1, p2, partials, counters, d, red, &is_last, s1, s2)) return;
     int c;
     if (combine_groups(d, s1, s2, red, c)) {
         s2 = rstd[c] * (s2 - mean[c] * s1);
@@ -339,7 +410,6 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         coef[c] = s1 * inv_m;          // dbeta / M
         coef[d.C + c] = s2 * inv_m;    // dgamma / M
     }
-    if (threadIdx.x == 0) counters[blockIdx.x] = 0;
 }
 
 // dx = a * (dy_m - dbeta/M - xhat * dgamma/M); optionally dres = dy_m.
@@ -394,7 +464,7 @@ bn_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __re
     }
 }
 
-static int make_dims(const char* what, long long M, int C, BnDims* d) {
+static int make_dims(const char* what, long long M, int C, BnDims* d, int ctas_per_sm = BN_CTAS_PER_SM) {
     if (M <= 0 || C < 8 || C > 2048 || (C & (C - 1))) {
         set_last_error(what, "C must be a power of two in [8, 2048]");
         return TONY_ERR_UNSUPPORTED;
@@ -413,7 +483,7 @@ static int make_dims(const char* what, long long M, int C, BnDims* d) {
     d->Mv = M / k;
     d->Cw = C * k;
     const int col_tiles = (d->Cw + 255) / 256;
-    long long slabs = std::max(1, (std::min(device_sm_count(), BN_MAX_SMS) * BN_CTAS_PER_SM) / col_tiles);
+    long long slabs = std::max(1, (std::min(device_sm_count(), BN_MAX_SMS) * ctas_per_sm) / col_tiles);
     slabs = std::min<long long>(slabs, std::max<long long>(1, d->Mv / 32));
     d->rows_per_slab = static_cast<int>((d->Mv + slabs - 1) / slabs);
     return TONY_OK;
@@ -456,7 +526,7 @@ extern "C" int tony_bn_fwd(const void* x, const void* residual, const void* gamm
     float* ab = partials + bn_partials_floats();
     const int col_tiles = (d.Cw + 255) / 256;
     const int slabs = static_cast<int>((d.Mv + d.rows_per_slab - 1) / d.rows_per_slab);
-    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, static_cast<size_t>(col_tiles) * 4, s));
+    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));   // tile counters + the group counters behind them
     bn_stats_kernel<<<dim3(col_tiles, slabs), BN_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(x), d, partials, counters, static_cast<const __nv_bfloat16*>(gamma),
         static_cast<const __nv_bfloat16*>(beta), eps, momentum, mean, rstd, ab, running_mean, running_var);
@@ -493,7 +563,7 @@ extern "C" int tony_bn_bwd(const void* dy, const void* x, const void* mask, cons
     if (!dy || !x || !gamma || !mean || !rstd || !dx || !dgamma || !dbeta || !scratch || (relu && !mask))
         return TONY_ERR_INVALID;
     BnDims d;
-    int rc = make_dims("tony_bn_bwd", M, C, &d);
+    int rc = make_dims("tony_bn_bwd", M, C, &d, BN_BWD_CTAS_PER_SM);
     if (rc != TONY_OK) return rc;
     if (scratch_bytes < tony_bn_scratch_bytes(C)) {
         set_last_error("tony_bn_bwd", "scratch too small (see tony_bn_scratch_bytes)");
@@ -507,7 +577,7 @@ extern "C" int tony_bn_bwd(const void* dy, const void* x, const void* mask, cons
     float* coef = partials + bn_partials_floats() + 2 * C;
     const int col_tiles = (d.Cw + 255) / 256;
     const int slabs = static_cast<int>((d.Mv + d.rows_per_slab - 1) / d.rows_per_slab);
-    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, static_cast<size_t>(col_tiles) * 4, s));
+    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));   // tile counters + the group counters behind them
     bn_bwd_reduce_kernel<<<dim3(col_tiles, slabs), BN_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
         static_cast<const unsigned char*>(mask), d, mean, rstd, relu, partials, counters,
