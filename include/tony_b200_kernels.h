@@ -118,6 +118,14 @@ size_t tony_colsum_scratch_bytes(int cols);
 int tony_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out, float* scratch,
                      size_t scratch_bytes, int accumulate, void* stream);
 
+/* Backward of a fused Linear + activation whose incoming gradient comes from outside the library, in one
+ * pass: dpre[r,c] = dy[r,c] * act'(pre[r,c]) and dbias[c] (+)= sum_r dpre[r,c] (dbias may be NULL).
+ * act: 1 ReLU (pre may also be the ReLU output), 2 exact GELU, 3 tanh GELU.  Same scratch as tony_colsum_bf16.
+ * Replaces the eager fp32 passes of torch's gelu_backward / threshold_backward plus sum(dim=0) in the towers of
+ * the ps/worker jobs (tony-examples/mnist-tensorflow/mnist_distributed.py:127-129). */
+int tony_act_bwd_colsum_bf16(const void* dy, const void* pre, void* dpre, int act, int rows, int cols, long long ld,
+                             void* dbias, float* scratch, size_t scratch_bytes, int accumulate, void* stream);
+
 /* Same result as tony_colsum_bf16, but the partial-sum scratch is a fixed 2 MiB device
  * array built into the library, so the call performs no allocation and needs no scratch
  * pointer.  For host programs that cannot allocate device memory themselves: a framework

@@ -172,6 +172,48 @@ def test_colsum():
     _close(out, x.float().sum(0) + o0.float(), rel=1e-2)
 
 
+@pytest.mark.parametrize("rows,cols", [(5000, 1032), (40000, 256), (16384, 1024), (70, 8)])
+def test_colsum_two_level_fold(rows, cols):
+    """Slab counts on both sides of the single-level / two-level switch, repeated so that a counter left
+    non-zero by one call would show in the next."""
+    x = _rand(rows, cols)
+    ref = x.float().sum(0)
+    for _ in range(3):
+        _close(F.colsum(x), ref, rel=1e-2)
+
+
+@pytest.mark.parametrize("act", ["relu", "gelu", "gelu_tanh"])
+def test_act_bwd_bias_grad(act):
+    rows, cols = 3000, 520
+    dy, pre = _rand(rows, cols), _rand(rows, cols, scale=1.5)
+    p = pre.float().requires_grad_(True)
+    if act == "relu":
+        y = torch.relu(p)
+    else:
+        y = torch.nn.functional.gelu(p, approximate="tanh" if act == "gelu_tanh" else "none")
+    (ref,) = torch.autograd.grad(y, p, dy.float())
+    bias = torch.zeros(cols, device=DEV, dtype=torch.bfloat16)
+    dpre, db = F.act_bwd_bias_grad(dy, pre, act, bias)
+    _close(dpre, ref, rel=1e-2)
+    _close(db, ref.sum(0), rel=1e-2)
+    dpre2, none = F.act_bwd_bias_grad(dy, pre, act, None)
+    assert none is None and torch.equal(dpre2, dpre)
+
+
+def test_linear_act_backward_matches_torch():
+    """Fused Linear + activation against autograd on the same bf16-rounded operands."""
+    x, w, b = _rand(1024, 256), _rand(512, 256, scale=0.05), _rand(512, scale=0.1)
+    for act, fn in (("relu", torch.relu), ("gelu", torch.nn.functional.gelu)):
+        xs = [t.clone().requires_grad_(True) for t in (x, w, b)]
+        y = F.linear_act(xs[0], xs[1], xs[2], act=act)
+        dy = _rand(*y.shape)
+        y.backward(dy)
+        rs = [t.float().clone().requires_grad_(True) for t in (x, w, b)]
+        fn(rs[0] @ rs[1].t() + rs[2]).backward(dy.float())
+        for got, ref in zip(xs, rs):
+            _close(got.grad, ref.grad, rel=2e-2)
+
+
 def test_adamw_flat_matches_torch():
     from tony_b200.ops import optim as O
 

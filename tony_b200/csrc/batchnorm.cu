@@ -38,7 +38,6 @@ static size_t bn_slab_partials_floats() {   // slabs * 2 * Cw  <=  4 * SMs * 2 *
 }
 // second fold level: at most 64 groups of slabs x 2 x Cw, and groups ~ sqrt(slabs) with slabs * Cw <= 4 * SMs * 256
 constexpr size_t BN_GROUP_PARTIALS_FLOATS = 65536;
-constexpr int BN_GROUP_COUNTER0 = 64;
 __device__ __forceinline__ size_t bn_slab_partials_floats_dev() {
     return static_cast<size_t>(BN_CTAS_PER_SM) * BN_MAX_SMS * 2 * 256;
 }        // counters[0..63]: one per column tile; then 64 group counters per tile
@@ -107,96 +106,6 @@ __device__ __forceinline__ bool combine_groups(const BnDims& d, float& s1, float
     return true;
 }
 
-// Sum nparts rows of [2][cols] partials for columns col0 .. col0+255: warp w takes rows w, w+8, ..., two rows (8
-// float4 loads) in flight per thread, then the 8 warp sums meet in shared memory.  Thread t gets column col0 + t.
-__device__ __forceinline__ void fold_partials2_256(const float* __restrict__ partials, int nparts, int col0, int cols,
-                                                   float (*red)[256], float& s1, float& s2) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int c = col0 + lane * 8;
-    const size_t stride = static_cast<size_t>(2) * cols;
-    float t1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    float t2[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    if (c < cols) {
-        for (int k = warp; k < nparts; k += 16) {
-            float4 a[2][4];
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                const int kk = k + q * 8;
-                if (kk < nparts) {
-                    const float4* p = reinterpret_cast<const float4*>(partials + static_cast<size_t>(kk) * stride + c);
-                    const float4* p2 = reinterpret_cast<const float4*>(partials + static_cast<size_t>(kk) * stride + cols + c);
-                    a[q][0] = __ldcg(p);
-                    a[q][1] = __ldcg(p + 1);
-                    a[q][2] = __ldcg(p2);
-                    a[q][3] = __ldcg(p2 + 1);
-                } else {
-                    a[q][0] = a[q][1] = a[q][2] = a[q][3] = make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-            }
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                t1[0] += a[q][0].x; t1[1] += a[q][0].y; t1[2] += a[q][0].z; t1[3] += a[q][0].w;
-                t1[4] += a[q][1].x; t1[5] += a[q][1].y; t1[6] += a[q][1].z; t1[7] += a[q][1].w;
-                t2[0] += a[q][2].x; t2[1] += a[q][2].y; t2[2] += a[q][2].z; t2[3] += a[q][2].w;
-                t2[4] += a[q][3].x; t2[5] += a[q][3].y; t2[6] += a[q][3].z; t2[7] += a[q][3].w;
-            }
-        }
-    }
-    s1 = cta_colsum(t1, red);
-    s2 = cta_colsum(t2, red);
-}
-
-// Every CTA of the (column tile, slab) grid hands in its two column partials; exactly one CTA per column tile
-// returns true with the totals (thread t: column tile * 256 + t).  Two levels, each closed by the CTA that
-// arrives last: groups of ~sqrt(slabs) slabs, then the group sums - a fixed summation order, and neither level
-// reads more than ~25 rows (one CTA walking all 592 slab rows was 25 us behind an 8 us streaming pass).
-__device__ __noinline__ bool fold_slab_partials(float p1, float p2, float* __restrict__ partials,
-                                                   unsigned int* __restrict__ counters, const BnDims& d,
-                                                   float (*red)[256], unsigned int* flag, float& s1, float& s2) {
-    const int nparts = static_cast<int>(gridDim.y);
-    int gs = 8;
-    while (gs * gs < nparts) ++gs;
-    const int ngroups = (nparts + gs - 1) / gs;
-    const int grp = static_cast<int>(blockIdx.y) / gs;
-    const int gsize = min(gs, nparts - grp * gs);
-    const int gc = blockIdx.x * 256 + threadIdx.x;
-    float* gparts = partials + bn_slab_partials_floats_dev();
-    unsigned int* gcount = counters + BN_GROUP_COUNTER0 + blockIdx.x * 64 + grp;
-    float* my = partials + static_cast<size_t>(blockIdx.y) * 2 * d.Cw;
-    if (gc < d.Cw) {
-        my[gc] = p1;
-        my[d.Cw + gc] = p2;
-    }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) *flag = (atomicAdd(gcount, 1u) == static_cast<unsigned int>(gsize - 1)) ? 1u : 0u;
-    __syncthreads();
-    if (!*flag) return false;
-    __threadfence();
-    fold_partials2_256(partials + static_cast<size_t>(grp) * gs * 2 * d.Cw, gsize, blockIdx.x * 256, d.Cw, red, s1, s2);
-    if (ngroups == 1) {
-        if (threadIdx.x == 0) *gcount = 0;
-        return true;
-    }
-    float* gp = gparts + static_cast<size_t>(grp) * 2 * d.Cw;
-    if (gc < d.Cw) {
-        gp[gc] = s1;
-        gp[d.Cw + gc] = s2;
-    }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        *gcount = 0;
-        *flag = (atomicAdd(&counters[blockIdx.x], 1u) == static_cast<unsigned int>(ngroups - 1)) ? 1u : 0u;
-    }
-    __syncthreads();
-    if (!*flag) return false;
-    __threadfence();
-    fold_partials2_256(gparts, ngroups, blockIdx.x * 256, d.Cw, red, s1, s2);
-    if (threadIdx.x == 0) counters[blockIdx.x] = 0;
-    return true;
-}
-
 __global__ void __launch_bounds__(BN_THREADS, BN_CTAS_PER_SM)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, const BnDims d, float* __restrict__ partials,
                 unsigned int* __restrict__ counters, const __nv_bfloat16* __restrict__ gamma,
@@ -233,8 +142,11 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, const BnDims d, float* __re
     }
     const float p1 = cta_colsum(a1, red);
     const float p2 = cta_colsum(a2, red);
-    float s1, s2;
-    if (!fold_slab_partials(p1, p2, partials, counters, d, red, &is_last, s1, s2)) return;
+    const float pp[2] = {p1, p2};
+    float ss[2];
+    if (!fold_two_level_256<2>(pp, partials, partials + bn_slab_partials_floats_dev(), counters, d.Cw, red, &is_last, ss))
+        return;
+    float s1 = ss[0], s2 = ss[1];
     int c;
     if (combine_groups(d, s1, s2, red, c)) {
         const float inv_m = 1.0f / static_cast<float>(d.M);
@@ -399,8 +311,11 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     }
     const float p1 = cta_colsum(a1, red);
     const float p2 = cta_colsum(a2, red);
-    float s1, s2;
-    if (!fold_slab_partials(p1, p2, partials, counters, d, red, &is_last, s1, s2)) return;
+    const float pp[2] = {p1, p2};
+    float ss[2];
+    if (!fold_two_level_256<2>(pp, partials, partials + bn_slab_partials_floats_dev(), counters, d.Cw, red, &is_last, ss))
+        return;
+    float s1 = ss[0], s2 = ss[1];
     int c;
     if (combine_groups(d, s1, s2, red, c)) {
         s2 = rstd[c] * (s2 - mean[c] * s1);

@@ -58,15 +58,21 @@ __global__ void colsum_finalize_kernel(const float* __restrict__ partials, int s
     out[c] = __float2bfloat16(s);
 }
 
-// Single-launch form used by tony_colsum_bf16: every CTA publishes its partial row, the last
-// CTA of each column tile (found with a counter that it resets to zero again) folds the
-// slabs and writes the bf16 result.  Saves one ~6 us launch per bias gradient (121 per
-// BERT-large step).  Counters live in the first 4 KB of the caller's scratch; the host clears
+// Single-launch form used by tony_colsum_bf16: every CTA publishes its partial row and the slabs are folded
+// in two levels by the CTAs that arrive last (fold_two_level_256 in common.cuh).  Saves one ~6 us launch per bias
+// gradient (121 per BERT-large step).  Counters live in the first 4 KB of the caller's scratch; the host clears
 // them on the stream before each launch.
+//
+// ACT != 0 turns the pass into the backward of a fused Linear + activation whose incoming gradient arrives from
+// outside the library: g = x * act'(pre) is written to `gout` and its column sums (the bias gradient) come out of
+// the same read - one pass instead of ATen's three fp32 passes plus a separate column sum.
+// ACT: 1 ReLU (pre may be the ReLU output), 2 exact GELU, 3 tanh GELU.
+template <int ACT>
 __global__ void __launch_bounds__(CS_THREADS)
 colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, long long ld,
-                    int rows_per_slab, float* __restrict__ partials, unsigned int* __restrict__ counters,
-                    __nv_bfloat16* __restrict__ out, int accumulate) {
+                    int rows_per_slab, float* __restrict__ partials, float* __restrict__ gparts,
+                    unsigned int* __restrict__ counters, __nv_bfloat16* __restrict__ out, int accumulate,
+                    const __nv_bfloat16* __restrict__ pre, __nv_bfloat16* __restrict__ gout) {
     __shared__ float red[CS_THREADS / 32][256];
     __shared__ unsigned int is_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -75,24 +81,53 @@ colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, lon
     const int r1 = min(rows, r0 + rows_per_slab);
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (col < cols) {
-        // eight rows in flight per warp; the last batch is predicated instead of falling back to a
-        // one-row-at-a-time loop (each of those iterations was a full memory round trip)
+        // rows in flight per warp: eight (four with the second operand); the last batch is predicated instead of
+        // falling back to a one-row-at-a-time loop (each of those iterations was a full memory round trip)
         constexpr int W = CS_THREADS / 32;
-        for (int r = r0 + warp; r < r1; r += 8 * W) {
-            uint4 u[8];
+        constexpr int Q = ACT ? 4 : 8;
+        for (int r = r0 + warp; r < r1; r += Q * W) {
+            uint4 u[Q], v[ACT ? Q : 1];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
+            for (int k = 0; k < Q; ++k) {
                 const int rr = r + k * W;
-                u[k] = rr < r1 ? ld_global_nc_v4(x + static_cast<size_t>(rr) * ld + col) : make_uint4(0, 0, 0, 0);
+                const size_t o = static_cast<size_t>(rr) * ld + col;
+                u[k] = rr < r1 ? ld_global_nc_v4(x + o) : make_uint4(0, 0, 0, 0);
+                if (ACT) v[k] = rr < r1 ? ld_global_nc_v4(pre + o) : make_uint4(0, 0, 0, 0);
             }
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
+            for (int k = 0; k < Q; ++k) {
                 const uint32_t w[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
+                if (ACT) {
+                    const uint32_t pw[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+                    uint32_t ow[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float2 f = unpack_bf16x2(w[j]);
-                    acc[2 * j] += f.x;
-                    acc[2 * j + 1] += f.y;
+                    for (int j = 0; j < 4; ++j) {
+                        float2 f = unpack_bf16x2(w[j]);
+                        const float2 q = unpack_bf16x2(pw[j]);
+                        if (ACT == 1) {
+                            f.x = q.x > 0.f ? f.x : 0.f;
+                            f.y = q.y > 0.f ? f.y : 0.f;
+                        } else if (ACT == 2) {
+                            f.x *= dgelu_erf(q.x);
+                            f.y *= dgelu_erf(q.y);
+                        } else {
+                            f.x *= dgelu_tanh(q.x);
+                            f.y *= dgelu_tanh(q.y);
+                        }
+                        ow[j] = pack_bf16x2(f.x, f.y);
+                        const float2 g = unpack_bf16x2(ow[j]);     // sum what was stored
+                        acc[2 * j] += g.x;
+                        acc[2 * j + 1] += g.y;
+                    }
+                    const int rr = r + k * W;
+                    if (rr < r1) st_global_v4(gout + static_cast<size_t>(rr) * ld + col, make_uint4(ow[0], ow[1], ow[2], ow[3]));
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float2 f = unpack_bf16x2(w[j]);
+                        acc[2 * j] += f.x;
+                        acc[2 * j + 1] += f.y;
+                    }
                 }
             }
         }
@@ -104,32 +139,25 @@ colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, lon
     float s = 0.f;
 #pragma unroll
     for (int w = 0; w < CS_THREADS / 32; ++w) s += red[w][c];
+    __syncthreads();
     const int gc = blockIdx.x * 256 + c;
-    if (gc < cols) partials[static_cast<size_t>(blockIdx.y) * cols + gc] = s;
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const unsigned int prev = atomicAdd(&counters[blockIdx.x], 1u);
-        is_last = (prev == gridDim.y - 1) ? 1u : 0u;
-    }
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    float t = fold_partials_256(partials, static_cast<size_t>(cols), static_cast<int>(gridDim.y),
-                                blockIdx.x * 256, cols, red);
-    if (gc < cols) {
+    const float pp[1] = {s};
+    float tt[1];
+    if (!fold_two_level_256<1>(pp, partials, gparts, counters, cols, red, &is_last, tt)) return;
+    if (gc < cols && out != nullptr) {
+        float t = tt[0];
         if (accumulate) t += __bfloat162float(out[gc]);
         out[gc] = __float2bfloat16(t);
     }
-    if (threadIdx.x == 0) counters[blockIdx.x] = 0;
 }
 
 }  // namespace tony
 
 using namespace tony;
 
+constexpr int CS_MAX_GROUPS = 16;   // second fold level: 160 slabs -> groups of 13
 static size_t colsum_partials_bytes(int cols) {
-    return static_cast<size_t>(CS_MAX_SLABS_FUSED) * static_cast<size_t>(cols) * sizeof(float);
+    return static_cast<size_t>(CS_MAX_SLABS_FUSED + CS_MAX_GROUPS) * static_cast<size_t>(cols) * sizeof(float);
 }
 
 extern "C" size_t tony_colsum_scratch_bytes(int cols) {
@@ -137,16 +165,16 @@ extern "C" size_t tony_colsum_scratch_bytes(int cols) {
     return 4096 + colsum_partials_bytes(cols);
 }
 
-extern "C" int tony_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out,
-                                float* scratch, size_t scratch_bytes, int accumulate,
-                                void* stream) {
-    if (!x || !out || !scratch || rows <= 0 || cols <= 0) return TONY_ERR_INVALID;
-    if ((cols % 8) != 0 || (ld % 8) != 0 || (reinterpret_cast<uintptr_t>(x) & 15)) {
-        set_last_error("tony_colsum_bf16", "cols and ld must be multiples of 8; x 16B aligned");
+static int colsum_launch(const char* what, const void* x, const void* pre, void* gout, int act, int rows, int cols,
+                         long long ld, void* out, float* scratch, size_t scratch_bytes, int accumulate, void* stream) {
+    if (!x || !scratch || rows <= 0 || cols <= 0) return TONY_ERR_INVALID;
+    if ((cols % 8) != 0 || (ld % 8) != 0 || (reinterpret_cast<uintptr_t>(x) & 15) ||
+        (reinterpret_cast<uintptr_t>(pre) & 15) || (reinterpret_cast<uintptr_t>(gout) & 15)) {
+        set_last_error(what, "cols and ld must be multiples of 8; matrices 16B aligned");
         return TONY_ERR_INVALID;
     }
     if (scratch_bytes < tony_colsum_scratch_bytes(cols)) {
-        set_last_error("tony_colsum_bf16", "scratch too small (see tony_colsum_scratch_bytes)");
+        set_last_error(what, "scratch too small (see tony_colsum_scratch_bytes)");
         return TONY_ERR_INVALID;
     }
     cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -155,22 +183,47 @@ extern "C" int tony_colsum_bf16(const void* x, int rows, int cols, long long ld,
     slabs = std::min(slabs, std::max(1, rows / 64));
     const int rows_per_slab = (rows + slabs - 1) / slabs;
     slabs = (rows + rows_per_slab - 1) / rows_per_slab;
-    // scratch layout: [4 KB of per-column-tile counters][partial rows].  The counters are
-    // cleared on the stream before every call, so nothing depends on what the caller's
-    // scratch held before (the last CTA also leaves them at zero).
-    if (col_tiles > 1024) {
-        set_last_error("tony_colsum_bf16", "more than 262144 columns");
+    // scratch layout: [4 KB of counters][partial rows][group rows].  The counters are cleared on the stream
+    // before every call, so nothing depends on what the caller's scratch held before (the closing CTAs also
+    // leave them at zero).
+    if (fold_counter_words(col_tiles, slabs) > 1024) {
+        set_last_error(what, "too many columns for the 4 KB of counters");
         return TONY_ERR_TOO_LARGE;
     }
     unsigned int* counters = reinterpret_cast<unsigned int*>(scratch);
     float* partials = scratch + 1024;
-    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, static_cast<size_t>(col_tiles) * 4, s));
-    colsum_fused_kernel<<<dim3(col_tiles, slabs), CS_THREADS, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(x), rows, cols, ld, rows_per_slab, partials, counters,
-        static_cast<__nv_bfloat16*>(out), accumulate);
+    float* gparts = partials + static_cast<size_t>(CS_MAX_SLABS_FUSED) * cols;
+    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
+    const dim3 grid(col_tiles, slabs);
+    const __nv_bfloat16* xx = static_cast<const __nv_bfloat16*>(x);
+    const __nv_bfloat16* pp = static_cast<const __nv_bfloat16*>(pre);
+    __nv_bfloat16* oo = static_cast<__nv_bfloat16*>(out);
+    __nv_bfloat16* gg = static_cast<__nv_bfloat16*>(gout);
+    switch (act) {
+        case 0: colsum_fused_kernel<0><<<grid, CS_THREADS, 0, s>>>(xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg); break;
+        case 1: colsum_fused_kernel<1><<<grid, CS_THREADS, 0, s>>>(xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg); break;
+        case 2: colsum_fused_kernel<2><<<grid, CS_THREADS, 0, s>>>(xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg); break;
+        default: colsum_fused_kernel<3><<<grid, CS_THREADS, 0, s>>>(xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg); break;
+    }
     count_launch();
     TONY_CUDA_CHECK(cudaGetLastError());
     return TONY_OK;
+}
+
+extern "C" int tony_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out,
+                                float* scratch, size_t scratch_bytes, int accumulate,
+                                void* stream) {
+    if (!out) return TONY_ERR_INVALID;
+    return colsum_launch("tony_colsum_bf16", x, nullptr, nullptr, 0, rows, cols, ld, out, scratch, scratch_bytes,
+                         accumulate, stream);
+}
+
+extern "C" int tony_act_bwd_colsum_bf16(const void* dy, const void* pre, void* dpre, int act, int rows, int cols,
+                                        long long ld, void* dbias, float* scratch, size_t scratch_bytes,
+                                        int accumulate, void* stream) {
+    if (!pre || !dpre || act < 1 || act > 3) return TONY_ERR_INVALID;
+    return colsum_launch("tony_act_bwd_colsum_bf16", dy, pre, dpre, act, rows, cols, ld, dbias, scratch, scratch_bytes,
+                         accumulate, stream);
 }
 
 // ---------------------------------------------------------------------------------------

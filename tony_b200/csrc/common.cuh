@@ -556,6 +556,129 @@ __device__ __forceinline__ float dgelu_tanh(float x) {
     return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * du;
 }
 
+// ---- two-level tail of the single-launch column reductions -----------------------------------------------------
+// Grid (column tile, slab).  Every CTA hands in NS column partials per thread (thread t: column tile * 256 + t);
+// exactly one CTA per column tile returns true holding the totals.  Slabs are folded in groups of ~sqrt(slabs) by
+// the CTA of the group that arrives last, the group sums by the last of those: a fixed summation order, and no CTA
+// reads more than ~25 rows (a single CTA walking 592 rows took 25 us behind an 8 us streaming pass).
+// partials: [slabs][NS][cols]; gparts: [groups][NS][cols]; counters: gridDim.x tile counters, then gridDim.x * groups
+// group counters, all zero on entry and zero again on exit (at most 1024 words: the hosts check it).
+template <int NS>
+__device__ __forceinline__ void fold_rows_256(const float* __restrict__ partials, int nparts, int col0, int cols,
+                                              float (*red)[256], float (&s)[NS]) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c = col0 + lane * 8;
+    const size_t stride = static_cast<size_t>(NS) * cols;
+    float t[NS][8];
+#pragma unroll
+    for (int i = 0; i < NS; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[i][j] = 0.f;
+    if (c < cols) {
+        constexpr int Q = NS == 1 ? 4 : 2;          // rows in flight per warp: 8 float4 loads per thread
+        for (int k = warp; k < nparts; k += 8 * Q) {
+            float4 a[Q][NS][2];
+#pragma unroll
+            for (int q = 0; q < Q; ++q) {
+                const int kk = k + q * 8;
+#pragma unroll
+                for (int i = 0; i < NS; ++i) {
+                    if (kk < nparts) {
+                        const float4* p = reinterpret_cast<const float4*>(partials + static_cast<size_t>(kk) * stride +
+                                                                          static_cast<size_t>(i) * cols + c);
+                        a[q][i][0] = __ldcg(p);
+                        a[q][i][1] = __ldcg(p + 1);
+                    } else {
+                        a[q][i][0] = a[q][i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < Q; ++q)
+#pragma unroll
+                for (int i = 0; i < NS; ++i) {
+                    t[i][0] += a[q][i][0].x; t[i][1] += a[q][i][0].y; t[i][2] += a[q][i][0].z; t[i][3] += a[q][i][0].w;
+                    t[i][4] += a[q][i][1].x; t[i][5] += a[q][i][1].y; t[i][6] += a[q][i][1].z; t[i][7] += a[q][i][1].w;
+                }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = t[i][j];
+        __syncthreads();
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) v += red[w][threadIdx.x];
+        __syncthreads();
+        s[i] = v;
+    }
+}
+
+__device__ __forceinline__ int fold_group_size(int nparts) {
+    int gs = 8;
+    while (gs * gs < nparts) ++gs;
+    return gs;
+}
+// words of counters a launch with `tiles` column tiles and `slabs` slabs touches (hosts check <= 1024)
+static inline int fold_counter_words(int tiles, int slabs) {
+    int gs = 8;
+    while (gs * gs < slabs) ++gs;
+    return tiles * (1 + (slabs + gs - 1) / gs);
+}
+// floats of group partials such a launch needs
+static inline size_t fold_group_floats(int slabs, int ns, int cols) {
+    int gs = 8;
+    while (gs * gs < slabs) ++gs;
+    return static_cast<size_t>((slabs + gs - 1) / gs) * ns * cols;
+}
+
+template <int NS>
+__device__ __noinline__ bool fold_two_level_256(const float (&p)[NS], float* __restrict__ partials,
+                                                float* __restrict__ gparts, unsigned int* __restrict__ counters,
+                                                int cols, float (*red)[256], unsigned int* flag, float (&s)[NS]) {
+    const int nparts = static_cast<int>(gridDim.y);
+    const int gs = fold_group_size(nparts);
+    const int ngroups = (nparts + gs - 1) / gs;
+    const int grp = static_cast<int>(blockIdx.y) / gs;
+    const int gsize = min(gs, nparts - grp * gs);
+    const int gc = blockIdx.x * 256 + threadIdx.x;
+    unsigned int* gcount = counters + gridDim.x + blockIdx.x * ngroups + grp;
+    float* my = partials + static_cast<size_t>(blockIdx.y) * NS * cols;
+    if (gc < cols) {
+#pragma unroll
+        for (int i = 0; i < NS; ++i) my[static_cast<size_t>(i) * cols + gc] = p[i];
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) *flag = (atomicAdd(gcount, 1u) == static_cast<unsigned int>(gsize - 1)) ? 1u : 0u;
+    __syncthreads();
+    if (!*flag) return false;
+    __threadfence();
+    fold_rows_256<NS>(partials + static_cast<size_t>(grp) * gs * NS * cols, gsize, blockIdx.x * 256, cols, red, s);
+    if (ngroups == 1) {
+        if (threadIdx.x == 0) *gcount = 0;
+        return true;
+    }
+    float* gp = gparts + static_cast<size_t>(grp) * NS * cols;
+    if (gc < cols) {
+#pragma unroll
+        for (int i = 0; i < NS; ++i) gp[static_cast<size_t>(i) * cols + gc] = s[i];
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        *gcount = 0;
+        *flag = (atomicAdd(&counters[blockIdx.x], 1u) == static_cast<unsigned int>(ngroups - 1)) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (!*flag) return false;
+    __threadfence();
+    fold_rows_256<NS>(gparts, ngroups, blockIdx.x * 256, cols, red, s);
+    if (threadIdx.x == 0) counters[blockIdx.x] = 0;
+    return true;
+}
+
 // Tail of the single-launch column reductions: the last CTA of a 256-column tile folds `nparts`
 // fp32 partial rows (`stride` floats apart) with ALL of its 8 warps — warp w takes parts w, w+8,
 // ..., lane l the columns [8l, 8l+8) with two 16-byte L2 loads per part, two parts in flight —

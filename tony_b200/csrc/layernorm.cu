@@ -13,6 +13,7 @@ namespace tony {
 
 constexpr int LN_WARPS = 8;
 constexpr int LN_MAX_PARTIALS = 512;
+constexpr int LN_MAX_GROUPS = 32;     // second fold level: groups of ~sqrt(slabs) slabs
 
 __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
     const uint32_t w[4] = {u.x, u.y, u.z, u.w};
@@ -202,30 +203,20 @@ layernorm_bwd_dgdb_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloa
         sg += red[0][w][c];
         sb += red[1][w][c];
     }
+    __syncthreads();
     const int gc = blockIdx.x * 256 + c;
-    float* my = partials + static_cast<size_t>(blockIdx.y) * 2 * H;
-    my[gc] = sg;
-    my[H + gc] = sb;
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const unsigned int prev = atomicAdd(&counters[blockIdx.x], 1u);
-        is_last = (prev == gridDim.y - 1) ? 1u : 0u;
-    }
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    float tg = fold_partials_256(partials, static_cast<size_t>(2) * H, static_cast<int>(gridDim.y),
-                                 blockIdx.x * 256, H, red[0]);
-    float tb = fold_partials_256(partials + H, static_cast<size_t>(2) * H, static_cast<int>(gridDim.y),
-                                 blockIdx.x * 256, H, red[1]);
+    const float pp[2] = {sg, sb};
+    float tt[2];
+    if (!fold_two_level_256<2>(pp, partials, partials + static_cast<size_t>(LN_MAX_PARTIALS) * 2 * H, counters, H, red[0],
+                               &is_last, tt))
+        return;
+    float tg = tt[0], tb = tt[1];
     if (accumulate) {
         tg += __bfloat162float(dgamma[gc]);
         tb += __bfloat162float(dbeta[gc]);
     }
     dgamma[gc] = __float2bfloat16(tg);
     dbeta[gc] = __float2bfloat16(tb);
-    if (threadIdx.x == 0) counters[blockIdx.x] = 0;
 }
 
 template <int NV>
@@ -253,13 +244,13 @@ static int launch_bwd(const void* dy, const void* x, const void* gamma, const fl
         static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<__nv_bfloat16*>(dx), rows,
         static_cast<const __nv_bfloat16*>(add));
     TONY_CUDA_CHECK(cudaGetLastError());
-    // scratch: [4 KB counters][partials: slabs x 2 x H floats]
+    // scratch: [4 KB counters][partials: slabs x 2 x H floats][group partials]
     const int col_tiles = H / 256;
     int slabs = std::max(1, std::min({LN_MAX_PARTIALS, (sms * 4) / col_tiles, std::max(1, rows / 16)}));
     const int rows_per_slab = (rows + slabs - 1) / slabs;
     slabs = (rows + rows_per_slab - 1) / rows_per_slab;
     unsigned int* counters = reinterpret_cast<unsigned int*>(scratch);
-    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, static_cast<size_t>(col_tiles) * 4, s));
+    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
     layernorm_bwd_dgdb_kernel<<<dim3(col_tiles, slabs), LN_RED_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x), mean, rstd, rows, H,
         rows_per_slab, scratch + 1024, counters, static_cast<__nv_bfloat16*>(dgamma),
@@ -294,7 +285,7 @@ extern "C" int tony_layernorm_fwd(const void* x, const void* gamma, const void* 
 }
 
 extern "C" size_t tony_layernorm_bwd_scratch_bytes(int H) {
-    return 4096 + static_cast<size_t>(LN_MAX_PARTIALS) * 2 * static_cast<size_t>(H) * sizeof(float);
+    return 4096 + static_cast<size_t>(LN_MAX_PARTIALS + LN_MAX_GROUPS) * 2 * static_cast<size_t>(H) * sizeof(float);
 }
 
 static int layernorm_bwd_impl(const void* dy, const void* x, const void* gamma, const float* mean,

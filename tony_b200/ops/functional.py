@@ -185,6 +185,32 @@ def _weight_bias_grad(dy2: torch.Tensor, x2: torch.Tensor, weight: torch.Tensor,
     return wdest.finish(out), bdest.finish(db)
 
 
+_ACT_BWD_KERNEL = {"relu": 1, "gelu": 2, "gelu_tanh": 3}
+
+
+def act_bwd_bias_grad(dy2: torch.Tensor, pre: torch.Tensor, act: str, bias: Optional[torch.Tensor]):
+    """One pass over ``dy2`` and ``pre``: returns ``(dy2 * act'(pre), bias gradient for autograd)``; the bias
+    gradient goes to the parameter's flat-bucket slot when it has one (``tony_act_bwd_colsum_bf16``)."""
+    _check_bf16(dy2, pre)
+    if not dy2.is_contiguous():
+        dy2 = dy2.contiguous()
+    rows, cols = dy2.shape
+    if cols % 8 or pre.stride(0) != dy2.stride(0) or pre.stride(1) != 1:
+        raise ValueError("act_bwd_bias_grad: needs a multiple of 8 columns and pre laid out like dy")
+    dpre = torch.empty_like(dy2)
+    dest = _GradDest(bias) if bias is not None else None
+    db = None
+    if dest is not None:
+        db = dest.tensor if dest.tensor is not None else torch.empty(cols, dtype=torch.bfloat16, device=dy2.device)
+    lib = _lib.lib()
+    nbytes = int(lib.tony_colsum_scratch_bytes(cols))
+    scratch = workspace("colsum", nbytes, dy2.device)
+    check(lib.tony_act_bwd_colsum_bf16(ptr(dy2), ptr(pre), ptr(dpre), _ACT_BWD_KERNEL[act], rows, cols, dy2.stride(0),
+                                       ptr(db), ptr(scratch), nbytes, int(dest.accumulate) if dest else 0,
+                                       cur_stream()), "tony_act_bwd_colsum_bf16")
+    return dpre, (dest.finish(db) if dest is not None else None)
+
+
 def _bias_grad(dy2: torch.Tensor, bias: Optional[torch.Tensor]):
     if bias is None:
         return None
@@ -314,22 +340,11 @@ class _LinearActFn(torch.autograd.Function):
         x2, weight, pre = ctx.saved_tensors
         N = weight.shape[0]
         dy2 = dy.reshape(-1, N)
-        if ctx.act == "relu":
-            dpre = dy2 * (pre > 0)
-        elif ctx.act == "gelu":
-            p = pre.float()
-            dpre = (dy2.float() * (0.5 * (1 + torch.erf(p * 0.7071067811865476))
-                                   + p * torch.exp(-0.5 * p * p) * 0.3989422804014327)).to(torch.bfloat16)
-        else:
-            p = pre.float()
-            u = 0.7978845608028654 * (p + 0.044715 * p ** 3)
-            t = torch.tanh(u)
-            dpre = (dy2.float() * (0.5 * (1 + t) + 0.5 * p * (1 - t * t) * 0.7978845608028654
-                                   * (1 + 3 * 0.044715 * p * p))).to(torch.bfloat16)
-        dpre = dpre.contiguous()
+        # the incoming gradient is not produced by a GEMM of ours, so the activation gradient cannot ride in an
+        # epilogue: one own pass computes it together with the bias gradient
+        dpre, db = act_bwd_bias_grad(dy2, pre, ctx.act, ctx.bias)
         dx = gemm(dpre, weight, b_mn=True).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
         dw = _weight_grad(dpre, x2, weight)
-        db = _bias_grad(dpre, ctx.bias)
         return dx, dw, db, None
 
 

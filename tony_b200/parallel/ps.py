@@ -82,17 +82,14 @@ class _AgLinearFn(torch.autograd.Function):
         dy2 = dy.reshape(-1, N)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        if ctx.act == "relu":
-            dy2 = (dy2 * (pre > 0)).contiguous()
-        elif ctx.act in ("gelu", "gelu_tanh"):
-            p = pre.float().requires_grad_(True)
-            with torch.enable_grad():
-                g = torch.nn.functional.gelu(p, approximate="tanh" if ctx.act == "gelu_tanh" else "none")
-            dy2 = torch.autograd.grad(g, p, dy2.float())[0].to(torch.bfloat16).contiguous()
+        db = None
+        if ctx.act in ("relu", "gelu", "gelu_tanh"):
+            dy2, db = F.act_bwd_bias_grad(dy2, pre, ctx.act, ctx.bias)     # `pre` is the ReLU output for relu
+        elif ctx.bias is not None:
+            db = F._bias_grad(dy2, ctx.bias)
         # the forward left a complete local copy of W in the flat parameter buffer
         dx = F.gemm(dy2, weight, b_mn=True).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
         dw = F._weight_grad(dy2, x2, weight)
-        db = F._bias_grad(dy2, ctx.bias)
         return dx, dw, db, None, None
 
 
