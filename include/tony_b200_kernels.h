@@ -91,7 +91,11 @@ int tony_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K
 int tony_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean,
                        float* rstd, int rows, int H, float eps, void* stream);
 /* dx, dgamma, dbeta.  `scratch` holds per-CTA fp32 partials for dgamma/dbeta:
- * tony_layernorm_bwd_scratch_bytes(H) bytes.  accumulate != 0 adds into dgamma/dbeta. */
+ * tony_layernorm_bwd_scratch_bytes(H) bytes.  accumulate != 0 adds into dgamma/dbeta.
+ * Scratch contract shared by tony_layernorm_bwd*, tony_colsum_bf16, tony_act_bwd_colsum_bf16, tony_bn_fwd and
+ * tony_bn_bwd: the first 4096 bytes are arrival counters that must be ZERO before the first call with a buffer
+ * (cudaMemset once after allocating it); every call leaves them zero, so nothing is cleared per call.  Calls
+ * sharing a buffer must be ordered on one stream.  TONY_B200_CLEAR_COUNTERS=1 clears them on every call. */
 size_t tony_layernorm_bwd_scratch_bytes(int H);
 int tony_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
                        const float* rstd, void* dx, void* dgamma, void* dbeta, int rows, int H,

@@ -344,7 +344,7 @@ def test_layernorm_bwd_h4096_and_accumulate():
     dg, db = dg0.clone(), db0.clone()
     lib = _lib.lib()
     nb = int(lib.tony_layernorm_bwd_scratch_bytes(H))
-    scratch = F.workspace("ln_bwd", nb, x.device)
+    scratch = F.workspace("ln_bwd", nb, x.device, counters=True)
     _lib.check(lib.tony_layernorm_bwd(_lib.ptr(dy), _lib.ptr(x), _lib.ptr(g), _lib.ptr(mean), _lib.ptr(rstd),
                                       _lib.ptr(dx), _lib.ptr(dg), _lib.ptr(db), rows, H, _lib.ptr(scratch), nb, 1,
                                       _lib.cur_stream()), "ln_bwd")

@@ -56,6 +56,7 @@ def test_static_scratch_colsum_matches_regular_entry_point_twice_in_a_row():
         got, want = init.clone(), init.clone()
         nbytes = lib.tony_colsum_scratch_bytes(cols)
         scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        scratch[:4096].zero_()      # the regular entry point's contract: its counters start at zero
         rc = lib.tony_colsum_bf16(x.data_ptr(), rows, cols, x.stride(0), want.data_ptr(), scratch.data_ptr(),
                                   nbytes, accumulate, stream)
         assert rc == 0, lib.tony_last_error()

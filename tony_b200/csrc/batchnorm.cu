@@ -441,7 +441,7 @@ extern "C" int tony_bn_fwd(const void* x, const void* residual, const void* gamm
     float* ab = partials + bn_partials_floats();
     const int col_tiles = (d.Cw + 255) / 256;
     const int slabs = static_cast<int>((d.Mv + d.rows_per_slab - 1) / d.rows_per_slab);
-    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));   // tile counters + the group counters behind them
+    if (clear_counters_each_call()) TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
     bn_stats_kernel<<<dim3(col_tiles, slabs), BN_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(x), d, partials, counters, static_cast<const __nv_bfloat16*>(gamma),
         static_cast<const __nv_bfloat16*>(beta), eps, momentum, mean, rstd, ab, running_mean, running_var);
@@ -492,7 +492,7 @@ extern "C" int tony_bn_bwd(const void* dy, const void* x, const void* mask, cons
     float* coef = partials + bn_partials_floats() + 2 * C;
     const int col_tiles = (d.Cw + 255) / 256;
     const int slabs = static_cast<int>((d.Mv + d.rows_per_slab - 1) / d.rows_per_slab);
-    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));   // tile counters + the group counters behind them
+    if (clear_counters_each_call()) TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
     bn_bwd_reduce_kernel<<<dim3(col_tiles, slabs), BN_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
         static_cast<const unsigned char*>(mask), d, mean, rstd, relu, partials, counters,

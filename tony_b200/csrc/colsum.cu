@@ -68,7 +68,7 @@ __global__ void colsum_finalize_kernel(const float* __restrict__ partials, int s
 // the same read - one pass instead of ATen's three fp32 passes plus a separate column sum.
 // ACT: 1 ReLU (pre may be the ReLU output), 2 exact GELU, 3 tanh GELU.
 template <int ACT>
-__global__ void __launch_bounds__(CS_THREADS)
+__global__ void __launch_bounds__(CS_THREADS, 4)   // with no minimum ptxas aims lower and serialises the row loads
 colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, long long ld,
                     int rows_per_slab, float* __restrict__ partials, float* __restrict__ gparts,
                     unsigned int* __restrict__ counters, __nv_bfloat16* __restrict__ out, int accumulate,
@@ -84,20 +84,38 @@ colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, lon
         // rows in flight per warp: eight (four with the second operand); the last batch is predicated instead of
         // falling back to a one-row-at-a-time loop (each of those iterations was a full memory round trip)
         constexpr int W = CS_THREADS / 32;
-        constexpr int Q = ACT ? 4 : 8;
-        for (int r = r0 + warp; r < r1; r += Q * W) {
-            uint4 u[Q], v[ACT ? Q : 1];
+        if constexpr (ACT == 0) {
+            for (int r = r0 + warp; r < r1; r += 8 * W) {
+                uint4 u[8];
 #pragma unroll
-            for (int k = 0; k < Q; ++k) {
-                const int rr = r + k * W;
-                const size_t o = static_cast<size_t>(rr) * ld + col;
-                u[k] = rr < r1 ? ld_global_nc_v4(x + o) : make_uint4(0, 0, 0, 0);
-                if (ACT) v[k] = rr < r1 ? ld_global_nc_v4(pre + o) : make_uint4(0, 0, 0, 0);
+                for (int k = 0; k < 8; ++k) {
+                    const int rr = r + k * W;
+                    u[k] = rr < r1 ? ld_global_nc_v4(x + static_cast<size_t>(rr) * ld + col) : make_uint4(0, 0, 0, 0);
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const uint32_t w[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float2 f = unpack_bf16x2(w[j]);
+                        acc[2 * j] += f.x;
+                        acc[2 * j + 1] += f.y;
+                    }
+                }
             }
+        } else {
+            for (int r = r0 + warp; r < r1; r += 4 * W) {
+                uint4 u[4], v[4];
 #pragma unroll
-            for (int k = 0; k < Q; ++k) {
-                const uint32_t w[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
-                if (ACT) {
+                for (int k = 0; k < 4; ++k) {
+                    const int rr = r + k * W;
+                    const size_t o = static_cast<size_t>(rr) * ld + col;
+                    u[k] = rr < r1 ? ld_global_nc_v4(x + o) : make_uint4(0, 0, 0, 0);
+                    v[k] = rr < r1 ? ld_global_nc_v4(pre + o) : make_uint4(0, 0, 0, 0);
+                }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t w[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
                     const uint32_t pw[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
                     uint32_t ow[4];
 #pragma unroll
@@ -121,13 +139,6 @@ colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, lon
                     }
                     const int rr = r + k * W;
                     if (rr < r1) st_global_v4(gout + static_cast<size_t>(rr) * ld + col, make_uint4(ow[0], ow[1], ow[2], ow[3]));
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const float2 f = unpack_bf16x2(w[j]);
-                        acc[2 * j] += f.x;
-                        acc[2 * j + 1] += f.y;
-                    }
                 }
             }
         }
@@ -193,7 +204,7 @@ static int colsum_launch(const char* what, const void* x, const void* pre, void*
     unsigned int* counters = reinterpret_cast<unsigned int*>(scratch);
     float* partials = scratch + 1024;
     float* gparts = partials + static_cast<size_t>(CS_MAX_SLABS_FUSED) * cols;
-    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
+    if (clear_counters_each_call()) TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
     const dim3 grid(col_tiles, slabs);
     const __nv_bfloat16* xx = static_cast<const __nv_bfloat16*>(x);
     const __nv_bfloat16* pp = static_cast<const __nv_bfloat16*>(pre);

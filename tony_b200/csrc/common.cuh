@@ -28,6 +28,10 @@ namespace tony {
 void set_last_error(const char* what, const char* detail);
 void count_launch(int n = 1);  // bench accounting: kernels launched by this library
 int device_sm_count();         // SM count of the current device (cached)
+// The column reductions keep their arrival counters in the first 4 KB of the caller's scratch and leave them at
+// zero, so the caller zeroes that head ONCE; TONY_B200_CLEAR_COUNTERS=1 clears it on the stream before every call
+// again (one memset node per launch: ~250 per BERT-large step).
+bool clear_counters_each_call();
 // 2-D bf16 tensor map, 128-byte swizzle, `inner` contiguous (defined in gemm_tcgen05.cu)
 int make_tmap_2d_bf16(CUtensorMap* map, const void* ptr, long long inner_extent, long long outer_extent,
                       long long ld, int box_inner, int box_outer);
@@ -634,7 +638,7 @@ static inline size_t fold_group_floats(int slabs, int ns, int cols) {
 }
 
 template <int NS>
-__device__ __noinline__ bool fold_two_level_256(const float (&p)[NS], float* __restrict__ partials,
+__device__ __forceinline__ bool fold_two_level_256(const float (&p)[NS], float* __restrict__ partials,
                                                 float* __restrict__ gparts, unsigned int* __restrict__ counters,
                                                 int cols, float (*red)[256], unsigned int* flag, float (&s)[NS]) {
     const int nparts = static_cast<int>(gridDim.y);

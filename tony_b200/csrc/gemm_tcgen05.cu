@@ -1020,6 +1020,15 @@ static int make_tmap_2d_bf16_mode(CUtensorMap* map, const void* ptr, long long i
     return TONY_OK;
 }
 
+bool clear_counters_each_call() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("TONY_B200_CLEAR_COUNTERS");
+        v = (e && atoi(e) != 0) ? 1 : 0;
+    }
+    return v == 1;
+}
+
 int device_sm_count() {
     static int cached[64] = {0};
     int dev = 0;

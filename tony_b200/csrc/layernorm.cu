@@ -142,9 +142,10 @@ layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat1
     }
 }
 
+constexpr int LN_RED_CTAS_PER_SM = 3;   // 80 registers hold the 8 row vectors in flight; the grid is sized to match
 constexpr int LN_RED_THREADS = 256;  // 8 warps x 32 lanes x 8 columns = 256 columns per CTA
 
-__global__ void __launch_bounds__(LN_RED_THREADS)
+__global__ void __launch_bounds__(LN_RED_THREADS, LN_RED_CTAS_PER_SM)
 layernorm_bwd_dgdb_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                           const float* __restrict__ mean, const float* __restrict__ rstd, int rows, int H,
                           int rows_per_slab, float* __restrict__ partials, unsigned int* __restrict__ counters,
@@ -246,11 +247,11 @@ static int launch_bwd(const void* dy, const void* x, const void* gamma, const fl
     TONY_CUDA_CHECK(cudaGetLastError());
     // scratch: [4 KB counters][partials: slabs x 2 x H floats][group partials]
     const int col_tiles = H / 256;
-    int slabs = std::max(1, std::min({LN_MAX_PARTIALS, (sms * 4) / col_tiles, std::max(1, rows / 16)}));
+    int slabs = std::max(1, std::min({LN_MAX_PARTIALS, (sms * LN_RED_CTAS_PER_SM) / col_tiles, std::max(1, rows / 16)}));
     const int rows_per_slab = (rows + slabs - 1) / slabs;
     slabs = (rows + rows_per_slab - 1) / rows_per_slab;
     unsigned int* counters = reinterpret_cast<unsigned int*>(scratch);
-    TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
+    if (clear_counters_each_call()) TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
     layernorm_bwd_dgdb_kernel<<<dim3(col_tiles, slabs), LN_RED_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x), mean, rstd, rows, H,
         rows_per_slab, scratch + 1024, counters, static_cast<__nv_bfloat16*>(dgamma),

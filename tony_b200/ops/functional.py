@@ -42,12 +42,15 @@ _ACT_BWD = {"gelu": EPI_DGELU_ERF, "gelu_tanh": EPI_DGELU_TANH, "relu": EPI_DREL
 _workspaces: dict = {}
 
 
-def workspace(name: str, nbytes: int, device) -> torch.Tensor:
-    """Per-device cached scratch buffer (never shrinks)."""
+def workspace(name: str, nbytes: int, device, counters: bool = False) -> torch.Tensor:
+    """Per-device cached scratch buffer (never shrinks).  ``counters=True``: the kernels keep arrival counters in
+    the first 4 KB and leave them at zero, so that head is zeroed here once, when the buffer is created."""
     key = (name, torch.device(device).index)
     buf = _workspaces.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        if counters:
+            buf[:4096].zero_()
         _workspaces[key] = buf
     return buf
 
@@ -116,7 +119,7 @@ def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool
         accumulate = False
     lib = _lib.lib()
     nbytes = int(lib.tony_colsum_scratch_bytes(cols))
-    scratch = workspace("colsum", nbytes, x.device)
+    scratch = workspace("colsum", nbytes, x.device, counters=True)
     check(lib.tony_colsum_bf16(ptr(x), rows, cols, x.stride(0), ptr(out), ptr(scratch), nbytes,
                                int(accumulate), cur_stream()), "tony_colsum_bf16")
     return out
@@ -204,7 +207,7 @@ def act_bwd_bias_grad(dy2: torch.Tensor, pre: torch.Tensor, act: str, bias: Opti
         db = dest.tensor if dest.tensor is not None else torch.empty(cols, dtype=torch.bfloat16, device=dy2.device)
     lib = _lib.lib()
     nbytes = int(lib.tony_colsum_scratch_bytes(cols))
-    scratch = workspace("colsum", nbytes, dy2.device)
+    scratch = workspace("colsum", nbytes, dy2.device, counters=True)
     check(lib.tony_act_bwd_colsum_bf16(ptr(dy2), ptr(pre), ptr(dpre), _ACT_BWD_KERNEL[act], rows, cols, dy2.stride(0),
                                        ptr(db), ptr(scratch), nbytes, int(dest.accumulate) if dest else 0,
                                        cur_stream()), "tony_act_bwd_colsum_bf16")
@@ -394,7 +397,7 @@ class _LayerNormFn(torch.autograd.Function):
             dg_t, db_t = dg.tensor, db.tensor
             acc = dg.accumulate
         nbytes = int(lib.tony_layernorm_bwd_scratch_bytes(H))
-        scratch = workspace("ln_bwd", nbytes, x2.device)
+        scratch = workspace("ln_bwd", nbytes, x2.device, counters=True)
         check(lib.tony_layernorm_bwd(ptr(dy2), ptr(x2), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx),
                                      ptr(dg_t), ptr(db_t), rows, H, ptr(scratch), nbytes, int(acc),
                                      cur_stream()), "tony_layernorm_bwd")
@@ -449,7 +452,7 @@ class _LayerNormResidualFn(torch.autograd.Function):
             dg_t, db_t = dg.tensor, db.tensor
             acc = dg.accumulate
         nbytes = int(lib.tony_layernorm_bwd_scratch_bytes(H))
-        scratch = workspace("ln_bwd", nbytes, x2.device)
+        scratch = workspace("ln_bwd", nbytes, x2.device, counters=True)
         if dres is None:
             check(lib.tony_layernorm_bwd(ptr(dy2), ptr(x2), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx),
                                          ptr(dg_t), ptr(db_t), rows, H, ptr(scratch), nbytes, int(acc),
@@ -630,7 +633,7 @@ class _BatchNormActFn(torch.autograd.Function):
                                                    cur_stream()), "tony_bn_fwd_from_sums")
         else:
             nbytes = _lib.lib().tony_bn_scratch_bytes(C)
-            scratch = workspace("batchnorm", nbytes, x.device)
+            scratch = workspace("batchnorm", nbytes, x.device, counters=True)
             check(_lib.lib().tony_bn_fwd(ptr(x), ptr(res), ptr(gamma), ptr(beta), ptr(y), ptr(mask), ptr(mean),
                                          ptr(rstd), ptr(running_mean), ptr(running_var), M, C, eps, momentum,
                                          int(relu), ptr(scratch), nbytes, cur_stream()), "tony_bn_fwd")
@@ -647,7 +650,7 @@ class _BatchNormActFn(torch.autograd.Function):
         dres = torch.empty_like(x) if has_res else None
         dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(gamma)
         nbytes = _lib.lib().tony_bn_scratch_bytes(C)
-        scratch = workspace("batchnorm", nbytes, x.device)
+        scratch = workspace("batchnorm", nbytes, x.device, counters=True)
         check(_lib.lib().tony_bn_bwd(ptr(dy), ptr(x), ptr(mask), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx),
                                      ptr(dres), ptr(dgamma), ptr(dbeta), M, C, relu, ptr(scratch), nbytes,
                                      cur_stream()), "tony_bn_bwd")
