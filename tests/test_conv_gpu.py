@@ -102,6 +102,39 @@ def test_conv2d_autograd_function_channels_last():
         _close(w.grad.permute(0, 3, 1, 2), wr.grad, what=f"dw {C}->{K} {R}x{R}/{stride}")
 
 
+@pytest.mark.parametrize("stride_d,with_stats", [(1, False), (2, False), (2, True), (1, True)])
+def test_conv1x1_pair_accumulates_both_data_gradients(stride_d, with_stats):
+    """Projection block entry: main 1x1 and (strided) shortcut 1x1 read the same input; dx must be the SUM of
+    both data gradients (the shortcut's kernel accumulates into the main path's result)."""
+    from tony_b200.ops import functional as F
+
+    dev = torch.device("cuda")
+    torch.manual_seed(11)
+    C, K1, Kd = 128, 64, 256
+    x = torch.randn(4, C, 12, 12, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    x.requires_grad_(True)
+    w1 = (torch.randn(K1, 1, 1, C, device=dev) / C ** 0.5).to(torch.bfloat16).requires_grad_(True)
+    wd = (torch.randn(Kd, 1, 1, C, device=dev) / C ** 0.5).to(torch.bfloat16).requires_grad_(True)
+    s1 = torch.zeros(2, K1, device=dev) if with_stats else None
+    sd = torch.zeros(2, Kd, device=dev) if with_stats else None
+    y1, yd = F.conv1x1_pair(x, w1, wd, stride_d, s1, sd)
+    g1, gd = torch.randn_like(y1), torch.randn_like(yd)
+    torch.autograd.backward([y1, yd], [g1, gd])
+    xr = x.detach().float().requires_grad_(True)
+    w1r = w1.detach().float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    wdr = wd.detach().float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    r1 = torch.nn.functional.conv2d(xr, w1r)
+    rd = torch.nn.functional.conv2d(xr, wdr, stride=stride_d)
+    torch.autograd.backward([r1, rd], [g1.float(), gd.float()])
+    _close(y1, r1, what="main fwd")
+    _close(yd, rd, what="shortcut fwd")
+    _close(x.grad, xr.grad, what="dx (sum of both branches)")
+    _close(w1.grad.permute(0, 3, 1, 2), w1r.grad, what="dw main")
+    _close(wd.grad.permute(0, 3, 1, 2), wdr.grad, what="dw shortcut")
+    if with_stats:
+        _close(sd[0], yd.float().sum(dim=(0, 2, 3)), tol=1e-2, what="shortcut column sums")
+
+
 def test_stem_conv7x7s2_space_to_depth_matches_fp32():
     """The 3-channel 7x7/2 stem through the space-to-depth + overlapping-window tensor map."""
     from tony_b200.ops import functional as F

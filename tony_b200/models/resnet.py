@@ -79,6 +79,17 @@ class ConvBN(nn.Module):
         return self.bn(y, stats=stats), idt
 
 
+def conv_bn_pair(main: "ConvBN", short: "ConvBN", x):
+    """-> (main(x), short(x)) for the first block of a stage: both pointwise convolutions read the block input and
+    the shortcut's data gradient accumulates into the main path's (``F.conv1x1_pair``)."""
+    arena = main._arena[0]
+    take = main.use_stats and arena is not None and main.training
+    s1 = arena.take(main.weight.shape[0]) if take else None
+    sd = arena.take(short.weight.shape[0]) if take else None
+    y1, yd = F.conv1x1_pair(x, main.weight, short.weight, short.stride, s1, sd)
+    return main.bn(y1, stats=s1), short.bn(yd, stats=sd)
+
+
 class StemConvBN(nn.Module):
     """7x7/2 convolution of the 3-channel image (space-to-depth form) -> BatchNorm -> ReLU."""
 
@@ -150,6 +161,9 @@ class Bottleneck(nn.Module):
     def forward(self, x):
         if self.fused and self.down is None and isinstance(self.cb1, ConvBN) and x.requires_grad:
             y, idt = self.cb1.forward_fork(x)          # identity block: x feeds conv1 AND the residual add
+            return self.cb3(self.cb2(y), residual=idt)
+        if self.fused and self.down is not None and isinstance(self.cb1, ConvBN) and x.requires_grad:
+            y, idt = conv_bn_pair(self.cb1, self.down, x)     # projection block: one node for both readers of x
             return self.cb3(self.cb2(y), residual=idt)
         idt = x if self.down is None else self.down(x)
         if self.fused:      # ReLU and the residual add ride in the BatchNorm kernels

@@ -877,6 +877,68 @@ def conv1x1_fork(x, weight, stats: Optional[torch.Tensor] = None):
     return _PointwiseConvForkFn.apply(x, weight, stats)
 
 
+class _PointwiseConvPairFn(torch.autograd.Function):
+    """``(conv1x1(x, w1), conv1x1(x, wd, stride))`` as ONE autograd node: the first block of a ResNet stage feeds
+    its input to the main path and to the (possibly strided) projection shortcut.  Backward computes the main
+    path's data gradient and lets the shortcut's data-gradient kernel ACCUMULATE into it, so the sum of the two
+    branch gradients never runs as a separate elementwise kernel over the activation."""
+
+    @staticmethod
+    def forward(ctx, x, w1, wd, stride_d, stats1, statsd):
+        x = x.contiguous(memory_format=torch.channels_last)
+        xn = x.permute(0, 2, 3, 1)
+        N, H, W, C = xn.shape
+        K1, Kd = w1.shape[0], wd.shape[0]
+        if stats1 is None:
+            y1 = gemm(xn.reshape(N * H * W, C), w1.view(K1, C)).view(N, H, W, K1)
+        else:
+            y1 = conv2d_nhwc(xn, w1, 1, 0, stats=stats1)
+        if stride_d == 1 and statsd is None:
+            yd = gemm(xn.reshape(N * H * W, C), wd.view(Kd, C)).view(N, H, W, Kd)
+        else:
+            yd = conv2d_nhwc(xn, wd, stride_d, 0, stats=statsd)
+        ctx.save_for_backward(xn, w1, wd)
+        ctx.stride_d = stride_d
+        return y1.permute(0, 3, 1, 2), yd.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy1, dyd):
+        xn, w1, wd = ctx.saved_tensors
+        sd = ctx.stride_d
+        N, H, W, C = xn.shape
+        M = N * H * W
+        K1, Kd = w1.shape[0], wd.shape[0]
+        d1 = dy1.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1)
+        dd = dyd.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1)
+        dx = None
+        if ctx.needs_input_grad[0]:                      # both data gradients before either weight slot closes
+            dxn = gemm(d1.reshape(M, K1), w1.view(K1, C), b_mn=True).view(N, H, W, C)
+            if sd == 1:
+                gemm(dd.reshape(M, Kd), wd.view(Kd, C), b_mn=True, out=dxn.view(M, C), flags=EPI_ACCUMULATE)
+            else:
+                conv2d_dgrad_nhwc(dd, wd, xn.shape, sd, 0, out=dxn, accumulate=True)
+            dx = dxn.permute(0, 3, 1, 2)
+        dest = _GradDest(w1)
+        g1 = gemm(d1.reshape(M, K1), xn.reshape(M, C), a_mn=True, b_mn=True,
+                  out=dest.tensor.view(K1, C) if dest.tensor is not None else None,
+                  flags=EPI_ACCUMULATE if dest.accumulate else 0).view(K1, 1, 1, C)
+        g1 = dest.finish(g1)
+        dest = _GradDest(wd)
+        if sd == 1:
+            gd = gemm(dd.reshape(M, Kd), xn.reshape(M, C), a_mn=True, b_mn=True,
+                      out=dest.tensor.view(Kd, C) if dest.tensor is not None else None,
+                      flags=EPI_ACCUMULATE if dest.accumulate else 0).view(Kd, 1, 1, C)
+        else:
+            gd = conv2d_wgrad_nhwc(dd, xn, wd.shape, sd, 0, out=dest.tensor, accumulate=dest.accumulate)
+        return dx, g1, dest.finish(gd), None, None, None
+
+
+def conv1x1_pair(x, w1, wd, stride_d: int = 1, stats1: Optional[torch.Tensor] = None,
+                 statsd: Optional[torch.Tensor] = None):
+    """``(conv2d(x, w1), conv2d(x, wd, stride_d))`` for two pointwise filters (see ``_PointwiseConvPairFn``)."""
+    return _PointwiseConvPairFn.apply(x, w1, wd, stride_d, stats1, statsd)
+
+
 def conv2d(x, weight, stride: int = 1, pad: int = 0, stats: Optional[torch.Tensor] = None):
     """``conv2d`` for a bf16 channels-last ``x`` ``[N, C, H, W]`` and a ``[K, R, S, C]`` (KRSC) filter."""
     return _Conv2dFn.apply(x, weight, stride, pad, stats)
