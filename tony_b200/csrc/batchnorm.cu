@@ -62,6 +62,12 @@ __device__ __forceinline__ uint4 pack8f(const float (&v)[8]) {
     return o;
 }
 
+__device__ __forceinline__ void load8f(const float* __restrict__ p, float (&v)[8]) {   // p 32-byte aligned
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+    v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+
 struct BnDims {
     long long M;      // rows of the real [M, C] matrix
     int C;            // channels
@@ -191,23 +197,24 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
     const int cg = static_cast<int>(tid % groups);
     const long long row0 = tid / groups;
     const long long row_stride = static_cast<long long>(gridDim.x) * BN_THREADS / groups;
+    // per-channel coefficients with 16-byte loads: as 8 scalar loads per array, lanes 32 bytes apart, this prologue
+    // was ~20 us of L1 wavefronts on the 7x7 / 14x14 layers whose whole pass moves 25-50 MB
     float a[8], b[8];
     if (sums.sum == nullptr) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            a[j] = ab[cg * 8 + j];
-            b[j] = ab[C + cg * 8 + j];
-        }
+        load8f(ab + cg * 8, a);
+        load8f(ab + C + cg * 8, b);
     } else {
         const float inv_m = 1.0f / static_cast<float>(M);
-        float g[8], be[8];
+        float g[8], be[8], s1[8], s2[8];
         unpack8f(__ldg(reinterpret_cast<const uint4*>(sums.gamma + cg * 8)), g);
         unpack8f(__ldg(reinterpret_cast<const uint4*>(sums.beta + cg * 8)), be);
+        load8f(sums.sum + cg * 8, s1);
+        load8f(sums.sqsum + cg * 8, s2);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int c = cg * 8 + j;
-            const float mu = sums.sum[c] * inv_m;
-            const float var = fmaxf(sums.sqsum[c] * inv_m - mu * mu, 0.f);
+            const float mu = s1[j] * inv_m;
+            const float var = fmaxf(s2[j] * inv_m - mu * mu, 0.f);
             const float rs = rsqrtf(var + sums.eps);
             a[j] = g[j] * rs;
             b[j] = be[j] - mu * a[j];
@@ -266,7 +273,8 @@ __global__ void __launch_bounds__(BN_THREADS, BN_BWD_CTAS_PER_SM)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const unsigned char* __restrict__ mask, const BnDims d, const float* __restrict__ mean,
                      const float* __restrict__ rstd, int relu, float* __restrict__ partials, unsigned int* __restrict__ counters,
-                     __nv_bfloat16* __restrict__ dgamma, __nv_bfloat16* __restrict__ dbeta, float* __restrict__ coef) {
+                     __nv_bfloat16* __restrict__ dgamma, __nv_bfloat16* __restrict__ dbeta, float* __restrict__ coef,
+                     const __nv_bfloat16* __restrict__ gamma) {
     __shared__ float red[8][256];
     __shared__ unsigned int is_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -318,38 +326,35 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     float s1 = ss[0], s2 = ss[1];
     int c;
     if (combine_groups(d, s1, s2, red, c)) {
-        s2 = rstd[c] * (s2 - mean[c] * s1);
+        const float rs = rstd[c], mu = mean[c];
+        s2 = rs * (s2 - mu * s1);
         dbeta[c] = __float2bfloat16(s1);
         dgamma[c] = __float2bfloat16(s2);
+        // dx = a*(g - c1 - (x - mu)*rs*c2) = a*g + P*x + Q with c1 = dbeta/M, c2 = dgamma/M: the elementwise
+        // pass reads three ready vectors instead of deriving them from five in every thread
         const float inv_m = 1.0f / static_cast<float>(d.M);
-        coef[c] = s1 * inv_m;          // dbeta / M
-        coef[d.C + c] = s2 * inv_m;    // dgamma / M
+        const float c1 = s1 * inv_m, c2 = s2 * inv_m;
+        const float a = __bfloat162float(gamma[c]) * rs;
+        coef[c] = a;
+        coef[d.C + c] = -a * rs * c2;
+        coef[2 * d.C + c] = a * (rs * c2 * mu - c1);
     }
 }
 
 // dx = a * (dy_m - dbeta/M - xhat * dgamma/M); optionally dres = dy_m.
 __global__ void __launch_bounds__(BN_THREADS, 4)
 bn_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                 const unsigned char* __restrict__ mask, const float* __restrict__ mean,
-                 const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ gamma,
-                 const float* __restrict__ coef, int relu, __nv_bfloat16* __restrict__ dx,
-                 __nv_bfloat16* __restrict__ dres, long long M, int C) {
+                 const unsigned char* __restrict__ mask, const float* __restrict__ coef, int relu,
+                 __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, long long M, int C) {
     const int groups = C / 8;
     const long long tid = static_cast<long long>(blockIdx.x) * BN_THREADS + threadIdx.x;
     const int cg = static_cast<int>(tid % groups);
     const long long row0 = tid / groups;
     const long long row_stride = static_cast<long long>(gridDim.x) * BN_THREADS / groups;
-    // dx = a*(g - c1 - (x - mu)*rs*c2) = a*g + P*x + Q  with  P = -a*rs*c2,  Q = a*(rs*c2*mu - c1):
-    // three per-channel vectors in registers instead of five, two FMAs per element
-    float aa[8], P[8], Q[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const int c = cg * 8 + j;
-        const float rs = rstd[c], mu = mean[c];
-        aa[j] = __bfloat162float(gamma[c]) * rs;
-        P[j] = -aa[j] * rs * coef[C + c];
-        Q[j] = aa[j] * (rs * coef[C + c] * mu - coef[c]);
-    }
+    float aa[8], P[8], Q[8];          // written by the reduction's closing CTA
+    load8f(coef + cg * 8, aa);
+    load8f(coef + C + cg * 8, P);
+    load8f(coef + 2 * C + cg * 8, Q);
     for (long long r = row0; r < M; r += 2 * row_stride) {      // two rows (four 16-byte loads) in flight
         const long long r2 = r + row_stride;
         const bool two = r2 < M;
@@ -409,7 +414,7 @@ static int elementwise_grid(long long M, int C) {
     const long long rows_per_block = std::max(1, BN_THREADS / groups);
     long long blocks = (M + rows_per_block - 1) / rows_per_block;
     if (groups > BN_THREADS) blocks = M * ((groups + BN_THREADS - 1) / BN_THREADS);
-    return static_cast<int>(std::min<long long>(blocks, device_sm_count() * 16LL));
+    return static_cast<int>(std::min<long long>(blocks, device_sm_count() * 8LL));   // one wave of 8 CTAs per SM
 }
 
 }  // namespace tony
@@ -418,9 +423,9 @@ using namespace tony;
 
 extern "C" size_t tony_bn_scratch_bytes(int C) {
     const int Cw = C < 256 ? 256 : C;
-    // [4 KB counters][partials: slabs x 2 x Cw][ab: 2 x C][coef: 2 x C]
+    // [4 KB counters][partials: slabs x 2 x Cw + group partials][ab: 2 x C][coef: 3 x C]
     (void)Cw;
-    return 4096 + (bn_partials_floats() + 4 * static_cast<size_t>(C)) * sizeof(float);
+    return 4096 + (bn_partials_floats() + 8 * static_cast<size_t>(C)) * sizeof(float);
 }
 
 extern "C" int tony_bn_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
@@ -496,12 +501,12 @@ extern "C" int tony_bn_bwd(const void* dy, const void* x, const void* mask, cons
     bn_bwd_reduce_kernel<<<dim3(col_tiles, slabs), BN_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
         static_cast<const unsigned char*>(mask), d, mean, rstd, relu, partials, counters,
-        static_cast<__nv_bfloat16*>(dgamma), static_cast<__nv_bfloat16*>(dbeta), coef);
+        static_cast<__nv_bfloat16*>(dgamma), static_cast<__nv_bfloat16*>(dbeta), coef,
+        static_cast<const __nv_bfloat16*>(gamma));
     TONY_CUDA_CHECK(cudaGetLastError());
     bn_bwd_dx_kernel<<<elementwise_grid(M, C), BN_THREADS, 0, s>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
-        static_cast<const unsigned char*>(mask), mean, rstd, static_cast<const __nv_bfloat16*>(gamma), coef, relu,
-        static_cast<__nv_bfloat16*>(dx),
+        static_cast<const unsigned char*>(mask), coef, relu, static_cast<__nv_bfloat16*>(dx),
         static_cast<__nv_bfloat16*>(dres), M, C);
     TONY_CUDA_CHECK(cudaGetLastError());
     count_launch(2);
