@@ -144,6 +144,44 @@ def test_resnet50_conv1x1_and_generic_ddp_hooks():
     assert all(l == l for l in losses) and losses[-1] < losses[0], losses
 
 
+@pytest.mark.parametrize("fused_layers", [False, True])
+def test_ddp_no_sync_accumulates_like_one_big_batch(fused_layers):
+    """Two micro-batches under no_sync() + one synchronising backward must move the parameters like a single
+    backward over the three batches at once; covers the hook path (stock nn.Linear) and the producers that
+    write straight into the flat bucket (models.nn.Linear + LayerNorm), and a step after it starts clean."""
+    import copy
+
+    from tony_b200.models import nn as tnn
+    from tony_b200.parallel.ddp import DistributedDataParallel
+
+    dev = torch.device("cuda")
+    torch.manual_seed(5)
+    if fused_layers:
+        net = torch.nn.Sequential(tnn.Linear(64, 256, device=dev), tnn.LayerNorm(256, device=dev),
+                                  tnn.Linear(256, 32, device=dev))
+    else:
+        net = torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.Tanh(), torch.nn.Linear(128, 32)).to(dev)
+    a = DistributedDataParallel(copy.deepcopy(net), device=dev, optimizer="sgd", lr=0.05, momentum=0.0,
+                                weight_decay=0.0, bucket_mb=0.01)
+    b = DistributedDataParallel(copy.deepcopy(net), device=dev, optimizer="sgd", lr=0.05, momentum=0.0,
+                                weight_decay=0.0, bucket_mb=0.01)
+    xs = [torch.randn(256, 64, device=dev).to(torch.bfloat16) for _ in range(3)]
+    start = a.store.param_buf.clone()
+    for _round in range(2):
+        with a.no_sync():
+            for x in xs[:2]:
+                (a(x).float().pow(2).mean() / 3).backward()
+        (a(xs[2]).float().pow(2).mean() / 3).backward()
+        a.step()
+        b(torch.cat(xs)).float().pow(2).mean().backward()      # one backward over the same 768 rows
+        b.step()
+        torch.cuda.synchronize()
+        moved = (b.store.param_buf.float() - start.float()).abs().max().item()
+        diff = (a.store.param_buf.float() - b.store.param_buf.float()).abs().max().item()
+        assert moved > 0 and diff <= 0.05 * moved + 2e-3, (diff, moved)
+    a.store.comm.check_status()
+
+
 def test_checkpoint_roundtrip(tmp_path):
     from tony_b200 import runtime
     from tony_b200.models import gpt2

@@ -66,7 +66,7 @@ class ParamSlot:
     """Where one parameter's gradient lives inside the flat gradient buffer."""
 
     __slots__ = ("store", "name", "offset", "numel", "shape", "grad_view", "expected", "written",
-                 "bucket")
+                 "bucket", "carried")
 
     def __init__(self, store, name, offset, numel, shape):
         self.store = store
@@ -77,15 +77,16 @@ class ParamSlot:
         self.grad_view: Optional[torch.Tensor] = None
         self.expected = 1   # gradient contributions per step (2 for tied embeddings)
         self.written = 0
+        self.carried = False  # holds the sum of earlier micro-batches (gradient accumulation, see no_sync)
         self.bucket: Optional[Bucket] = None
 
     def begin_write(self) -> bool:
         """True if an earlier contribution exists this step (the producer must accumulate)."""
-        return self.written > 0
+        return self.written > 0 or self.carried
 
     def end_write(self) -> None:
         self.written += 1
-        if self.written == self.expected:
+        if self.written == self.expected and not self.store._defer:
             self.store._slot_ready(self)
 
 
@@ -179,6 +180,7 @@ class FlatParamStore:
                 mask[slot.offset // ALIGN: _round_up(slot.offset + slot.numel, ALIGN) // ALIGN] = 1
         self.wd_mask = mask.to(self.device)
         self._ready_cb = None
+        self._defer = False       # inside no_sync(): gradients pile up in the flat buffer, nothing is launched
         self.reset_step()
 
     # -- bookkeeping -------------------------------------------------------------------
@@ -189,9 +191,31 @@ class FlatParamStore:
         """Declare that ``p`` receives ``uses`` gradient contributions per step (tied weights)."""
         self._by_param[id(p)].expected = uses
 
+    def end_micro_step(self) -> None:
+        """Close a backward pass whose gradients stay local (gradient accumulation): what was written is kept
+        and the next backward pass adds to it; slots it did not touch keep their earlier state."""
+        self.flush_hook_grads()
+        for s in self.slots:
+            if s.written:
+                s.carried = True
+                s.written = 0
+
+    def flush_hook_grads(self) -> None:
+        """Generic (hook) path: move gradients that are still waiting for the rest of their bucket."""
+        leftovers = getattr(self, "_pending_hook_grads", None)
+        if not leftovers:
+            return
+        for idx, lst in leftovers.items():
+            if lst:
+                torch._foreach_copy_([s_.grad_view for s_, _ in lst], [g_ for _, g_ in lst])
+                leftovers[idx] = []
+                for s_, _ in lst:
+                    s_.written += 1
+
     def reset_step(self) -> None:
         for s in self.slots:
             s.written = 0
+            s.carried = False
         for b in self.buckets:
             b.pending = len(b.slots)
             b.launched = False
@@ -345,19 +369,12 @@ class FusedOptimizer:
         (a replayed CUDA graph), so the per-slot bookkeeping is skipped."""
         st = self.store
         cur = torch.cuda.current_stream()
-        leftovers = getattr(st, "_pending_hook_grads", None)
-        if leftovers:
-            for idx, lst in leftovers.items():
-                if lst:
-                    torch._foreach_copy_([s_.grad_view for s_, _ in lst], [g_ for _, g_ in lst])
-                    for s_, _ in lst:
-                        s_.written += 1
-                    leftovers[idx] = []
+        st.flush_hook_grads()
         for b in st.buckets:
             if b.launched:
                 continue
             for s in b.slots:
-                if s.written == 0 and not grads_complete:
+                if s.written == 0 and not s.carried and not grads_complete:
                     s.grad_view.zero_()  # parameter unused this step
             if self.overlap:
                 self._bucket_ready(b)
@@ -370,7 +387,7 @@ class FusedOptimizer:
         st.reset_step()
 
     def zero_grad(self, set_to_none: bool = True):
-        pass  # gradients are overwritten, never accumulated across steps
+        pass  # gradients are overwritten by the next step's producers (or accumulated under no_sync)
 
     # -- checkpoint --------------------------------------------------------------------
     def state_dict(self):
