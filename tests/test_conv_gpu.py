@@ -25,11 +25,22 @@ CASES = [
     (1, 20, 12, 192, 320, 3, 1, 1),     # non-square, several 64-channel blocks, N tail over 256
     (2, 9, 11, 64, 72, 3, 2, 1),        # odd extents with stride 2, K % 64 != 0
     (4, 8, 8, 64, 64, 1, 1, 0),         # pointwise through the conv kernel itself (statistics path)
+    (3, 20, 20, 64, 64, 3, 1, 1),       # halo kernel, whole filter resident; ragged 16 x 8 tiles in both directions
+    (2, 33, 9, 128, 128, 3, 1, 1),      # halo kernel, filter ring, two channel blocks, three row tiles
 ]
 
 
+@pytest.fixture(params=["im2col", "halo"])
+def conv_form(request, monkeypatch):
+    """3x3 / stride-1 layers with <= 128 output channels can also run on the halo kernel (opt-in switch)."""
+    monkeypatch.setenv("TONY_B200_CONV_HALO", "1" if request.param == "halo" else "0")
+    return request.param
+
+
 @pytest.mark.parametrize("N,H,W,C,K,R,stride,pad", CASES)
-def test_conv2d_fprop_dgrad_wgrad_match_fp32(N, H, W, C, K, R, stride, pad):
+def test_conv2d_fprop_dgrad_wgrad_match_fp32(N, H, W, C, K, R, stride, pad, conv_form):
+    if conv_form == "halo" and not (R == 3 and stride == 1 and pad == 1):
+        pytest.skip("halo form covers 3x3 / stride 1 only")
     from tony_b200.ops import functional as F
 
     dev = torch.device("cuda")

@@ -112,7 +112,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
     uint64_t* o_free = pv_done + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_free + 1);
 
-    const int warp_idx = threadIdx.x >> 5;
+    const int warp_idx = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform: role branches and their loops stay on the uniform datapath
     const int lane = threadIdx.x & 31;
 
     if (warp_idx == 0 && lane == 0) {
@@ -494,7 +494,7 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
     uint64_t* dq_done = ds_full + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dq_done + 1);
 
-    const int warp_idx = threadIdx.x >> 5;
+    const int warp_idx = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform: role branches and their loops stay on the uniform datapath
     const int lane = threadIdx.x & 31;
     const int nq = p.seq / ATT_BM;
     const int bh = static_cast<int>(blockIdx.x) / nq;
@@ -699,7 +699,7 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmap_qkv128,
     uint64_t* acc_done = pd_full + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_done + 1);
 
-    const int warp_idx = threadIdx.x >> 5;
+    const int warp_idx = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform: role branches and their loops stay on the uniform datapath
     const int lane = threadIdx.x & 31;
     const int nk = p.seq / ATT_BM;
     const int bh = static_cast<int>(blockIdx.x) / nk;

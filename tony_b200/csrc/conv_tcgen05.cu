@@ -43,6 +43,25 @@ constexpr int CV_STAGING_BYTES = CV_EPI_WARPS * 2048;
 constexpr int CV_CHUNK_BYTES = 64 * 128;   // [64 rows][128 B]
 constexpr int CV_MAX_TAPS = 16;
 
+// Division by a launch-time constant as multiply + shift: q = (n * mul) >> shr, exact for 0 <= n < 2^31
+// (mul = floor(2^shr / d) + 1 with shr = 31 + ceil(log2 d)).  The tile -> (image, row, column) index math runs in
+// every warp for every tile; as 32-bit divisions it was a third of the instructions the epilogue warps issued.
+struct FastDiv {
+    uint32_t d, mul, shr;
+};
+static inline FastDiv make_fastdiv(int d) {
+    FastDiv f;
+    f.d = d > 0 ? static_cast<uint32_t>(d) : 1u;
+    uint32_t s = 0;
+    while ((1ull << s) < f.d) ++s;
+    f.shr = 31 + s;
+    f.mul = static_cast<uint32_t>((1ull << f.shr) / f.d + 1);
+    return f;
+}
+__device__ __forceinline__ int fdiv(int n, const FastDiv& f) {
+    return static_cast<int>((static_cast<unsigned long long>(static_cast<uint32_t>(n)) * f.mul) >> f.shr);
+}
+
 struct ConvTap {
     unsigned short off_w, off_h;   // im2col offsets from the tile's base pixel
     int wsel;                      // tap slot (r * S + s) inside the filter
@@ -70,17 +89,35 @@ struct ConvParams {
     // coordinate shift and the padding is the map's out-of-range zero fill.  An experiment kept as an option:
     // it is correct but not faster than the im2col form (see tony_conv2d_wgrad_bf16).
     int tiled, bw, bh, nbw, nbh, pad_w, pad_h;
+    // halo form (conv3x3_halo_tcgen05_kernel): a tile is a 16 x 8 patch of one image's output pixels
+    int halo, tiles_x, tiles_y, b_resident;
+    FastDiv fd_splits, fd_nblk, fd_tx, fd_ty, fd_pq, fd_q;   // filled by fill_fastdiv() right before the launch
 };
+static inline void fill_fastdiv(ConvParams& p) {
+    p.fd_splits = make_fastdiv(p.splits);
+    p.fd_nblk = make_fastdiv(p.num_n_blocks);
+    p.fd_tx = make_fastdiv(p.tiles_x);
+    p.fd_ty = make_fastdiv(p.tiles_y);
+    p.fd_pq = make_fastdiv(p.P * p.Q);
+    p.fd_q = make_fastdiv(p.Q);
+}
 
 __device__ __forceinline__ void tma_load_im2col_4d(const CUtensorMap* map, uint64_t* bar, void* smem_dst,
                                                    int32_t c, int32_t w, int32_t h, int32_t n,
                                                    uint16_t off_w, uint16_t off_h) {
+    // the two 16-bit offsets enter as 32-bit operands and are narrowed inside the asm block: as "h" operands
+    // fed from the uniform datapath they came out wrong
     asm volatile(
+        "{\n\t"
+        ".reg .b16 ow, oh;\n\t"
+        "cvt.u16.u32 ow, %7;\n\t"
+        "cvt.u16.u32 oh, %8;\n\t"
         "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
-        " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2], {ow, oh};\n\t"
+        "}\n"
         :
         : "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c), "r"(w),
-          "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+          "r"(h), "r"(n), "r"(static_cast<uint32_t>(off_w)), "r"(static_cast<uint32_t>(off_h))
         : "memory");
 }
 
@@ -90,13 +127,218 @@ __device__ __forceinline__ uint32_t cv_stg_addr(uint32_t base, int row, int unit
 
 // pixel index -> row index of the output tensor (rows of `ldc` elements)
 __device__ __forceinline__ long long cv_out_row(const ConvParams& p, int m) {
+    if (p.halo) {      // row (y, x) = (loc / 8, loc % 8) of tile (img, ty, tx); rows past the image are dropped
+        const int mt = m >> 7, loc = m & 127;
+        const int t2 = fdiv(mt, p.fd_tx), tx = mt - t2 * p.tiles_x;
+        const int img = fdiv(t2, p.fd_ty), ty = t2 - img * p.tiles_y;
+        const int y = ty * 16 + (loc >> 3), x = tx * 8 + (loc & 7);
+        if (y >= p.P || x >= p.Q) return -1;
+        return (static_cast<long long>(img) * p.P + y) * p.Q + x;
+    }
     if (!p.out_strided) return m;
     const int pq = p.P * p.Q;
-    const int n = m / pq;
+    const int n = fdiv(m, p.fd_pq);
     const int rem = m - n * pq;
-    const int pp = rem / p.Q;
+    const int pp = fdiv(rem, p.fd_q);
     const int qq = rem - pp * p.Q;
     return (static_cast<long long>(n) * p.OH + pp * p.osh + p.oph) * p.OW + qq * p.osw + p.opw;
+}
+
+// Epilogue role (warps 2..17 of both convolution kernels): TMEM -> registers -> per-warp transposed staging tile
+// -> 16-byte global stores of whole rows, with the optional accumulate, split-K partial and BatchNorm-statistics
+// paths.  `staging` is CV_STAGING_BYTES of shared memory, `stat_acc` 2 * BLOCK_N floats (zeroed by the caller).
+template <int BLOCK_N, int CS>
+__device__ __forceinline__ void cv_epilogue_role(const ConvParams& p, uint8_t* staging, float* stat_acc,
+                                                 uint32_t tmem_base, uint64_t* tmem_full_bar,
+                                                 uint64_t* tmem_empty_bar, int worker, int num_workers, int num_units,
+                                                 uint32_t crank, int warp_idx, int lane) {
+    const int quarter = warp_idx & 3;
+    const int group = (warp_idx - 2) >> 2;
+    const uint32_t stg = smem_u32(staging + (warp_idx - 2) * 2048);
+    const int unit16 = lane & 3;
+    const int etid = threadIdx.x - 64;     // 0..511 among the epilogue warps
+    int stat_nblk = -1;
+    // one column of BatchNorm partials per lane and 32-column chunk this warp owns (see the epilogue loop)
+    constexpr int STAT_SLOTS = (BLOCK_N / 32 + CV_EPI_WARPS / 4 - 1) / (CV_EPI_WARPS / 4);
+    static_assert(STAT_SLOTS <= 2, "the slot select below assumes at most two chunks per warp");
+    float acc1[STAT_SLOTS], acc2[STAT_SLOTS];
+#pragma unroll
+    for (int i = 0; i < STAT_SLOTS; ++i) acc1[i] = acc2[i] = 0.f;
+    // the four quarter warps of a group own the same columns: meet in shared memory, once per column block
+    auto stat_fold = [&]() {
+#pragma unroll
+        for (int i = 0; i < STAT_SLOTS; ++i) {
+            const int lc = (group + i * (CV_EPI_WARPS / 4)) * 32 + unit16 * 8 + (lane >> 2);
+            if (lc < BLOCK_N) {
+                atomicAdd(stat_acc + lc, acc1[i]);
+                atomicAdd(stat_acc + BLOCK_N + lc, acc2[i]);
+            }
+            acc1[i] = acc2[i] = 0.f;
+        }
+    };
+    int iter = 0;
+    for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
+        const int tile = fdiv(unit, p.fd_splits);
+        const int split = unit - tile * p.splits;
+        const int m_grp = fdiv(tile, p.fd_nblk);
+        const int m_blk = m_grp * CS + static_cast<int>(crank);
+        const int n_blk = tile - m_grp * p.num_n_blocks;
+        if (p.stat_sum != nullptr && n_blk != stat_nblk) {
+            if (stat_nblk >= 0) {
+                // this CTA moves on to another column block: hand the finished partials over
+                stat_fold();
+                asm volatile("bar.sync 1, 512;" ::: "memory");
+                for (int i = etid; i < 2 * BLOCK_N; i += 512) {
+                    const int col = stat_nblk * BLOCK_N + (i % BLOCK_N);
+                    if (col < p.N) atomicAdd((i < BLOCK_N ? p.stat_sum : p.stat_sqsum) + col, stat_acc[i]);
+                    stat_acc[i] = 0.f;
+                }
+                asm volatile("bar.sync 1, 512;" ::: "memory");
+            }
+            stat_nblk = n_blk;
+        }
+        const int as = iter & 1;
+        const uint32_t aphase = (iter >> 1) & 1;
+        const int row0 = m_blk * CV_BLOCK_M + quarter * 32;
+        // the four output rows this lane stores (and, for ACCUMULATE, loads) in every 32-column chunk
+        long long orow[4];
+        if (p.halo) {
+            // a tile is one 16 x 8 patch: its image / patch position once per tile (warp-uniform divisions), the
+            // row inside it by shifts.  (cv_out_row per row - four divisions each - made the epilogue the limit.)
+            const int t2 = fdiv(m_blk, p.fd_tx), tx = m_blk - t2 * p.tiles_x;
+            const int img = fdiv(t2, p.fd_ty), ty = t2 - img * p.tiles_y;
+            const long long base = static_cast<long long>(img) * p.P * p.Q;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int loc = quarter * 32 + i * 8 + (lane >> 2);
+                const int y = ty * 16 + (loc >> 3), x = tx * 8 + (loc & 7);
+                orow[i] = (y < p.P && x < p.Q) ? base + static_cast<long long>(y) * p.Q + x : -1;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int m = row0 + i * 8 + (lane >> 2);
+                orow[i] = m < p.M ? cv_out_row(p, m) : -1;
+            }
+        }
+        mbar_wait(&tmem_full_bar[as], aphase);
+        tcgen05_fence_after();
+        const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BLOCK_N;
+#pragma unroll 1
+        for (int c = group; c < BLOCK_N / 32; c += CV_EPI_WARPS / 4) {
+            uint32_t r[32];
+            tmem_ld_32x32(taddr0 + c * 32, r);
+            tmem_ld_wait();
+            const int col0 = n_blk * BLOCK_N + c * 32;
+            if (col0 >= p.N || row0 >= p.M) continue;   // warp-uniform
+            if (p.splits > 1) {
+                const int row = row0 + lane;
+                if (row < p.M) {
+                    float* dst = p.workspace + (static_cast<size_t>(split) * p.M + row) * p.N + col0;
+#pragma unroll
+                    for (int g = 0; g < 8; ++g) {
+                        if (col0 + g * 4 < p.N)
+                            *reinterpret_cast<float4*>(dst + g * 4) =
+                                make_float4(__uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]),
+                                            __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]));
+                    }
+                }
+                continue;
+            }
+            const int gc = col0 + unit16 * 8;
+            if (p.flags & TONY_EPI_ACCUMULATE) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint4 v = make_uint4(0, 0, 0, 0);
+                    if (orow[i] >= 0 && gc < p.N) v = ld_global_v4(p.C + orow[i] * p.ldc + gc);
+                    st_shared_v4(cv_stg_addr(stg, i * 8 + (lane >> 2), unit16), v);
+                }
+                __syncwarp();
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const uint4 v = ld_shared_v4(cv_stg_addr(stg, lane, u));
+                    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float2 f = unpack_bf16x2(w[j]);
+                        r[u * 8 + 2 * j] = __float_as_uint(__uint_as_float(r[u * 8 + 2 * j]) + f.x);
+                        r[u * 8 + 2 * j + 1] = __float_as_uint(__uint_as_float(r[u * 8 + 2 * j + 1]) + f.y);
+                    }
+                }
+                __syncwarp();
+            }
+            uint32_t o[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                o[j] = pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                st_shared_v4(cv_stg_addr(stg, lane, u), make_uint4(o[4 * u], o[4 * u + 1], o[4 * u + 2], o[4 * u + 3]));
+            __syncwarp();
+            float s1[8], s2[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint4 v = ld_shared_v4(cv_stg_addr(stg, i * 8 + (lane >> 2), unit16));
+                if (orow[i] >= 0 && gc < p.N) {
+                    st_global_v4(p.C + orow[i] * p.ldc + gc, v);
+                    if (p.stat_sum != nullptr) {
+                        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float2 f = unpack_bf16x2(w[j]);
+                            s1[2 * j] += f.x;
+                            s1[2 * j + 1] += f.y;
+                            s2[2 * j] = fmaf(f.x, f.x, s2[2 * j]);
+                            s2[2 * j + 1] = fmaf(f.y, f.y, s2[2 * j + 1]);
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (p.stat_sum != nullptr) {
+                // lanes with equal (lane & 3) hold the same 8 columns for different rows.  Fold the 8 row groups
+                // with a halving exchange (7 shuffles per array, not 24): lane (rg, unit16) ends with the warp's
+                // sum for column unit16 * 8 + rg and keeps it in a register until this CTA leaves the column block
+                const int rg = lane >> 2;
+                float k1[4], k2[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float snd1 = (rg & 4) ? s1[j] : s1[j + 4], snd2 = (rg & 4) ? s2[j] : s2[j + 4];
+                    k1[j] = ((rg & 4) ? s1[j + 4] : s1[j]) + __shfl_xor_sync(0xffffffffu, snd1, 16);
+                    k2[j] = ((rg & 4) ? s2[j + 4] : s2[j]) + __shfl_xor_sync(0xffffffffu, snd2, 16);
+                }
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const float snd1 = (rg & 2) ? k1[j] : k1[j + 2], snd2 = (rg & 2) ? k2[j] : k2[j + 2];
+                    k1[j] = ((rg & 2) ? k1[j + 2] : k1[j]) + __shfl_xor_sync(0xffffffffu, snd1, 8);
+                    k2[j] = ((rg & 2) ? k2[j + 2] : k2[j]) + __shfl_xor_sync(0xffffffffu, snd2, 8);
+                }
+                const float snd1 = (rg & 1) ? k1[0] : k1[1], snd2 = (rg & 1) ? k2[0] : k2[1];
+                const float f1 = ((rg & 1) ? k1[1] : k1[0]) + __shfl_xor_sync(0xffffffffu, snd1, 4);
+                const float f2 = ((rg & 1) ? k2[1] : k2[0]) + __shfl_xor_sync(0xffffffffu, snd2, 4);
+                if (STAT_SLOTS == 1 || c == group) {
+                    acc1[0] += f1;
+                    acc2[0] += f2;
+                } else {
+                    acc1[STAT_SLOTS - 1] += f1;
+                    acc2[STAT_SLOTS - 1] += f2;
+                }
+            }
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
+    }
+    if (p.stat_sum != nullptr && stat_nblk >= 0) {
+        stat_fold();
+        asm volatile("bar.sync 1, 512;" ::: "memory");
+        for (int i = etid; i < 2 * BLOCK_N; i += 512) {
+            const int col = stat_nblk * BLOCK_N + (i % BLOCK_N);
+            if (col < p.N) atomicAdd((i < BLOCK_N ? p.stat_sum : p.stat_sqsum) + col, stat_acc[i]);
+        }
+    }
 }
 
 // CS > 1 (MODE 0 only): CS CTAs of a cluster work on CS consecutive pixel tiles of the same column block in
@@ -132,7 +374,7 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     // one column block and added to global memory once (one atomic per column per CTA, not per warp)
     float* stat_acc = reinterpret_cast<float*>(tmem_base_slot + 4);
 
-    const int warp_idx = threadIdx.x >> 5;
+    const int warp_idx = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform: role branches and their loops stay on the uniform datapath
     const int lane = threadIdx.x & 31;
 
     if (p.stat_sum != nullptr)
@@ -176,17 +418,18 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
             uint32_t phase = 0;
             pdl_wait();
             for (int unit = worker; unit < num_units; unit += num_workers) {
-                const int tile = unit / p.splits;
+                const int tile = fdiv(unit, p.fd_splits);
                 const int split = unit - tile * p.splits;
-                const int m_blk = (tile / p.num_n_blocks) * CS + static_cast<int>(crank);
-                const int n_blk = tile % p.num_n_blocks;
+                const int m_grp = fdiv(tile, p.fd_nblk);
+                const int m_blk = m_grp * CS + static_cast<int>(crank);
+                const int n_blk = tile - m_grp * p.num_n_blocks;
                 const int kb0 = split * p.kb_per_split;
                 const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
                 if (MODE == 0) {
                     const int m0 = m_blk * CV_BLOCK_M;
-                    const int img = m0 / pq;
+                    const int img = fdiv(m0, p.fd_pq);
                     const int rem = m0 - img * pq;
-                    const int p0 = rem / p.Q;
+                    const int p0 = fdiv(rem, p.fd_q);
                     const int q0 = rem - p0 * p.Q;
                     const int cw = p.lower_w + q0 * p.stride_w;
                     const int ch = p.lower_h + p0 * p.stride_h;
@@ -293,9 +536,9 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                             continue;
                         }
                         const int k0 = kb * CV_BLOCK_K;
-                        const int img = k0 / pq;
+                        const int img = fdiv(k0, p.fd_pq);
                         const int rem = k0 - img * pq;
-                        const int p0 = rem / p.Q;
+                        const int p0 = fdiv(rem, p.fd_q);
                         const int q0 = rem - p0 * p.Q;
                         const int cw = p.lower_w + q0 * p.stride_w;
                         const int ch = p.lower_h + p0 * p.stride_h;
@@ -344,11 +587,13 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
             const uint32_t b_lbo = b_mn ? CV_CHUNK_BYTES : 16;
             const uint32_t a_kstep = a_mn ? (CV_UMMA_K * 128) >> 4 : (CV_UMMA_K * 2) >> 4;
             const uint32_t b_kstep = b_mn ? (CV_UMMA_K * 128) >> 4 : (CV_UMMA_K * 2) >> 4;
+            const uint64_t da0 = make_umma_desc_sw128(smem_u32(smem), a_lbo, 1024);
+            const uint64_t db0 = make_umma_desc_sw128(smem_u32(smem) + A_BYTES, b_lbo, 1024);
             int stage = 0;
             uint32_t phase = 0;
             int iter = 0;
             for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
-                const int tile = unit / p.splits;
+                const int tile = fdiv(unit, p.fd_splits);
                 const int split = unit - tile * p.splits;
                 const int as = iter & 1;
                 const uint32_t aphase = (iter >> 1) & 1;
@@ -360,10 +605,10 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tcgen05_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
-                    const uint32_t sb = sa + A_BYTES;
-                    const uint64_t da = make_umma_desc_sw128(sa, a_lbo, 1024);
-                    const uint64_t db = make_umma_desc_sw128(sb, b_lbo, 1024);
+                    // descriptors of stage 0 are built once; a stage is a fixed number of 16-byte units further
+                    // (the start-address field cannot carry: shared memory ends below 2^18 bytes)
+                    const uint64_t da = da0 + static_cast<uint64_t>(stage) * (STAGE_BYTES >> 4);
+                    const uint64_t db = db0 + static_cast<uint64_t>(stage) * (STAGE_BYTES >> 4);
                     if (elect_one()) {
 #pragma unroll
                         for (int k = 0; k < CV_BLOCK_K / CV_UMMA_K; ++k)
@@ -383,183 +628,241 @@ conv_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         }
     } else {
         // ---------------------------------------------------------------- epilogue warps (2..17)
-        const int quarter = warp_idx & 3;
-        const int group = (warp_idx - 2) >> 2;
-        const uint32_t stg = smem_u32(staging + (warp_idx - 2) * 2048);
-        const int unit16 = lane & 3;
-        const int etid = threadIdx.x - 64;     // 0..511 among the epilogue warps
-        int stat_nblk = -1;
-        // one column of BatchNorm partials per lane and 32-column chunk this warp owns (see the epilogue loop)
-        constexpr int STAT_SLOTS = (BLOCK_N / 32 + CV_EPI_WARPS / 4 - 1) / (CV_EPI_WARPS / 4);
-        static_assert(STAT_SLOTS <= 2, "the slot select below assumes at most two chunks per warp");
-        float acc1[STAT_SLOTS], acc2[STAT_SLOTS];
-#pragma unroll
-        for (int i = 0; i < STAT_SLOTS; ++i) acc1[i] = acc2[i] = 0.f;
-        // the four quarter warps of a group own the same columns: meet in shared memory, once per column block
-        auto stat_fold = [&]() {
-#pragma unroll
-            for (int i = 0; i < STAT_SLOTS; ++i) {
-                const int lc = (group + i * (CV_EPI_WARPS / 4)) * 32 + unit16 * 8 + (lane >> 2);
-                if (lc < BLOCK_N) {
-                    atomicAdd(stat_acc + lc, acc1[i]);
-                    atomicAdd(stat_acc + BLOCK_N + lc, acc2[i]);
-                }
-                acc1[i] = acc2[i] = 0.f;
-            }
-        };
-        int iter = 0;
-        for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
-            const int tile = unit / p.splits;
-            const int split = unit - tile * p.splits;
-            const int m_blk = (tile / p.num_n_blocks) * CS + static_cast<int>(crank);
-            const int n_blk = tile % p.num_n_blocks;
-            if (p.stat_sum != nullptr && n_blk != stat_nblk) {
-                if (stat_nblk >= 0) {
-                    // this CTA moves on to another column block: hand the finished partials over
-                    stat_fold();
-                    asm volatile("bar.sync 1, 512;" ::: "memory");
-                    for (int i = etid; i < 2 * BLOCK_N; i += 512) {
-                        const int col = stat_nblk * BLOCK_N + (i % BLOCK_N);
-                        if (col < p.N) atomicAdd((i < BLOCK_N ? p.stat_sum : p.stat_sqsum) + col, stat_acc[i]);
-                        stat_acc[i] = 0.f;
-                    }
-                    asm volatile("bar.sync 1, 512;" ::: "memory");
-                }
-                stat_nblk = n_blk;
-            }
-            const int as = iter & 1;
-            const uint32_t aphase = (iter >> 1) & 1;
-            const int row0 = m_blk * CV_BLOCK_M + quarter * 32;
-            // the four output rows this lane stores (and, for ACCUMULATE, loads) in every 32-column chunk
-            long long orow[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int m = row0 + i * 8 + (lane >> 2);
-                orow[i] = m < p.M ? cv_out_row(p, m) : -1;
-            }
-            mbar_wait(&tmem_full_bar[as], aphase);
-            tcgen05_fence_after();
-            const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BLOCK_N;
-#pragma unroll 1
-            for (int c = group; c < BLOCK_N / 32; c += CV_EPI_WARPS / 4) {
-                uint32_t r[32];
-                tmem_ld_32x32(taddr0 + c * 32, r);
-                tmem_ld_wait();
-                const int col0 = n_blk * BLOCK_N + c * 32;
-                if (col0 >= p.N || row0 >= p.M) continue;   // warp-uniform
-                if (p.splits > 1) {
-                    const int row = row0 + lane;
-                    if (row < p.M) {
-                        float* dst = p.workspace + (static_cast<size_t>(split) * p.M + row) * p.N + col0;
-#pragma unroll
-                        for (int g = 0; g < 8; ++g) {
-                            if (col0 + g * 4 < p.N)
-                                *reinterpret_cast<float4*>(dst + g * 4) =
-                                    make_float4(__uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]),
-                                                __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]));
-                        }
-                    }
-                    continue;
-                }
-                const int gc = col0 + unit16 * 8;
-                if (p.flags & TONY_EPI_ACCUMULATE) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        uint4 v = make_uint4(0, 0, 0, 0);
-                        if (orow[i] >= 0 && gc < p.N) v = ld_global_v4(p.C + orow[i] * p.ldc + gc);
-                        st_shared_v4(cv_stg_addr(stg, i * 8 + (lane >> 2), unit16), v);
-                    }
-                    __syncwarp();
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const uint4 v = ld_shared_v4(cv_stg_addr(stg, lane, u));
-                        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const float2 f = unpack_bf16x2(w[j]);
-                            r[u * 8 + 2 * j] = __float_as_uint(__uint_as_float(r[u * 8 + 2 * j]) + f.x);
-                            r[u * 8 + 2 * j + 1] = __float_as_uint(__uint_as_float(r[u * 8 + 2 * j + 1]) + f.y);
-                        }
-                    }
-                    __syncwarp();
-                }
-                uint32_t o[16];
-#pragma unroll
-                for (int j = 0; j < 16; ++j)
-                    o[j] = pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
-#pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    st_shared_v4(cv_stg_addr(stg, lane, u), make_uint4(o[4 * u], o[4 * u + 1], o[4 * u + 2], o[4 * u + 3]));
-                __syncwarp();
-                float s1[8], s2[8];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const uint4 v = ld_shared_v4(cv_stg_addr(stg, i * 8 + (lane >> 2), unit16));
-                    if (orow[i] >= 0 && gc < p.N) {
-                        st_global_v4(p.C + orow[i] * p.ldc + gc, v);
-                        if (p.stat_sum != nullptr) {
-                            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                const float2 f = unpack_bf16x2(w[j]);
-                                s1[2 * j] += f.x;
-                                s1[2 * j + 1] += f.y;
-                                s2[2 * j] = fmaf(f.x, f.x, s2[2 * j]);
-                                s2[2 * j + 1] = fmaf(f.y, f.y, s2[2 * j + 1]);
-                            }
-                        }
-                    }
-                }
-                __syncwarp();
-                if (p.stat_sum != nullptr) {
-                    // lanes with equal (lane & 3) hold the same 8 columns for different rows.  Fold the 8 row groups
-                    // with a halving exchange (7 shuffles per array, not 24): lane (rg, unit16) ends with the warp's
-                    // sum for column unit16 * 8 + rg and keeps it in a register until this CTA leaves the column block
-                    const int rg = lane >> 2;
-                    float k1[4], k2[4];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const float snd1 = (rg & 4) ? s1[j] : s1[j + 4], snd2 = (rg & 4) ? s2[j] : s2[j + 4];
-                        k1[j] = ((rg & 4) ? s1[j + 4] : s1[j]) + __shfl_xor_sync(0xffffffffu, snd1, 16);
-                        k2[j] = ((rg & 4) ? s2[j + 4] : s2[j]) + __shfl_xor_sync(0xffffffffu, snd2, 16);
-                    }
-#pragma unroll
-                    for (int j = 0; j < 2; ++j) {
-                        const float snd1 = (rg & 2) ? k1[j] : k1[j + 2], snd2 = (rg & 2) ? k2[j] : k2[j + 2];
-                        k1[j] = ((rg & 2) ? k1[j + 2] : k1[j]) + __shfl_xor_sync(0xffffffffu, snd1, 8);
-                        k2[j] = ((rg & 2) ? k2[j + 2] : k2[j]) + __shfl_xor_sync(0xffffffffu, snd2, 8);
-                    }
-                    const float snd1 = (rg & 1) ? k1[0] : k1[1], snd2 = (rg & 1) ? k2[0] : k2[1];
-                    const float f1 = ((rg & 1) ? k1[1] : k1[0]) + __shfl_xor_sync(0xffffffffu, snd1, 4);
-                    const float f2 = ((rg & 1) ? k2[1] : k2[0]) + __shfl_xor_sync(0xffffffffu, snd2, 4);
-                    if (STAT_SLOTS == 1 || c == group) {
-                        acc1[0] += f1;
-                        acc2[0] += f2;
-                    } else {
-                        acc1[STAT_SLOTS - 1] += f1;
-                        acc2[STAT_SLOTS - 1] += f2;
-                    }
-                }
-            }
-            tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
-        }
-        if (p.stat_sum != nullptr && stat_nblk >= 0) {
-            stat_fold();
-            asm volatile("bar.sync 1, 512;" ::: "memory");
-            for (int i = etid; i < 2 * BLOCK_N; i += 512) {
-                const int col = stat_nblk * BLOCK_N + (i % BLOCK_N);
-                if (col < p.N) atomicAdd((i < BLOCK_N ? p.stat_sum : p.stat_sqsum) + col, stat_acc[i]);
-            }
-        }
+        cv_epilogue_role<BLOCK_N, CS>(p, staging, stat_acc, tmem_base, tmem_full_bar, tmem_empty_bar, worker, num_workers,
+                                      num_units, crank, warp_idx, lane);
     }
 
     __syncwarp();
     tcgen05_fence_before();
     if (CS > 1) cluster_sync_all(); else __syncthreads();   // no CTA leaves while peers may still write to it
+    if (warp_idx == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc<TMEM_COLS>(tmem_base);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// 3x3 / stride 1 convolution (forward, and the data gradient as the same traversal with mirrored taps) with the
+// activation read ONCE per tile.
+//
+// The im2col kernel above fetches the 128 x 64 activation tile of every filter tap separately, so a 3x3 layer
+// pulls each input pixel through L2 -> shared memory nine times; at 64 / 128 channels that traffic (24-32 KB per
+// k-block against ~43 B/clk/SM) is what bounds it.  Here a tile is a 16 x 8 patch of one image's output pixels
+// and ONE tiled TMA load brings its 18 x 10 halo (64 channels, 128 B per pixel, SWIZZLE_128B, out-of-range pixels
+// zero = the padding) into shared memory.  Tap (r, s) is then only a different START ADDRESS for the same bytes:
+// row m = (y, x) of the A operand is halo pixel (y + r) * 10 + (x + s), so the descriptor starts (r * 10 + s) * 128
+// bytes into the patch and its 8-row groups are one halo row = 1280 bytes apart.  The hardware applies the
+// 128-byte swizzle to the absolute shared-memory address, so a start that is off the 1024-byte period and a group
+// stride that is not a multiple of it read exactly what TMA wrote (tools/probes/umma_halo_probe.cu: all nine taps
+// exact with the descriptor's base-offset field left 0).
+// Filter tiles travel through their own ring; when the whole filter of the column block fits (64 -> 64 channels:
+// 72 KB) it is loaded once per CTA and stays.
+constexpr int HALO_TH = 16, HALO_TW = 8, HALO_PH = HALO_TH + 2, HALO_PW = HALO_TW + 2;
+constexpr uint32_t HALO_PATCH_BYTES = HALO_PH * HALO_PW * 128;          // 23040
+constexpr uint32_t HALO_A_STAGE = (HALO_PATCH_BYTES + 1023) / 1024 * 1024;   // 23552 -> keep stages 1024-aligned
+constexpr uint32_t HALO_BAR_BYTES = 512;
+constexpr int HALO_TAPS = 9;
+
+template <int BLOCK_N, int A_STAGES, int B_STAGES>
+__global__ void __launch_bounds__(CV_THREADS, 1)
+conv3x3_halo_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                            const ConvParams p) {
+    constexpr uint32_t B_BYTES = BLOCK_N * CV_BLOCK_K * 2;
+    constexpr uint32_t TMEM_COLS = (2 * BLOCK_N < 32) ? 32 : 2 * BLOCK_N;
+    constexpr int N_CHUNKS = BLOCK_N / 64;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    if ((smem_u32(smem_raw) & 1023u) != 0) __trap();
+    uint8_t* smem_a = smem_raw;
+    uint8_t* smem_b = smem_a + A_STAGES * HALO_A_STAGE;
+    uint8_t* staging = smem_b + B_STAGES * B_BYTES;
+    uint64_t* full_a = reinterpret_cast<uint64_t*>(staging + CV_STAGING_BYTES);
+    uint64_t* empty_a = full_a + A_STAGES;
+    uint64_t* full_b = empty_a + A_STAGES;
+    uint64_t* empty_b = full_b + B_STAGES;
+    uint64_t* tmem_full_bar = empty_b + B_STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+    static_assert((2 * A_STAGES + 2 * B_STAGES + 4) * 8 + 16 <= HALO_BAR_BYTES, "barrier block too small");
+    float* stat_acc = reinterpret_cast<float*>(staging + CV_STAGING_BYTES + HALO_BAR_BYTES);
+
+    const int warp_idx = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform: role branches and their loops stay on the uniform datapath
+    const int lane = threadIdx.x & 31;
+    if (p.stat_sum != nullptr)
+        for (int i = threadIdx.x; i < 2 * BLOCK_N; i += CV_THREADS) stat_acc[i] = 0.f;
+    if (warp_idx == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+        for (int s = 0; s < A_STAGES; ++s) {
+            mbar_init(&full_a[s], 1);
+            mbar_init(&empty_a[s], 1);
+        }
+        for (int s = 0; s < B_STAGES; ++s) {
+            mbar_init(&full_b[s], 1);
+            mbar_init(&empty_b[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full_bar[s], 1);
+            mbar_init(&tmem_empty_bar[s], CV_EPI_WARPS);
+        }
+        fence_barrier_init();
+    }
+    if (warp_idx == 1) tmem_alloc<TMEM_COLS>(tmem_base_slot);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_base_slot;
+    pdl_launch_dependents();
+
+    const int num_units = p.num_m_blocks * p.num_n_blocks;
+    const int worker = static_cast<int>(blockIdx.x);
+    const int num_workers = static_cast<int>(gridDim.x);
+    const int resident = p.b_resident;          // B stage of (channel block, tap) = cb * ntaps + tap, loaded once
+
+    if (warp_idx == 0) {
+        // ---------------------------------------------------------------- TMA producer
+        int sa = 0, sb = 0;
+        uint32_t pa = 0, pb = 0;
+        bool first = true;
+        pdl_wait();
+        for (int unit = worker; unit < num_units; unit += num_workers) {
+            const int m_tile = fdiv(unit, p.fd_nblk);
+            const int n_blk = unit - m_tile * p.num_n_blocks;
+            const int t2 = fdiv(m_tile, p.fd_tx), tx = m_tile - t2 * p.tiles_x;
+            const int img = fdiv(t2, p.fd_ty), ty = t2 - img * p.tiles_y;
+            for (int cb = 0; cb < p.cblocks; ++cb) {
+                mbar_wait(&empty_a[sa], pa ^ 1);
+                if (elect_one()) {
+                    if (p.dbg & 1) {      // timing experiments only: no activation loads
+                        mbar_arrive(&full_a[sa]);
+                    } else {
+                        mbar_expect_tx(&full_a[sa], HALO_PATCH_BYTES);
+                        tma_load_4d(&tmap_a, &full_a[sa], smem_a + sa * HALO_A_STAGE, cb * 64, tx * HALO_TW + p.lower_w,
+                                    ty * HALO_TH + p.lower_h, img);
+                    }
+                }
+                __syncwarp();
+                if (++sa == A_STAGES) {
+                    sa = 0;
+                    pa ^= 1;
+                }
+                if (resident && !first) continue;
+                for (int t = 0; t < HALO_TAPS; ++t) {
+                    const int slot = resident ? cb * HALO_TAPS + t : sb;
+                    if (!resident) mbar_wait(&empty_b[slot], pb ^ 1);
+                    const int winner = p.taps[t].wsel * p.w_tap_stride;
+                    uint8_t* dst = smem_b + slot * B_BYTES;
+                    if (elect_one()) {
+                        mbar_expect_tx(&full_b[slot], B_BYTES);
+                        if (!p.b_mn_major) {
+                            tma_load_2d(&tmap_b, &full_b[slot], dst, winner + cb * 64, n_blk * BLOCK_N);
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < N_CHUNKS; ++c)
+                                tma_load_2d(&tmap_b, &full_b[slot], dst + c * CV_CHUNK_BYTES,
+                                            winner + n_blk * BLOCK_N + c * 64, cb * 64);
+                        }
+                    }
+                    __syncwarp();
+                    if (!resident && ++sb == B_STAGES) {
+                        sb = 0;
+                        pb ^= 1;
+                    }
+                }
+            }
+            first = false;
+        }
+    } else if (warp_idx == 1) {
+        // ---------------------------------------------------------------- MMA issuer (whole warp, elected lane)
+        // Everything an MMA needs beyond two 64-bit adds is prepared outside the tile loop: the nine tap offsets,
+        // the descriptors of A stage 0 and B slot 0.  With N <= 128 a k-block is only 192-256 clk of tensor work,
+        // so the instructions between two UTCHMMA decide the speed of this kernel.
+        const uint32_t b_mn = static_cast<uint32_t>(p.b_mn_major);
+        const uint32_t idesc = make_idesc_bf16(CV_BLOCK_M, BLOCK_N, 0u, b_mn);
+        const uint32_t b_lbo = b_mn ? CV_CHUNK_BYTES : 16;
+        constexpr uint32_t A_KSTEP = (CV_UMMA_K * 2) >> 4;
+        const uint32_t b_kstep = b_mn ? (CV_UMMA_K * 128) >> 4 : (CV_UMMA_K * 2) >> 4;
+        uint32_t toff[HALO_TAPS];
+#pragma unroll
+        for (int t = 0; t < HALO_TAPS; ++t) toff[t] = ((p.taps[t].off_h * HALO_PW + p.taps[t].off_w) * 128) >> 4;
+        const uint64_t da00 = make_umma_desc_sw128(smem_u32(smem_a), 16, HALO_PW * 128);
+        const uint64_t db00 = make_umma_desc_sw128(smem_u32(smem_b), b_lbo, 1024);
+        int sa = 0, sb = 0;
+        uint32_t pa = 0, pb = 0;
+        bool first = true;
+        int iter = 0;
+        for (int unit = worker; unit < num_units; unit += num_workers, ++iter) {
+            const int as = iter & 1;
+            const uint32_t aphase = (iter >> 1) & 1;
+            mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
+            tcgen05_fence_after();
+            const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+            for (int cb = 0; cb < p.cblocks; ++cb) {
+                mbar_wait(&full_a[sa], pa);
+                tcgen05_fence_after();
+                const uint64_t da0 = da00 + static_cast<uint64_t>(sa) * (HALO_A_STAGE >> 4);
+                if (resident) {
+                    if (first) {
+#pragma unroll 1
+                        for (int t = 0; t < HALO_TAPS; ++t) mbar_wait(&full_b[cb * HALO_TAPS + t], 0u);
+                        tcgen05_fence_after();
+                    }
+                    const uint64_t dbc = db00 + static_cast<uint64_t>(cb * HALO_TAPS) * (B_BYTES >> 4);
+                    if (elect_one()) {
+                        if (!(p.dbg & 4)) {   // timing experiments only: dbg 4 issues no MMAs
+#pragma unroll
+                            for (int t = 0; t < HALO_TAPS; ++t) {
+                                const uint64_t da = da0 + toff[t];
+                                const uint64_t db = dbc + static_cast<uint64_t>(t) * (B_BYTES >> 4);
+#pragma unroll
+                                for (int k = 0; k < CV_BLOCK_K / CV_UMMA_K; ++k)
+                                    umma_bf16(d_tmem, da + k * A_KSTEP, db + k * b_kstep, idesc,
+                                              (cb > 0 || t > 0 || k > 0) ? 1u : 0u);
+                            }
+                        }
+                        umma_commit(&empty_a[sa]);
+                    }
+                    __syncwarp();
+                } else {
+#pragma unroll
+                    for (int t = 0; t < HALO_TAPS; ++t) {
+                        mbar_wait(&full_b[sb], pb);
+                        tcgen05_fence_after();
+                        const uint64_t da = da0 + toff[t];
+                        const uint64_t db = db00 + static_cast<uint64_t>(sb) * (B_BYTES >> 4);
+                        if (elect_one()) {
+                            if (!(p.dbg & 4)) {
+#pragma unroll
+                                for (int k = 0; k < CV_BLOCK_K / CV_UMMA_K; ++k)
+                                    umma_bf16(d_tmem, da + k * A_KSTEP, db + k * b_kstep, idesc,
+                                              (cb > 0 || t > 0 || k > 0) ? 1u : 0u);
+                            }
+                            umma_commit(&empty_b[sb]);
+                            if (t == HALO_TAPS - 1) umma_commit(&empty_a[sa]);
+                        }
+                        __syncwarp();
+                        if (++sb == B_STAGES) {
+                            sb = 0;
+                            pb ^= 1;
+                        }
+                    }
+                }
+                if (++sa == A_STAGES) {
+                    sa = 0;
+                    pa ^= 1;
+                }
+            }
+            if (elect_one()) umma_commit(&tmem_full_bar[as]);
+            __syncwarp();
+            first = false;
+        }
+    } else {
+        cv_epilogue_role<BLOCK_N, 1>(p, staging, stat_acc, tmem_base, tmem_full_bar, tmem_empty_bar, worker, num_workers,
+                                     num_units, 0u, warp_idx, lane);
+    }
+
+    __syncwarp();
+    tcgen05_fence_before();
+    __syncthreads();
     if (warp_idx == 1) {
         tcgen05_fence_after();
         tmem_dealloc<TMEM_COLS>(tmem_base);
@@ -820,7 +1123,9 @@ static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvP
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    TONY_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_bf16_tcgen05_kernel<BLOCK_N, STAGES, MODE, CS>, ta, tb, p));
+    ConvParams pf = p;
+    fill_fastdiv(pf);
+    TONY_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_bf16_tcgen05_kernel<BLOCK_N, STAGES, MODE, CS>, ta, tb, pf));
     count_launch();
     return TONY_OK;
 }
@@ -859,6 +1164,73 @@ static int filter_box_rows(int block_n, int b_mn_major, int cs) {
     if (!b_mn_major) return block_n / cs;
     const int chunks = block_n / 64;
     return chunks >= cs ? 64 : 64 / (cs / chunks);
+}
+
+template <int BLOCK_N, int A_STAGES, int B_STAGES>
+static int launch_halo(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, int grid, cudaStream_t stream) {
+    constexpr size_t SMEM = static_cast<size_t>(A_STAGES) * HALO_A_STAGE + static_cast<size_t>(B_STAGES) * BLOCK_N * 128 +
+                            CV_STAGING_BYTES + HALO_BAR_BYTES + 2 * BLOCK_N * 4;
+    static_assert(SMEM <= 232448, "over the 227 KB of shared memory a CTA can have");
+    static bool configured[64] = {false};
+    int dev = 0;
+    TONY_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        TONY_CUDA_CHECK(cudaFuncSetAttribute(conv3x3_halo_tcgen05_kernel<BLOCK_N, A_STAGES, B_STAGES>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SMEM)));
+        configured[dev] = true;
+    }
+    ConvParams pf = p;
+    fill_fastdiv(pf);
+    conv3x3_halo_tcgen05_kernel<BLOCK_N, A_STAGES, B_STAGES><<<grid, CV_THREADS, SMEM, stream>>>(ta, tb, pf);
+    count_launch();
+    TONY_CUDA_CHECK(cudaGetLastError());
+    return TONY_OK;
+}
+
+// Which 3x3 / stride-1 layers with <= 128 output channels take the halo kernel.  Unset: only those whose whole filter
+// stays resident in shared memory (64 -> 64 channels: 74.7 us against 87.0 us for the im2col kernel at 256 x 56 x 56);
+// with the filter streaming through its ring the 12-23 % of MMA rows its 16 x 8 tiles waste on 28 x 28 images
+// outweigh the saved activation traffic (62.5 vs 58.4 us).  TONY_B200_CONV_HALO=1: every eligible layer, 0: none.
+// Read on every call (tests switch it); a getenv is ~100 ns.
+static int conv_halo_mode() {
+    const char* e = getenv("TONY_B200_CONV_HALO");
+    return e ? (atoi(e) != 0 ? 2 : 0) : 1;
+}
+
+// Fills the halo-form fields of `p` (taps, M, tile grid) and launches; `mirror`: data-gradient traversal.
+// x: the tensor the patch is cut from ([N, H, W, C] dense), output [N, H, W, p.N].
+constexpr int HALO_DECLINED = -12345;   // run_halo: this layer stays on the im2col kernel
+static int run_halo(ConvParams p, const void* x, int N, int H, int W, int C, const CUtensorMap& tb, int block_n, bool mirror,
+                    cudaStream_t stream) {
+    p.halo = 1;
+    p.tiles_x = (W + HALO_TW - 1) / HALO_TW;
+    p.tiles_y = (H + HALO_TH - 1) / HALO_TH;
+    p.num_m_blocks = N * p.tiles_x * p.tiles_y;
+    p.M = p.num_m_blocks * CV_BLOCK_M;
+    p.P = H;
+    p.Q = W;
+    p.lower_w = p.lower_h = -1;
+    p.out_strided = 0;
+    p.ntaps = 9;
+    p.cblocks = (C + 63) / 64;
+    p.splits = 1;
+    for (int r = 0; r < 3; ++r)
+        for (int s = 0; s < 3; ++s) {
+            ConvTap& t = p.taps[r * 3 + s];
+            t.off_h = static_cast<unsigned short>(mirror ? 2 - r : r);
+            t.off_w = static_cast<unsigned short>(mirror ? 2 - s : s);
+            t.wsel = r * 3 + s;
+        }
+    const int b_stages = block_n == 64 ? 9 : 6;
+    p.b_resident = (p.ntaps * p.cblocks <= b_stages && p.num_n_blocks == 1) ? 1 : 0;
+    if (!p.b_resident && conv_halo_mode() < 2) return HALO_DECLINED;
+    CUtensorMap ta;
+    int rc = make_patch_tmap(&ta, x, N, H, W, C, HALO_PW, HALO_PH, 1, 1);
+    if (rc) return rc;
+    const long long units = static_cast<long long>(p.num_m_blocks) * p.num_n_blocks;
+    const int grid = static_cast<int>(std::min<long long>(units, device_sm_count()));
+    if (block_n == 64) return launch_halo<64, 4, 9>(ta, tb, p, grid, stream);
+    return launch_halo<128, 3, 6>(ta, tb, p, grid, stream);
 }
 
 static int pick_block_n(int n) { return n <= 64 ? 64 : (n <= 128 ? 128 : 256); }
@@ -932,6 +1304,16 @@ extern "C" int tony_conv2d_fprop_bf16(const tony_conv_desc* d, const void* x, co
         const char* e = getenv("TONY_B200_CONV_DBG");
         p.dbg = e ? atoi(e) : 0;
     }
+    if (conv_halo_mode() && d->R == 3 && d->S == 3 && d->stride == 1 && d->pad == 1 && !d->pad_h_only &&
+        (d->pad_hi < 0 || d->pad_hi == 1) && !d->x_stride_w && !d->x_stride_h && !d->x_stride_n && d->C % 64 == 0 &&
+        block_n <= 128) {
+        CUtensorMap tbh;
+        rc = make_tmap_2d_bf16(&tbh, w, static_cast<long long>(p.ntaps) * d->C, d->K, static_cast<long long>(p.ntaps) * d->C,
+                               64, filter_box_rows(block_n, 0, 1));
+        if (rc) return rc;
+        rc = run_halo(p, x, d->N, d->H, d->W, d->C, tbh, block_n, false, stream);
+        if (rc != HALO_DECLINED) return rc;
+    }
     CUtensorMap ta, tb;
     rc = make_im2col_tmap(&ta, x, d->N, d->H, d->W, d->C, -pad_w, -d->pad, pad_hi_w - (d->S - 1),
                           pad_hi_h - (d->R - 1), d->stride, d->stride, CV_BLOCK_M, d->x_stride_w, d->x_stride_h,
@@ -969,6 +1351,23 @@ extern "C" int tony_conv2d_dgrad_bf16(const tony_conv_desc* d, const void* dy, c
     rc = make_tmap_2d_bf16(&tb, w, static_cast<long long>(d->R) * d->S * d->C, d->K,
                            static_cast<long long>(d->R) * d->S * d->C, 64, filter_box_rows(block_n, 1, cs));
     if (rc) return rc;
+    if (conv_halo_mode() && d->R == 3 && d->S == 3 && st == 1 && d->pad == 1 && d->K % 64 == 0 && block_n <= 128) {
+        // dX = 3x3 traversal of dY with mirrored taps and the filter read MN-major
+        ConvParams p = {};
+        p.N = d->C;
+        p.num_n_blocks = (p.N + block_n - 1) / block_n;
+        p.b_mn_major = 1;
+        p.w_tap_stride = d->C;
+        p.C = static_cast<__nv_bfloat16*>(dx);
+        p.ldc = d->C;
+        p.flags = flags;
+        CUtensorMap tbh;
+        rc = make_tmap_2d_bf16(&tbh, w, static_cast<long long>(d->R) * d->S * d->C, d->K,
+                               static_cast<long long>(d->R) * d->S * d->C, 64, filter_box_rows(block_n, 1, 1));
+        if (rc) return rc;
+        rc = run_halo(p, dy, d->N, P, Q, d->K, tbh, block_n, true, stream);
+        if (rc != HALO_DECLINED) return rc;
+    }
     // a parity class with no filter tap (1x1 stride 2: every odd row / column) receives no gradient
     bool need_zero = false;
     for (int ph = 0; ph < st; ++ph) {

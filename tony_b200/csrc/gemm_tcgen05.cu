@@ -386,7 +386,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;
     uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
-    const int warp_idx = threadIdx.x >> 5;
+    const int warp_idx = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform: role branches and their loops stay on the uniform datapath
     const int lane = threadIdx.x & 31;
 
     if (warp_idx == 0 && lane == 0) {
@@ -625,7 +625,7 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a,
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;
     uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
-    const int warp_idx = threadIdx.x >> 5;
+    const int warp_idx = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform: role branches and their loops stay on the uniform datapath
     const int lane = threadIdx.x & 31;
     const uint32_t cta_rank = cluster_ctarank();
     const bool leader = cta_rank == 0;
