@@ -275,16 +275,25 @@ __device__ __forceinline__ void cv_epilogue_role(const ConvParams& p, uint8_t* s
             for (int u = 0; u < 4; ++u)
                 st_shared_v4(cv_stg_addr(stg, lane, u), make_uint4(o[4 * u], o[4 * u + 1], o[4 * u + 2], o[4 * u + 3]));
             __syncwarp();
-            float s1[8], s2[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
+            // stores first, then - under ONE warp-uniform branch - the statistics of what was stored: with the
+            // test inside the store loop the compiler predicated the 48 unpack / add / fma instructions per chunk
+            // and every launch without statistics (all data gradients) issued them for nothing
+            uint4 sv[4];
+            bool ok[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const uint4 v = ld_shared_v4(cv_stg_addr(stg, i * 8 + (lane >> 2), unit16));
-                if (orow[i] >= 0 && gc < p.N) {
-                    st_global_v4(p.C + orow[i] * p.ldc + gc, v);
-                    if (p.stat_sum != nullptr) {
-                        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+                sv[i] = ld_shared_v4(cv_stg_addr(stg, i * 8 + (lane >> 2), unit16));
+                ok[i] = orow[i] >= 0 && gc < p.N;
+                if (ok[i]) st_global_v4(p.C + orow[i] * p.ldc + gc, sv[i]);
+            }
+            float s1[8], s2[8];
+            if (p.stat_sum != nullptr) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if (ok[i]) {
+                        const uint32_t w[4] = {sv[i].x, sv[i].y, sv[i].z, sv[i].w};
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             const float2 f = unpack_bf16x2(w[j]);
