@@ -118,6 +118,8 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, const BnDims d, float* __re
                 const __nv_bfloat16* __restrict__ beta, float eps, float momentum, float* __restrict__ mean,
                 float* __restrict__ rstd, float* __restrict__ ab, float* __restrict__ running_mean,
                 float* __restrict__ running_var) {
+    pdl_wait();                // launched with programmatic stream serialization: see launch_pdl_kernel
+    pdl_launch_dependents();
     __shared__ float red[8][256];
     __shared__ unsigned int is_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -192,6 +194,8 @@ __global__ void __launch_bounds__(BN_THREADS, 4)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ residual,
                 const float* __restrict__ ab, __nv_bfloat16* __restrict__ y, unsigned char* __restrict__ mask,
                 long long M, int C, int relu, const BnSums sums) {
+    pdl_wait();                // launched with programmatic stream serialization: see launch_pdl_kernel
+    pdl_launch_dependents();
     const int groups = C / 8;                                    // divides 256 for every supported C
     const long long tid = static_cast<long long>(blockIdx.x) * BN_THREADS + threadIdx.x;
     const int cg = static_cast<int>(tid % groups);
@@ -275,6 +279,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                      const float* __restrict__ rstd, int relu, float* __restrict__ partials, unsigned int* __restrict__ counters,
                      __nv_bfloat16* __restrict__ dgamma, __nv_bfloat16* __restrict__ dbeta, float* __restrict__ coef,
                      const __nv_bfloat16* __restrict__ gamma) {
+    pdl_wait();                // launched with programmatic stream serialization: see launch_pdl_kernel
+    pdl_launch_dependents();
     __shared__ float red[8][256];
     __shared__ unsigned int is_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -346,6 +352,8 @@ __global__ void __launch_bounds__(BN_THREADS, 4)
 bn_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                  const unsigned char* __restrict__ mask, const float* __restrict__ coef, int relu,
                  __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, long long M, int C) {
+    pdl_wait();                // launched with programmatic stream serialization: see launch_pdl_kernel
+    pdl_launch_dependents();
     const int groups = C / 8;
     const long long tid = static_cast<long long>(blockIdx.x) * BN_THREADS + threadIdx.x;
     const int cg = static_cast<int>(tid % groups);
@@ -447,14 +455,12 @@ extern "C" int tony_bn_fwd(const void* x, const void* residual, const void* gamm
     const int col_tiles = (d.Cw + 255) / 256;
     const int slabs = static_cast<int>((d.Mv + d.rows_per_slab - 1) / d.rows_per_slab);
     if (clear_counters_each_call()) TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
-    bn_stats_kernel<<<dim3(col_tiles, slabs), BN_THREADS, 0, s>>>(
+    TONY_CUDA_CHECK(launch_pdl_kernel(bn_stats_kernel, dim3(dim3(col_tiles, slabs)), dim3(BN_THREADS), 0, s,
         static_cast<const __nv_bfloat16*>(x), d, partials, counters, static_cast<const __nv_bfloat16*>(gamma),
-        static_cast<const __nv_bfloat16*>(beta), eps, momentum, mean, rstd, ab, running_mean, running_var);
-    TONY_CUDA_CHECK(cudaGetLastError());
-    bn_apply_kernel<<<elementwise_grid(M, C), BN_THREADS, 0, s>>>(
+        static_cast<const __nv_bfloat16*>(beta), eps, momentum, mean, rstd, ab, running_mean, running_var));
+    TONY_CUDA_CHECK(launch_pdl_kernel(bn_apply_kernel, dim3(elementwise_grid(M, C)), dim3(BN_THREADS), 0, s,
         static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(residual), ab,
-        static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(mask), M, C, relu, BnSums{});
-    TONY_CUDA_CHECK(cudaGetLastError());
+        static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(mask), M, C, relu, BnSums{}));
     count_launch(2);
     return TONY_OK;
 }
@@ -469,10 +475,9 @@ extern "C" int tony_bn_fwd_from_sums(const void* x, const void* residual, const 
     if (rc != TONY_OK) return rc;
     BnSums sums{stat_sum, stat_sqsum, static_cast<const __nv_bfloat16*>(gamma), static_cast<const __nv_bfloat16*>(beta),
                 eps, momentum, mean, rstd, running_mean, running_var};
-    bn_apply_kernel<<<elementwise_grid(M, C), BN_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+    TONY_CUDA_CHECK(launch_pdl_kernel(bn_apply_kernel, dim3(elementwise_grid(M, C)), dim3(BN_THREADS), 0, static_cast<cudaStream_t>(stream),
         static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(residual), nullptr,
-        static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(mask), M, C, relu, sums);
-    TONY_CUDA_CHECK(cudaGetLastError());
+        static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(mask), M, C, relu, sums));
     count_launch(1);
     return TONY_OK;
 }
@@ -498,17 +503,15 @@ extern "C" int tony_bn_bwd(const void* dy, const void* x, const void* mask, cons
     const int col_tiles = (d.Cw + 255) / 256;
     const int slabs = static_cast<int>((d.Mv + d.rows_per_slab - 1) / d.rows_per_slab);
     if (clear_counters_each_call()) TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
-    bn_bwd_reduce_kernel<<<dim3(col_tiles, slabs), BN_THREADS, 0, s>>>(
+    TONY_CUDA_CHECK(launch_pdl_kernel(bn_bwd_reduce_kernel, dim3(dim3(col_tiles, slabs)), dim3(BN_THREADS), 0, s,
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
         static_cast<const unsigned char*>(mask), d, mean, rstd, relu, partials, counters,
         static_cast<__nv_bfloat16*>(dgamma), static_cast<__nv_bfloat16*>(dbeta), coef,
-        static_cast<const __nv_bfloat16*>(gamma));
-    TONY_CUDA_CHECK(cudaGetLastError());
-    bn_bwd_dx_kernel<<<elementwise_grid(M, C), BN_THREADS, 0, s>>>(
+        static_cast<const __nv_bfloat16*>(gamma)));
+    TONY_CUDA_CHECK(launch_pdl_kernel(bn_bwd_dx_kernel, dim3(elementwise_grid(M, C)), dim3(BN_THREADS), 0, s,
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
         static_cast<const unsigned char*>(mask), coef, relu, static_cast<__nv_bfloat16*>(dx),
-        static_cast<__nv_bfloat16*>(dres), M, C);
-    TONY_CUDA_CHECK(cudaGetLastError());
+        static_cast<__nv_bfloat16*>(dres), M, C));
     count_launch(2);
     return TONY_OK;
 }

@@ -73,6 +73,8 @@ colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, lon
                     int rows_per_slab, float* __restrict__ partials, float* __restrict__ gparts,
                     unsigned int* __restrict__ counters, __nv_bfloat16* __restrict__ out, int accumulate,
                     const __nv_bfloat16* __restrict__ pre, __nv_bfloat16* __restrict__ gout) {
+    pdl_wait();                // launched with programmatic stream serialization: see launch_pdl_kernel
+    pdl_launch_dependents();
     __shared__ float red[CS_THREADS / 32][256];
     __shared__ unsigned int is_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -211,10 +213,10 @@ static int colsum_launch(const char* what, const void* x, const void* pre, void*
     __nv_bfloat16* oo = static_cast<__nv_bfloat16*>(out);
     __nv_bfloat16* gg = static_cast<__nv_bfloat16*>(gout);
     switch (act) {
-        case 0: colsum_fused_kernel<0><<<grid, CS_THREADS, 0, s>>>(xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg); break;
-        case 1: colsum_fused_kernel<1><<<grid, CS_THREADS, 0, s>>>(xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg); break;
-        case 2: colsum_fused_kernel<2><<<grid, CS_THREADS, 0, s>>>(xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg); break;
-        default: colsum_fused_kernel<3><<<grid, CS_THREADS, 0, s>>>(xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg); break;
+        case 0: TONY_CUDA_CHECK(launch_pdl_kernel(colsum_fused_kernel<0>, grid, dim3(CS_THREADS), 0, s, xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg)); break;
+        case 1: TONY_CUDA_CHECK(launch_pdl_kernel(colsum_fused_kernel<1>, grid, dim3(CS_THREADS), 0, s, xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg)); break;
+        case 2: TONY_CUDA_CHECK(launch_pdl_kernel(colsum_fused_kernel<2>, grid, dim3(CS_THREADS), 0, s, xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg)); break;
+        default: TONY_CUDA_CHECK(launch_pdl_kernel(colsum_fused_kernel<3>, grid, dim3(CS_THREADS), 0, s, xx, rows, cols, ld, rows_per_slab, partials, gparts, counters, oo, accumulate, pp, gg)); break;
     }
     count_launch();
     TONY_CUDA_CHECK(cudaGetLastError());

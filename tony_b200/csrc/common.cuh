@@ -32,6 +32,27 @@ int device_sm_count();         // SM count of the current device (cached)
 // zero, so the caller zeroes that head ONCE; TONY_B200_CLEAR_COUNTERS=1 clears it on the stream before every call
 // again (one memset node per launch: ~250 per BERT-large step).
 bool clear_counters_each_call();
+bool pdl_enabled();            // TONY_B200_PDL != 0 (default on)
+
+// Launch with programmatic stream serialization: the kernel's CTAs may be placed while the previous kernel of
+// the stream is still draining.  Every kernel launched this way starts with pdl_wait() (blocks until the previous
+// kernel has completed and its writes are visible) followed by pdl_launch_dependents(), so a chain of them
+// overlaps each launch latency with the predecessor's tail and nothing else.
+template <typename Kern, typename... Args>
+static inline cudaError_t launch_pdl_kernel(Kern kern, dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                            Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, args...);
+}
 // 2-D bf16 tensor map, 128-byte swizzle, `inner` contiguous (defined in gemm_tcgen05.cu)
 int make_tmap_2d_bf16(CUtensorMap* map, const void* ptr, long long inner_extent, long long outer_extent,
                       long long ld, int box_inner, int box_outer);

@@ -860,6 +860,8 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, i
                                      uint32_t flags, const __nv_bfloat16* __restrict__ bias,
                                      const float* __restrict__ rowsum_ws, __nv_bfloat16* __restrict__ rowsum_out,
                                      int rowsum_accumulate) {
+    pdl_wait();                // launched with programmatic stream serialization: see launch_pdl_kernel
+    pdl_launch_dependents();
     if (rowsum_out) {   // partial row sums of the split-K units (see GemmParams::rowsum_out)
         for (size_t r = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; r < static_cast<size_t>(M);
              r += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -1018,6 +1020,15 @@ static int make_tmap_2d_bf16_mode(CUtensorMap* map, const void* ptr, long long i
         return TONY_ERR_CUDA;
     }
     return TONY_OK;
+}
+
+bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("TONY_B200_PDL");
+        v = (e && atoi(e) == 0) ? 0 : 1;
+    }
+    return v == 1;
 }
 
 bool clear_counters_each_call() {
@@ -1310,12 +1321,12 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
         const int threads = 256;
         const int blocks = static_cast<int>(std::min<size_t>((total4 + threads - 1) / threads,
                                                              static_cast<size_t>(sms) * 8));
-        splitk_reduce_kernel<<<blocks, threads, 0, stream>>>(
-            static_cast<const float*>(workspace), splits, M, N, static_cast<__nv_bfloat16*>(C), ldc,
-            alpha, flags, static_cast<const __nv_bfloat16*>(bias), p.rowsum_ws,
-            static_cast<__nv_bfloat16*>(rowsum_out), rowsum_accumulate);
+        TONY_CUDA_CHECK(launch_pdl_kernel(
+            splitk_reduce_kernel, dim3(blocks), dim3(threads), 0, stream, static_cast<const float*>(workspace), splits, M,
+            N, static_cast<__nv_bfloat16*>(C), static_cast<long long>(ldc), alpha, static_cast<uint32_t>(flags),
+            static_cast<const __nv_bfloat16*>(bias), static_cast<const float*>(p.rowsum_ws),
+            static_cast<__nv_bfloat16*>(rowsum_out), rowsum_accumulate));
         count_launch();
-        TONY_CUDA_CHECK(cudaGetLastError());
     }
     return TONY_OK;
 }
@@ -1327,10 +1338,10 @@ int tony::launch_splitk_reduce(const float* ws, int splits, int M, int N, __nv_b
     const int threads = 256;
     const int blocks = static_cast<int>(std::min<size_t>((total4 + threads - 1) / threads,
                                                          static_cast<size_t>(device_sm_count()) * 8));
-    splitk_reduce_kernel<<<blocks, threads, 0, stream>>>(ws, splits, M, N, C, ldc, alpha, flags, nullptr, nullptr,
-                                                         nullptr, 0);
+    TONY_CUDA_CHECK(launch_pdl_kernel(splitk_reduce_kernel, dim3(blocks), dim3(threads), 0, stream, ws, splits, M, N, C, ldc,
+                                      alpha, static_cast<uint32_t>(flags), static_cast<const __nv_bfloat16*>(nullptr),
+                                      static_cast<const float*>(nullptr), static_cast<__nv_bfloat16*>(nullptr), 0));
     count_launch();
-    TONY_CUDA_CHECK(cudaGetLastError());
     return TONY_OK;
 }
 

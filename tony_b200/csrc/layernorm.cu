@@ -38,6 +38,8 @@ __global__ void __launch_bounds__(LN_WARPS * 32)
 layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ gamma,
                      const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                      float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, float eps) {
+    pdl_wait();                // launched with programmatic stream serialization: see launch_pdl_kernel
+    pdl_launch_dependents();
     constexpr int H = NV * 256;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int row = blockIdx.x * LN_WARPS + warp; row < rows; row += gridDim.x * LN_WARPS) {
@@ -93,6 +95,8 @@ layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat1
                         const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean,
                         const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx, int rows,
                         const __nv_bfloat16* __restrict__ add) {
+    pdl_wait();                // launched with programmatic stream serialization: see launch_pdl_kernel
+    pdl_launch_dependents();
     constexpr int H = NV * 256;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int row = blockIdx.x * LN_WARPS + warp; row < rows; row += gridDim.x * LN_WARPS) {
@@ -151,6 +155,8 @@ layernorm_bwd_dgdb_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloa
                           int rows_per_slab, float* __restrict__ partials, unsigned int* __restrict__ counters,
                           __nv_bfloat16* __restrict__ dgamma, __nv_bfloat16* __restrict__ dbeta,
                           int accumulate) {
+    pdl_wait();                // launched with programmatic stream serialization: see launch_pdl_kernel
+    pdl_launch_dependents();
     __shared__ float red[2][LN_RED_THREADS / 32][256];
     __shared__ unsigned int is_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -224,12 +230,11 @@ template <int NV>
 static int launch_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean,
                       float* rstd, int rows, float eps, cudaStream_t s) {
     const int grid = std::min((rows + LN_WARPS - 1) / LN_WARPS, device_sm_count() * 8);
-    layernorm_fwd_kernel<NV><<<grid, LN_WARPS * 32, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(gamma),
-        static_cast<const __nv_bfloat16*>(beta), static_cast<__nv_bfloat16*>(y), mean, rstd, rows,
-        eps);
+    TONY_CUDA_CHECK(launch_pdl_kernel(layernorm_fwd_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), 0, s,
+                                      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(gamma),
+                                      static_cast<const __nv_bfloat16*>(beta), static_cast<__nv_bfloat16*>(y), mean, rstd,
+                                      rows, eps));
     count_launch();
-    TONY_CUDA_CHECK(cudaGetLastError());
     return TONY_OK;
 }
 
@@ -240,11 +245,10 @@ static int launch_bwd(const void* dy, const void* x, const void* gamma, const fl
     constexpr int H = NV * 256;
     const int sms = device_sm_count();
     const int grid = std::min((rows + LN_WARPS - 1) / LN_WARPS, sms * 8);
-    layernorm_bwd_dx_kernel<NV><<<grid, LN_WARPS * 32, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
-        static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<__nv_bfloat16*>(dx), rows,
-        static_cast<const __nv_bfloat16*>(add));
-    TONY_CUDA_CHECK(cudaGetLastError());
+    TONY_CUDA_CHECK(launch_pdl_kernel(layernorm_bwd_dx_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), 0, s,
+                                      static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
+                                      static_cast<const __nv_bfloat16*>(gamma), mean, rstd,
+                                      static_cast<__nv_bfloat16*>(dx), rows, static_cast<const __nv_bfloat16*>(add)));
     // scratch: [4 KB counters][partials: slabs x 2 x H floats][group partials]
     const int col_tiles = H / 256;
     int slabs = std::max(1, std::min({LN_MAX_PARTIALS, (sms * LN_RED_CTAS_PER_SM) / col_tiles, std::max(1, rows / 16)}));
@@ -252,12 +256,11 @@ static int launch_bwd(const void* dy, const void* x, const void* gamma, const fl
     slabs = (rows + rows_per_slab - 1) / rows_per_slab;
     unsigned int* counters = reinterpret_cast<unsigned int*>(scratch);
     if (clear_counters_each_call()) TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
-    layernorm_bwd_dgdb_kernel<<<dim3(col_tiles, slabs), LN_RED_THREADS, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x), mean, rstd, rows, H,
-        rows_per_slab, scratch + 1024, counters, static_cast<__nv_bfloat16*>(dgamma),
-        static_cast<__nv_bfloat16*>(dbeta), accumulate);
+    TONY_CUDA_CHECK(launch_pdl_kernel(layernorm_bwd_dgdb_kernel, dim3(col_tiles, slabs), dim3(LN_RED_THREADS), 0, s,
+                                      static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x), mean,
+                                      rstd, rows, H, rows_per_slab, scratch + 1024, counters,
+                                      static_cast<__nv_bfloat16*>(dgamma), static_cast<__nv_bfloat16*>(dbeta), accumulate));
     count_launch(2);
-    TONY_CUDA_CHECK(cudaGetLastError());
     return TONY_OK;
 }
 
