@@ -315,6 +315,10 @@ def run_arm(args, impl, model_key, rank, world, device, sample_clocks=True):
     e2e = None
     if not args.skip_e2e:
         h2d = sum(v.numel() * v.element_size() for v in host[0].values())
+        # untimed warm-up of THIS path too: its first calls allocate the three resident input sets (77 MB each
+        # for ResNet-50) and order them against the compute stream, which is not a per-step cost
+        for i in range(min(3, max(1, args.warmup))):
+            trainer.step_async(host[i % nb]).result()
         sync_all()
         e0.record()
         # public pipelined API: step i's loss is read (D2H, pinned) after step i+2 is enqueued
