@@ -1,11 +1,18 @@
-import sys, time, torch
-sys.path.insert(0, '/root/repo')
+"""ResNet-50 step time with device-resident inputs vs the pipelined end-to-end call, the staging alone and a
+raw 77 MB host-to-device copy (was the end-to-end path itself slow, or its first calls?)."""
+import os
+import sys
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from tony_b200 import runtime
 from tony_b200.models import resnet
 dev = torch.device('cuda')
 torch.manual_seed(0)
 model = resnet.ResNet50(device=dev)
-tr = runtime.Trainer(model, lr=0.05, optimizer='sgd', device=dev) if 'optimizer' in runtime.Trainer.__init__.__code__.co_varnames else runtime.Trainer(model, lr=0.05, device=dev)
+tr = runtime.Trainer(model, lr=0.05, device=dev)
 host = [resnet.synthetic_batch(256, 'cpu', True, s) for s in range(4)]
 devb = {k: v.to(dev) for k, v in host[0].items()}
 def timed(fn, n=8):
