@@ -600,7 +600,7 @@ __device__ __forceinline__ void fold_rows_256(const float* __restrict__ partials
 #pragma unroll
         for (int j = 0; j < 8; ++j) t[i][j] = 0.f;
     if (c < cols) {
-        constexpr int Q = NS == 1 ? 4 : 2;          // rows in flight per warp: 8 float4 loads per thread
+        constexpr int Q = NS == 1 ? 4 : (NS == 2 ? 2 : 1);   // rows in flight per warp: >= 8 float4 loads per thread
         for (int k = warp; k < nparts; k += 8 * Q) {
             float4 a[Q][NS][2];
 #pragma unroll
@@ -658,18 +658,27 @@ static inline size_t fold_group_floats(int slabs, int ns, int cols) {
     return static_cast<size_t>((slabs + gs - 1) / gs) * ns * cols;
 }
 
+// (tile, ntiles, slab, nslabs): which 256-column tile / slab this call hands in; -1 = from blockIdx / gridDim of a
+// (column tile, slab) grid.  A kernel whose CTAs each cover several column tiles calls it once per tile.
 template <int NS>
 __device__ __forceinline__ bool fold_two_level_256(const float (&p)[NS], float* __restrict__ partials,
-                                                float* __restrict__ gparts, unsigned int* __restrict__ counters,
-                                                int cols, float (*red)[256], unsigned int* flag, float (&s)[NS]) {
-    const int nparts = static_cast<int>(gridDim.y);
+                                                   float* __restrict__ gparts, unsigned int* __restrict__ counters,
+                                                   int cols, float (*red)[256], unsigned int* flag, float (&s)[NS],
+                                                   int tile = -1, int ntiles = -1, int slab = -1, int nslabs = -1) {
+    if (tile < 0) {
+        tile = static_cast<int>(blockIdx.x);
+        ntiles = static_cast<int>(gridDim.x);
+        slab = static_cast<int>(blockIdx.y);
+        nslabs = static_cast<int>(gridDim.y);
+    }
+    const int nparts = nslabs;
     const int gs = fold_group_size(nparts);
     const int ngroups = (nparts + gs - 1) / gs;
-    const int grp = static_cast<int>(blockIdx.y) / gs;
+    const int grp = slab / gs;
     const int gsize = min(gs, nparts - grp * gs);
-    const int gc = blockIdx.x * 256 + threadIdx.x;
-    unsigned int* gcount = counters + gridDim.x + blockIdx.x * ngroups + grp;
-    float* my = partials + static_cast<size_t>(blockIdx.y) * NS * cols;
+    const int gc = tile * 256 + threadIdx.x;
+    unsigned int* gcount = counters + ntiles + tile * ngroups + grp;
+    float* my = partials + static_cast<size_t>(slab) * NS * cols;
     if (gc < cols) {
 #pragma unroll
         for (int i = 0; i < NS; ++i) my[static_cast<size_t>(i) * cols + gc] = p[i];
@@ -680,7 +689,7 @@ __device__ __forceinline__ bool fold_two_level_256(const float (&p)[NS], float* 
     __syncthreads();
     if (!*flag) return false;
     __threadfence();
-    fold_rows_256<NS>(partials + static_cast<size_t>(grp) * gs * NS * cols, gsize, blockIdx.x * 256, cols, red, s);
+    fold_rows_256<NS>(partials + static_cast<size_t>(grp) * gs * NS * cols, gsize, tile * 256, cols, red, s);
     if (ngroups == 1) {
         if (threadIdx.x == 0) *gcount = 0;
         return true;
@@ -694,13 +703,13 @@ __device__ __forceinline__ bool fold_two_level_256(const float (&p)[NS], float* 
     __syncthreads();
     if (threadIdx.x == 0) {
         *gcount = 0;
-        *flag = (atomicAdd(&counters[blockIdx.x], 1u) == static_cast<unsigned int>(ngroups - 1)) ? 1u : 0u;
+        *flag = (atomicAdd(&counters[tile], 1u) == static_cast<unsigned int>(ngroups - 1)) ? 1u : 0u;
     }
     __syncthreads();
     if (!*flag) return false;
     __threadfence();
-    fold_rows_256<NS>(gparts, ngroups, blockIdx.x * 256, cols, red, s);
-    if (threadIdx.x == 0) counters[blockIdx.x] = 0;
+    fold_rows_256<NS>(gparts, ngroups, tile * 256, cols, red, s);
+    if (threadIdx.x == 0) counters[tile] = 0;
     return true;
 }
 
