@@ -130,6 +130,13 @@ int tony_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out,
 int tony_act_bwd_colsum_bf16(const void* dy, const void* pre, void* dpre, int act, int rows, int cols, long long ld,
                              void* dbias, float* scratch, size_t scratch_bytes, int accumulate, void* stream);
 
+/* packed[r, p*H + c] = {a, b, c}[p][r, c] (three [rows, H] matrices with their own row strides -> [rows, 3H]) and
+ * dbias[3H] (+)= column sums of packed, in one pass; H a multiple of 256; scratch as tony_colsum_bf16 for 3H columns.
+ * Serves the fused QKV projection's backward when the attention core is a library that returns dq / dk / dv apart. */
+int tony_pack3_rows_colsum(const void* a, const void* b, const void* c, long long lda, long long ldb, long long ldc,
+                           void* packed, int rows, int H, void* dbias, float* scratch, size_t scratch_bytes,
+                           int accumulate, void* stream);
+
 /* Same result as tony_colsum_bf16, but the partial-sum scratch is a fixed 2 MiB device
  * array built into the library, so the call performs no allocation and needs no scratch
  * pointer.  For host programs that cannot allocate device memory themselves: a framework

@@ -214,6 +214,30 @@ def test_linear_act_backward_matches_torch():
             _close(got.grad, ref.grad, rel=2e-2)
 
 
+def test_pack3_rows_colsum_matches_separate_ops():
+    """dq / dk / dv with their own row strides -> packed [rows, 3H] plus the column sums of what was written."""
+    from tony_b200.ops import _lib
+
+    rows, H = 3000, 512
+    parts = [_rand(rows, H + 64)[:, :H] for _ in range(3)]          # row stride H + 64: not contiguous
+    packed = torch.empty(rows, 3 * H, device=DEV, dtype=torch.bfloat16)
+    db0 = _rand(3 * H)
+    db = db0.clone()
+    lib = _lib.lib()
+    nbytes = int(lib.tony_colsum_scratch_bytes(3 * H))
+    scratch = F.workspace("colsum", nbytes, DEV, counters=True)
+    for acc in (0, 1):
+        _lib.check(lib.tony_pack3_rows_colsum(_lib.ptr(parts[0]), _lib.ptr(parts[1]), _lib.ptr(parts[2]),
+                                              parts[0].stride(0), parts[1].stride(0), parts[2].stride(0),
+                                              _lib.ptr(packed), rows, H, _lib.ptr(db), _lib.ptr(scratch), nbytes, acc,
+                                              _lib.cur_stream()), "tony_pack3_rows_colsum")
+        want = torch.cat(parts, dim=1)
+        assert torch.equal(packed, want)
+        ref = want.float().sum(0) + (db0.float() if acc else 0)
+        _close(db, ref, rel=1e-2)
+        db = db0.clone()
+
+
 def test_adamw_flat_matches_torch():
     from tony_b200.ops import optim as O
 

@@ -164,6 +164,67 @@ colsum_fused_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, lon
     }
 }
 
+// Interleave three [rows, H] matrices (the separate dq / dk / dv a library attention backward returns) into the
+// packed [rows, 3H] gradient of the fused QKV projection AND produce that projection's bias gradient - the column
+// sums of what is written - in the same pass.  Same structure as colsum_fused_kernel; a 256-column tile never
+// straddles two sources because H is a multiple of 256 here.
+__global__ void __launch_bounds__(CS_THREADS, 4)
+pack3_colsum_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
+                    const __nv_bfloat16* __restrict__ c, long long lda, long long ldb, long long ldc, int H, int rows,
+                    int rows_per_slab, __nv_bfloat16* __restrict__ packed, float* __restrict__ partials,
+                    float* __restrict__ gparts, unsigned int* __restrict__ counters, __nv_bfloat16* __restrict__ out,
+                    int accumulate) {
+    pdl_wait();
+    pdl_launch_dependents();
+    __shared__ float red[CS_THREADS / 32][256];
+    __shared__ unsigned int is_last;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int cols = 3 * H;
+    const int col = blockIdx.x * 256 + lane * 8;
+    const int part = (blockIdx.x * 256) / H;
+    const int pc = col - part * H;
+    const __nv_bfloat16* src = part == 0 ? a : (part == 1 ? b : c);
+    const long long ld = part == 0 ? lda : (part == 1 ? ldb : ldc);
+    const int r0 = blockIdx.y * rows_per_slab;
+    const int r1 = min(rows, r0 + rows_per_slab);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    constexpr int W = CS_THREADS / 32;
+    for (int r = r0 + warp; r < r1; r += 8 * W) {
+        uint4 u[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int rr = r + k * W;
+            u[k] = rr < r1 ? ld_global_nc_v4(src + static_cast<size_t>(rr) * ld + pc) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int rr = r + k * W;
+            if (rr < r1) st_global_v4(packed + static_cast<size_t>(rr) * cols + col, u[k]);
+            const uint32_t w[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(w[j]);
+                acc[2 * j] += f.x;
+                acc[2 * j + 1] += f.y;
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = acc[j];
+    __syncthreads();
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < W; ++w) s += red[w][threadIdx.x];
+    __syncthreads();
+    const float pp[1] = {s};
+    float tt[1];
+    if (!fold_two_level_256<1>(pp, partials, gparts, counters, cols, red, &is_last, tt)) return;
+    const int gc = blockIdx.x * 256 + threadIdx.x;
+    float t = tt[0];
+    if (accumulate) t += __bfloat162float(out[gc]);
+    out[gc] = __float2bfloat16(t);
+}
+
 }  // namespace tony
 
 using namespace tony;
@@ -237,6 +298,41 @@ extern "C" int tony_act_bwd_colsum_bf16(const void* dy, const void* pre, void* d
     if (!pre || !dpre || act < 1 || act > 3) return TONY_ERR_INVALID;
     return colsum_launch("tony_act_bwd_colsum_bf16", dy, pre, dpre, act, rows, cols, ld, dbias, scratch, scratch_bytes,
                          accumulate, stream);
+}
+
+extern "C" int tony_pack3_rows_colsum(const void* a, const void* b, const void* c, long long lda, long long ldb,
+                                      long long ldc, void* packed, int rows, int H, void* dbias, float* scratch,
+                                      size_t scratch_bytes, int accumulate, void* stream) {
+    if (!a || !b || !c || !packed || !dbias || !scratch || rows <= 0 || H <= 0) return TONY_ERR_INVALID;
+    if ((H % 256) || (lda % 8) || (ldb % 8) || (ldc % 8) ||
+        ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(c) |
+          reinterpret_cast<uintptr_t>(packed)) & 15)) {
+        set_last_error("tony_pack3_rows_colsum", "H must be a multiple of 256, strides multiples of 8, pointers 16B aligned");
+        return TONY_ERR_UNSUPPORTED;
+    }
+    const int cols = 3 * H;
+    if (scratch_bytes < tony_colsum_scratch_bytes(cols)) {
+        set_last_error("tony_pack3_rows_colsum", "scratch too small (see tony_colsum_scratch_bytes(3 * H))");
+        return TONY_ERR_INVALID;
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int col_tiles = cols / 256;
+    int slabs = std::max(1, std::min(CS_MAX_SLABS_FUSED, (device_sm_count() * 4) / col_tiles));
+    slabs = std::min(slabs, std::max(1, rows / 64));
+    const int rows_per_slab = (rows + slabs - 1) / slabs;
+    slabs = (rows + rows_per_slab - 1) / rows_per_slab;
+    if (fold_counter_words(col_tiles, slabs) > 1024) return TONY_ERR_TOO_LARGE;
+    unsigned int* counters = reinterpret_cast<unsigned int*>(scratch);
+    float* partials = scratch + 1024;
+    float* gparts = partials + static_cast<size_t>(CS_MAX_SLABS_FUSED) * cols;
+    if (clear_counters_each_call()) TONY_CUDA_CHECK(cudaMemsetAsync(counters, 0, 4096, s));
+    TONY_CUDA_CHECK(launch_pdl_kernel(pack3_colsum_kernel, dim3(col_tiles, slabs), dim3(CS_THREADS), 0, s,
+                                      static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b),
+                                      static_cast<const __nv_bfloat16*>(c), lda, ldb, ldc, H, rows, rows_per_slab,
+                                      static_cast<__nv_bfloat16*>(packed), partials, gparts, counters,
+                                      static_cast<__nv_bfloat16*>(dbias), accumulate));
+    count_launch();
+    return TONY_OK;
 }
 
 // ---------------------------------------------------------------------------------------

@@ -125,6 +125,8 @@ def _declare(lib) -> None:
     lib.tony_colsum_scratch_bytes.restype = c_size_t
     lib.tony_colsum_bf16.argtypes = [vp, c_int, c_int, c_longlong, vp, vp, c_size_t, c_int, vp]
     lib.tony_act_bwd_colsum_bf16.argtypes = [vp, vp, vp, c_int, c_int, c_int, c_longlong, vp, vp, c_size_t, c_int, vp]
+    lib.tony_pack3_rows_colsum.argtypes = [vp, vp, vp, c_longlong, c_longlong, c_longlong, vp, c_int, c_int, vp, vp,
+                                           c_size_t, c_int, vp]
     lib.tony_colsum_bf16_static.argtypes = [vp, c_int, c_int, c_longlong, vp, c_int, vp]
     lib.tony_adamw_flat.argtypes = [vp, vp, vp, vp, vp, c_size_t, c_float, c_float, c_float, c_float,
                                     c_float, c_float, c_float, c_float, vp, c_size_t, vp]

@@ -1061,7 +1061,7 @@ class _PackedAttentionFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dout):
         saved, ctx.saved_core = ctx.saved_core, None
-        return _attention_core_backward(saved, dout), None
+        return _attention_core_backward(saved, dout)[0], None
 
 
 def fused_attention_supported(qkv) -> bool:
@@ -1086,8 +1086,12 @@ def _attention_core_forward(qkv, causal):
     return o.detach().transpose(1, 2).reshape(B, S, nh * hd), ("library", q, k, v, o, (B, S, nh, hd))
 
 
-def _attention_core_backward(saved, dout):
-    """-> packed gradient ``[B, S, 3, heads, head_dim]``."""
+_NOT_DONE = object()     # _attention_core_backward: the caller still owes the bias gradient
+
+
+def _attention_core_backward(saved, dout, bias=None):
+    """-> (packed gradient ``[B, S, 3, heads, head_dim]``, bias-gradient result or ``_NOT_DONE``).  With ``bias``
+    (the fused QKV projection's bias) the library path packs dq / dk / dv AND sums their columns in one kernel."""
     if saved[0] == "tcgen05":
         _, qkv, out, lse, (B, S, nh, hd, causal, scale) = saved
         dout = dout.contiguous()
@@ -1096,7 +1100,7 @@ def _attention_core_backward(saved, dout):
         check(_lib.lib().tony_attention_bwd_bf16(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(delta),
                                                  ptr(dqkv), B, S, nh, hd, causal, scale, cur_stream()),
               "tony_attention_bwd_bf16")
-        return dqkv
+        return dqkv, _NOT_DONE
     _, q, k, v, o, (B, S, nh, hd) = saved
     do = dout.reshape(B, S, nh, hd).transpose(1, 2)
     dq, dk, dv = torch.autograd.grad(o, (q, k, v), do)
@@ -1110,13 +1114,22 @@ def _attention_core_backward(saved, dout):
 
     strides = [rows_view(t) for t in parts]
     if dout.dtype == torch.bfloat16 and H % 8 == 0 and all(st is not None for st in strides):
+        if bias is not None and H % 256 == 0:
+            dest = _GradDest(bias)
+            db = dest.tensor if dest.tensor is not None else torch.empty(3 * H, dtype=torch.bfloat16, device=dout.device)
+            nbytes = int(_lib.lib().tony_colsum_scratch_bytes(3 * H))
+            scratch = workspace("colsum", nbytes, dout.device, counters=True)
+            check(_lib.lib().tony_pack3_rows_colsum(ptr(parts[0]), ptr(parts[1]), ptr(parts[2]), strides[0], strides[1],
+                                                    strides[2], ptr(dqkv), B * S, H, ptr(db), ptr(scratch), nbytes,
+                                                    int(dest.accumulate), cur_stream()), "tony_pack3_rows_colsum")
+            return dqkv, dest.finish(db)
         check(_lib.lib().tony_pack3_rows(ptr(parts[0]), ptr(parts[1]), ptr(parts[2]), strides[0],
                                          strides[1], strides[2], ptr(dqkv), B * S, H, cur_stream()),
               "tony_pack3_rows")
     else:
         for i, t in enumerate(parts):
             dqkv[:, :, i].copy_(t)
-    return dqkv
+    return dqkv, _NOT_DONE
 
 
 class _AttentionBlockFn(torch.autograd.Function):
@@ -1153,12 +1166,16 @@ class _AttentionBlockFn(torch.autograd.Function):
         # dgrad GEMMs before the matching wgrad: see the ordering note in _MlpFn.backward
         do = gemm(dy2, wo, b_mn=True)
         dwo, dbo = _weight_bias_grad(dy2, o2, wo, ctx.bo)
-        dqkv = _attention_core_backward(ctx.saved_core, do.view(B, S, H)).view(B * S, 3 * H)
+        dqkv, dbqkv = _attention_core_backward(ctx.saved_core, do.view(B, S, H), ctx.bqkv)
+        dqkv = dqkv.view(B * S, 3 * H)
         ctx.saved_core = None
         dx = None
         if ctx.needs_input_grad[0]:
             dx = gemm(dqkv, wqkv, b_mn=True, flags=EPI_RESIDUAL, aux=dy2).view(B, S, H)
-        dwqkv, dbqkv = _weight_bias_grad(dqkv, x2, wqkv, ctx.bqkv)
+        if dbqkv is _NOT_DONE:
+            dwqkv, dbqkv = _weight_bias_grad(dqkv, x2, wqkv, ctx.bqkv)
+        else:
+            dwqkv = _weight_grad(dqkv, x2, wqkv)
         return dx, dwqkv, dbqkv, dwo, dbo, None, None
 
 
