@@ -1181,10 +1181,24 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
         if (force_block_n == 512) {
             use_2cta = true;
         } else if ((force_block_n == 0 || (ag != nullptr && force_block_n == 256)) && N >= 256 && M >= 256) {
-            // measured on BERT-large (profiles/): the pair kernel wins on every such shape,
+            // measured on BERT-large (profiles/): the pair kernel wins on every such shape with many tiles,
             // even where its wave quantisation is worse, because each SM moves a third less
             // operand traffic and the smem ring is 6 deep
             use_2cta = true;
+            if (ag == nullptr && force_block_n == 0 && rowsum_out == nullptr) {
+                // few tiles (ResNet's 7x7 / 14x14 pointwise gradients: 12544 x 512 is 98 pair tiles on 74 pairs):
+                // compare SM-time per wave x waves of the three tilings instead of assuming the pair kernel
+                const long long ta_ = static_cast<long long>((M + 255) / 256) * ((N + 255) / 256);
+                const long long tb_ = static_cast<long long>(num_m) * ((N + 255) / 256);
+                const long long tc_ = static_cast<long long>(num_m) * ((N + 127) / 128);
+                const double cost_a = static_cast<double>((ta_ + workers / 2 - 1) / (workers / 2)) * 32768.0 / 1.12;
+                const double cost_b = static_cast<double>((tb_ + workers - 1) / workers) * 32768.0;
+                const double cost_c = static_cast<double>((tc_ + workers - 1) / workers) * 16384.0 * 1.08;
+                if (ta_ * 2 > workers / 2 && std::min(cost_b, cost_c) < 0.9 * cost_a) {
+                    use_2cta = false;
+                    block_n = cost_c < cost_b ? 128 : 256;
+                }
+            }
         }
     }
     if (rowsum_out && !use_2cta) {
@@ -1212,7 +1226,10 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
     if (splittable) {
         if (force_splits > 1) {
             splits = force_splits;
-        } else if (force_splits == 0 && (tiles * 2 <= workers || wave_efficiency(tiles, workers) < 0.75)) {
+        } else if (force_splits == 0 &&
+                   (tiles * 2 <= workers ||
+                    (wave_efficiency(tiles, workers) < 0.75 && static_cast<long long>(M) * N <= (4ll << 20)))) {
+            // (a big output pays for its fp32 partials: 12544 x 512 split three ways wrote and re-read 77 MB)
             double best = wave_efficiency(tiles, workers);
             // up to 16 splits normally; very long reductions over one or two output tiles (pointwise-convolution
             // weight gradients: K = every pixel of the batch) may use one split per SM

@@ -30,12 +30,22 @@ def timeit(fn, do_flush):
 
 
 T = 16384
-shapes = [("fwd qkv", T, 3072, 1024, False, False), ("fwd attn_out", T, 1024, 1024, False, False),
+# ResNet-50 (256 images): the pointwise convolutions' data / weight gradients run on this kernel as GEMMs over the
+# [N*H*W, C] activation.  name, M, N, K, a_mn, b_mn
+RESNET = []
+for tag, px, cin, cout in (("l1 64->256 @56", 802816, 64, 256), ("l1 256->64 @56", 802816, 256, 64),
+                           ("l2 128->512 @28", 200704, 128, 512), ("l2 512->128 @28", 200704, 512, 128),
+                           ("l3 256->1024 @14", 50176, 256, 1024), ("l3 1024->256 @14", 50176, 1024, 256),
+                           ("l4 512->2048 @7", 12544, 512, 2048), ("l4 2048->512 @7", 12544, 2048, 512)):
+    RESNET.append((f"resnet dgrad {tag}", px, cin, cout, False, True))
+    RESNET.append((f"resnet wgrad {tag}", cout, cin, px, True, True))
+BERT = [("fwd qkv", T, 3072, 1024, False, False), ("fwd attn_out", T, 1024, 1024, False, False),
           ("fwd ffn1", T, 4096, 1024, False, False), ("fwd ffn2", T, 1024, 4096, False, False),
           ("dgrad ffn2", T, 4096, 1024, False, True), ("dgrad ffn1", T, 1024, 4096, False, True),
           ("dgrad qkv", T, 1024, 3072, False, True),
           ("wgrad ffn1", 4096, 1024, T, True, True), ("wgrad attn_out", 1024, 1024, T, True, True),
           ("wgrad qkv", 3072, 1024, T, True, True)]
+shapes = RESNET if (len(sys.argv) > 1 and sys.argv[1] == "resnet") else BERT
 for name, M, N, K, a_mn, b_mn in shapes:
     A = torch.randn(M, K, device=dev).to(torch.bfloat16)
     B = torch.randn(N, K, device=dev).to(torch.bfloat16)
