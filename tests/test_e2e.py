@@ -313,11 +313,11 @@ def test_mnist_pytorch_two_workers_gloo(cluster):
     assert client.submit_to_first_step_ms is not None
 
 
-def _example(cluster, rel, script, extra_conf=()):
+def _example(cluster, rel, script, extra_conf=(), conf="tony.xml"):
     repo = os.path.dirname(os.path.dirname(SCRIPTS))
     ex = os.path.join(repo, "examples", rel)
     client = cluster.new_client()
-    argv = ["--conf_file", os.path.join(ex, "tony.xml"), "--executes", os.path.join(ex, script),
+    argv = ["--conf_file", os.path.join(ex, conf), "--executes", os.path.join(ex, script),
             "--python_binary_path", PY, "--conf", "tony.am.wait-client-signal-stop-timeout-sec=2"]
     for c in extra_conf:
         argv += ["--conf", c]
@@ -330,6 +330,35 @@ def test_example_tensorflow_ps_worker(cluster):
     assert rc == 0
     st = statuses(client)
     assert st["worker:0"] == st["worker:1"] == TaskStatus.SUCCEEDED and st["ps:0"] == TaskStatus.FINISHED
+
+
+def test_example_tensorflow_multiworker(cluster):
+    """MultiWorkerMirrored-shaped job: workers only, gradients all-reduced over the TF_CONFIG addresses."""
+    rc, client = _example(cluster, "mnist-tensorflow", "mnist_multiworker.py", conf="tony-multiworker.xml")
+    assert rc == 0
+    assert statuses(client) == {"worker:0": TaskStatus.SUCCEEDED, "worker:1": TaskStatus.SUCCEEDED}
+
+
+def test_example_tensorflow_estimator_chief_worker_evaluator(cluster, tmp_path):
+    """train_and_evaluate-shaped job: chief + worker train; the untracked evaluator is outside their TF_CONFIG."""
+    client = cluster.new_client()
+    repo = os.path.dirname(os.path.dirname(SCRIPTS))
+    ex = os.path.join(repo, "examples", "mnist-tensorflow")
+    assert client.init(["--conf_file", os.path.join(ex, "tony-estimator.xml"),
+                        "--executes", os.path.join(ex, "mnist_estimator_style.py"), "--python_binary_path", PY,
+                        "--task_params", f"--model_dir {tmp_path}/model",
+                        "--conf", "tony.am.wait-client-signal-stop-timeout-sec=2"])
+    assert client.start() == 0
+    st = statuses(client)
+    assert st["chief:0"] == st["worker:0"] == TaskStatus.SUCCEEDED
+    assert st["evaluator:0"] in (TaskStatus.FINISHED, TaskStatus.SUCCEEDED)
+    assert os.path.exists(os.path.join(str(tmp_path), "model", "DONE"))
+
+
+def test_example_ray_shaped_program_on_head_and_workers(cluster):
+    rc, client = _example(cluster, "ray-on-tony", "example.py")
+    assert rc == 0
+    assert statuses(client)["head:0"] == TaskStatus.SUCCEEDED
 
 
 def test_example_mxnet_dmlc_roles(cluster):

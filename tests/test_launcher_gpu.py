@@ -86,6 +86,21 @@ def test_horovod_shaped_mnist_job_through_launcher():
         assert "done: loss" in text, text[-2000:]
 
 
+def test_horovod_keras_shaped_job_with_callbacks_through_launcher():
+    """examples/horovod-on-tony/torch_mnist_hvd_callbacks.py: fit() driven by broadcast / metric-average /
+    learning-rate warm-up / rank-0 checkpoint callbacks (the reference's tensorflow2_keras_mnist.py shape)."""
+    os.environ["TONY_B200_QUIET"] = "1"
+    os.environ.pop("TONY_B200_FAKE_GPUS", None)
+    n = min(2, torch.cuda.device_count())
+    with MiniCluster() as cluster:
+        rc, client = _submit(cluster, "horovod-on-tony/torch_mnist_hvd_callbacks.py", "--epochs 3 --batches 8 --batch 128",
+                             ["tony.application.framework=horovod", f"tony.worker.instances={n}",
+                              "tony.worker.gpus=1"])
+        assert rc == 0, _logs(client)
+        text = _logs(client)
+        assert "done: loss" in text and "epoch 2: mean loss" in text, text[-2000:]
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs (1 ps + 1 worker at least)")
 def test_widedeep_dedicated_parameter_servers_through_launcher():
     """BASELINE config 4's role split: ps tasks on their own GPUs own the shards and run only the fused

@@ -203,6 +203,15 @@ class DistributedOptimizer:
     def synchronize(self):
         torch.cuda.current_stream().wait_stream(self.opt.comm_stream)
 
+    def set_lr(self, lr: float) -> None:
+        """Learning-rate schedules / warm-up callbacks (the rate is a launch argument of the fused kernel, so the
+        next ``step()`` uses it)."""
+        self.opt.lr = float(lr)
+
+    @property
+    def lr(self) -> float:
+        return self.opt.lr
+
     def check(self):
         """Raise if a fused collective gave up waiting for a peer (GPU-side hang detection)."""
         self.store.comm.check_status()
