@@ -1192,3 +1192,31 @@ def packed_attention(qkv, causal: bool = False):
     sm_100 flash kernel, which the own kernels do not beat yet (profiles/r1_attention_*.md has
     the measured comparison), and the default follows the measurement."""
     return _PackedAttentionFn.apply(qkv, causal)
+
+
+# ---------------------------------------------------------------------------------------
+# Optional NVTX ranges around every public op (TONY_B200_NVTX=1): a timeline tool then shows which
+# framework call each kernel belongs to.  Off by default: a range is two driver calls per op.
+# ---------------------------------------------------------------------------------------
+def _nvtx_wrap(fn, label):
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(*args, **kwargs):
+        torch.cuda.nvtx.range_push(label)
+        try:
+            return fn(*args, **kwargs)
+        finally:
+            torch.cuda.nvtx.range_pop()
+
+    return wrapped
+
+
+NVTX_OPS = ("gemm", "colsum", "act_bwd_bias_grad", "linear", "mlp", "linear_act", "layer_norm", "softmax_cross_entropy",
+            "embedding", "embedding_sum", "packed_attention", "attention_block", "conv2d_nhwc", "conv2d_dgrad_nhwc",
+            "conv2d_wgrad_nhwc", "conv2d", "conv1x1_fork", "conv1x1_pair", "stem_conv7x7s2", "batch_norm_act",
+            "max_pool_3x3_s2")
+if os.environ.get("TONY_B200_NVTX", "0") == "1":
+    for _name in NVTX_OPS:
+        if _name in globals():
+            globals()[_name] = _nvtx_wrap(globals()[_name], "tony." + _name)
