@@ -94,7 +94,7 @@ def build(force: bool = False, selftest: bool = False, verbose: bool = False) ->
     LIB_DIR.mkdir(exist_ok=True)
     OBJ_DIR.mkdir(exist_ok=True)
     srcs = existing_sources()
-    deps = srcs + [CSRC / "common.cuh", INCLUDE / "tony_b200_kernels.h"]
+    deps = srcs + [CSRC / "common.cuh", CSRC / "host_math.h", INCLUDE / "tony_b200_kernels.h"]
     stamp = LIB_DIR / ".build_stamp"
     digest = _digest(deps)
     lib = LIB_DIR / LIB_NAME

@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "host_math.h"
 #include "tony_b200_kernels.h"
 
 namespace tony {
@@ -640,23 +641,7 @@ __device__ __forceinline__ void fold_rows_256(const float* __restrict__ partials
     }
 }
 
-__device__ __forceinline__ int fold_group_size(int nparts) {
-    int gs = 8;
-    while (gs * gs < nparts) ++gs;
-    return gs;
-}
-// words of counters a launch with `tiles` column tiles and `slabs` slabs touches (hosts check <= 1024)
-static inline int fold_counter_words(int tiles, int slabs) {
-    int gs = 8;
-    while (gs * gs < slabs) ++gs;
-    return tiles * (1 + (slabs + gs - 1) / gs);
-}
-// floats of group partials such a launch needs
-static inline size_t fold_group_floats(int slabs, int ns, int cols) {
-    int gs = 8;
-    while (gs * gs < slabs) ++gs;
-    return static_cast<size_t>((slabs + gs - 1) / gs) * ns * cols;
-}
+// fold_group_size / fold_counter_words / fold_group_floats: host_math.h
 
 // (tile, ntiles, slab, nslabs): which 256-column tile / slab this call hands in; -1 = from blockIdx / gridDim of a
 // (column tile, slab) grid.  A kernel whose CTAs each cover several column tiles calls it once per tile.

@@ -43,24 +43,7 @@ constexpr int CV_STAGING_BYTES = CV_EPI_WARPS * 2048;
 constexpr int CV_CHUNK_BYTES = 64 * 128;   // [64 rows][128 B]
 constexpr int CV_MAX_TAPS = 16;
 
-// Division by a launch-time constant as multiply + shift: q = (n * mul) >> shr, exact for 0 <= n < 2^31
-// (mul = floor(2^shr / d) + 1 with shr = 31 + ceil(log2 d)).  The tile -> (image, row, column) index math runs in
-// every warp for every tile; as 32-bit divisions it was a third of the instructions the epilogue warps issued.
-struct FastDiv {
-    uint32_t d, mul, shr;
-};
-static inline FastDiv make_fastdiv(int d) {
-    FastDiv f;
-    f.d = d > 0 ? static_cast<uint32_t>(d) : 1u;
-    uint32_t s = 0;
-    while ((1ull << s) < f.d) ++s;
-    f.shr = 31 + s;
-    f.mul = static_cast<uint32_t>((1ull << f.shr) / f.d + 1);
-    return f;
-}
-__device__ __forceinline__ int fdiv(int n, const FastDiv& f) {
-    return static_cast<int>((static_cast<unsigned long long>(static_cast<uint32_t>(n)) * f.mul) >> f.shr);
-}
+// FastDiv / fdiv (division by launch-time constants as multiply + shift) live in host_math.h
 
 struct ConvTap {
     unsigned short off_w, off_h;   // im2col offsets from the tile's base pixel

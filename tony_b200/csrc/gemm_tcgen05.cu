@@ -1125,10 +1125,7 @@ static int two_cta_mode() {
     return mode;
 }
 
-static double wave_efficiency(long long units, int sms) {
-    const long long waves = (units + sms - 1) / sms;
-    return static_cast<double>(units) / static_cast<double>(waves * sms);
-}
+// wave_efficiency: host_math.h
 
 }  // namespace tony
 
@@ -1186,17 +1183,12 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
             // operand traffic and the smem ring is 6 deep
             use_2cta = true;
             if (ag == nullptr && force_block_n == 0 && rowsum_out == nullptr) {
-                // few tiles (ResNet's 7x7 / 14x14 pointwise gradients: 12544 x 512 is 98 pair tiles on 74 pairs):
-                // compare SM-time per wave x waves of the three tilings instead of assuming the pair kernel
-                const long long ta_ = static_cast<long long>((M + 255) / 256) * ((N + 255) / 256);
-                const long long tb_ = static_cast<long long>(num_m) * ((N + 255) / 256);
-                const long long tc_ = static_cast<long long>(num_m) * ((N + 127) / 128);
-                const double cost_a = static_cast<double>((ta_ + workers / 2 - 1) / (workers / 2)) * 32768.0 / 1.12;
-                const double cost_b = static_cast<double>((tb_ + workers - 1) / workers) * 32768.0;
-                const double cost_c = static_cast<double>((tc_ + workers - 1) / workers) * 16384.0 * 1.08;
-                if (ta_ * 2 > workers / 2 && std::min(cost_b, cost_c) < 0.9 * cost_a) {
+                // few tiles (ResNet's 7x7 / 14x14 pointwise gradients, N not a multiple of 256): compare SM-time per
+                // wave x waves of the three tilings instead of assuming the pair kernel
+                const int pick = choose_gemm_tiling(M, N, workers);     // host_math.h
+                if (pick != 512) {
                     use_2cta = false;
-                    block_n = cost_c < cost_b ? 128 : 256;
+                    block_n = pick;
                 }
             }
         }
