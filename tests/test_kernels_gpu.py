@@ -565,9 +565,11 @@ def test_fused_batchnorm_matches_aten(C, relu, with_res):
         assert (d > 5e-2 * scale).float().mean().item() < 2e-3
 
 
-def test_maxpool_3x3_s2_matches_aten():
+@pytest.mark.parametrize("H,W", [(30, 23), (31, 16), (7, 7), (112, 112)])
+def test_maxpool_3x3_s2_matches_aten(H, W):
+    """Even / odd extents: the backward works on 2 x 2 pixel blocks, the last block row / column may be half empty."""
     torch.manual_seed(6)
-    x = _rand(4, 64, 30, 23).contiguous(memory_format=torch.channels_last)
+    x = _rand(2, 64, H, W).contiguous(memory_format=torch.channels_last)
     a = x.clone().requires_grad_()
     b = x.float().requires_grad_()
     y = F.max_pool_3x3_s2(a)

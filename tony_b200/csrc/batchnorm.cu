@@ -575,38 +575,65 @@ maxpool3x3s2_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __re
 __global__ void __launch_bounds__(256)
 maxpool3x3s2_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const unsigned char* __restrict__ idx,
                         __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int OH, int OW) {
+    // One thread per 2 x 2 block of input pixels (rows 2i, 2i+1; columns 2j, 2j+1) and 8 channels.  The block is
+    // covered by exactly the windows (i + u, j + v), u, v in {0, 1}: pixel (a, b) of the block sits at row
+    // r = a + 1 - 2u, column s = b + 1 - 2v of window (u, v), which is inside the window for u <= a, v <= b.
+    // Each window's (dy, position) pair is loaded once per block - 4 loads for 4 pixels, where one thread per pixel
+    // looked at 1 / 2 / 2 / 4 windows (9 loads per block, 1.4 GB through L2 for the ResNet stem).
     const int groups = C / 8;
-    const long long total = static_cast<long long>(N) * H * W * groups;
+    const int HB = (H + 1) / 2, WB = (W + 1) / 2;
+    const long long total = static_cast<long long>(N) * HB * WB * groups;
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<long long>(gridDim.x) * blockDim.x) {
         const int cg = static_cast<int>(i % groups);
         long long t = i / groups;
-        const int iw = static_cast<int>(t % W);
-        t /= W;
-        const int ih = static_cast<int>(t % H);
-        const int n = static_cast<int>(t / H);
-        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        const int oh_lo = max(0, ih / 2), oh_hi = min(OH - 1, (ih + 1) / 2);       // windows with oh*2-1 <= ih <= oh*2+1
-        const int ow_lo = max(0, iw / 2), ow_hi = min(OW - 1, (iw + 1) / 2);
-        for (int oh = oh_lo; oh <= oh_hi; ++oh) {
-            const int r = ih - (oh * 2 - 1);
-            if (r < 0 || r > 2) continue;
-            for (int ow = ow_lo; ow <= ow_hi; ++ow) {
-                const int s = iw - (ow * 2 - 1);
-                if (s < 0 || s > 2) continue;
-                const int p = r * 3 + s;
+        const int jb = static_cast<int>(t % WB);
+        t /= WB;
+        const int ib = static_cast<int>(t % HB);
+        const int n = static_cast<int>(t / HB);
+        float acc[2][2][8];
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[a][b][j] = 0.f;
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int oh = ib + u;
+            if (oh >= OH) continue;
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                const int ow = jb + v;
+                if (ow >= OW) continue;
                 const size_t o = ((static_cast<size_t>(n) * OH + oh) * OW + ow) * C + cg * 8;
                 const uint2 packed = *reinterpret_cast<const uint2*>(idx + o);
                 float g[8];
                 unpack8f(ld_global_nc_v4(dy + o), g);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const int pj = ((j < 4 ? packed.x : packed.y) >> ((j & 3) * 8)) & 0xff;
-                    if (pj == p) acc[j] += g[j];
-                }
+                for (int a = u; a < 2; ++a)
+#pragma unroll
+                    for (int b = v; b < 2; ++b) {
+                        const int p = (a + 1 - 2 * u) * 3 + (b + 1 - 2 * v);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int pj = ((j < 4 ? packed.x : packed.y) >> ((j & 3) * 8)) & 0xff;
+                            if (pj == p) acc[a][b][j] += g[j];
+                        }
+                    }
             }
         }
-        st_global_v4(dx + ((static_cast<size_t>(n) * H + ih) * W + iw) * C + cg * 8, pack8f(acc));
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+            const int ih = 2 * ib + a;
+            if (ih >= H) continue;
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                const int iw = 2 * jb + b;
+                if (iw >= W) continue;
+                st_global_v4(dx + ((static_cast<size_t>(n) * H + ih) * W + iw) * C + cg * 8, pack8f(acc[a][b]));
+            }
+        }
     }
 }
 
@@ -629,9 +656,9 @@ extern "C" int tony_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, 
                                      void* stream) {
     if (!dy || !dx || !idx || N <= 0 || H <= 0 || W <= 0 || C <= 0 || (C % 8)) return TONY_ERR_INVALID;
     const int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
-    const long long total = static_cast<long long>(N) * H * W * (C / 8);
-    const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, device_sm_count() * 32LL));
-    maxpool3x3s2_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    const long long total = static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);   // 2 x 2 pixel blocks
+    const int bgrid = static_cast<int>(std::min<long long>((total + 255) / 256, device_sm_count() * 32LL));
+    maxpool3x3s2_bwd_kernel<<<bgrid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const __nv_bfloat16*>(dy), static_cast<const unsigned char*>(idx), static_cast<__nv_bfloat16*>(dx),
         N, H, W, C, OH, OW);
     count_launch();
