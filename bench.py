@@ -394,7 +394,8 @@ def _brief(r):
 def main(argv=None) -> int:
     args = parse_args(argv)
     if args.impl == "reference":
-        print(json.dumps({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE}))
+        if int(os.environ.get("RANK", "0")) == 0:       # under torchrun every rank gets here: ONE line
+            print(json.dumps({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE}))
         return 0
 
     # Libraries (NCCL's version banner, cuDNN notices) write to the C-level stdout; the contract is
