@@ -71,6 +71,17 @@ int main() {
                 const int t = choose_gemm_tiling(M, N, workers);
                 CHECK(t == 512 || t == 256 || t == 128);
             }
+    // split-K: the partials' traffic is part of the cost, not only the wave count
+    CHECK(choose_splitk(16, 196, 74, 2048LL * 512, 16, 1.0) == 4);      // ResNet 7x7 weight gradient (measured best: 4)
+    CHECK(choose_splitk(16, 256, 74, 1024LL * 1024, 16, 1.0) == 4);     // BERT attention-output weight gradient
+    CHECK(choose_splitk(48, 256, 74, 3072LL * 1024, 16, 1.0) == 3);     // BERT QKV weight gradient
+    CHECK(choose_splitk(1, 12544, 74, 256LL * 64, 74, 1.0) >= 32);      // one tile, K = every pixel: one split per SM pair
+    CHECK(choose_splitk(64, 256, 74, 4096LL * 1024, 16, 1.0) == 1);     // already a full wave
+    for (int tiles = 1; tiles <= 80; ++tiles)
+        for (int nk : {8, 16, 100, 1000, 12544}) {
+            const int s1 = choose_splitk(tiles, nk, 74, 1LL << 20, 16, 1.0);
+            CHECK(s1 >= 1 && s1 <= 16 && (s1 == 1 || nk / s1 >= 8));
+        }
     std::printf("host_math: %llu divisions checked, %d failure(s)\n", checked, failures);
     return failures ? 1 : 0;
 }

@@ -1222,20 +1222,16 @@ static int gemm_host(const void* A, const void* B, void* C, int M, int N, int K,
                    (tiles * 2 <= workers ||
                     (wave_efficiency(tiles, workers) < 0.75 && static_cast<long long>(M) * N <= (4ll << 20)))) {
             // (a big output pays for its fp32 partials: 12544 x 512 split three ways wrote and re-read 77 MB)
-            double best = wave_efficiency(tiles, workers);
             // up to 16 splits normally; very long reductions over one or two output tiles (pointwise-convolution
             // weight gradients: K = every pixel of the batch) may use one split per SM
             int max_s = 16;
             if (tiles * 32 <= workers) max_s = static_cast<int>(workers / tiles);
-            for (int s = 2; s <= max_s; ++s) {
-                if (num_k / s < 8) break;  // keep >= 512 reduction elements per split
-                const double e = wave_efficiency(tiles * s, workers);
-                if (e > best + 0.05) {
-                    best = e;
-                    splits = s;
-                }
-            }
+            // k-block time of this tiling relative to the pair kernel's 256 x 256 x 64 block
+            const double tile_scale = use_2cta ? 1.0 : (block_n == 256 ? 1.12 : 0.6);
+            splits = choose_splitk(tiles, num_k, workers, static_cast<long long>(M) * N, max_s, tile_scale);   // host_math.h
         }
+    }
+    if (splittable) {
         splits = std::min(splits, num_k);
         while (splits > 1 &&
                static_cast<size_t>(splits) * M * (static_cast<size_t>(N) + (rowsum_out ? 1 : 0)) * 4 > workspace_bytes)

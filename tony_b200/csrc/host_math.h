@@ -77,4 +77,25 @@ TONY_HD int choose_gemm_tiling(int M, int N, int workers) {
     return 512;
 }
 
+// Split count for a GEMM whose `tiles` output tiles cannot fill `workers` (SMs, or SM pairs for the pair kernel).
+// Cost in units of one k-block of one tile: waves x k-blocks per split, plus what the fp32 partials cost - every
+// split writes and the reduce kernel re-reads out_elems x 4 bytes, at ~1.75 MB per k-block time (HBM rate x the
+// ~0.27 us a 256 x 256 x 64 block takes), plus ~11 units for launching the reduce kernel.  Choosing for wave
+// efficiency alone picked 9 splits where 4 run 20 % faster (profiles/r2_c91_gemm_tiling_probe.txt).
+TONY_HD int choose_splitk(long long tiles, int num_k, int workers, long long out_elems, int max_s, double tile_scale) {
+    int best_s = 1;
+    double best = static_cast<double>((tiles + workers - 1) / workers) * num_k * tile_scale;
+    for (int s = 2; s <= max_s; ++s) {
+        if (num_k / s < 8) break;                       // keep >= 512 reduction elements per split
+        const int kb = (num_k + s - 1) / s;
+        const double mma = static_cast<double>((tiles * s + workers - 1) / workers) * kb * tile_scale;
+        const double partials = static_cast<double>(s) * static_cast<double>(out_elems) * 8.0 / 1.75e6 + 11.0;
+        if (mma + partials < 0.97 * best) {
+            best = mma + partials;
+            best_s = s;
+        }
+    }
+    return best_s;
+}
+
 }  // namespace tony
