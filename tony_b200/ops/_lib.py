@@ -244,7 +244,20 @@ def ptr(t):
     return c_void_p(t.data_ptr()) if t is not None else c_void_p(None)
 
 
+_raw_stream = None
+
+
 def cur_stream():
+    """``cudaStream_t`` of the calling thread's current stream on the current device.  Goes through the raw C
+    accessor: ``torch.cuda.current_stream().cuda_stream`` builds a Stream object per call and measured 16 us -
+    4.5 ms of host time per ResNet-50 step at 270 kernel launches."""
+    global _raw_stream
     import torch
 
-    return c_void_p(torch.cuda.current_stream().cuda_stream)
+    if _raw_stream is None:
+        raw = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+        if raw is not None:
+            _raw_stream = lambda: raw(torch.cuda.current_device())      # noqa: E731
+        else:
+            _raw_stream = lambda: torch.cuda.current_stream().cuda_stream   # noqa: E731
+    return c_void_p(_raw_stream())
