@@ -125,7 +125,7 @@ def parse_args(argv=None):
     ap.add_argument("--cuda-graph", type=int, default=-1,
                     help="1/0: replay forward+backward as one CUDA graph (default: Trainer's own default)")
     ap.add_argument("--bucket-mb", type=float, default=64.0)
-    ap.add_argument("--comm-ctas", type=int, default=32)
+    ap.add_argument("--comm-ctas", type=int, default=0, help="CTAs of the overlapped reduce+optimizer kernel (0 = by world size)")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--compare", type=int, default=1,
                     help="1: after the own arm, run the stock-PyTorch arms (fp32 params + autocast, and "

@@ -154,7 +154,7 @@ class Trainer:
 
     def __init__(self, model, *, lr: float = 1e-4, optimizer: str = "adamw", weight_decay: float = 0.01,
                  betas=(0.9, 0.999), eps: float = 1e-8, momentum: float = 0.9, bucket_mb: float = 64.0,
-                 overlap: bool = True, comm_ctas: int = 32, device=None, group=None,
+                 overlap: bool = True, comm_ctas: int = 0, device=None, group=None,
                  broadcast: bool = True, generic_hooks: bool = False, ps_sharded=None,
                  cuda_graph: Optional[bool] = None, roles=None):
         import torch
